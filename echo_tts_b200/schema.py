@@ -1,0 +1,287 @@
+"""State-dict schema + deterministic synthetic weights.
+
+The engine accepts the *reference* ``state_dict`` key names (EchoDiT: reference
+``model.py:472-560``; DAC decode path: reference ``autoencoder.py:1144-1192``) so
+that HF checkpoints and parity tests can share one dict.  There is no network in
+the build/GPU boxes, so weights are synthetic: every tensor is drawn from its own
+``torch.Generator`` seeded by ``crc32(key) ^ seed`` -- independent of module
+construction order, identical on every machine, never stored in git.
+"""
+from __future__ import annotations
+
+import zlib
+from dataclasses import dataclass, asdict
+from typing import Dict, Tuple
+
+import torch
+
+
+@dataclass(frozen=True)
+class DiTConfig:
+    """Mirror of the kwargs hard-coded at reference ``inference.py:23-42``."""
+    latent_size: int = 80
+    model_size: int = 2048
+    num_layers: int = 24
+    num_heads: int = 16
+    intermediate_size: int = 5888
+    norm_eps: float = 1e-5
+    text_vocab_size: int = 256
+    text_model_size: int = 1280
+    text_num_layers: int = 14
+    text_num_heads: int = 10
+    text_intermediate_size: int = 3328
+    speaker_patch_size: int = 4
+    speaker_model_size: int = 1280
+    speaker_num_layers: int = 14
+    speaker_num_heads: int = 10
+    speaker_intermediate_size: int = 3328
+    timestep_embed_size: int = 512
+    adaln_rank: int = 256
+
+    def kwargs(self) -> dict:
+        return asdict(self)
+
+    @property
+    def head_dim(self) -> int:
+        return self.model_size // self.num_heads
+
+
+ECHO_BASE = DiTConfig()
+
+# Reduced architecture used by fast parity tests (same structure, head_dim 128).
+ECHO_TINY = DiTConfig(
+    model_size=256, num_layers=2, num_heads=2, intermediate_size=384,
+    text_model_size=256, text_num_layers=2, text_num_heads=2, text_intermediate_size=384,
+    speaker_model_size=256, speaker_num_layers=2, speaker_num_heads=2,
+    speaker_intermediate_size=384, timestep_embed_size=128, adaln_rank=64,
+)
+
+
+@dataclass(frozen=True)
+class AEConfig:
+    """Decode-path dimensions of ``build_ae()`` (reference ``autoencoder.py:1144-1192``)."""
+    latent_dim: int = 1024
+    tr_layers: int = 8
+    tr_heads: int = 16
+    tr_head_dim: int = 64
+    tr_ffn: int = 3072
+    tr_window: int = 128
+    tr_block_size: int = 4096
+    tr_eps: float = 1e-5
+    up_factors: Tuple[int, ...] = (2, 2)
+    convnext_ratio: int = 4
+    decoder_dim: int = 1536
+    decoder_rates: Tuple[int, ...] = (8, 8, 4, 2)
+
+    @property
+    def hop(self) -> int:
+        h = 1
+        for f in self.up_factors:
+            h *= f
+        for r in self.decoder_rates:
+            h *= r
+        return h
+
+
+AE_BASE = AEConfig()
+# Small AE for fast oracle-vs-kernel tests (not constructible by the reference's build_ae()).
+AE_TINY = AEConfig(latent_dim=128, tr_layers=2, tr_heads=2, tr_head_dim=64, tr_ffn=256,
+                   tr_window=16, tr_block_size=512, decoder_dim=256, decoder_rates=(4, 2, 2, 2))
+
+
+# --------------------------------------------------------------------------------------
+# key -> shape
+# --------------------------------------------------------------------------------------
+
+def _encoder_block_keys(prefix: str, d: int, h: int, f: int) -> Dict[str, Tuple[int, ...]]:
+    hd = d // h
+    out = {}
+    for w in ("wq", "wk", "wv", "wo", "gate"):
+        out[f"{prefix}.attention.{w}.weight"] = (d, d)
+    out[f"{prefix}.attention.q_norm.weight"] = (h, hd)
+    out[f"{prefix}.attention.k_norm.weight"] = (h, hd)
+    out[f"{prefix}.mlp.w1.weight"] = (f, d)
+    out[f"{prefix}.mlp.w3.weight"] = (f, d)
+    out[f"{prefix}.mlp.w2.weight"] = (d, f)
+    out[f"{prefix}.attention_norm.weight"] = (d,)
+    out[f"{prefix}.mlp_norm.weight"] = (d,)
+    return out
+
+
+def dit_schema(cfg: DiTConfig = ECHO_BASE, blockwise: bool = True) -> Dict[str, Tuple[int, ...]]:
+    """All EchoDiT parameter names with shapes (reference ``model.py:472-560``)."""
+    s: Dict[str, Tuple[int, ...]] = {}
+    d, dt, ds = cfg.model_size, cfg.text_model_size, cfg.speaker_model_size
+    s["text_encoder.text_embedding.weight"] = (cfg.text_vocab_size, dt)
+    for i in range(cfg.text_num_layers):
+        s.update(_encoder_block_keys(f"text_encoder.blocks.{i}", dt, cfg.text_num_heads,
+                                     cfg.text_intermediate_size))
+    encs = ["speaker_encoder"] + (["latent_encoder"] if blockwise else [])
+    for enc in encs:
+        s[f"{enc}.in_proj.weight"] = (ds, cfg.latent_size * cfg.speaker_patch_size)
+        s[f"{enc}.in_proj.bias"] = (ds,)
+        for i in range(cfg.speaker_num_layers):
+            s.update(_encoder_block_keys(f"{enc}.blocks.{i}", ds, cfg.speaker_num_heads,
+                                         cfg.speaker_intermediate_size))
+    s["text_norm.weight"] = (dt,)
+    s["speaker_norm.weight"] = (ds,)
+    if blockwise:
+        s["latent_norm.weight"] = (ds,)
+    s["cond_module.0.weight"] = (d, cfg.timestep_embed_size)
+    s["cond_module.2.weight"] = (d, d)
+    s["cond_module.4.weight"] = (3 * d, d)
+    s["in_proj.weight"] = (d, cfg.latent_size)
+    s["in_proj.bias"] = (d,)
+    for i in range(cfg.num_layers):
+        p = f"blocks.{i}"
+        for w in ("wq", "wk", "wv", "gate", "wo"):
+            s[f"{p}.attention.{w}.weight"] = (d, d)
+        s[f"{p}.attention.wk_text.weight"] = (d, dt)
+        s[f"{p}.attention.wv_text.weight"] = (d, dt)
+        s[f"{p}.attention.wk_speaker.weight"] = (d, ds)
+        s[f"{p}.attention.wv_speaker.weight"] = (d, ds)
+        if blockwise:
+            s[f"{p}.attention.wk_latent.weight"] = (d, ds)
+            s[f"{p}.attention.wv_latent.weight"] = (d, ds)
+        s[f"{p}.attention.q_norm.weight"] = (cfg.num_heads, cfg.head_dim)
+        s[f"{p}.attention.k_norm.weight"] = (cfg.num_heads, cfg.head_dim)
+        s[f"{p}.mlp.w1.weight"] = (cfg.intermediate_size, d)
+        s[f"{p}.mlp.w3.weight"] = (cfg.intermediate_size, d)
+        s[f"{p}.mlp.w2.weight"] = (d, cfg.intermediate_size)
+        for ada in ("attention_adaln", "mlp_adaln"):
+            for part in ("shift", "scale", "gate"):
+                s[f"{p}.{ada}.{part}_down.weight"] = (cfg.adaln_rank, d)
+                s[f"{p}.{ada}.{part}_up.weight"] = (d, cfg.adaln_rank)
+                s[f"{p}.{ada}.{part}_up.bias"] = (d,)
+    s["out_norm.weight"] = (d,)
+    s["out_proj.weight"] = (cfg.latent_size, d)
+    s["out_proj.bias"] = (cfg.latent_size,)
+    return s
+
+
+def ae_decode_schema(cfg: AEConfig = AE_BASE) -> Dict[str, Tuple[int, ...]]:
+    """Parameters on the ``DAC.decode_zq`` path (reference ``autoencoder.py:1128-1132``)."""
+    s: Dict[str, Tuple[int, ...]] = {}
+    D = cfg.latent_dim
+    pm = "quantizer.post_module"
+    qkv = 3 * cfg.tr_heads * cfg.tr_head_dim
+    for i in range(cfg.tr_layers):
+        p = f"{pm}.layers.{i}"
+        s[f"{p}.attention.wqkv.weight"] = (qkv, D)
+        s[f"{p}.attention.wo.weight"] = (D, cfg.tr_heads * cfg.tr_head_dim)
+        s[f"{p}.feed_forward.w1.weight"] = (cfg.tr_ffn, D)
+        s[f"{p}.feed_forward.w3.weight"] = (cfg.tr_ffn, D)
+        s[f"{p}.feed_forward.w2.weight"] = (D, cfg.tr_ffn)
+        s[f"{p}.ffn_norm.weight"] = (D,)
+        s[f"{p}.attention_norm.weight"] = (D,)
+        s[f"{p}.attention_layer_scale.gamma"] = (D,)
+        s[f"{p}.ffn_layer_scale.gamma"] = (D,)
+    s[f"{pm}.norm.weight"] = (D,)
+    for u, f in enumerate(cfg.up_factors):
+        p = f"quantizer.upsample.{u}"
+        s[f"{p}.0.conv.weight"] = (D, D, f)
+        s[f"{p}.0.conv.bias"] = (D,)
+        s[f"{p}.1.gamma"] = (D,)
+        s[f"{p}.1.dwconv.conv.weight"] = (D, 1, 7)
+        s[f"{p}.1.dwconv.conv.bias"] = (D,)
+        s[f"{p}.1.norm.weight"] = (D,)
+        s[f"{p}.1.norm.bias"] = (D,)
+        s[f"{p}.1.pwconv1.weight"] = (cfg.convnext_ratio * D, D)
+        s[f"{p}.1.pwconv1.bias"] = (cfg.convnext_ratio * D,)
+        s[f"{p}.1.pwconv2.weight"] = (D, cfg.convnext_ratio * D)
+        s[f"{p}.1.pwconv2.bias"] = (D,)
+
+    C = cfg.decoder_dim
+    dm = "decoder.model"
+
+    def wnconv(prefix: str, cout: int, cin: int, k: int):
+        s[f"{prefix}.conv.bias"] = (cout,)
+        s[f"{prefix}.conv.parametrizations.weight.original0"] = (cout, 1, 1)
+        s[f"{prefix}.conv.parametrizations.weight.original1"] = (cout, cin, k)
+
+    def wnconvT(prefix: str, cin: int, cout: int, k: int):
+        s[f"{prefix}.conv.bias"] = (cout,)
+        s[f"{prefix}.conv.parametrizations.weight.original0"] = (cin, 1, 1)
+        s[f"{prefix}.conv.parametrizations.weight.original1"] = (cin, cout, k)
+
+    wnconv(f"{dm}.0", C, D, 7)
+    c_in = C
+    for i, r in enumerate(cfg.decoder_rates):
+        c_out = c_in // 2
+        b = f"{dm}.{i + 1}.block"
+        s[f"{b}.0.alpha"] = (1, c_in, 1)
+        wnconvT(f"{b}.1", c_in, c_out, 2 * r)
+        for j in range(3):
+            ru = f"{b}.{2 + j}.block"
+            s[f"{ru}.0.alpha"] = (1, c_out, 1)
+            wnconv(f"{ru}.1", c_out, c_out, 7)
+            s[f"{ru}.2.alpha"] = (1, c_out, 1)
+            wnconv(f"{ru}.3", c_out, c_out, 1)
+        c_in = c_out
+    n = len(cfg.decoder_rates)
+    s[f"{dm}.{n + 1}.alpha"] = (1, c_in, 1)
+    wnconv(f"{dm}.{n + 2}", 1, c_in, 7)
+    return s
+
+
+# --------------------------------------------------------------------------------------
+# deterministic synthetic weights
+# --------------------------------------------------------------------------------------
+
+def _gen(key: str, seed: int) -> torch.Generator:
+    g = torch.Generator(device="cpu")
+    g.manual_seed((zlib.crc32(key.encode()) ^ (seed * 0x9E3779B1)) & 0x7FFFFFFF)
+    return g
+
+
+def _fan_in(shape: Tuple[int, ...]) -> int:
+    f = 1
+    for x in shape[1:]:
+        f *= x
+    return max(f, 1)
+
+
+def synth_tensor(key: str, shape: Tuple[int, ...], seed: int) -> torch.Tensor:
+    """One deterministic fp32 tensor.  The rules keep activations O(1) and make every
+    parameter matter (non-unit norm weights, non-zero biases, non-trivial gates)."""
+    g = _gen(key, seed)
+    leaf = key.rsplit(".", 1)[-1]
+    if leaf == "alpha":                       # Snake1d alpha > 0
+        return 0.5 + torch.rand(shape, generator=g)
+    if leaf == "gamma":                       # LayerScale / ConvNeXt gamma
+        return 0.2 * (0.5 + torch.rand(shape, generator=g))
+    if leaf == "original0":                   # weight-norm g (positive)
+        if shape[0] == 1:                     # final 1-channel conv: keep tanh in its linear range
+            return 0.01 * (0.5 + torch.rand(shape, generator=g))
+        return 0.5 + torch.rand(shape, generator=g)
+    if key.endswith("norm.weight") and len(shape) <= 2:
+        return 1.0 + 0.2 * (torch.rand(shape, generator=g) - 0.5)
+    if leaf == "bias":
+        return 0.1 * (torch.rand(shape, generator=g) - 0.5)
+    if "text_embedding" in key:
+        return torch.randn(shape, generator=g)
+    bound = (3.0 / _fan_in(shape)) ** 0.5     # unit-gain uniform
+    if "dwconv" in key:
+        bound = (3.0 / 7) ** 0.5
+    return (torch.rand(shape, generator=g) * 2 - 1) * bound
+
+
+def synth_state_dict(schema: Dict[str, Tuple[int, ...]], seed: int = 1234) -> Dict[str, torch.Tensor]:
+    return {k: synth_tensor(k, shp, seed) for k, shp in schema.items()}
+
+
+def ae_rope_table(cfg: AEConfig = AE_BASE) -> torch.Tensor:
+    """``quantizer.post_module.freqs_cis`` buffer: [block_size, head_dim/2, 2] rounded to
+    **bf16** exactly as the reference builds it (``autoencoder.py:805-813``)."""
+    n = cfg.tr_head_dim
+    freqs = 1.0 / (10000 ** (torch.arange(0, n, 2)[: n // 2].float() / n))
+    t = torch.arange(cfg.tr_block_size)
+    freqs = torch.outer(t, freqs)
+    fc = torch.polar(torch.ones_like(freqs), freqs)
+    return torch.stack([fc.real, fc.imag], dim=-1).to(torch.bfloat16)
+
+
+def synth_ae_state_dict(cfg: AEConfig = AE_BASE, seed: int = 4321) -> Dict[str, torch.Tensor]:
+    sd = synth_state_dict(ae_decode_schema(cfg), seed)
+    sd["quantizer.post_module.freqs_cis"] = ae_rope_table(cfg)
+    return sd
