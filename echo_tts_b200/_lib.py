@@ -1,0 +1,141 @@
+"""ctypes binding of libecho_b200.so (C ABI declared in include/echo_b200.h).
+
+The library holds every kernel of the product path.  There is NO fallback: if the shared object is
+missing or a call is made without a CUDA device, this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libecho_b200.so")
+
+c_p = C.c_void_p
+i32, i64, f32 = C.c_int32, C.c_int64, C.c_float
+
+
+class GemmSection(C.Structure):
+    _fields_ = [("type", i32), ("_pad", i32), ("out", c_p), ("norm_weight", c_p)]
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("a", c_p), ("b", c_p), ("lda", i64), ("a_batch_stride", i64), ("ldb", i64),
+        ("rows", i32), ("batch", i32), ("n", i32), ("k_tap", i32), ("taps", i32),
+        ("tap_shift", i32 * 8), ("epilogue", i32), ("impl", i32), ("block_n", i32), ("act", i32),
+        ("bias", c_p), ("gate", c_p), ("gate_ld", i64), ("rows_per_gate", i32), ("_pad0", i32),
+        ("resid", c_p), ("ld_resid", i64), ("out_f32", c_p), ("ld_out_f32", i64),
+        ("out_bf16", c_p), ("ld_out_bf16", i64), ("out2_bf16", c_p), ("ld_out2_bf16", i64),
+        ("snake_alpha", c_p),
+        ("n_sections", i32), ("section_width", i32), ("head_dim", i32), ("rope_heads", i32),
+        ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("_pad1", i32),
+        ("eps", f32), ("_pad2", f32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
+        ("sections", GemmSection * 4),
+    ]
+
+
+class SgemmDesc(C.Structure):
+    _fields_ = [
+        ("a", c_p), ("lda", i64), ("a_zstride", i64),
+        ("w", c_p), ("ldw", i64), ("w_zstride", i64),
+        ("bias", c_p), ("bias_zstride", i64),
+        ("addend", c_p), ("ld_addend", i64), ("addend_zstride", i64),
+        ("out", c_p), ("ldo", i64), ("out_zstride", i64),
+        ("out_bf16", c_p), ("ldo_bf16", i64), ("out_bf16_zstride", i64),
+        ("m", i32), ("n", i32), ("k", i32), ("nz", i32),
+        ("pre_silu", i32), ("post", i32), ("out_scale", f32), ("_pad", f32),
+    ]
+
+
+class AttnSegment(C.Structure):
+    _fields_ = [
+        ("k", c_p), ("v", c_p), ("row_stride", i64), ("batch_stride", i64),
+        ("len", i32), ("kv_batch_mod", i32), ("mask", c_p), ("mask_stride", i64),
+        ("extent", c_p), ("kv_scale", c_p), ("causal", i32), ("window", i32),
+    ]
+
+
+class AttnDesc(C.Structure):
+    _fields_ = [
+        ("q", c_p), ("q_row_stride", i64), ("q_batch_stride", i64), ("gate", c_p), ("out", c_p),
+        ("rows", i32), ("seq", i32), ("heads", i32), ("head_dim", i32),
+        ("n_seg", i32), ("_pad", i32), ("softmax_scale", f32), ("_pad1", f32),
+        ("seg", AttnSegment * 4),
+    ]
+
+
+class TailDesc(C.Structure):
+    _fields_ = [
+        ("h", c_p), ("ldh", i64), ("norm_w", c_p), ("w_out", c_p), ("b_out", c_p),
+        ("x_t", c_p), ("v_out", c_p), ("v_comb_out", c_p), ("sched", c_p), ("step", c_p),
+        ("positions", i32), ("d", i32), ("latent", i32), ("branches", i32),
+        ("eps", f32), ("cfg_text", f32), ("cfg_speaker", f32), ("rescale_k", f32), ("rescale_sigma", f32),
+        ("use_rescale", i32), ("update_x", i32), ("_pad", i32),
+    ]
+
+
+EPI_GENERIC, EPI_SECTIONS, EPI_SWIGLU = 0, 1, 2
+ACT_NONE, ACT_GELU, ACT_SILU = 0, 1, 2
+SEC_PLAIN, SEC_NORM_ROPE, SEC_SIGMOID, SEC_ROPE = 0, 1, 2, 3
+POST_NONE, POST_PLUS1, POST_TANH, POST_SILU = 0, 1, 2, 3
+
+EXPORTS = {
+    "echo_last_error": (C.c_char_p, []),
+    "echo_version": (C.c_int, []),
+    "echo_launch_count": (C.c_ulonglong, []),
+    "echo_reset_launch_count": (None, []),
+    "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
+    "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),
+    "echo_timestep_embedding": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p]),
+    "echo_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, C.c_int, c_p, i64, c_p, i64, c_p]),
+    "echo_attention": (C.c_int, [C.POINTER(AttnDesc), c_p]),
+    "echo_mask_extent": (C.c_int, [c_p, C.c_int, C.c_int, i64, c_p, c_p]),
+    "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),
+    "echo_step_advance": (C.c_int, [c_p, c_p]),
+    "echo_embedding": (C.c_int, [c_p, C.c_int, c_p, C.c_int, c_p, c_p]),
+    "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
+    "echo_conv_out_tanh": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
+    "echo_cast_snake": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
+    "echo_flattening_point": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, f32, f32, c_p, c_p]),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """dlopen the kernel library (built in-tree by ``__graft_entry__.build()``); fail loudly."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: the CUDA extension is required (no CPU fallback). "
+                "Run `python __graft_entry__.py build` (needs nvcc, sm_100a).")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in EXPORTS.items():
+            fn = getattr(lib, name)          # AttributeError if the .so lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise RuntimeError(f"echo_b200 error {rc}: {load().echo_last_error().decode()}")
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    """Device pointer of a CUDA tensor (None -> NULL).  Non-CUDA tensors are refused: no CPU path."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("echo_b200: expected a CUDA tensor (there is no CPU fallback)")
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream

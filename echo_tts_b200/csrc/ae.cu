@@ -1,0 +1,184 @@
+// S1-DAC decode helpers that are not GEMM-shaped (HBM-bound), time-major [B, T, C] activations,
+// plus the flattening-point search.
+#include "common.cuh"
+#include "../../include/echo_b200.h"
+
+namespace {
+
+// ConvNeXt front (autoencoder.py:362-364): causal depthwise conv k=7 then LayerNorm over channels.
+// One CTA per time step, one thread per channel (coalesced across channels), two-pass variance.
+__global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_len, const float* __restrict__ w,
+                                 const float* __restrict__ b, const float* __restrict__ ln_w,
+                                 const float* __restrict__ ln_b, float eps, bf16* __restrict__ y) {
+  const int t = blockIdx.x, bt = blockIdx.y;
+  const float* xb = x + (long long)bt * t_len * c_len;
+  __shared__ float red[32];
+  __shared__ float stat;
+  const int nper = (c_len + blockDim.x - 1) / blockDim.x;
+  float vals[4];
+  float sum = 0.f;
+  for (int i = 0; i < nper; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+    float acc = 0.f;
+    if (c < c_len) {
+      acc = b[c];
+#pragma unroll
+      for (int k = 0; k < 7; ++k) {
+        const int tt = t - 6 + k;
+        if (tt >= 0) acc = fmaf(w[c * 7 + k], xb[(long long)tt * c_len + c], acc);
+      }
+      sum += acc;
+    }
+    vals[i] = acc;
+  }
+  auto block_sum = [&](float v) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.f;
+      for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += red[i];
+      stat = s;
+    }
+    __syncthreads();
+    const float r = stat;
+    __syncthreads();
+    return r;
+  };
+  const float mean = block_sum(sum) / (float)c_len;
+  float sq = 0.f;
+  for (int i = 0; i < nper; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+    if (c < c_len) { const float dlt = vals[i] - mean; sq += dlt * dlt; }
+  }
+  const float rstd = rsqrtf(block_sum(sq) / (float)c_len + eps);
+  bf16* yr = y + ((long long)bt * t_len + t) * c_len;
+  for (int i = 0; i < nper; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+    if (c < c_len) yr[c] = __float2bfloat16((vals[i] - mean) * rstd * ln_w[c] + ln_b[c]);
+  }
+}
+
+// Last stage (autoencoder.py:994): causal conv k=7, C -> 1, + tanh on Snake'd bf16 input.
+// 256 outputs per CTA; the (256+6) x C input window is staged in shared memory with odd row stride.
+__global__ void __launch_bounds__(256) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
+                                                            const float* __restrict__ w, float bias,
+                                                            float* __restrict__ wav) {
+  extern __shared__ float sx[];                 // [(256+6)][c_len+1] fp32
+  float* sw = sx + (256 + 6) * (c_len + 1);     // [7][c_len]
+  const int bt = blockIdx.y, t0 = blockIdx.x * 256;
+  const bf16* xb = x + (long long)bt * t_len * c_len;
+  for (int i = threadIdx.x; i < 7 * c_len; i += 256) sw[i] = w[i];
+  const int n = (256 + 6) * c_len;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const int r = i / c_len, c = i % c_len;
+    const int tt = t0 - 6 + r;
+    sx[r * (c_len + 1) + c] = (tt >= 0 && tt < t_len) ? bf2f(xb[(long long)tt * c_len + c]) : 0.f;
+  }
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t >= t_len) return;
+  float acc = bias;
+  for (int k = 0; k < 7; ++k) {
+    const float* row = sx + (threadIdx.x + k) * (c_len + 1);
+    const float* wk = sw + k * c_len;
+    for (int c = 0; c < c_len; ++c) acc = fmaf(row[c], wk[c], acc);
+  }
+  wav[(long long)bt * t_len + t] = tanhf(acc);
+}
+
+__global__ void cast_snake_kernel(const float* __restrict__ x, long long n, int c_len, const float* __restrict__ alpha,
+                                  bf16* __restrict__ y) {
+  const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const float4 v = *reinterpret_cast<const float4*>(x + i);
+  float o[4] = {v.x, v.y, v.z, v.w};
+  if (alpha) {
+    const int c = (int)(i % c_len);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = snakef_(o[j], alpha[c + j]);
+  }
+  *reinterpret_cast<uint2*>(y + i) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+}
+
+// find_flattening_point (inference.py:315-330).  Per-row (sum, sum of squares) in fp64, then every
+// window start i checks unbiased std < thr and |mean - target| < 0.1; the smallest hit wins.
+__global__ void flattening_kernel(const float* __restrict__ x, int len, int width, int window, float thr, float target,
+                                  int* __restrict__ out) {
+  extern __shared__ double sd[];           // [len + window][2]
+  const int padded = len + window;
+  for (int r = threadIdx.x >> 5; r < padded; r += blockDim.x >> 5) {
+    double s = 0.0, q = 0.0;
+    if (r < len)
+      for (int c = threadIdx.x & 31; c < width; c += 32) {
+        const double v = (double)x[(long long)r * width + c];
+        s += v; q += v * v;
+      }
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if ((threadIdx.x & 31) == 0) { sd[2 * r] = s; sd[2 * r + 1] = q; }
+  }
+  __shared__ int best;
+  if (threadIdx.x == 0) best = len;
+  __syncthreads();
+  const double n = (double)window * width;
+  for (int i = threadIdx.x; i < len; i += blockDim.x) {
+    double s = 0.0, q = 0.0;
+    for (int k = 0; k < window; ++k) { s += sd[2 * (i + k)]; q += sd[2 * (i + k) + 1]; }
+    const double mean = s / n;
+    const double var = (q - s * mean) / (n - 1.0);
+    const float stdv = (float)sqrt(var > 0.0 ? var : 0.0);
+    if (stdv < thr && fabsf((float)mean - target) < 0.1f) atomicMin(&best, i);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out[0] = best;
+}
+}  // namespace
+
+extern "C" int echo_dwconv_layernorm(const float* x, int batch, int t, int c, const float* w_dw, const float* b_dw,
+                                     const float* ln_w, const float* ln_b, float eps, void* y, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && w_dw && b_dw && ln_w && ln_b && y && batch > 0 && t > 0, "dwconv_ln: bad argument");
+  ECHO_CHECK_ARG(c > 0 && c <= 1024, "dwconv_ln: c must be <= 1024");
+  const int threads = c >= 256 ? 256 : ((c + 31) / 32) * 32;
+  dwconv_ln_kernel<<<dim3(t, batch), threads, 0, (cudaStream_t)stream>>>(x, t, c, w_dw, b_dw, ln_w, ln_b, eps, (bf16*)y);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_conv_out_tanh(const void* x, int batch, int t, int c, const float* w, float bias, float* wav,
+                                  echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && w && wav && batch > 0 && t > 0 && c > 0 && c <= 128, "conv_out: bad argument");
+  const size_t smem = ((size_t)(256 + 6) * (c + 1) + 7 * c) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    ECHO_CUDA(cudaFuncSetAttribute(conv_out_tanh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  conv_out_tanh_kernel<<<dim3(ceil_div(t, 256), batch), 256, smem, (cudaStream_t)stream>>>((const bf16*)x, t, c, w, bias, wav);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && y && rows > 0 && c > 0 && c % 4 == 0, "cast_snake: bad argument");
+  const long long n = rows * c;
+  cast_snake_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, n, c, alpha, (bf16*)y);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_flattening_point(const float* latent, int len, int width, int window, float std_threshold,
+                                     float target, int32_t* index_out, echo_stream_t stream) {
+  ECHO_CHECK_ARG(latent && index_out && len > 0 && width > 0 && window > 0, "flattening: bad argument");
+  const size_t smem = (size_t)(len + window) * 2 * sizeof(double);
+  ECHO_CHECK_ARG(smem <= 48 * 1024, "flattening: latent too long");
+  flattening_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(latent, len, width, window, std_threshold, target, index_out);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}

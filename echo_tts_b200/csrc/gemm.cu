@@ -1,0 +1,286 @@
+// bf16 GEMM / implicit causal conv for sm_100a.
+//   impl 0: TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> shared memory ring -> tcgen05.mma (one issuing
+//           thread, fp32 accumulator in TMEM) -> tcgen05.ld epilogue.  Warp roles: 0 = TMA producer,
+//           1 = TMEM owner + MMA issuer, 2..5 = epilogue (one TMEM lane quarter each).
+//   impl 1: legacy mma.sync.m16n8k16 kernel (same epilogues) kept as A/B baseline.
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "gemm_epilogue.cuh"
+
+struct GemmShape {
+  int k_blocks_per_tap, taps, k_tap;
+  int tap_shift[8];
+  int rows, n;
+  long long lda, a_batch_stride, ldb;
+  const bf16* a;
+  const bf16* b;
+};
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+
+template <int BN>
+struct TcCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct TmemLoader {
+  uint32_t taddr;
+  __device__ __forceinline__ void load32(int col, float* v) { ptx::tmem_ld32(taddr + (uint32_t)col, v); }
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(192, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P) {
+  using C = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + C::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + C::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, batch = blockIdx.z;
+  const int total_kb = G.k_blocks_per_tap * G.taps;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < C::STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    ptx::mbar_init(tmem_full_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, BN);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < total_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+        const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
+        uint8_t* sa = smem + s * C::STAGE_BYTES;
+        uint8_t* sb = sa + C::A_BYTES;
+        ptx::mbar_arrive_expect_tx(&full_bar[s], C::STAGE_BYTES);
+        ptx::tma_load_3d(sa, &tmap_a, &full_bar[s], kk * BK, m0 + G.tap_shift[tap], batch);
+        ptx::tma_load_2d(sb, &tmap_b, &full_bar[s], tap * G.k_tap + kk * BK, n0);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN);
+      for (int kb = 0; kb < total_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        ptx::mbar_wait(&full_bar[s], ph);
+        ptx::tc_fence_after();
+        const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
+        const uint64_t da = ptx::umma_desc_sw128(sa);
+        const uint64_t db = ptx::umma_desc_sw128(sa + C::A_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)   // 16 bf16 = 32 B = 2 descriptor units per UMMA_K step
+          ptx::umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+        ptx::umma_commit(&empty_bar[s]);     // frees the smem slot once these MMAs retire
+      }
+      ptx::umma_commit(tmem_full_bar);       // accumulator complete
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;                  // TMEM lane quarter this warp may read
+    ptx::mbar_wait(tmem_full_bar, 0);
+    ptx::tc_fence_after();
+    TmemLoader L{tmem_base + ((uint32_t)(q * 32) << 16)};
+    run_epilogue<BN, EPI>(P, L, batch, m0 + q * 32 + lane, n0);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, BN);
+}
+
+// -------------------------------------------------------------------------------------------
+// host side: tensor maps through the driver entry point (no link-time libcuda dependency)
+// -------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+static int make_tmap(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                     const cuuint32_t* box) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) { echo_set_error("cuTensorMapEncodeTiled entry point unavailable"); return ECHO_ERR_CUDA; }
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_b, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { echo_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return ECHO_ERR_CUDA; }
+  return ECHO_OK;
+}
+
+template <int BN, int EPI>
+static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+  using C = TcCfg<BN>;
+  CUtensorMap ta, tb;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
+    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)G.rows * G.lda) * 2};
+    cuuint32_t box[3] = {BK, BM, 1};
+    int rc = make_tmap(&ta, G.a, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)G.taps * G.k_tap, (cuuint64_t)G.n};
+    cuuint64_t str[1] = {(cuuint64_t)G.ldb * 2};
+    cuuint32_t box[2] = {BK, BN};
+    int rc = make_tmap(&tb, G.b, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    ECHO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(G.n, BN), ceil_div(G.rows, BM), batch);
+  gemm_tcgen05_kernel<BN, EPI><<<grid, 192, C::SMEM, st>>>(ta, tb, G, P);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+template <int EPI>
+int launch_legacy(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm_legacy.cu
+
+static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
+  ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
+  ECHO_CHECK_ARG(d->rows > 0 && d->batch > 0 && d->n > 0 && d->k_tap > 0, "gemm: bad shape");
+  ECHO_CHECK_ARG(d->taps >= 1 && d->taps <= 8, "gemm: taps must be 1..8");
+  ECHO_CHECK_ARG(d->k_tap % 8 == 0 && d->lda % 8 == 0 && d->ldb % 8 == 0, "gemm: k/lda/ldb must be multiples of 8");
+  ECHO_CHECK_ARG(d->n % 8 == 0, "gemm: n must be a multiple of 8");
+  ECHO_CHECK_ARG(((uintptr_t)d->a % 16) == 0 && ((uintptr_t)d->b % 16) == 0, "gemm: operands must be 16-byte aligned");
+  ECHO_CHECK_ARG(d->ldb >= (long long)d->taps * d->k_tap, "gemm: ldb < taps*k_tap");
+  memset(&G, 0, sizeof(G));
+  memset(&P, 0, sizeof(P));
+  G.k_blocks_per_tap = ceil_div(d->k_tap, BK);
+  G.taps = d->taps; G.k_tap = d->k_tap;
+  for (int i = 0; i < 8; ++i) G.tap_shift[i] = d->tap_shift[i];
+  G.rows = d->rows; G.n = d->n; G.lda = d->lda; G.a_batch_stride = d->a_batch_stride; G.ldb = d->ldb;
+  G.a = (const bf16*)d->a; G.b = (const bf16*)d->b;
+  P.kind = d->epilogue; P.rows = d->rows; P.n = d->n; P.act = d->act;
+  P.bias = d->bias; P.gate = d->gate; P.gate_ld = d->gate_ld; P.rows_per_gate = d->rows_per_gate > 0 ? d->rows_per_gate : 1;
+  P.resid = d->resid; P.ld_resid = d->ld_resid; P.out_f32 = d->out_f32; P.ld_out_f32 = d->ld_out_f32;
+  P.out_bf16 = (bf16*)d->out_bf16; P.ld_out_bf16 = d->ld_out_bf16;
+  P.out2_bf16 = (bf16*)d->out2_bf16; P.ld_out2_bf16 = d->ld_out2_bf16; P.snake_alpha = d->snake_alpha;
+  P.n_sections = d->n_sections; P.section_width = d->section_width; P.head_dim = d->head_dim;
+  P.rope_heads = d->rope_heads; P.pos_offset = d->pos_offset; P.pos_stride = d->pos_stride;
+  P.rows_per_seq = d->rows_per_seq > 0 ? d->rows_per_seq : 1; P.eps = d->eps;
+  P.rope_cos = d->rope_cos; P.rope_sin = d->rope_sin; P.ld_sec_out = d->ld_sec_out;
+  for (int i = 0; i < 4; ++i) {
+    P.sec[i].type = d->sections[i].type; P.sec[i].out = (bf16*)d->sections[i].out;
+    P.sec[i].norm_w = d->sections[i].norm_weight;
+  }
+  if (d->epilogue == ECHO_EPI_GENERIC) {
+    ECHO_CHECK_ARG(d->out_f32 || d->out_bf16 || d->out2_bf16, "gemm: no output");
+    ECHO_CHECK_ARG(!d->out2_bf16 || d->snake_alpha, "gemm: out2 needs snake_alpha");
+    ECHO_CHECK_ARG((!d->out_f32 || d->ld_out_f32 % 4 == 0) && (!d->resid || d->ld_resid % 4 == 0) &&
+                   (!d->out_bf16 || d->ld_out_bf16 % 8 == 0) && (!d->out2_bf16 || d->ld_out2_bf16 % 8 == 0),
+                   "gemm: output leading dims must keep 16-byte alignment");
+  } else if (d->epilogue == ECHO_EPI_SECTIONS) {
+    ECHO_CHECK_ARG(d->n_sections >= 1 && d->n_sections <= 4 && d->n == d->n_sections * d->section_width,
+                   "gemm: sections do not tile n");
+    ECHO_CHECK_ARG(d->head_dim == 64 || d->head_dim == 128, "gemm: head_dim must be 64 or 128");
+    ECHO_CHECK_ARG(d->section_width % d->head_dim == 0 && d->ld_sec_out % 8 == 0, "gemm: bad section layout");
+    for (int i = 0; i < d->n_sections; ++i) {
+      ECHO_CHECK_ARG(d->sections[i].out, "gemm: section output missing");
+      ECHO_CHECK_ARG(d->sections[i].type != ECHO_SEC_NORM_ROPE || d->sections[i].norm_weight, "gemm: norm weight missing");
+      ECHO_CHECK_ARG((d->sections[i].type != ECHO_SEC_NORM_ROPE && d->sections[i].type != ECHO_SEC_ROPE) ||
+                     d->rope_heads == 0 || (d->rope_cos && d->rope_sin), "gemm: rope table missing");
+    }
+  } else if (d->epilogue == ECHO_EPI_SWIGLU) {
+    ECHO_CHECK_ARG(d->out_bf16 && d->n % 128 == 0 && d->ld_out_bf16 % 8 == 0, "gemm: swiglu needs out_bf16, n%%128==0");
+  } else {
+    ECHO_CHECK_ARG(false, "gemm: unknown epilogue %d", d->epilogue);
+  }
+  return ECHO_OK;
+}
+
+static int pick_block_n(const echo_gemm_desc* d) {
+  int bn = d->block_n;
+  if (bn == 0) {
+    // fewest wasted columns first, then enough CTAs to cover 148 SMs
+    const long long mt = (long long)ceil_div(d->rows, BM) * d->batch;
+    bn = 256;
+    if (d->n % 256 != 0 || mt * (d->n / 256) < 148) bn = 128;
+    if (bn == 128 && d->n <= 64) bn = 64;
+  }
+  if (d->epilogue == ECHO_EPI_SECTIONS) {
+    if (bn < d->head_dim) bn = d->head_dim;
+    while (d->section_width % bn != 0 && bn > d->head_dim) bn >>= 1;
+  }
+  if (d->epilogue == ECHO_EPI_SWIGLU && bn < 128) bn = 128;
+  return bn;
+}
+
+template <int EPI>
+static int dispatch_bn(int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+  switch (bn) {
+    case 256: return launch_tc<256, EPI>(G, P, batch, st);
+    case 128: return launch_tc<128, EPI>(G, P, batch, st);
+    case 64:
+      if (EPI == ECHO_EPI_GENERIC) return launch_tc<64, ECHO_EPI_GENERIC>(G, P, batch, st);
+      if (EPI == ECHO_EPI_SECTIONS) return launch_tc<64, ECHO_EPI_SECTIONS>(G, P, batch, st);
+  }
+  echo_set_error("gemm: unsupported block_n %d for epilogue %d", bn, EPI);
+  return ECHO_ERR_UNSUPPORTED;
+}
+
+extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
+  GemmShape G;
+  EpiParams P;
+  int rc = fill_params(d, G, P);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->impl == 1) {
+    if (d->epilogue == ECHO_EPI_SECTIONS) ECHO_CHECK_ARG(d->section_width % 128 == 0, "legacy gemm: section_width %% 128");
+    switch (d->epilogue) {
+      case ECHO_EPI_GENERIC: return launch_legacy<ECHO_EPI_GENERIC>(G, P, d->batch, st);
+      case ECHO_EPI_SECTIONS: return launch_legacy<ECHO_EPI_SECTIONS>(G, P, d->batch, st);
+      default: return launch_legacy<ECHO_EPI_SWIGLU>(G, P, d->batch, st);
+    }
+  }
+  ECHO_CHECK_ARG(d->impl == 0, "gemm: unknown impl %d", d->impl);
+  const int bn = pick_block_n(d);
+  if (d->epilogue == ECHO_EPI_SECTIONS)
+    ECHO_CHECK_ARG(d->section_width % bn == 0 && bn % d->head_dim == 0, "gemm: block_n %d does not tile sections", bn);
+  switch (d->epilogue) {
+    case ECHO_EPI_GENERIC: return dispatch_bn<ECHO_EPI_GENERIC>(bn, G, P, d->batch, st);
+    case ECHO_EPI_SECTIONS: return dispatch_bn<ECHO_EPI_SECTIONS>(bn, G, P, d->batch, st);
+    default: return dispatch_bn<ECHO_EPI_SWIGLU>(bn, G, P, d->batch, st);
+  }
+}

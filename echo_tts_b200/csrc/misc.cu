@@ -1,0 +1,221 @@
+// Error plumbing + the small fp32 / bandwidth-bound kernels of the path.
+#include "common.cuh"
+#include "../../include/echo_b200.h"
+#include <stdarg.h>
+
+static thread_local char g_err[512] = "";
+unsigned long long g_echo_launches = 0;
+
+void echo_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* echo_last_error(void) { return g_err; }
+extern "C" int echo_version(void) { return 100; }
+extern "C" unsigned long long echo_launch_count(void) { return g_echo_launches; }
+extern "C" void echo_reset_launch_count(void) { g_echo_launches = 0; }
+
+// ---------------------------------------------------------------------------------------------
+// RMS-normalise (+ AdaLN modulate) fp32 rows -> bf16.  One warp per row, float4 loads, row kept
+// in registers (d <= 4096).  HBM-bound: 4 B in + 2 B out per element.
+// ---------------------------------------------------------------------------------------------
+template <int VEC_ITERS>
+__global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restrict__ x, long long ldx, int m, int d,
+                                                          float eps, const float* __restrict__ scale1,
+                                                          const float* __restrict__ shift, long long mod_ld,
+                                                          int rows_per_mod, const int* __restrict__ step,
+                                                          long long mod_step_stride, bf16* __restrict__ y,
+                                                          long long ldy) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= m) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
+  float4 v[VEC_ITERS];
+  float ssq = 0.f;
+  const int nvec = d >> 2;
+#pragma unroll
+  for (int i = 0; i < VEC_ITERS; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) {
+      v[i] = xr[c];
+      ssq += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+    }
+  }
+  ssq = warp_sum(ssq);
+  const float rstd = rsqrtf(ssq / (float)d + eps);
+  long long g = row / rows_per_mod;
+  if (step) g += (long long)step[0] * mod_step_stride;
+  const float4* sc = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
+  const float4* sh = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
+  uint2* yr = reinterpret_cast<uint2*>(y + (long long)row * ldy);
+#pragma unroll
+  for (int i = 0; i < VEC_ITERS; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) {
+      const float4 s = __ldg(sc + c);
+      float4 o = make_float4(v[i].x * rstd * s.x, v[i].y * rstd * s.y, v[i].z * rstd * s.z, v[i].w * rstd * s.w);
+      if (sh) {
+        const float4 b = __ldg(sh + c);
+        o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+      }
+      yr[c] = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+    }
+  }
+}
+
+extern "C" int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float eps, const float* scale1,
+                                const float* shift, int64_t mod_ld, int rows_per_mod, const int32_t* step,
+                                int64_t mod_step_stride, void* y, int64_t ldy, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && scale1 && y && m > 0, "rmsnorm: null argument");
+  ECHO_CHECK_ARG(d % 4 == 0 && d <= 4096 && ldx % 4 == 0 && ldy % 4 == 0 && mod_ld % 4 == 0, "rmsnorm: d must be <=4096, %%4");
+  if (rows_per_mod <= 0) rows_per_mod = 1 << 30;
+  dim3 grid(ceil_div(m, 8));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d <= 1024)
+    rmsnorm_mod_kernel<8><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+  else if (d <= 2048)
+    rmsnorm_mod_kernel<16><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+  else
+    rmsnorm_mod_kernel<32><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp32 CUDA-core GEMM: 64x64 tile, 16x16 threads, 4x4 micro-tile, K step 16.  Small/accuracy-critical.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo_sgemm_desc D) {
+  __shared__ float sA[16][64 + 4];
+  __shared__ float sW[16][64 + 4];
+  const int z = blockIdx.z;
+  const float* A = D.a + z * D.a_zstride;
+  const float* W = D.w + z * D.w_zstride;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < D.k; k0 += 16) {
+    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+      const int r = i >> 4, kk = i & 15;
+      const int k = k0 + kk;
+      float a = 0.f, w = 0.f;
+      if (k < D.k) {
+        if (m0 + r < D.m) {
+          a = A[(long long)(m0 + r) * D.lda + k];
+          if (D.pre_silu) a = a / (1.f + expf(-a));
+        }
+        if (n0 + r < D.n) w = W[(long long)(n0 + r) * D.ldw + k];
+      }
+      sA[kk][r] = a;
+      sW[kk][r] = w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], w[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = sA[kk][ty * 4 + i]; w[i] = sW[kk][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= D.m) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= D.n) continue;
+      float v = acc[i][j];
+      if (D.bias) v += D.bias[z * D.bias_zstride + n];
+      v *= D.out_scale;
+      if (D.addend) v += D.addend[z * D.addend_zstride + (long long)m * D.ld_addend + n];
+      if (D.post == ECHO_POST_PLUS1) v += 1.f;
+      else if (D.post == ECHO_POST_TANH) v = tanhf(v);
+      else if (D.post == ECHO_POST_SILU) v = v / (1.f + expf(-v));
+      if (D.out) D.out[z * D.out_zstride + (long long)m * D.ldo + n] = v;
+      if (D.out_bf16) ((bf16*)D.out_bf16)[z * D.out_bf16_zstride + (long long)m * D.ldo_bf16 + n] = __float2bfloat16(v);
+    }
+  }
+}
+
+extern "C" int echo_sgemm_f32(const echo_sgemm_desc* d, echo_stream_t stream) {
+  ECHO_CHECK_ARG(d && d->a && d->w && (d->out || d->out_bf16), "sgemm: null argument");
+  ECHO_CHECK_ARG(d->m > 0 && d->n > 0 && d->k > 0 && d->nz > 0, "sgemm: bad shape");
+  dim3 grid(ceil_div(d->n, 64), ceil_div(d->m, 64), d->nz);
+  sgemm_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*d);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+// timestep embedding, model.py:27-43 (frequencies computed exactly like torch: exp(-ln(1e4) * j / half) * 1000)
+__global__ void timestep_embedding_kernel(const float* t, int n, int size, float* out) {
+  const int half = size / 2;
+  const int i = blockIdx.x, j = threadIdx.x + blockIdx.y * blockDim.x;
+  if (j >= half) return;
+  const float w = 1000.f * expf(-logf(10000.f) * (float)j / (float)half);
+  const float a = t[i] * w;
+  out[(long long)i * size + j] = cosf(a);
+  out[(long long)i * size + half + j] = sinf(a);
+}
+extern "C" int echo_timestep_embedding(const float* t, int n, int size, float* out, echo_stream_t stream) {
+  ECHO_CHECK_ARG(t && out && n > 0 && size > 0 && size % 2 == 0, "timestep_embedding: bad argument");
+  dim3 grid(n, ceil_div(size / 2, 128));
+  timestep_embedding_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(t, n, size, out);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+__global__ void embedding_kernel(const int* ids, int n, const float* table, int d, float* out) {
+  const int i = blockIdx.x;
+  const float4* src = reinterpret_cast<const float4*>(table + (long long)ids[i] * d);
+  float4* dst = reinterpret_cast<float4*>(out + (long long)i * d);
+  for (int c = threadIdx.x; c < d / 4; c += blockDim.x) dst[c] = src[c];
+}
+extern "C" int echo_embedding(const int32_t* ids, int n, const float* table, int d, float* out, echo_stream_t stream) {
+  ECHO_CHECK_ARG(ids && table && out && n > 0 && d % 4 == 0, "embedding: bad argument");
+  embedding_kernel<<<n, 128, 0, (cudaStream_t)stream>>>(ids, n, table, d, out);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+__global__ void mask_extent_kernel(const uint8_t* mask, int len, long long stride, int* extent) {
+  const uint8_t* row = mask + (long long)blockIdx.x * stride;
+  int best = 0;
+  for (int j = threadIdx.x; j < len; j += blockDim.x)
+    if (row[j]) best = max(best, j + 1);
+  __shared__ int s[32];
+  for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = max(best, s[w]);
+    extent[blockIdx.x] = best;
+  }
+}
+extern "C" int echo_mask_extent(const uint8_t* mask, int rows, int len, int64_t stride, int32_t* extent,
+                                echo_stream_t stream) {
+  ECHO_CHECK_ARG(mask && extent && rows > 0 && len >= 0, "mask_extent: bad argument");
+  mask_extent_kernel<<<rows, 256, 0, (cudaStream_t)stream>>>(mask, len, stride, extent);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+__global__ void step_advance_kernel(int* step) { step[0] += 1; }
+extern "C" int echo_step_advance(int32_t* step, echo_stream_t stream) {
+  ECHO_CHECK_ARG(step, "step_advance: null");
+  step_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}

@@ -1,0 +1,120 @@
+// Fused sampler tail (fp32): out_norm -> out_proj -> CFG combine -> temporal score rescale -> Euler.
+// One CTA owns PP latent positions x all CFG branches: the normalised rows live in shared memory,
+// each warp streams one out_proj weight row at a time (L2-resident, 80 x d fp32) and reduces it
+// against every row with warp shuffles; the combine/update happens in registers.
+#include "common.cuh"
+#include "../../include/echo_b200.h"
+
+namespace {
+constexpr int PP = 2;
+
+__global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_constant__ echo_tail_desc D) {
+  extern __shared__ float sm[];
+  const int nrows = D.branches * PP;
+  float* srow = sm;                       // [nrows][d]
+  float* sv = sm + (size_t)nrows * D.d;   // [nrows][latent]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pos0 = blockIdx.x * PP;
+  const int nvec = D.d >> 2;
+
+  for (int r = warp; r < nrows; r += 8) {
+    const int br = r / PP, p = pos0 + (r % PP);
+    float4* dst = reinterpret_cast<float4*>(srow + (size_t)r * D.d);
+    if (p >= D.positions) {
+      for (int c = lane; c < nvec; c += 32) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      continue;
+    }
+    const float4* src = reinterpret_cast<const float4*>(D.h + ((long long)br * D.positions + p) * D.ldh);
+    float ssq = 0.f;
+    for (int c = lane; c < nvec; c += 32) {
+      const float4 v = src[c];
+      ssq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ssq = warp_sum(ssq);
+    const float rstd = rsqrtf(ssq / (float)D.d + D.eps);
+    const float4* nw = reinterpret_cast<const float4*>(D.norm_w);
+    for (int c = lane; c < nvec; c += 32) {
+      const float4 v = src[c], w = __ldg(nw + c);
+      dst[c] = make_float4(v.x * rstd * w.x, v.y * rstd * w.y, v.z * rstd * w.z, v.w * rstd * w.w);
+    }
+  }
+  __syncthreads();
+
+  for (int o = warp; o < D.latent; o += 8) {
+    const float4* w = reinterpret_cast<const float4*>(D.w_out + (long long)o * D.d);
+    float acc[3 * PP];
+#pragma unroll
+    for (int r = 0; r < 3 * PP; ++r) acc[r] = 0.f;
+    for (int c = lane; c < nvec; c += 32) {
+      const float4 wv = __ldg(w + c);
+#pragma unroll
+      for (int r = 0; r < 3 * PP; ++r) {
+        if (r < nrows) {
+          const float4 xv = reinterpret_cast<const float4*>(srow + (size_t)r * D.d)[c];
+          acc[r] = fmaf(wv.x, xv.x, fmaf(wv.y, xv.y, fmaf(wv.z, xv.z, fmaf(wv.w, xv.w, acc[r]))));
+        }
+      }
+    }
+    const float b = __ldg(D.b_out + o);
+#pragma unroll
+    for (int r = 0; r < 3 * PP; ++r) {
+      if (r < nrows) {
+        const float s = warp_sum(acc[r]);
+        if (lane == 0) sv[r * D.latent + o] = s + b;
+      }
+    }
+  }
+  __syncthreads();
+
+  const int s = D.step ? D.step[0] : 0;
+  const float t = D.sched ? D.sched[s * 4 + 0] : 0.f, dt = D.sched ? D.sched[s * 4 + 1] : 0.f;
+  for (int i = threadIdx.x; i < PP * D.latent; i += blockDim.x) {
+    const int pl = i / D.latent, c = i % D.latent;
+    const int p = pos0 + pl;
+    if (p >= D.positions) continue;
+    const float vc = sv[(0 * PP + pl) * D.latent + c];
+    float v = vc;
+    if (D.v_out) D.v_out[((long long)0 * D.positions + p) * D.latent + c] = vc;
+    if (D.branches == 3) {
+      const float vt = sv[(1 * PP + pl) * D.latent + c];
+      const float vs = sv[(2 * PP + pl) * D.latent + c];
+      if (D.v_out) {
+        D.v_out[((long long)1 * D.positions + p) * D.latent + c] = vt;
+        D.v_out[((long long)2 * D.positions + p) * D.latent + c] = vs;
+      }
+      v = vc + D.cfg_text * (vc - vt) + D.cfg_speaker * (vc - vs);   // inference.py:526-530
+    }
+    const long long xi = (long long)p * D.latent + c;
+    if (D.update_x) {
+      const float x = D.x_t[xi];
+      if (D.use_rescale && t < 1.f) {                                  // inference.py:431-443
+        const float omt = 1.f - t;
+        const float snr = (omt * omt) / (t * t);
+        const float sg2 = D.rescale_sigma * D.rescale_sigma;
+        const float ratio = (snr * sg2 + 1.f) / (snr * sg2 / D.rescale_k + 1.f);
+        v = 1.f / omt * (ratio * (omt * v + x) - x);
+      }
+      D.x_t[xi] = x + v * dt;                                          // inference.py:558
+    }
+    if (D.v_comb_out) D.v_comb_out[xi] = v;
+  }
+}
+}  // namespace
+
+extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream) {
+  ECHO_CHECK_ARG(d && d->h && d->norm_w && d->w_out && d->b_out, "tail: null argument");
+  ECHO_CHECK_ARG(d->branches == 1 || d->branches == 3, "tail: branches must be 1 or 3");
+  ECHO_CHECK_ARG(d->d % 4 == 0 && d->ldh % 4 == 0 && d->positions > 0 && d->latent > 0, "tail: bad shape");
+  ECHO_CHECK_ARG(!d->update_x || (d->x_t && d->sched), "tail: x_t/sched required when update_x");
+  ECHO_CHECK_ARG(d->update_x || d->v_out || d->v_comb_out, "tail: nothing to write");
+  const size_t smem = ((size_t)d->branches * PP * (d->d + d->latent)) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > configured) {
+    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  cfg_euler_tail_kernel<<<ceil_div(d->positions, PP), 256, smem, (cudaStream_t)stream>>>(*d);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}

@@ -1,0 +1,356 @@
+"""EchoDiT engine: the reference's model object (``model.py:472-642``) re-built on the sm_100a kernels.
+
+Same duck-typed surface the reference samplers use (``.device``, ``.dtype``, ``__call__``,
+``get_kv_cache_text/speaker/latent``), but nothing here is an ``nn.Module``: weights are repacked once
+at load (wq|wk|wv|gate fused to one N=4d operand, w1/w3 interleaved for the SwiGLU epilogue, per-layer
+K|V projections of the conditioning fused, everything GEMM-shaped in bf16, everything t-only or tiny
+kept fp32), and a forward is ~8 fused kernel launches per layer.
+
+Precision policy: fp32 residual stream, fp32 timestep / AdaLN tables / in_proj / out_proj,
+bf16 tensor-core operands with fp32 accumulation, fp32 softmax statistics.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import _lib as L
+from . import ops
+from .schema import DiTConfig, ECHO_BASE
+
+KVCache = List[Tuple[torch.Tensor, torch.Tensor]]
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+class KVList(list):
+    """List[(K, V)] per decoder layer, all views of one buffer ``buf`` bf16 [layers, 2, B*L, D]."""
+    buf: torch.Tensor
+
+    @staticmethod
+    def from_buffer(buf: torch.Tensor, B: int, Ls: int, H: int) -> "KVList":
+        out = KVList((buf[l, 0].view(B, Ls, H, 128), buf[l, 1].view(B, Ls, H, 128)) for l in range(buf.shape[0]))
+        out.buf = buf
+        return out
+
+
+def rope_table(head_dim: int, n_pos: int, device) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(cos, sin) fp32 [n_pos, head_dim/2], computed on the host exactly as the reference does
+    (model.py:9-14) and uploaded once instead of on every forward (model.py:579)."""
+    inv = 1.0 / (10000.0 ** (torch.arange(0, head_dim, 2)[: head_dim // 2] / head_dim))
+    ang = torch.outer(torch.arange(n_pos), inv)
+    return torch.cos(ang).to(device).contiguous(), torch.sin(ang).to(device).contiguous()
+
+
+class _EncoderWeights:
+    """Packed weights of a 14-layer conditioning encoder (TextEncoder / SpeakerEncoder, model.py:392-469)."""
+
+    def __init__(self, sd, prefix: str, n_layers: int, heads: int, dev):
+        self.heads = heads
+        self.layers = []
+        for i in range(n_layers):
+            p = f"{prefix}.blocks.{i}"
+            a = f"{p}.attention"
+            g = lambda k: sd[k].to(dev)
+            self.layers.append(dict(
+                qkvg=torch.cat([g(f"{a}.wq.weight"), g(f"{a}.wk.weight"), g(f"{a}.wv.weight"),
+                                g(f"{a}.gate.weight")], 0).to(BF16).contiguous(),
+                qn=g(f"{a}.q_norm.weight").float().reshape(-1).contiguous(),
+                kn=g(f"{a}.k_norm.weight").float().reshape(-1).contiguous(),
+                wo=g(f"{a}.wo.weight").to(BF16).contiguous(),
+                w13=ops.pack_w13(g(f"{p}.mlp.w1.weight"), g(f"{p}.mlp.w3.weight")).to(BF16),
+                w2=g(f"{p}.mlp.w2.weight").to(BF16).contiguous(),
+                an=g(f"{p}.attention_norm.weight").float().contiguous(),
+                mn=g(f"{p}.mlp_norm.weight").float().contiguous(),
+            ))
+
+
+class EchoDiT:
+    """Drop-in for the reference ``EchoDiT`` on the sampling path (inference only)."""
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], cfg: DiTConfig = ECHO_BASE, device="cuda",
+                 dtype: torch.dtype = torch.bfloat16, max_positions: int = 8192):
+        L.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("echo_tts_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        if dtype != torch.bfloat16:
+            raise ValueError("echo_tts_b200 computes GEMMs in bf16 (fp32 accumulate); pass dtype=torch.bfloat16")
+        assert cfg.head_dim == 128, "kernels are specialised for head_dim 128"
+        self.cfg = cfg
+        self._device = torch.device(device)
+        self._dtype = dtype
+        dev = self._device
+        sd = state_dict
+        g = lambda k: sd[k].to(dev)
+        D, Lr = cfg.model_size, cfg.num_layers
+        self.has_blockwise = "latent_norm.weight" in sd
+
+        # fp32 small / t-only weights
+        self.cond_w = [g(f"cond_module.{i}.weight").float().contiguous() for i in (0, 2, 4)]
+        self.in_w, self.in_b = g("in_proj.weight").float().contiguous(), g("in_proj.bias").float().contiguous()
+        self.out_norm = g("out_norm.weight").float().contiguous()
+        self.out_w, self.out_b = g("out_proj.weight").float().contiguous(), g("out_proj.bias").float().contiguous()
+        parts = ("shift", "scale", "gate")
+        adas = ("attention_adaln", "mlp_adaln")
+        self.ada_down = [torch.cat([g(f"blocks.{l}.{a}.{p}_down.weight").float() for l in range(Lr) for a in adas], 0)
+                         .contiguous() for p in parts]                      # 3 x [L*2*r, D]
+        self.ada_up = [torch.stack([g(f"blocks.{l}.{a}.{p}_up.weight").float() for l in range(Lr) for a in adas], 0)
+                       .contiguous() for p in parts]                        # 3 x [L*2, D, r]
+        self.ada_up_b = [torch.stack([g(f"blocks.{l}.{a}.{p}_up.bias").float() for l in range(Lr) for a in adas], 0)
+                         .contiguous() for p in parts]                      # 3 x [L*2, D]
+
+        # decoder layers (bf16 tensor-core operands)
+        self.layers = []
+        for l in range(Lr):
+            a = f"blocks.{l}.attention"
+            lw = dict(
+                qkvg=torch.cat([g(f"{a}.wq.weight"), g(f"{a}.wk.weight"), g(f"{a}.wv.weight"), g(f"{a}.gate.weight")],
+                               0).to(BF16).contiguous(),
+                qn=g(f"{a}.q_norm.weight").float().reshape(-1).contiguous(),
+                kn=g(f"{a}.k_norm.weight").float().reshape(-1).contiguous(),
+                wo=g(f"{a}.wo.weight").to(BF16).contiguous(),
+                w13=ops.pack_w13(g(f"blocks.{l}.mlp.w1.weight"), g(f"blocks.{l}.mlp.w3.weight")).to(BF16),
+                w2=g(f"blocks.{l}.mlp.w2.weight").to(BF16).contiguous(),
+                kv_text=torch.cat([g(f"{a}.wk_text.weight"), g(f"{a}.wv_text.weight")], 0).to(BF16).contiguous(),
+                kv_speaker=torch.cat([g(f"{a}.wk_speaker.weight"), g(f"{a}.wv_speaker.weight")], 0).to(BF16).contiguous(),
+            )
+            if self.has_blockwise:
+                lw["kv_latent"] = torch.cat([g(f"{a}.wk_latent.weight"), g(f"{a}.wv_latent.weight")], 0).to(BF16).contiguous()
+            self.layers.append(lw)
+
+        # conditioning encoders
+        self.text_emb = g("text_encoder.text_embedding.weight").float().contiguous()
+        self.text_enc = _EncoderWeights(sd, "text_encoder", cfg.text_num_layers, cfg.text_num_heads, dev)
+        self.text_norm = g("text_norm.weight").float().contiguous()
+        self.spk_enc = _EncoderWeights(sd, "speaker_encoder", cfg.speaker_num_layers, cfg.speaker_num_heads, dev)
+        self.spk_in_w = g("speaker_encoder.in_proj.weight").float().contiguous()
+        self.spk_in_b = g("speaker_encoder.in_proj.bias").float().contiguous()
+        self.spk_norm = g("speaker_norm.weight").float().contiguous()
+        if self.has_blockwise:
+            self.lat_enc = _EncoderWeights(sd, "latent_encoder", cfg.speaker_num_layers, cfg.speaker_num_heads, dev)
+            self.lat_in_w = g("latent_encoder.in_proj.weight").float().contiguous()
+            self.lat_in_b = g("latent_encoder.in_proj.bias").float().contiguous()
+            self.lat_norm = g("latent_norm.weight").float().contiguous()
+
+        self.rope = rope_table(cfg.head_dim, max_positions, dev)
+        self._ws: Dict[Tuple[int, int], dict] = {}
+        self._ones = torch.ones(1, device=dev, dtype=F32)
+
+    # ------------------------------------------------------------------------------------------
+    @property
+    def device(self) -> torch.device:
+        return self._device
+
+    @property
+    def dtype(self) -> torch.dtype:
+        return self._dtype
+
+    def eval(self):
+        return self
+
+    # ------------------------------------------------------------------------------------------
+    # t-only work: timestep embedding -> cond_module -> all 48 LowRankAdaLN modulations, once per
+    # schedule instead of once per forward (model.py:583, 70-74, 81).
+    # ------------------------------------------------------------------------------------------
+    def build_mod_table(self, t: torch.Tensor) -> torch.Tensor:
+        """t fp32 [T] -> table fp32 [T, L, 2, 3, D]: (shift, 1 + scale, tanh(gate)) for (attention, mlp)."""
+        cfg = self.cfg
+        D, Lr, r = cfg.model_size, cfg.num_layers, cfg.adaln_rank
+        T = t.numel()
+        dev = self._device
+        t = t.to(dev, F32).contiguous()
+        emb = ops.timestep_embedding(t, cfg.timestep_embed_size)
+        h1 = torch.empty((T, D), device=dev, dtype=F32)
+        h2 = torch.empty((T, D), device=dev, dtype=F32)
+        cond = torch.empty((T, 3 * D), device=dev, dtype=F32)
+        ops.sgemm(emb, self.cond_w[0], out=h1, post=L.POST_SILU)
+        ops.sgemm(h1, self.cond_w[1], out=h2, post=L.POST_SILU)
+        ops.sgemm(h2, self.cond_w[2], out=cond)
+        table = torch.empty((T, Lr, 2, 3, D), device=dev, dtype=F32)
+        tv = table.view(T, Lr * 2, 3, D)
+        lo = torch.empty((T, Lr * 2 * r), device=dev, dtype=F32)
+        for p, post in enumerate((L.POST_NONE, L.POST_PLUS1, L.POST_TANH)):
+            c_p = cond[:, p * D:(p + 1) * D]
+            ops.sgemm(c_p, self.ada_down[p], out=lo, pre_silu=True)
+            ops.sgemm(lo.view(T, Lr * 2, r).permute(1, 0, 2), self.ada_up[p], bias=self.ada_up_b[p], addend=c_p,
+                      out=tv[:, :, p, :].permute(1, 0, 2), post=post)
+        return table
+
+    # ------------------------------------------------------------------------------------------
+    # conditioning encoders (once per prompt)
+    # ------------------------------------------------------------------------------------------
+    def _run_encoder(self, enc: _EncoderWeights, x: torch.Tensor, B: int, Ls: int, *, causal: bool,
+                     mask: Optional[torch.Tensor]) -> torch.Tensor:
+        """x fp32 [B*Ls, d] residual stream, updated in place (EncoderTransformerBlock, model.py:335-339)."""
+        cfg = self.cfg
+        d = x.shape[1]
+        H = enc.heads
+        M = B * Ls
+        dev = self._device
+        xn = torch.empty((M, d), device=dev, dtype=BF16)
+        qkvg = torch.empty((4, M, d), device=dev, dtype=BF16)
+        ao = torch.empty((M, d), device=dev, dtype=BF16)
+        hmid = torch.empty((M, enc.layers[0]["w2"].shape[1]), device=dev, dtype=BF16)
+        ext = ops.mask_extent(mask) if mask is not None else None
+        for lw in enc.layers:
+            ops.rmsnorm_mod(x, lw["an"], None, xn, cfg.norm_eps)
+            ops.gemm_sections(xn, lw["qkvg"],
+                              [(L.SEC_NORM_ROPE, qkvg[0], lw["qn"]), (L.SEC_NORM_ROPE, qkvg[1], lw["kn"]),
+                               (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
+                              head_dim=128, rope_heads=H, rope=self.rope, rows_per_seq=Ls, eps=cfg.norm_eps)
+            seg = ops.Segment(qkvg[1].view(B, Ls, H, 128), qkvg[2].view(B, Ls, H, 128), mask=mask, extent=ext,
+                              causal=causal)
+            ops.attention(qkvg[0].view(B, Ls, H, 128), [seg], ao, gate=qkvg[3])
+            ops.gemm_generic(ao, lw["wo"], resid=x, out_f32=x)
+            ops.rmsnorm_mod(x, lw["mn"], None, xn, cfg.norm_eps)
+            ops.gemm_swiglu(xn, lw["w13"], hmid)
+            ops.gemm_generic(hmid, lw["w2"], resid=x, out_f32=x)
+        return x
+
+    def _project_kv(self, state: torch.Tensor, norm_w: torch.Tensor, key: str, B: int, Ls: int,
+                    rope_patch: bool = False) -> KVCache:
+        """state fp32 [B*Ls, d_enc] -> per decoder layer (K, V) bf16 [B, Ls, H, 128]  (model.py:270-293)."""
+        cfg = self.cfg
+        D, H = cfg.model_size, cfg.num_heads
+        M = B * Ls
+        sn = torch.empty((M, state.shape[1]), device=self._device, dtype=BF16)
+        ops.rmsnorm_mod(state, norm_w, None, sn, cfg.norm_eps)
+        buf = torch.empty((cfg.num_layers, 2, M, D), device=self._device, dtype=BF16)
+        for l, lw in enumerate(self.layers):
+            ops.gemm_sections(sn, lw[key], [(L.SEC_NORM_ROPE, buf[l, 0], lw["kn"]), (L.SEC_PLAIN, buf[l, 1], None)],
+                              head_dim=128, rope_heads=(H // 2 if rope_patch else 0), rope=self.rope,
+                              pos_stride=(cfg.speaker_patch_size if rope_patch else 1), rows_per_seq=Ls,
+                              eps=cfg.norm_eps)
+        return KVList.from_buffer(buf, B, Ls, H)
+
+    @torch.inference_mode()
+    def get_kv_cache_text(self, text_input_ids: torch.Tensor, text_mask: Optional[torch.Tensor]) -> KVCache:
+        """model.py:606-613."""
+        B, Lt = text_input_ids.shape
+        ids = text_input_ids.to(self._device, torch.int32).contiguous().view(-1)
+        x = ops.embedding(ids, self.text_emb)
+        mask = text_mask.to(self._device).contiguous() if text_mask is not None else None
+        self._run_encoder(self.text_enc, x, B, Lt, causal=False, mask=mask)
+        return self._project_kv(x, self.text_norm, "kv_text", B, Lt)
+
+    def _patch_encode(self, enc, in_w, in_b, latent: torch.Tensor):
+        cfg = self.cfg
+        B, T, Cc = latent.shape
+        p = cfg.speaker_patch_size
+        assert T % p == 0, "latent length must be a multiple of the patch size (model.py:459)"
+        Ls = T // p
+        xin = latent.to(self._device, F32).contiguous().view(B * Ls, Cc * p)
+        x = torch.empty((B * Ls, in_w.shape[0]), device=self._device, dtype=F32)
+        ops.sgemm(xin, in_w, bias=in_b, out=x, out_scale=1.0 / 6.0)          # model.py:461-462
+        self._run_encoder(enc, x, B, Ls, causal=True, mask=None)
+        return x, B, Ls
+
+    @torch.inference_mode()
+    def get_kv_cache_speaker(self, speaker_latent: torch.Tensor) -> KVCache:
+        """model.py:615-621."""
+        x, B, Ls = self._patch_encode(self.spk_enc, self.spk_in_w, self.spk_in_b, speaker_latent)
+        return self._project_kv(x, self.spk_norm, "kv_speaker", B, Ls)
+
+    @torch.inference_mode()
+    def get_kv_cache_latent(self, prefix_latent: torch.Tensor) -> KVCache:
+        """model.py:623-636 (+ half-head RoPE at positions 4*patch, model.py:284-293)."""
+        if not self.has_blockwise:
+            raise RuntimeError("blockwise modules were deleted at load (delete_blockwise_modules=True)")
+        if prefix_latent.shape[1] == 0:
+            z = torch.empty((prefix_latent.shape[0], 0, self.cfg.num_heads, 128), device=self._device, dtype=BF16)
+            return [(z, z) for _ in range(self.cfg.num_layers)]
+        x, B, Ls = self._patch_encode(self.lat_enc, self.lat_in_w, self.lat_in_b, prefix_latent)
+        return self._project_kv(x, self.lat_norm, "kv_latent", B, Ls, rope_patch=True)
+
+    # ------------------------------------------------------------------------------------------
+    # one velocity evaluation (EchoDiT.forward, model.py:563-604) -- ends at the final residual stream;
+    # out_norm/out_proj live in the fused sampler tail.
+    # ------------------------------------------------------------------------------------------
+    def workspace(self, rows: int, S: int) -> dict:
+        key = (rows, S)
+        ws = self._ws.get(key)
+        if ws is None:
+            cfg, dev = self.cfg, self._device
+            M, D = rows * S, cfg.model_size
+            ws = dict(x=torch.empty((M, D), device=dev, dtype=F32), xn=torch.empty((M, D), device=dev, dtype=BF16),
+                      qkvg=torch.empty((4, M, D), device=dev, dtype=BF16), ao=torch.empty((M, D), device=dev, dtype=BF16),
+                      h=torch.empty((M, cfg.intermediate_size), device=dev, dtype=BF16))
+            self._ws[key] = ws
+        return ws
+
+    def forward_hidden(self, x_in: torch.Tensor, mod: torch.Tensor, B: int, *, text_mask, text_extent, spk_mask,
+                       spk_extent, kv_text: KVCache, kv_speaker: KVCache, kv_latent: Optional[KVCache] = None,
+                       start_pos: int = 0, n_prefix: int = 0, spk_scale: Optional[torch.Tensor] = None,
+                       x_rows: Optional[int] = None) -> torch.Tensor:
+        """x_in fp32 [x_rows*S... see below] -> final residual stream fp32 [R*S, D].
+
+        x_in: [Bx, S, latent] fp32 with Bx == R (one input per row) or Bx == B (CFG: the three branches
+        share x_t, inference.py:516 -- in_proj is evaluated once per prompt and broadcast).
+        mod:  fp32 [R or 1, L, 2, 3, D] modulation rows (row g serves rows g*S..); text_mask/spk_mask
+        uint8/bool [R, L_t] / [R, L_s] (patch rate) with their extents; spk_scale: fp32 [L] per-layer
+        speaker K/V multiplier (speaker_kv_scale, inference.py:420-428) or None.
+        """
+        cfg = self.cfg
+        D, H, Lr = cfg.model_size, cfg.num_heads, cfg.num_layers
+        Bx, S, lat = x_in.shape
+        R = text_mask.shape[0]
+        M = R * S
+        ws = self.workspace(R, S)
+        x, xn, qkvg, ao, hmid = ws["x"], ws["xn"], ws["qkvg"], ws["ao"], ws["h"]
+        # in_proj (fp32, model.py:586); for CFG rows the same [B*S, D] result is written to all three branches
+        xin2 = x_in.reshape(Bx * S, lat)
+        reps = R // Bx
+        ops.sgemm(xin2.unsqueeze(0).expand(reps, -1, -1) if reps > 1 else xin2,
+                  self.in_w.unsqueeze(0).expand(reps, -1, -1) if reps > 1 else self.in_w,
+                  bias=self.in_b, out=x.view(reps, Bx * S, D) if reps > 1 else x)
+        mod_rows = mod.shape[0]
+        rows_per_mod = S if mod_rows > 1 else 0
+        mod_ld = mod.stride(0)
+        kv_mod = lambda c: (B if c[0][0].shape[0] != R else 0)
+        for l, lw in enumerate(self.layers):
+            ops.rmsnorm_mod(x, mod[0, l, 0, 1], mod[0, l, 0, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
+            ops.gemm_sections(xn, lw["qkvg"],
+                              [(L.SEC_NORM_ROPE, qkvg[0], lw["qn"]), (L.SEC_NORM_ROPE, qkvg[1], lw["kn"]),
+                               (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
+                              head_dim=128, rope_heads=H // 2, rope=self.rope, pos_offset=start_pos, rows_per_seq=S,
+                              eps=cfg.norm_eps)
+            segs = [ops.Segment(qkvg[1].view(R, S, H, 128), qkvg[2].view(R, S, H, 128))]
+            if kv_latent is not None and n_prefix > 0:
+                segs.append(ops.Segment(kv_latent[l][0], kv_latent[l][1], kv_batch_mod=kv_mod(kv_latent),
+                                        length=n_prefix))
+            segs.append(ops.Segment(kv_text[l][0], kv_text[l][1], kv_batch_mod=kv_mod(kv_text), mask=text_mask,
+                                    extent=text_extent))
+            segs.append(ops.Segment(kv_speaker[l][0], kv_speaker[l][1], kv_batch_mod=kv_mod(kv_speaker), mask=spk_mask,
+                                    extent=spk_extent, kv_scale=(spk_scale[l:l + 1] if spk_scale is not None else None)))
+            ops.attention(qkvg[0].view(R, S, H, 128), segs, ao, gate=qkvg[3])
+            ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
+            ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
+            ops.gemm_swiglu(xn, lw["w13"], hmid)
+            ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
+        return x
+
+    @torch.inference_mode()
+    def __call__(self, x, t, text_mask, speaker_mask, kv_cache_text, kv_cache_speaker, start_pos=None,
+                 kv_cache_latent=None) -> torch.Tensor:
+        """Reference-compatible forward (model.py:563-604): velocities fp32 [R, S, latent].
+        Third-party samplers written against the reference call this; our own sampler bypasses it."""
+        cfg, dev = self.cfg, self._device
+        start_pos = start_pos or 0
+        R, S, lat = x.shape
+        mod = self.build_mod_table(t.to(dev).float().reshape(-1))
+        tm = text_mask.to(dev).contiguous()
+        sm = speaker_mask.to(dev)[..., ::cfg.speaker_patch_size].contiguous()
+        n_prefix = 0
+        if kv_cache_latent is not None and kv_cache_latent[0][0].shape[1] > 0:
+            n_prefix = min(kv_cache_latent[0][0].shape[1], -(-start_pos // cfg.speaker_patch_size))
+        Bkv = kv_cache_text[0][0].shape[0]
+        h = self.forward_hidden(x.to(dev).float().contiguous(), mod, Bkv, text_mask=tm, text_extent=ops.mask_extent(tm),
+                                spk_mask=sm, spk_extent=ops.mask_extent(sm), kv_text=kv_cache_text,
+                                kv_speaker=kv_cache_speaker, kv_latent=kv_cache_latent, start_pos=start_pos,
+                                n_prefix=n_prefix)
+        v = torch.empty((R * S, lat), device=dev, dtype=F32)
+        ops.cfg_euler_tail(h, self.out_norm, self.out_w, self.out_b, positions=R * S, branches=1, eps=cfg.norm_eps,
+                           v_out=v, update_x=False)
+        return v.view(R, S, lat)
+
+    forward = __call__

@@ -1,0 +1,231 @@
+"""Euler sampler with independent text/speaker guidance on the sm_100a engine.
+
+Host control loop of reference ``inference.py:446-560`` / ``inference_blockwise.py:14-123`` re-designed:
+every t-only quantity (schedule, CFG window, AdaLN modulation table, speaker-KV multipliers) is computed
+once per request; the three CFG branches share ONE conditioning cache (rows index it modulo B, masks drop a
+modality); out_norm/out_proj/CFG-combine/rescale/Euler are one fused kernel; there is no host sync inside
+the loop, and the whole 40-step loop replays as a single CUDA graph.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import ops
+from .model import EchoDiT, KVCache, KVList, BF16, F32
+
+INIT_SCALE = 0.999  # inference.py:470
+
+
+class StepPlan:
+    """Host-side schedule logic, bit-exact with the reference's fp32 device-scalar comparisons."""
+
+    def __init__(self, device, num_steps: int, cfg_min_t: float, cfg_max_t: float, speaker_kv_scale, speaker_kv_max_layers,
+                 speaker_kv_min_t, num_layers: int, initial_multiplier: Optional[List[float]] = None):
+        t_sched = torch.linspace(1.0, 0.0, num_steps + 1, device=device) * INIT_SCALE      # inference.py:477
+        th = t_sched.cpu()
+        t, tn = th[:-1], th[1:]
+        self.t_dev = t_sched[:-1].contiguous()
+        self.has_cfg: List[bool] = ((t >= cfg_min_t) * (t <= cfg_max_t)).tolist()          # inference.py:511
+        sched = torch.zeros((num_steps, 4), device=device, dtype=F32)
+        sched[:, 0] = t_sched[:-1]
+        sched[:, 1] = t_sched[1:] - t_sched[:-1]                                           # inference.py:558
+        self.sched = sched
+        n_scaled = num_layers if speaker_kv_max_layers is None else min(speaker_kv_max_layers, num_layers)
+        mult = list(initial_multiplier) if initial_multiplier is not None else [1.0] * num_layers
+        self.kv_mult_rows: List[List[float]] = []
+        self.unscale_after: Optional[int] = None
+        if speaker_kv_scale is not None:
+            for l in range(n_scaled):                                                      # inference.py:485-486
+                mult[l] *= speaker_kv_scale
+            crossing = ((tn < speaker_kv_min_t) * (t >= speaker_kv_min_t)).tolist()        # inference.py:546-550
+        else:
+            crossing = [False] * num_steps
+        for i in range(num_steps):
+            self.kv_mult_rows.append(list(mult))
+            if crossing[i]:
+                if self.unscale_after is None:
+                    self.unscale_after = i
+                for l in range(n_scaled):
+                    mult[l] *= 1.0 / speaker_kv_scale                                      # inference.py:551-553
+        self.final_multiplier = mult
+        self.uses_kv_scale = speaker_kv_scale is not None
+        self.kv_mult = torch.tensor(self.kv_mult_rows, device=device, dtype=F32) if self.uses_kv_scale else None
+
+
+def _prep_masks(model: EchoDiT, text_mask: torch.Tensor, speaker_mask: torch.Tensor):
+    """Row layout (cond | text-dropped | speaker-dropped), inference.py:494-497; speaker mask at patch rate
+    (model.py:581).  Returns uint8 masks + per-row extents for 3B rows; the first B rows serve plain steps."""
+    dev = model.device
+    p = model.cfg.speaker_patch_size
+    tm = text_mask.to(dev).to(torch.uint8).contiguous()
+    sm = speaker_mask.to(dev)[..., ::p].to(torch.uint8).contiguous()
+    tm3 = torch.cat([tm, torch.zeros_like(tm), tm], 0).contiguous()
+    sm3 = torch.cat([sm, sm, torch.zeros_like(sm)], 0).contiguous()
+    return tm3, ops.mask_extent(tm3), sm3, ops.mask_extent(sm3)
+
+
+def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tensor, B: int, masks, kv_text: KVCache,
+              kv_spk: KVCache, p: dict, *, start_pos: int = 0, kv_latent: Optional[KVCache] = None, n_prefix: int = 0,
+              trace: Optional[list] = None) -> None:
+    """The hot loop (inference.py:508-558): x_t fp32 [B, S, latent] updated in place; launches only."""
+    cfg = model.cfg
+    tm3, te3, sm3, se3 = masks
+    S = x_t.shape[1]
+    use_rescale = p["rescale_k"] is not None and p["rescale_sigma"] is not None
+    for i, has_cfg in enumerate(plan.has_cfg):
+        R = 3 * B if has_cfg else B
+        h = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[:R], text_extent=te3[:R], spk_mask=sm3[:R],
+                                 spk_extent=se3[:R], kv_text=kv_text, kv_speaker=kv_spk, kv_latent=kv_latent,
+                                 start_pos=start_pos, n_prefix=n_prefix,
+                                 spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
+        v_out = v_comb = None
+        if trace is not None:
+            v_out = torch.empty((R * S, cfg.latent_size), device=x_t.device, dtype=F32)
+            v_comb = torch.empty((B * S, cfg.latent_size), device=x_t.device, dtype=F32)
+            x_in = x_t.clone()
+        ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=(3 if has_cfg else 1),
+                           eps=cfg.norm_eps, x_t=x_t, sched=plan.sched[i], cfg_text=p["cfg_scale_text"],
+                           cfg_speaker=p["cfg_scale_speaker"], rescale_k=p["rescale_k"] if use_rescale else None,
+                           rescale_sigma=p["rescale_sigma"] if use_rescale else None, v_out=v_out, v_comb_out=v_comb)
+        if trace is not None:
+            trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
+
+
+class _GraphEntry:
+    def __init__(self):
+        self.calls = 0
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.static: Dict[str, torch.Tensor] = {}
+
+
+def _use_graphs() -> bool:
+    return os.environ.get("ECHO_CUDA_GRAPH", "1") != "0"
+
+
+@torch.inference_mode()
+def sample_euler_cfg_independent_guidances(
+        model: EchoDiT, speaker_latent: torch.Tensor, speaker_mask: torch.Tensor, text_input_ids: torch.Tensor,
+        text_mask: torch.Tensor, rng_seed: int, num_steps: int, cfg_scale_text: float, cfg_scale_speaker: float,
+        cfg_min_t: float, cfg_max_t: float, truncation_factor: Optional[float], rescale_k: Optional[float],
+        rescale_sigma: Optional[float], speaker_kv_scale: Optional[float], speaker_kv_max_layers: Optional[int],
+        speaker_kv_min_t: Optional[float], sequence_length: Optional[int] = None, *,
+        _noise: Optional[torch.Tensor] = None, _trace: Optional[list] = None) -> torch.Tensor:
+    """Drop-in for reference ``inference.py:446-560`` (same positional/keyword arguments, fp32 [B, S, 80] out).
+    ``_noise`` injects x_T and ``_trace`` collects per-step velocities (parity tests only)."""
+    if sequence_length is None:
+        sequence_length = 640
+    if speaker_kv_scale is not None and speaker_kv_min_t is None:
+        raise TypeError("'<' not supported between instances of 'Tensor' and 'NoneType'")   # inference.py:548
+    cfg, dev = model.cfg, model.device
+    B, S = text_input_ids.shape[0], sequence_length
+    p = dict(cfg_scale_text=float(cfg_scale_text), cfg_scale_speaker=float(cfg_scale_speaker), rescale_k=rescale_k,
+             rescale_sigma=rescale_sigma)
+    plan = StepPlan(dev, num_steps, cfg_min_t, cfg_max_t, speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t,
+                    cfg.num_layers)
+    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)                           # inference.py:482
+    kv_spk = model.get_kv_cache_speaker(speaker_latent)                                    # inference.py:483
+    masks = _prep_masks(model, text_mask, speaker_mask)
+    if _noise is not None:
+        x_t = _noise.to(dev, F32).clone()
+    else:
+        rng = torch.Generator(device=dev).manual_seed(rng_seed)                            # inference.py:475
+        x_t = torch.randn((B, S, cfg.latent_size), device=dev, dtype=F32, generator=rng)   # inference.py:499
+    if truncation_factor is not None:
+        x_t = x_t * truncation_factor
+
+    if _trace is not None or not _use_graphs():
+        mod = model.build_mod_table(plan.t_dev)
+        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, trace=_trace)
+        return x_t.view(B, S, cfg.latent_size)
+
+    # ---- CUDA-graph path: static buffers keyed by everything baked into the captured launches ----
+    key = ("euler", B, S, text_input_ids.shape[1], kv_spk[0][0].shape[1], num_steps, tuple(plan.has_cfg),
+           p["cfg_scale_text"], p["cfg_scale_speaker"], rescale_k, rescale_sigma, plan.uses_kv_scale)
+    cache = model.__dict__.setdefault("_graphs", {})
+    ent: _GraphEntry = cache.setdefault(key, _GraphEntry())
+    ent.calls += 1
+    if ent.calls == 1:                      # first request with this shape: plain launches (also warms kernels up)
+        mod = model.build_mod_table(plan.t_dev)
+        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p)
+        return x_t.view(B, S, cfg.latent_size)
+    st = ent.static
+    if ent.graph is None:
+        st["x_t"] = x_t.clone()
+        st["mod"] = model.build_mod_table(plan.t_dev)
+        st["masks"] = tuple(m.clone() for m in masks)
+        H = cfg.num_heads
+        st["kv_text"] = KVList.from_buffer(kv_text.buf.clone(), B, kv_text[0][0].shape[1], H)
+        st["kv_spk"] = KVList.from_buffer(kv_spk.buf.clone(), B, kv_spk[0][0].shape[1], H)
+        st["plan"] = plan
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            run_steps(model, st["x_t"], plan, st["mod"], B, st["masks"], st["kv_text"], st["kv_spk"], p)
+        ent.graph = g
+    st["x_t"].copy_(x_t)
+    for dst, src in zip(st["masks"], masks):
+        dst.copy_(src)
+    st["kv_text"].buf.copy_(kv_text.buf)
+    st["kv_spk"].buf.copy_(kv_spk.buf)
+    if plan.uses_kv_scale:
+        st["plan"].kv_mult.copy_(plan.kv_mult)
+    st["plan"].sched.copy_(plan.sched)
+    ent.graph.replay()
+    return st["x_t"].clone().view(B, S, cfg.latent_size)
+
+
+@torch.inference_mode()
+def sample_blockwise_euler_cfg_independent_guidances(
+        model: EchoDiT, speaker_latent: torch.Tensor, speaker_mask: torch.Tensor, text_input_ids: torch.Tensor,
+        text_mask: torch.Tensor, rng_seed: int, block_sizes: Sequence[int], num_steps: int, cfg_scale_text: float,
+        cfg_scale_speaker: float, cfg_min_t: float, cfg_max_t: float, truncation_factor: Optional[float],
+        rescale_k: Optional[float], rescale_sigma: Optional[float], speaker_kv_scale: Optional[float],
+        speaker_kv_max_layers: Optional[int], speaker_kv_min_t: Optional[float],
+        continuation_latent: Optional[torch.Tensor] = None, *, _noises: Optional[Sequence[torch.Tensor]] = None,
+        on_block=None) -> torch.Tensor:
+    """Drop-in for reference ``inference_blockwise.py:14-123``.  Differences in HOW, not WHAT: the latent-prefix KV
+    is encoded for B rows (the reference encodes three identical copies, :72-74) and un-generated patches are
+    skipped by length instead of masked; ``on_block(start, stop, prefix)`` (optional) is the streaming hook."""
+    if speaker_kv_scale is not None and speaker_kv_min_t is None:
+        raise TypeError("'<' not supported between instances of 'Tensor' and 'NoneType'")
+    cfg, dev = model.cfg, model.device
+    B = text_input_ids.shape[0]
+    p = dict(cfg_scale_text=float(cfg_scale_text), cfg_scale_speaker=float(cfg_scale_speaker), rescale_k=rescale_k,
+             rescale_sigma=rescale_sigma)
+    rng = torch.Generator(device=dev).manual_seed(rng_seed)
+    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)
+    kv_spk = model.get_kv_cache_speaker(speaker_latent)
+    masks = _prep_masks(model, text_mask, speaker_mask)
+    prefix = torch.zeros((B, sum(block_sizes), cfg.latent_size), device=dev, dtype=F32)
+    start = 0
+    if continuation_latent is not None:
+        prefix = torch.cat([continuation_latent.to(dev, F32), prefix], 1)
+        start = continuation_latent.shape[1]
+    mult = None
+    mod = None
+    for bi, bs in enumerate(block_sizes):
+        # the reference re-applies speaker_kv_scale at every block (inference_blockwise.py:68-70): carry the multiplier
+        plan = StepPlan(dev, num_steps, cfg_min_t, cfg_max_t, speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t,
+                        cfg.num_layers, initial_multiplier=mult)
+        mult = plan.final_multiplier
+        if mod is None:
+            mod = model.build_mod_table(plan.t_dev)
+        kv_lat = model.get_kv_cache_latent(prefix) if prefix.shape[1] >= cfg.speaker_patch_size else None
+        n_prefix = 0
+        if kv_lat is not None:
+            n_prefix = min(kv_lat[0][0].shape[1], -(-start // cfg.speaker_patch_size))     # model.py:243-244
+        if _noises is not None:
+            x_t = _noises[bi].to(dev, F32).clone()
+        else:
+            x_t = torch.randn((B, bs, cfg.latent_size), device=dev, dtype=F32, generator=rng)
+        if truncation_factor is not None:
+            x_t = x_t * truncation_factor
+        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, start_pos=start, kv_latent=kv_lat,
+                  n_prefix=n_prefix)
+        prefix[:, start:start + bs] = x_t
+        if on_block is not None:
+            on_block(start, start + bs, prefix)
+        start += bs
+    return prefix

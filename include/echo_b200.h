@@ -1,0 +1,206 @@
+/* echo_b200.h -- C ABI of libecho_b200.so (hand-written sm_100a kernels for the Echo-TTS
+ * sampling hot path).  Plain pointers and sizes only; every pointer is a DEVICE pointer owned
+ * by the caller (PyTorch tensors on the Python side), every call is asynchronous on `stream`,
+ * nothing is allocated inside.  Return value: 0 ok, <0 error (echo_last_error() has the text).
+ *
+ * The upstream project (CoreBedtime/echo-tts) is pure Python/PyTorch and has no FFI; each entry
+ * point below names the reference code it replaces (file:line in the upstream repo) -- the
+ * binding a maintainer would add is the ctypes stub shown in INTEGRATION.md.
+ */
+#ifndef ECHO_B200_H
+#define ECHO_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* echo_stream_t; /* cudaStream_t */
+
+const char* echo_last_error(void);
+int echo_version(void);
+unsigned long long echo_launch_count(void); /* kernels launched by this library so far */
+void echo_reset_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * bf16 tensor-core GEMM with implicit-conv taps and fused epilogues.
+ *   acc[b, m, n] = sum_t sum_k A[b, m + tap_shift[t], k] * B[n, t*k_tap + k]     (fp32 accumulate)
+ * Rows outside [0, rows) read as zero (causal left padding of CausalConvNet,
+ * autoencoder.py:285-289).  impl 0 = tcgen05.mma + TMEM accumulators + TMA loads (the product
+ * path); impl 1 = legacy mma.sync kernel kept as an A/B baseline and debugging aid.
+ * Replaces every nn.Linear / Conv1d / ConvTranspose1d on the path: model.py:217-224, 266, 308;
+ * autoencoder.py:285-316, 365-367, 667, 704, 717.
+ * ------------------------------------------------------------------------------------------ */
+enum { ECHO_EPI_GENERIC = 0, ECHO_EPI_SECTIONS = 1, ECHO_EPI_SWIGLU = 2 };
+enum { ECHO_ACT_NONE = 0, ECHO_ACT_GELU = 1, ECHO_ACT_SILU = 2, ECHO_ACT_SIGMOID = 3, ECHO_ACT_TANH = 4 };
+enum { ECHO_SEC_PLAIN = 0, ECHO_SEC_NORM_ROPE = 1, ECHO_SEC_SIGMOID = 2, ECHO_SEC_ROPE = 3 };
+
+typedef struct echo_gemm_section {
+  int32_t type;             /* ECHO_SEC_* */
+  int32_t _pad;
+  void* out;                /* bf16 [batch*rows, ld_sec_out] */
+  const float* norm_weight; /* fp32 [section_width] (per-head RMSNorm weight, model.py:192-193) */
+} echo_gemm_section;
+
+typedef struct echo_gemm_desc {
+  const void* a;            /* bf16 [batch][rows][lda] */
+  const void* b;            /* bf16 [n][ldb], ldb >= taps*k_tap */
+  int64_t lda, a_batch_stride, ldb;
+  int32_t rows, batch, n, k_tap, taps;
+  int32_t tap_shift[8];
+  int32_t epilogue;         /* ECHO_EPI_* */
+  int32_t impl;             /* 0 tcgen05, 1 legacy mma.sync */
+  int32_t block_n;          /* 0 = auto; 64 / 128 / 256 */
+  int32_t act;              /* GENERIC: activation applied after bias */
+  /* GENERIC: v = act(acc + bias[n]) * gate[(m / rows_per_gate) * gate_ld + n] + resid[m, n]
+   *          out_f32 / out_bf16 <- v ; out2_bf16 <- snake(v, snake_alpha[n])  (any may be NULL) */
+  const float* bias;
+  const float* gate;
+  int64_t gate_ld;
+  int32_t rows_per_gate;
+  int32_t _pad0;
+  const float* resid;
+  int64_t ld_resid;
+  float* out_f32;
+  int64_t ld_out_f32;
+  void* out_bf16;
+  int64_t ld_out_bf16;
+  void* out2_bf16;
+  int64_t ld_out2_bf16;
+  const float* snake_alpha;
+  /* SECTIONS: n = n_sections * section_width; per-head RMSNorm (+ interleaved-pair RoPE on heads
+   * < rope_heads at position pos_offset + (m % rows_per_seq) * pos_stride) / plain / sigmoid.
+   * Replaces model.py:221-232, 199-202, 17-24, 264 (sigmoid of the gate) and 270-293. */
+  int32_t n_sections, section_width, head_dim, rope_heads;
+  int32_t pos_offset, pos_stride, rows_per_seq, _pad1;
+  float eps;
+  float _pad2;
+  const float* rope_cos;    /* fp32 [max_pos][head_dim/2] */
+  const float* rope_sin;
+  int64_t ld_sec_out;
+  echo_gemm_section sections[4];
+  /* SWIGLU: B rows interleaved in groups of 64 (w1 | w3); out_bf16[m, j] = silu(a)*b (model.py:308) */
+} echo_gemm_desc;
+
+int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * fp32 CUDA-core GEMM for the accuracy-critical small projections:
+ *   out[z, m, n] = post( sum_k pre(A[z, m, k]) * W[z, n, k] + bias[z, n] + addend[m, n] )
+ * Replaces cond_module + LowRankAdaLN (model.py:70-74, 532-538), in_proj (model.py:586),
+ * SpeakerEncoder.in_proj (model.py:461-462) and the PCA inverse (inference.py:234).
+ * ------------------------------------------------------------------------------------------ */
+enum { ECHO_POST_NONE = 0, ECHO_POST_PLUS1 = 1, ECHO_POST_TANH = 2, ECHO_POST_SILU = 3 };
+typedef struct echo_sgemm_desc {
+  const float* a; int64_t lda, a_zstride;
+  const float* w; int64_t ldw, w_zstride;
+  const float* bias; int64_t bias_zstride;
+  const float* addend; int64_t ld_addend, addend_zstride;
+  float* out; int64_t ldo, out_zstride;
+  void* out_bf16; int64_t ldo_bf16, out_bf16_zstride;
+  int32_t m, n, k, nz;
+  int32_t pre_silu, post;
+  float out_scale;   /* applied after bias, before addend/post (1/6 of model.py:462; 1/latent_scale) */
+  float _pad;
+} echo_sgemm_desc;
+int echo_sgemm_f32(const echo_sgemm_desc* d, echo_stream_t stream);
+
+/* timestep embedding cat[cos(t w), sin(t w)] (model.py:27-43): t fp32 [n] -> out fp32 [n, size] */
+int echo_timestep_embedding(const float* t, int n, int size, float* out, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Row normalisation -> bf16 GEMM operand.
+ *   y[m, :] = x[m, :] * rsqrt(mean(x^2) + eps) * scale1[g, :] + shift[g, :],  g = mod_base + m / rows_per_mod
+ * (LowRankAdaLN.forward model.py:76-79 with scale1 = 1 + scale; RMSNorm model.py:99-104 with
+ * shift = NULL, scale1 = weight; autoencoder.py:726-731).  `step` (device int, nullable) adds
+ * step[0] * mod_step_stride rows to the table offset so one CUDA graph serves every Euler step.
+ * ------------------------------------------------------------------------------------------ */
+int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float eps, const float* scale1,
+                     const float* shift, int64_t mod_ld, int rows_per_mod, const int32_t* step,
+                     int64_t mod_step_stride, void* y_bf16, int64_t ldy, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Flash-style attention over up to four KV segments walked in place (no concat):
+ * replaces torch.cat + F.scaled_dot_product_attention + sigmoid gating at model.py:246-264 and
+ * 148-157, _concat_kv_caches / _multiply_kv_cache (inference.py:409-428) and the dense window
+ * mask of autoencoder.py:762-797.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct echo_attn_segment {
+  const void* k;            /* bf16; key j of kv-row b, head h at k + b*batch_stride + j*row_stride + h*head_dim */
+  const void* v;
+  int64_t row_stride, batch_stride;
+  int32_t len;              /* keys in this segment */
+  int32_t kv_batch_mod;     /* kv-row = row % kv_batch_mod (0: kv-row = row): CFG rows share one cache */
+  const uint8_t* mask;      /* [rows, mask_stride] key-valid bytes, NULL = all valid */
+  int64_t mask_stride;
+  const int32_t* extent;    /* per-row 1 + last valid key (tile skipping), NULL = len */
+  const float* kv_scale;    /* device scalar multiplying K and V (speaker_kv_scale), NULL = 1 */
+  int32_t causal;           /* key j visible to query i iff j <= i (+ window: j > i - window) */
+  int32_t window;
+} echo_attn_segment;
+
+typedef struct echo_attn_desc {
+  const void* q;            /* bf16 [rows, seq, heads, head_dim] */
+  int64_t q_row_stride, q_batch_stride; /* elements between consecutive queries / rows */
+  const void* gate;         /* bf16 sigmoid(gate) [rows*seq, heads*head_dim] or NULL */
+  void* out;                /* bf16 [rows*seq, heads*head_dim] */
+  int32_t rows, seq, heads, head_dim;
+  int32_t n_seg, _pad;
+  float softmax_scale, _pad1;
+  echo_attn_segment seg[4];
+} echo_attn_desc;
+int echo_attention(const echo_attn_desc* d, echo_stream_t stream);
+
+/* extent[r] = 1 + index of last non-zero byte of mask[r, :len] (0 if none) */
+int echo_mask_extent(const uint8_t* mask, int rows, int len, int64_t stride, int32_t* extent,
+                     echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused sampler tail: out_norm -> out_proj -> 3-branch CFG combine -> temporal score rescale ->
+ * Euler update, fp32, x_t updated in place.  Replaces model.py:601-604 and inference.py:514-530,
+ * 431-443, 558.  h: final residual stream fp32 [branches*B*S, d] (branch-major: cond | text-
+ * dropped | speaker-dropped).  sched: fp32 [steps][4] = {t, t_next - t, unused, unused} read at
+ * row step[0] (device) so the call is CUDA-graph replayable.  v_out (nullable): per-branch
+ * velocities fp32 [branches*B*S, latent] for parity tests.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct echo_tail_desc {
+  const float* h; int64_t ldh;
+  const float* norm_w; const float* w_out; const float* b_out;  /* [d], [latent, d], [latent] */
+  float* x_t;               /* fp32 [B*S, latent] in/out */
+  float* v_out;
+  float* v_comb_out;        /* nullable: combined (post-rescale) velocity fp32 [B*S, latent] */
+  const float* sched; const int32_t* step;
+  int32_t positions;        /* B*S */
+  int32_t d, latent, branches;
+  float eps, cfg_text, cfg_speaker, rescale_k, rescale_sigma;
+  int32_t use_rescale;
+  int32_t update_x;         /* 0: only write velocities (model.__call__ compatibility path) */
+  int32_t _pad;
+} echo_tail_desc;
+int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream);
+int echo_step_advance(int32_t* step, echo_stream_t stream); /* step[0] += 1 */
+
+/* text embedding lookup (model.py:420): ids int32 [n] -> out fp32 [n, d] */
+int echo_embedding(const int32_t* ids, int n, const float* table, int d, float* out, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * S1-DAC decode helpers (time-major [B, T, C] activations).
+ * ------------------------------------------------------------------------------------------ */
+/* ConvNeXt front: causal depthwise conv k=7 + LayerNorm(eps) -> bf16 (autoencoder.py:362-364) */
+int echo_dwconv_layernorm(const float* x, int batch, int t, int c, const float* w_dw /*[c,7]*/,
+                          const float* b_dw, const float* ln_w, const float* ln_b, float eps,
+                          void* y_bf16, echo_stream_t stream);
+/* last stage: causal conv k=7, C -> 1, + tanh (autoencoder.py:994): x bf16 [B,T,C] (already Snake'd) */
+int echo_conv_out_tanh(const void* x_bf16, int batch, int t, int c, const float* w /*[7][c]*/, float bias,
+                       float* wav, echo_stream_t stream);
+/* element-wise fp32 -> bf16 with optional Snake (autoencoder.py:96-102) over [rows, c] */
+int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
+
+/* find_flattening_point (inference.py:315-330): latent fp32 [len, width] -> index (device int32) */
+int echo_flattening_point(const float* latent, int len, int width, int window, float std_threshold,
+                          float target, int32_t* index_out, echo_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ECHO_B200_H */

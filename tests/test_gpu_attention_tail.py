@@ -1,0 +1,154 @@
+"""Attention, sampler tail and small kernels on a B200 against torch fp32 references."""
+import math
+
+import pytest
+import torch
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from echo_tts_b200 import ops as o
+    return o
+
+
+def _rand(shape, seed, scale=1.0, dtype=F32):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, device="cuda", generator=g) * scale).to(dtype)
+
+
+def _ref_attention(q, segs, gate):
+    """fp32 dense reference: concat segments (what the reference model does, model.py:246-261)."""
+    R, S, H, Dh = q.shape
+    ks, vs, ms = [], [], []
+    for s in segs:
+        Lk = s["k"].shape[1]
+        idx = torch.arange(R, device=q.device) % s["k"].shape[0]
+        f = s.get("scale", 1.0)
+        ks.append(s["k"].float()[idx] * f)
+        vs.append(s["v"].float()[idx] * f)
+        m = s["mask"].bool() if s.get("mask") is not None else torch.ones(R, Lk, dtype=torch.bool, device=q.device)
+        m = m[:, None, :].expand(R, S, Lk).clone()
+        if s.get("causal"):
+            i = torch.arange(S, device=q.device)[:, None]
+            j = torch.arange(Lk, device=q.device)[None, :]
+            c = j <= i
+            if s.get("window", 0) > 0:
+                c &= j > i - s["window"]
+            m &= c[None]
+        ms.append(m)
+    K, V, Mk = torch.cat(ks, 1), torch.cat(vs, 1), torch.cat(ms, 2)
+    sc = torch.einsum("rshd,rlhd->rhsl", q.float(), K) / math.sqrt(Dh)
+    sc = sc.masked_fill(~Mk[:, None], float("-inf"))
+    o = torch.einsum("rhsl,rlhd->rshd", torch.softmax(sc, -1), V).reshape(R * S, H * Dh)
+    return o * gate.float() if gate is not None else o
+
+
+def test_joint_attention_segments(ops):
+    """CFG layout: 3B rows share B-row caches; dropped modalities via zero masks; speaker K/V scaled."""
+    B, S, H, Dh, Lt, Ls, Lp = 2, 200, 3, 128, 150, 37, 20
+    R = 3 * B
+    q, k, v = (_rand((R, S, H, Dh), i, dtype=BF16) for i in (1, 2, 3))
+    kt, vt, ksp, vsp, kl, vl = (_rand((B, n, H, Dh), 4 + i, dtype=BF16) for i, n in enumerate((Lt, Lt, Ls, Ls, Lp, Lp)))
+    gate = torch.sigmoid(_rand((R * S, H * Dh), 10)).to(BF16)
+    tm = torch.zeros(B, Lt, dtype=torch.uint8, device="cuda"); tm[0, :70] = 1; tm[1, :133] = 1; tm[1, 5] = 0
+    sm = torch.ones(B, Ls, dtype=torch.uint8, device="cuda"); sm[1, 20:] = 0
+    tm3 = torch.cat([tm, torch.zeros_like(tm), tm]); sm3 = torch.cat([sm, sm, torch.zeros_like(sm)])
+    scale = torch.tensor([1.5], device="cuda")
+    n_prefix = 13
+    out = torch.empty((R * S, H * Dh), device="cuda", dtype=BF16)
+    ops.attention(q, [ops.Segment(k, v), ops.Segment(kl, vl, kv_batch_mod=B, length=n_prefix),
+                      ops.Segment(kt, vt, kv_batch_mod=B, mask=tm3, extent=ops.mask_extent(tm3)),
+                      ops.Segment(ksp, vsp, kv_batch_mod=B, mask=sm3, extent=ops.mask_extent(sm3), kv_scale=scale)],
+                  out, gate=gate)
+    ref = _ref_attention(q, [dict(k=k, v=v), dict(k=kl[:, :n_prefix], v=vl[:, :n_prefix]), dict(k=kt, v=vt, mask=tm3),
+                             dict(k=ksp, v=vsp, mask=sm3, scale=1.5)], gate)
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
+@pytest.mark.parametrize("Dh,window", [(128, 0), (64, 16), (64, 128)])
+def test_causal_window_attention(ops, Dh, window):
+    B, S, H = 2, 333, 4
+    q, k, v = (_rand((B, S, H, Dh), i, dtype=BF16) for i in (11, 12, 13))
+    out = torch.empty((B * S, H * Dh), device="cuda", dtype=BF16)
+    ops.attention(q, [ops.Segment(k, v, causal=True, window=window)], out)
+    ref = _ref_attention(q, [dict(k=k, v=v, causal=True, window=window)], None)
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
+def test_key_padding_attention_strided_views(ops):
+    """encoder-style: q/k/v are slices of one fused buffer; key padding mask with extent."""
+    B, S, H, Dh = 3, 90, 2, 128
+    buf = _rand((3, B, S, H, Dh), 14, dtype=BF16)
+    mask = torch.zeros(B, S, dtype=torch.uint8, device="cuda"); mask[0, :90] = 1; mask[1, :10] = 1; mask[2, :64] = 1
+    out = torch.empty((B * S, H * Dh), device="cuda", dtype=BF16)
+    ops.attention(buf[0], [ops.Segment(buf[1], buf[2], mask=mask, extent=ops.mask_extent(mask))], out)
+    ref = _ref_attention(buf[0], [dict(k=buf[1], v=buf[2], mask=mask)], None)
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
+@pytest.mark.parametrize("branches,rescale", [(3, False), (3, True), (1, True)])
+def test_cfg_euler_tail(ops, branches, rescale):
+    from oracle import echo_oracle as O
+    B, S, D, lat = 2, 37, 512, 80
+    P = B * S
+    h = _rand((branches * P, D), 20, 2.0)
+    nw, w, b = _rand((D,), 21).abs() + 0.5, _rand((lat, D), 22, D ** -0.5), _rand((lat,), 23)
+    x0 = _rand((P, lat), 24)
+    t, tn = 0.7243, 0.6991
+    sched = torch.tensor([t, tn - t, 0, 0], device="cuda", dtype=F32)
+    x = x0.clone()
+    vout = torch.empty((branches * P, lat), device="cuda")
+    vc = torch.empty((P, lat), device="cuda")
+    ops.cfg_euler_tail(h, nw, w, b, positions=P, branches=branches, eps=1e-5, x_t=x, sched=sched, cfg_text=3.0,
+                       cfg_speaker=8.0, rescale_k=1.2 if rescale else None, rescale_sigma=3.0 if rescale else None,
+                       v_out=vout, v_comb_out=vc)
+    hn = O.rms_norm(h.cpu(), nw.cpu(), 1e-5)
+    v = hn @ w.cpu().t() + b.cpu()
+    assert rel_l2(vout.cpu(), v) < 1e-5
+    if branches == 3:
+        a, bb, c = v.chunk(3, 0)
+        v = a + 3.0 * (a - bb) + 8.0 * (a - c)
+    if rescale:
+        v = O.temporal_score_rescale(v, x0.cpu(), torch.tensor(t), 1.2, 3.0)
+    assert rel_l2(vc.cpu(), v) < 2e-5
+    tt = sched.cpu()
+    assert rel_l2(x.cpu(), x0.cpu() + v * tt[1]) < 1e-5
+
+
+def test_small_kernels(ops):
+    from oracle import echo_oracle as O
+    t = torch.tensor([0.999, 0.5, 0.0123], device="cuda")
+    assert rel_l2(ops.timestep_embedding(t, 512).cpu(), O.timestep_embedding(t.cpu(), 512)) < 1e-4
+    ids = torch.tensor([0, 5, 255, 7], device="cuda", dtype=torch.int32)
+    tab = _rand((256, 64), 30)
+    assert torch.equal(ops.embedding(ids, tab), tab[ids.long()])
+    m = torch.zeros(4, 50, dtype=torch.bool, device="cuda"); m[0, :7] = True; m[2, 49] = True; m[3, 0] = True
+    assert ops.mask_extent(m).tolist() == [7, 0, 50, 1]
+    x = _rand((2, 40, 128), 31)
+    w, b, lw, lb = _rand((128, 7), 32, 0.4), _rand((128,), 33, 0.1), _rand((128,), 34).abs() + 0.5, _rand((128,), 35, 0.1)
+    y = torch.empty((2, 40, 128), device="cuda", dtype=BF16)
+    ops.dwconv_layernorm(x, w, b, lw, lb, 1e-6, y)
+    xc = x.cpu().transpose(1, 2)
+    ref = O.causal_conv1d(xc, w.cpu()[:, None, :], b.cpu(), groups=128).transpose(1, 2)
+    ref = torch.nn.functional.layer_norm(ref, (128,), lw.cpu(), lb.cpu(), 1e-6)
+    assert rel_l2(y.float().cpu(), ref) < 4e-3
+    xs = _rand((1, 600, 96), 36, dtype=BF16)
+    wl = _rand((7, 96), 37, 0.05)
+    wav = torch.empty((1, 600), device="cuda")
+    ops.conv_out_tanh(xs, wl, 0.01, wav)
+    refw = torch.tanh(O.causal_conv1d(xs.float().cpu().transpose(1, 2), wl.cpu().t()[None], torch.tensor([0.01])))
+    assert rel_l2(wav.cpu(), refw[:, 0]) < 1e-4
+
+
+def test_flattening_point_matches_golden(ops):
+    import json, os
+    from conftest import GOLDEN
+    idx = {c["case"]: c["index"] for c in json.load(open(os.path.join(GOLDEN, "index_golden.json")))["flatten"]}
+    cases = torch.load(os.path.join(GOLDEN, "flatten_cases.pt"))
+    for name, data in cases.items():
+        assert int(ops.flattening_point(data.cuda().contiguous()).item()) == idx[name], name

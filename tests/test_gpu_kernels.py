@@ -1,0 +1,147 @@
+"""Per-kernel parity on a B200: each hand-written kernel (called through the C ABI) against a plain torch
+fp32 reference of the same op on the same inputs.  Tolerances: bf16-operand GEMM/attention outputs are
+compared with references computed from the SAME bf16-rounded operands in fp32, so only accumulation order and
+the final bf16 rounding differ (rel-L2 <= 4e-3); fp32 kernels <= 1e-5."""
+import math
+
+import pytest
+import torch
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from echo_tts_b200 import ops as o
+    return o
+
+
+@pytest.fixture(scope="module")
+def L():
+    from echo_tts_b200 import _lib
+    return _lib
+
+
+def _rand(shape, seed, scale=1.0, dtype=F32):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, device="cuda", generator=g) * scale).to(dtype)
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("M,N,K,bn", [(128, 256, 64, 0), (256, 512, 512, 256), (200, 384, 320, 128), (1920, 2048, 2048, 0),
+                                      (64, 96, 96, 0), (640, 2048, 5888, 128), (130, 64, 128, 64)])
+def test_gemm_plain(ops, impl, M, N, K, bn):
+    a, w = _rand((M, K), 1, dtype=BF16), _rand((N, K), 2, K ** -0.5, BF16)
+    bias = _rand((N,), 3)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=F32)
+    outb = torch.empty((M, N), device="cuda", dtype=BF16)
+    ops.gemm_generic(a, w, bias=bias, out_f32=out, out_bf16=outb, impl=impl, block_n=bn)
+    ref = a.float() @ w.float().t() + bias
+    assert rel_l2(out, ref) < 2e-5, (impl, M, N, K)
+    assert rel_l2(outb.float(), ref) < 4e-3
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_generic_epilogue_full(ops, L, impl):
+    M, N, K, S = 384, 256, 192, 128
+    a, w = _rand((M, K), 4, dtype=BF16), _rand((N, K), 5, K ** -0.5, BF16)
+    bias, gate, resid, alpha = _rand((N,), 6), _rand((M // S, N), 7), _rand((M, N), 8), _rand((N,), 9).abs() + 0.5
+    x = resid.clone()
+    sn = torch.empty((M, N), device="cuda", dtype=BF16)
+    ops.gemm_generic(a, w, bias=bias, act=L.ACT_GELU, gate=gate, rows_per_gate=S, resid=x, out_f32=x, out2_bf16=sn,
+                     snake_alpha=alpha, impl=impl)
+    ref = torch.nn.functional.gelu(a.float() @ w.float().t() + bias) * gate.repeat_interleave(S, 0) + resid
+    assert rel_l2(x, ref) < 2e-5
+    assert rel_l2(sn.float(), ref + torch.sin(alpha * ref) ** 2 / (alpha + 1e-9)) < 4e-3
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("dil,taps_n,C,N,B,T", [(1, 7, 128, 128, 2, 300), (9, 7, 96, 96, 1, 700), (3, 7, 64, 256, 3, 130)])
+def test_gemm_causal_conv_taps(ops, impl, dil, taps_n, C, N, B, T):
+    """implicit-GEMM causal dilated conv1d == F.conv1d on left-padded input (autoencoder.py:285-289)."""
+    x = _rand((B, T, C), 10, dtype=BF16)
+    w = _rand((N, C, taps_n), 11, (C * taps_n) ** -0.5, BF16)
+    wp = w.permute(0, 2, 1).reshape(N, taps_n * C).contiguous()
+    out = torch.empty((B * T, N), device="cuda", dtype=F32)
+    ops.gemm_generic(x.view(B * T, C), wp, taps=tuple(-(taps_n - 1 - k) * dil for k in range(taps_n)), batch=B,
+                     out_f32=out, impl=impl)
+    xin = torch.nn.functional.pad(x.float().transpose(1, 2), ((taps_n - 1) * dil, 0))
+    ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil).transpose(1, 2).reshape(B * T, N)
+    assert rel_l2(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_conv_transpose(ops, impl):
+    """2-tap GEMM == causal ConvTranspose1d(k=2s, stride s) with right trim (autoencoder.py:310-316)."""
+    from echo_tts_b200.autoencoder import _pack_convT
+    B, T, Cin, Cout, s = 2, 100, 128, 64, 4
+    x = _rand((B, T, Cin), 12, dtype=BF16)
+    w = _rand((Cin, Cout, 2 * s), 13, (2 * Cin) ** -0.5, BF16)
+    out = torch.empty((B * T, s * Cout), device="cuda", dtype=F32)
+    ops.gemm_generic(x.view(B * T, Cin), _pack_convT(w.float(), s), taps=(0, -1), batch=B, out_f32=out, impl=impl)
+    ref = torch.nn.functional.conv_transpose1d(x.float().transpose(1, 2), w.float(), stride=s)[..., : T * s]
+    assert rel_l2(out.view(B, T * s, Cout), ref.transpose(1, 2)) < 2e-5
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_swiglu(ops, impl):
+    M, K, F_ = 256, 256, 384
+    a = _rand((M, K), 14, dtype=BF16)
+    w1, w3 = _rand((F_, K), 15, K ** -0.5, BF16), _rand((F_, K), 16, K ** -0.5, BF16)
+    out = torch.empty((M, F_), device="cuda", dtype=BF16)
+    ops.gemm_swiglu(a, ops.pack_w13(w1, w3), out, impl=impl)
+    ref = torch.nn.functional.silu(a.float() @ w1.float().t()) * (a.float() @ w3.float().t())
+    assert rel_l2(out.float(), ref) < 4e-3
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("hd,H,rope_heads", [(128, 4, 2), (64, 4, 4)])
+def test_gemm_sections_norm_rope(ops, L, impl, hd, H, rope_heads):
+    from oracle import echo_oracle as O
+    R, S, K, start = 2, 96, 256, 5
+    D = H * hd
+    M = R * S
+    a = _rand((M, K), 17, dtype=BF16)
+    w = _rand((4 * D, K), 18, K ** -0.5, BF16)
+    qn, kn = _rand((D,), 19).abs() + 0.5, _rand((D,), 20).abs() + 0.5
+    cos, sin = O.rope_table(hd, 4096)
+    rope = (cos.cuda().contiguous(), sin.cuda().contiguous())
+    outs = torch.empty((4, M, D), device="cuda", dtype=BF16)
+    ops.gemm_sections(a, w, [(L.SEC_NORM_ROPE, outs[0], qn), (L.SEC_NORM_ROPE, outs[1], kn), (L.SEC_PLAIN, outs[2], None),
+                             (L.SEC_SIGMOID, outs[3], None)], head_dim=hd, rope_heads=rope_heads, rope=rope,
+                      pos_offset=start, rows_per_seq=S, eps=1e-5, impl=impl)
+    acc = (a.float() @ w.float().t()).cpu()
+    q, k, v, g = acc.split(D, dim=1)
+
+    def nr(t, wn):
+        t = O.rms_norm(t.reshape(R, S, H, hd), wn.cpu().reshape(H, hd), 1e-5)
+        rot = O.rope_apply(t[:, :, :rope_heads], cos[start:start + S], sin[start:start + S])
+        return torch.cat([rot, t[:, :, rope_heads:]], 2).reshape(M, D)
+    for got, ref in zip(outs, (nr(q, qn), nr(k, kn), v, torch.sigmoid(g))):
+        assert rel_l2(got.float().cpu(), ref) < 4e-3
+
+
+def test_sgemm_and_batched(ops, L):
+    a, w, b, add = _rand((70, 100), 21), _rand((90, 100), 22), _rand((90,), 23), _rand((70, 90), 24)
+    out = torch.empty((70, 90), device="cuda")
+    ops.sgemm(a, w, bias=b, addend=add, out=out, pre_silu=True, post=L.POST_TANH, out_scale=0.5)
+    ref = torch.tanh((torch.nn.functional.silu(a) @ w.t() + b) * 0.5 + add)
+    assert rel_l2(out, ref) < 1e-5
+    az, wz, bz = _rand((5, 33, 64), 25), _rand((5, 48, 64), 26), _rand((5, 48), 27)
+    outz = torch.empty((5, 33, 48), device="cuda")
+    ops.sgemm(az, wz, bias=bz, out=outz, post=L.POST_PLUS1)
+    assert rel_l2(outz, torch.einsum("zmk,znk->zmn", az, wz) + bz[:, None] + 1) < 1e-5
+
+
+def test_rmsnorm_mod(ops):
+    M, D, S = 96, 2048, 32
+    x = _rand((M, D), 28, 3.0)
+    tab = _rand((M // S, 2, D), 29)
+    y = torch.empty((M, D), device="cuda", dtype=BF16)
+    ops.rmsnorm_mod(x, tab[0, 1], tab[0, 0], y, 1e-5, rows_per_mod=S, mod_ld=tab.stride(0))
+    ref = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5) * tab[:, 1].repeat_interleave(S, 0) + \
+        tab[:, 0].repeat_interleave(S, 0)
+    assert rel_l2(y.float(), ref) < 3e-3

@@ -1,0 +1,136 @@
+"""End-to-end parity of the CUDA path (through the reference-shaped Python API -> C ABI -> sm_100a kernels)
+against (a) fixtures produced by executing the upstream reference in fp32 and (b) the CPU oracle on the same
+seeded inputs.  Tolerances are BASELINE.json's: per-step per-branch velocity rel-L2 <= 1e-2, final latent
+rel-L2 <= 2e-2 (bf16 tensor-core operands vs the reference's fp32 path); index handling bit-exact."""
+import os
+
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from echo_tts_b200 import schema as S
+
+pytestmark = pytest.mark.gpu
+V_TOL, X_TOL = 1e-2, 2e-2
+
+
+@pytest.fixture(scope="module")
+def tiny_model():
+    from echo_tts_b200.inference import load_model_from_state_dict
+    return load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_TINY)), cfg=S.ECHO_TINY)
+
+
+def _run_fixture(model, name):
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    g = torch.load(os.path.join(GOLDEN, name))
+    trace = []
+    out = sample(model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0,
+                 _noise=g["noise"], _trace=trace, **g["kwargs"])
+    return g, out.cpu(), trace
+
+
+@pytest.mark.parametrize("name", ["dit_tiny_sampler.pt", "dit_tiny_sampler_opts.pt"])
+def test_tiny_sampler_vs_reference_fixture(tiny_model, name):
+    g, out, trace = _run_fixture(tiny_model, name)
+    assert len(trace) == len(g["v_branches"])
+    for st, ref in zip(trace, g["v_branches"]):
+        assert st["v_branches"].shape == ref.shape
+        for br_mine, br_ref in zip(st["v_branches"].cpu().chunk(ref.shape[0] // g["noise"].shape[0], 0),
+                                   ref.float().chunk(ref.shape[0] // g["noise"].shape[0], 0)):
+            assert rel_l2(br_mine, br_ref) < V_TOL
+    assert rel_l2(out, g["x_final"]) < X_TOL
+
+
+def test_tiny_sampler_teacher_forced_vs_oracle(tiny_model):
+    """Each step's velocities at the ORACLE's x_t (no error accumulation): isolates the forward pass."""
+    from oracle import echo_oracle as O
+    g, out, trace = _run_fixture(tiny_model, "dit_tiny_sampler_opts.pt")
+    sd = S.synth_state_dict(S.dit_schema(S.ECHO_TINY))
+    otrace = []
+    O.sample_euler_cfg_independent_guidances(sd, S.ECHO_TINY, g["speaker_latent"], g["speaker_mask"], g["ids"],
+                                             g["text_mask"], 0, noise=g["noise"], trace=otrace, **g["kwargs"])
+    for a, b in zip(trace, otrace):
+        assert a["has_cfg"] == b["has_cfg"]
+        assert rel_l2(a["x_in"].cpu(), b["x_in"]) < X_TOL
+        assert rel_l2(a["v"].cpu(), b["v"]) < 5e-2          # combined velocity: CFG amplifies branch error ~10x
+
+
+def test_graph_replay_equals_eager(tiny_model):
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    g = torch.load(os.path.join(GOLDEN, "dit_tiny_sampler.pt"))
+    args = (tiny_model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0)
+    outs = [sample(*args, _noise=g["noise"], **g["kwargs"]).cpu() for _ in range(3)]   # eager, capture+replay, replay
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    assert rel_l2(outs[2], g["x_final"]) < X_TOL
+
+
+def test_model_call_compat_vs_oracle(tiny_model):
+    """The reference-shaped ``model(x, t, masks, caches)`` surface (third-party samplers)."""
+    from oracle import echo_oracle as O
+    cfg = S.ECHO_TINY
+    sd = S.synth_state_dict(S.dit_schema(cfg))
+    gen = torch.Generator().manual_seed(3)
+    ids, mask, _ = O.text_ids_and_mask(["compat path", "x"], None)
+    spk = torch.randn(2, 16, 80, generator=gen); sm = torch.ones(2, 16, dtype=torch.bool); sm[1, 8:] = False
+    x = torch.randn(2, 40, 80, generator=gen); t = torch.tensor([0.9, 0.3])
+    ref = O.dit_forward(sd, cfg, x, t, mask, sm, O.kv_cache_text(sd, cfg, ids, mask), O.kv_cache_speaker(sd, cfg, spk))
+    kt = tiny_model.get_kv_cache_text(ids.cuda(), mask.cuda())
+    ks = tiny_model.get_kv_cache_speaker(spk.cuda())
+    got = tiny_model(x.cuda(), t.cuda(), mask.cuda(), sm.cuda(), kt, ks)
+    assert got.dtype == torch.float32 and got.shape == ref.shape
+    assert rel_l2(got.cpu(), ref) < V_TOL
+
+
+def test_blockwise_vs_reference_fixture(tiny_model):
+    from echo_tts_b200.inference_blockwise import sample_blockwise_euler_cfg_independent_guidances as sample
+    g = torch.load(os.path.join(GOLDEN, "dit_tiny_blockwise.pt"))
+    out = sample(tiny_model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(),
+                 0, continuation_latent=g["continuation"].cuda(), _noises=g["noises"], **g["kwargs"]).cpu()
+    assert torch.equal(out[:, :8], g["continuation"])
+    assert rel_l2(out, g["out"]) < X_TOL
+
+
+def test_ae_tiny_vs_oracle():
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    cfg = S.AE_TINY
+    sd = S.synth_ae_state_dict(cfg)
+    ae = load_fish_ae_from_state_dict(sd, cfg=cfg)
+    z = torch.randn(2, cfg.latent_dim, 40, generator=torch.Generator().manual_seed(1))
+    ref = O.decode_zq(sd, cfg, z)
+    got = ae.decode_zq(z.cuda()).cpu()
+    assert got.shape == ref.shape == (2, 1, 40 * cfg.hop)
+    assert rel_l2(got, ref) < 2e-2
+
+
+def test_ae_base_vs_reference_fixture():
+    """Full-size S1-DAC decode of 12 latents vs the upstream model's fp32 output + causality identity."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, ae_decode, PCAState
+    g = torch.load(os.path.join(GOLDEN, "ae_base_decode.pt"))
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE))
+    comp, mean, scale = O.synth_pca()
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    wav = ae_decode(ae, pca, g["z"].cuda()).cpu()
+    assert wav.shape == g["wav"].shape
+    assert rel_l2(wav, g["wav"]) < 2e-2
+    wav6 = ae_decode(ae, pca, g["z"][:, :6].cuda()).cpu()
+    assert rel_l2(wav6, wav[..., : 6 * 2048]) < 1e-3      # strictly causal: prefix decode == decode prefix
+
+
+@pytest.mark.slow
+def test_full_arch_config1_vs_reference_fixture():
+    """BASELINE.json config 1 (full echo-tts-base architecture, S=64, 4 steps, 212-latent speaker ref):
+    the reference ran it in fp32 on CPU (oracle/gen_golden.py --full); we run bf16 on the B200."""
+    from echo_tts_b200.inference import load_model_from_state_dict
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE)))
+    g = torch.load(os.path.join(GOLDEN, "dit_base_c1.pt"))
+    trace = []
+    out = sample(model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0,
+                 _noise=g["noise"], _trace=trace, **g["kwargs"]).cpu()
+    B = g["noise"].shape[0]
+    for st, ref in zip(trace, g["v_branches"]):
+        for a, b in zip(st["v_branches"].cpu().chunk(ref.shape[0] // B, 0), ref.float().chunk(ref.shape[0] // B, 0)):
+            assert rel_l2(a, b) < V_TOL
+    assert rel_l2(out, g["x_final"]) < X_TOL
