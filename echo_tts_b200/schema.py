@@ -9,6 +9,7 @@ construction order, identical on every machine, never stored in git.
 """
 from __future__ import annotations
 
+import re
 import zlib
 from dataclasses import dataclass, asdict
 from typing import Dict, Tuple
@@ -251,9 +252,14 @@ def synth_tensor(key: str, shape: Tuple[int, ...], seed: int) -> torch.Tensor:
     if leaf == "gamma":                       # LayerScale / ConvNeXt gamma
         return 0.2 * (0.5 + torch.rand(shape, generator=g))
     if leaf == "original0":                   # weight-norm g (positive)
+        base = 0.5 + torch.rand(shape, generator=g)
         if shape[0] == 1:                     # final 1-channel conv: keep tanh in its linear range
-            return 0.01 * (0.5 + torch.rand(shape, generator=g))
-        return 0.5 + torch.rand(shape, generator=g)
+            return 1.5 * base
+        if re.search(r"block\.\d+\.block\.3\.conv", key):   # residual-unit output conv: small residual branch
+            return 0.2 * base
+        if re.search(r"model\.\d+\.block\.1\.conv", key):   # up-sampling transposed conv
+            return 0.9 * base
+        return base                           # (keeps activations O(1) so Snake's sin() is not chaotic in bf16)
     if key.endswith("norm.weight") and len(shape) <= 2:
         return 1.0 + 0.2 * (torch.rand(shape, generator=g) - 0.5)
     if leaf == "bias":
