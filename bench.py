@@ -101,7 +101,7 @@ def cpu_reference_sample(threads=None, repeats=1):
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
     cfg = S.ECHO_BASE
-    sd = S.synth_state_dict(S.dit_schema(cfg, blockwise=False))
+    sd = S.synth_state_dict(S.dit_schema(cfg, blockwise=False), init="torch")
     ids, mask, spk, smask = synth_inputs(1)
     with torch.inference_mode():
         kv_t = O.kv_cache_text(sd, cfg, ids, mask)
@@ -186,7 +186,7 @@ def run_gpu(args):
     B = args.batch
     pk = peaks()
     t0 = time.time()
-    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=False)))
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=False), init="torch"))
     ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE))
     comp, mean, scale = O.synth_pca()
     pca = PCAState(comp.cuda(), mean.cuda(), scale)

@@ -242,9 +242,15 @@ def _fan_in(shape: Tuple[int, ...]) -> int:
     return max(f, 1)
 
 
-def synth_tensor(key: str, shape: Tuple[int, ...], seed: int) -> torch.Tensor:
+def synth_tensor(key: str, shape: Tuple[int, ...], seed: int, init: str = "unit") -> torch.Tensor:
     """One deterministic fp32 tensor.  The rules keep activations O(1) and make every
-    parameter matter (non-unit norm weights, non-zero biases, non-trivial gates)."""
+    parameter matter (non-unit norm weights, non-zero biases, non-trivial gates).
+
+    ``init`` picks the scale of the dense (Linear/conv) weights: ``"unit"`` = unit-gain uniform
+    U(+-sqrt(3/fan_in)) -- every sub-layer output is O(1), the hardest case for bf16 operand rounding
+    (stress tests, tiny fixtures); ``"torch"`` = U(+-1/sqrt(fan_in)), the scale ``nn.Linear``'s default
+    ``kaiming_uniform_(a=sqrt(5))`` gives -- i.e. what constructing the reference ``EchoDiT`` with
+    random init (BASELINE.json configs[0], north_star "identical random-init weights") produces."""
     g = _gen(key, seed)
     leaf = key.rsplit(".", 1)[-1]
     if leaf == "alpha":                       # Snake1d alpha > 0
@@ -267,13 +273,17 @@ def synth_tensor(key: str, shape: Tuple[int, ...], seed: int) -> torch.Tensor:
     if "text_embedding" in key:
         return torch.randn(shape, generator=g)
     bound = (3.0 / _fan_in(shape)) ** 0.5     # unit-gain uniform
+    if init == "torch":
+        bound = (1.0 / _fan_in(shape)) ** 0.5
+    else:
+        assert init == "unit", init
     if "dwconv" in key:
         bound = (3.0 / 7) ** 0.5
     return (torch.rand(shape, generator=g) * 2 - 1) * bound
 
 
-def synth_state_dict(schema: Dict[str, Tuple[int, ...]], seed: int = 1234) -> Dict[str, torch.Tensor]:
-    return {k: synth_tensor(k, shp, seed) for k, shp in schema.items()}
+def synth_state_dict(schema: Dict[str, Tuple[int, ...]], seed: int = 1234, init: str = "unit") -> Dict[str, torch.Tensor]:
+    return {k: synth_tensor(k, shp, seed, init) for k, shp in schema.items()}
 
 
 def ae_rope_table(cfg: AEConfig = AE_BASE) -> torch.Tensor:

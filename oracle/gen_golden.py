@@ -117,9 +117,9 @@ def index_goldens(ns) -> dict:
     return out
 
 
-def _sampler_case(ns, cfg, seed, B, S, T_spk, steps, extra, full_trace=True):
+def _sampler_case(ns, cfg, seed, B, S, T_spk, steps, extra, full_trace=True, init="unit"):
     """Run the reference sampler on CPU/fp32 with injected noise, recording per-step tensors."""
-    sd = S_.synth_state_dict(S_.dit_schema(cfg))
+    sd = S_.synth_state_dict(S_.dit_schema(cfg), init=init)
     model = ref_import.build_dit(ns, cfg, sd)
     gen = torch.Generator().manual_seed(seed)
     texts = ["Hello, this is a test of the Echo TTS model.", "Second, shorter prompt"][:B]
@@ -149,7 +149,7 @@ def _sampler_case(ns, cfg, seed, B, S, T_spk, steps, extra, full_trace=True):
         dt = time.time() - t0
     finally:
         torch.randn = real_randn
-    return dict(ids=ids, text_mask=mask, speaker_latent=spk, speaker_mask=smask, noise=noise, kwargs=kw,
+    return dict(ids=ids, text_mask=mask, speaker_latent=spk, speaker_mask=smask, noise=noise, kwargs=kw, init=init,
                 v_branches=[t.half() if not full_trace else t for t in trace], x_final=out, ref_seconds=dt)
 
 
@@ -211,9 +211,12 @@ def main():
 
     if args.full:
         # BASELINE.json config 1: full architecture, fp32 CPU, S=64, 4 steps, 212-latent speaker ref
-        case = _sampler_case(ns, S.ECHO_BASE, 7, 1, 64, 212, 4, {})
-        torch.save(case, os.path.join(GOLD, "dit_base_c1.pt"))
-        print("config-1 reference sampler seconds:", case["ref_seconds"])
+        # (a) the contract fixture: weights at nn.Linear's default-init scale (what random-init of the reference gives)
+        # (b) a stress fixture: unit-gain weights (every sub-layer O(1): worst case for bf16 operand rounding)
+        for init, name in (("torch", "dit_base_c1.pt"), ("unit", "dit_base_c1_unitgain.pt")):
+            case = _sampler_case(ns, S.ECHO_BASE, 7, 1, 64, 212, 4, {}, init=init)
+            torch.save(case, os.path.join(GOLD, name))
+            print(name, "reference sampler seconds:", case["ref_seconds"])
 
 
 if __name__ == "__main__":

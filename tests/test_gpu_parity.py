@@ -119,18 +119,31 @@ def test_ae_base_vs_reference_fixture():
 
 
 @pytest.mark.slow
-def test_full_arch_config1_vs_reference_fixture():
+@pytest.mark.parametrize("name,v_tol,x_tol", [
+    # contract fixture: weights at nn.Linear's default-init scale == random-init of the reference (BASELINE config 1);
+    # BASELINE.json north_star tolerances.
+    ("dit_base_c1.pt", V_TOL, X_TOL),
+    # stress fixture: unit-gain weights make every sub-layer output O(1) of the residual stream, the worst case for
+    # bf16 operand rounding over 48 sub-layers (the reference's own bf16 path measures 1.1-1.4e-2 on the EASIER
+    # default-init weights).  Looser, documented bound; printed so regressions are visible.
+    ("dit_base_c1_unitgain.pt", 1.5e-2, 3e-2),
+])
+def test_full_arch_config1_vs_reference_fixture(name, v_tol, x_tol):
     """BASELINE.json config 1 (full echo-tts-base architecture, S=64, 4 steps, 212-latent speaker ref):
     the reference ran it in fp32 on CPU (oracle/gen_golden.py --full); we run bf16 on the B200."""
     from echo_tts_b200.inference import load_model_from_state_dict
     from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
-    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE)))
-    g = torch.load(os.path.join(GOLDEN, "dit_base_c1.pt"))
+    g = torch.load(os.path.join(GOLDEN, name))
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE), init=g["init"]))
     trace = []
     out = sample(model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0,
                  _noise=g["noise"], _trace=trace, **g["kwargs"]).cpu()
     B = g["noise"].shape[0]
+    worst = 0.0
     for st, ref in zip(trace, g["v_branches"]):
         for a, b in zip(st["v_branches"].cpu().chunk(ref.shape[0] // B, 0), ref.float().chunk(ref.shape[0] // B, 0)):
-            assert rel_l2(a, b) < V_TOL
-    assert rel_l2(out, g["x_final"]) < X_TOL
+            worst = max(worst, rel_l2(a, b))
+    xerr = rel_l2(out, g["x_final"])
+    print(f"{name}: worst per-branch velocity rel-L2 {worst:.3e} (tol {v_tol}), final latent rel-L2 {xerr:.3e} (tol {x_tol})")
+    assert worst < v_tol
+    assert xerr < x_tol
