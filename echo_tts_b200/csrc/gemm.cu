@@ -7,14 +7,6 @@
 #include "ptx_sm100.cuh"
 #include "gemm_epilogue.cuh"
 
-struct GemmShape {
-  int k_blocks_per_tap, taps, k_tap;
-  int tap_shift[8];
-  int rows, n;
-  long long lda, a_batch_stride, ldb;
-  const bf16* a;
-  const bf16* b;
-};
 
 constexpr int BM = 128;
 constexpr int BK = 64;
@@ -107,7 +99,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tc_fence_after();
     TmemLoader L{tmem_base + ((uint32_t)(q * 32) << 16)};
-    run_epilogue<BN, EPI>(P, L, batch, m0 + q * 32 + lane, n0);
+    run_epilogue<EPI>(BN, P, L, batch, m0 + q * 32 + lane, n0);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -132,8 +124,8 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
-static int make_tmap(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
-                     const cuuint32_t* box) {
+int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                        const cuuint32_t* box) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { echo_set_error("cuTensorMapEncodeTiled entry point unavailable"); return ECHO_ERR_CUDA; }
   cuuint32_t estr[3] = {1, 1, 1};
@@ -152,14 +144,14 @@ static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStre
     cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
     cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)G.rows * G.lda) * 2};
     cuuint32_t box[3] = {BK, BM, 1};
-    int rc = make_tmap(&ta, G.a, 3, dims, str, box);
+    int rc = echo_make_tmap_bf16(&ta, G.a, 3, dims, str, box);
     if (rc) return rc;
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)G.taps * G.k_tap, (cuuint64_t)G.n};
     cuuint64_t str[1] = {(cuuint64_t)G.ldb * 2};
     cuuint32_t box[2] = {BK, BN};
-    int rc = make_tmap(&tb, G.b, 2, dims, str, box);
+    int rc = echo_make_tmap_bf16(&tb, G.b, 2, dims, str, box);
     if (rc) return rc;
   }
   static bool attr_set = false;
@@ -176,6 +168,7 @@ static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStre
 
 template <int EPI>
 int launch_legacy(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm_legacy.cu
+int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm2.cu
 
 static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
@@ -260,6 +253,35 @@ static int dispatch_bn(int bn, const GemmShape& G, const EpiParams& P, int batch
   return ECHO_ERR_UNSUPPORTED;
 }
 
+// Tile width for the CTA-pair kernel: fewest (rounds x tile cost) over the 74 pairs; ties go to the wider tile.
+static int pick_block_n_pair(const echo_gemm_desc* d) {
+  if (d->block_n) return d->block_n;
+  static int npairs = 0;
+  if (!npairs) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    npairs = sms > 1 ? sms / 2 : 74;
+  }
+  const int cand_generic[] = {256, 192, 128, 96, 64};
+  const int cand_fused[] = {256, 128, 64};
+  const int* cand = d->epilogue == ECHO_EPI_GENERIC ? cand_generic : cand_fused;
+  const int ncand = d->epilogue == ECHO_EPI_GENERIC ? 5 : 3;
+  const long long tm = (long long)ceil_div(d->rows, 2 * BM) * d->batch;
+  int best = 0;
+  long long best_cost = 0;
+  for (int i = 0; i < ncand; ++i) {
+    const int bn = cand[i];
+    if (d->epilogue == ECHO_EPI_SECTIONS && (bn % d->head_dim != 0 || d->section_width % bn != 0)) continue;
+    if (d->epilogue == ECHO_EPI_SWIGLU && bn % 128 != 0) continue;
+    const long long tiles = tm * ceil_div(d->n, bn);
+    const long long rounds = (tiles + npairs - 1) / npairs;
+    const long long cost = rounds * (bn + 24);          // +24: per-tile fixed cost (pipeline refill) in column units
+    if (!best || cost < best_cost) { best = bn; best_cost = cost; }
+  }
+  return best;
+}
+
 extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
   GemmShape G;
   EpiParams P;
@@ -273,6 +295,14 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
       case ECHO_EPI_SECTIONS: return launch_legacy<ECHO_EPI_SECTIONS>(G, P, d->batch, st);
       default: return launch_legacy<ECHO_EPI_SWIGLU>(G, P, d->batch, st);
     }
+  }
+  if (d->impl == 2) {
+    const int bn = pick_block_n_pair(d);
+    ECHO_CHECK_ARG(bn > 0, "pair gemm: no tile width fits epilogue %d (n=%d)", d->epilogue, d->n);
+    if (d->epilogue == ECHO_EPI_SECTIONS)
+      ECHO_CHECK_ARG(d->section_width % bn == 0 && bn % d->head_dim == 0, "gemm: block_n %d does not tile sections", bn);
+    if (d->epilogue == ECHO_EPI_SWIGLU) ECHO_CHECK_ARG(bn % 128 == 0, "gemm: swiglu needs block_n %% 128 == 0");
+    return echo_launch_gemm_pair(d->epilogue, bn, G, P, d->batch, st);
   }
   ECHO_CHECK_ARG(d->impl == 0, "gemm: unknown impl %d", d->impl);
   const int bn = pick_block_n(d);

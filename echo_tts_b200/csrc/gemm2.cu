@@ -1,0 +1,212 @@
+// bf16 GEMM / implicit causal conv, CTA-pair edition (impl 2, the product path):
+//   * cluster of 2 CTAs = one 256 x BN output tile; tcgen05.mma.cta_group::2 issued by one thread of the leader
+//     CTA reads A (128 rows per CTA) and B (BN/2 rows per CTA) from BOTH CTAs' shared memory, so every SM
+//     stages half as many B bytes per MMA (64 B/clk/SM from L2 instead of 96) and the ring gets 6 stages;
+//   * persistent: grid = min(#pair tiles, #SM/2) clusters, static round-robin tile order with the M index
+//     fastest so that the pairs working concurrently share one weight (B) tile through L2;
+//   * two TMEM accumulator stages (2 x 256 columns): the fused epilogue of tile i runs while the MMAs of
+//     tile i+1 are issued;
+//   * warp roles per CTA: 0 = TMA producer (its CTA's halves; bytes land on the leader's mbarrier),
+//     1 = TMEM owner (+ MMA issuer in the leader CTA), 2..5 = epilogue (one TMEM lane quarter each).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "gemm_epilogue.cuh"
+
+namespace {
+constexpr int BM = 128;            // rows per CTA (256 per pair)
+constexpr int BK = 64;
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int B_BYTES_MAX = 128 * BK * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;
+constexpr int STAGES = 6;
+constexpr int ACC_STAGES = 2;
+constexpr int ACC_COLS = 256;
+constexpr int SMEM2 = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct Tiling {
+  int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
+  int tiles_m, tiles_n;   // pair tiles per batch entry
+  int num_tiles;          // tiles_m * tiles_n * batch
+};
+
+struct TmemLoader2 {
+  uint32_t taddr;
+  __device__ __forceinline__ void load32(int col, float* v) { ptx::tmem_ld32(taddr + (uint32_t)col, v); }
+};
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P,
+                 const __grid_constant__ Tiling T) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int total_kb = G.k_blocks_per_tap * G.taps;
+  const int half_n = T.bn >> 1;
+  const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_n * BK * 2);
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_a);
+    ptx::prefetch_tensormap(&tmap_b);
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);        // leader's producer: arrive.expect_tx (both CTAs' bytes)
+      ptx::mbar_init(&empty_bar[s], 1);       // tcgen05.commit multicast to both CTAs
+    }
+    for (int a = 0; a < ACC_STAGES; ++a) {
+      ptx::mbar_init(&tmem_full_bar[a], 1);   // tcgen05.commit multicast to both CTAs
+      ptx::mbar_init(&tmem_empty_bar[a], 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's barrier
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc_cg2(tmem_slot, ACC_STAGES * ACC_COLS);
+    ptx::tmem_relinquish_cg2();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = pair; tile < T.num_tiles; tile += npairs) {
+        const int mt = tile % T.tiles_m;
+        const int rest = tile / T.tiles_m;
+        const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
+        const int m0 = mt * (2 * BM) + (int)rank * BM;
+        const int n0 = nt * T.bn + (int)rank * half_n;
+        for (int kb = 0; kb < total_kb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+          const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], stage_tx);
+          const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
+          ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
+          ptx::tma_load_2d_cg2(sb, &tmap_b, lbar, tap * G.k_tap + kk * BK, n0);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (rank == 0 && lane == 0) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, T.bn);
+      uint32_t it = 0, tc = 0;
+      for (int tile = pair; tile < T.num_tiles; tile += npairs, ++tc) {
+        const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
+        ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
+        ptx::tc_fence_after();
+        const uint32_t tacc = tmem_base + as * ACC_COLS;
+        for (int kb = 0; kb < total_kb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&full_bar[s], ph);
+          ptx::tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          const uint64_t da = ptx::umma_desc_sw128(sa);
+          const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
+        }
+        ptx::umma_commit_cg2_mc(&tmem_full_bar[as], 0b11);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;                  // TMEM lane quarter this warp may read
+    uint32_t tc = 0;
+    for (int tile = pair; tile < T.num_tiles; tile += npairs, ++tc) {
+      const int mt = tile % T.tiles_m;
+      const int rest = tile / T.tiles_m;
+      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
+      const int m0 = mt * (2 * BM) + (int)rank * BM;
+      const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
+      ptx::mbar_wait(&tmem_full_bar[as], aph);
+      ptx::tc_fence_after();
+      TmemLoader2 L{tmem_base + as * ACC_COLS + ((uint32_t)(q * 32) << 16)};
+      run_epilogue<EPI>(T.bn, P, L, batch, m0 + q * 32 + lane, nt * T.bn);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
+    }
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync_all();
+  if (warp == 1) ptx::tmem_dealloc_cg2(tmem_base, ACC_STAGES * ACC_COLS);
+}
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+}  // namespace
+
+int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                        const cuuint32_t* box);   // gemm.cu
+
+template <int EPI>
+static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+  CUtensorMap ta, tb;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
+    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)G.rows * G.lda) * 2};
+    cuuint32_t box[3] = {BK, BM, 1};
+    int rc = echo_make_tmap_bf16(&ta, G.a, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)G.taps * G.k_tap, (cuuint64_t)G.n};
+    cuuint64_t str[1] = {(cuuint64_t)G.ldb * 2};
+    cuuint32_t box[2] = {BK, (cuuint32_t)(bn / 2)};
+    int rc = echo_make_tmap_bf16(&tb, G.b, 2, dims, str, box);
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    ECHO_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
+    attr_set = true;
+  }
+  Tiling T;
+  T.bn = bn;
+  T.tiles_m = ceil_div(G.rows, 2 * BM);
+  T.tiles_n = ceil_div(G.n, bn);
+  T.num_tiles = T.tiles_m * T.tiles_n * batch;
+  const int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
+  gemm_pair_kernel<EPI><<<dim3(2 * pairs), 192, SMEM2, st>>>(ta, tb, G, P, T);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+// bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
+int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+  if (bn < 64 || bn > 256 || bn % 32 != 0) {
+    echo_set_error("pair gemm: block_n %d must be a multiple of 32 in [64, 256]", bn);
+    return ECHO_ERR_UNSUPPORTED;
+  }
+  switch (epi) {
+    case ECHO_EPI_GENERIC: return launch_pair_t<ECHO_EPI_GENERIC>(bn, G, P, batch, st);
+    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, G, P, batch, st);
+    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, G, P, batch, st);
+  }
+}

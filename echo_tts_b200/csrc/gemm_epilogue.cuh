@@ -5,6 +5,15 @@
 #include "common.cuh"
 #include "../../include/echo_b200.h"
 
+struct GemmShape {
+  int k_blocks_per_tap, taps, k_tap;
+  int tap_shift[8];
+  int rows, n;
+  long long lda, a_batch_stride, ldb;
+  const bf16* a;
+  const bf16* b;
+};
+
 struct EpiSection {
   int type;
   bf16* out;
@@ -40,8 +49,8 @@ __device__ __forceinline__ void store_bf16x8(bf16* p, const float* v) {
 }
 
 // ---- GENERIC ------------------------------------------------------------------------------
-template <int BN, class Loader>
-__device__ __forceinline__ void epi_generic(const EpiParams& P, Loader& L, bool row_ok, long long m_glob,
+template <class Loader>
+__device__ __forceinline__ void epi_generic(const int BN, const EpiParams& P, Loader& L, bool row_ok, long long m_glob,
                                             int n0) {
   const float* gate_row = P.gate ? P.gate + (m_glob / P.rows_per_gate) * P.gate_ld : nullptr;
 #pragma unroll 1
@@ -94,8 +103,8 @@ __device__ __forceinline__ void epi_generic(const EpiParams& P, Loader& L, bool 
 }
 
 // ---- SECTIONS (q/k/v/gate style) ------------------------------------------------------------
-template <int BN, class Loader>
-__device__ __forceinline__ void epi_sections(const EpiParams& P, Loader& L, bool row_ok, long long m_glob,
+template <class Loader>
+__device__ __forceinline__ void epi_sections(const int BN, const EpiParams& P, Loader& L, bool row_ok, long long m_glob,
                                              int m_in_batch, int n0) {
   const int sec_idx = n0 / P.section_width;
   const EpiSection S = P.sec[sec_idx];
@@ -151,8 +160,8 @@ __device__ __forceinline__ void epi_sections(const EpiParams& P, Loader& L, bool
 }
 
 // ---- SWIGLU ---------------------------------------------------------------------------------
-template <int BN, class Loader>
-__device__ __forceinline__ void epi_swiglu(const EpiParams& P, Loader& L, bool row_ok, long long m_glob, int n0) {
+template <class Loader>
+__device__ __forceinline__ void epi_swiglu(const int BN, const EpiParams& P, Loader& L, bool row_ok, long long m_glob, int n0) {
 #pragma unroll 1
   for (int g0 = 0; g0 < BN; g0 += 128) {
     const int out_col0 = (n0 + g0) / 2;
@@ -171,11 +180,13 @@ __device__ __forceinline__ void epi_swiglu(const EpiParams& P, Loader& L, bool r
   }
 }
 
-template <int BN, int EPI, class Loader>
-__device__ __forceinline__ void run_epilogue(const EpiParams& P, Loader& L, int batch_idx, int m_in_batch, int n0) {
+// BN (tile width in columns, multiple of 32) is a run-time value: the column loops are not unrolled.
+template <int EPI, class Loader>
+__device__ __forceinline__ void run_epilogue(const int BN, const EpiParams& P, Loader& L, int batch_idx, int m_in_batch,
+                                             int n0) {
   const bool row_ok = m_in_batch < P.rows;
   const long long m_glob = (long long)batch_idx * P.rows + m_in_batch;
-  if (EPI == ECHO_EPI_GENERIC) epi_generic<BN>(P, L, row_ok, m_glob, n0);
-  else if (EPI == ECHO_EPI_SECTIONS) epi_sections<BN>(P, L, row_ok, m_glob, m_in_batch, n0);
-  else epi_swiglu<BN>(P, L, row_ok, m_glob, n0);
+  if (EPI == ECHO_EPI_GENERIC) epi_generic(BN, P, L, row_ok, m_glob, n0);
+  else if (EPI == ECHO_EPI_SECTIONS) epi_sections(BN, P, L, row_ok, m_glob, m_in_batch, n0);
+  else epi_swiglu(BN, P, L, row_ok, m_glob, n0);
 }

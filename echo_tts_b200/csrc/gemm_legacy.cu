@@ -4,14 +4,6 @@
 #include "common.cuh"
 #include "gemm_epilogue.cuh"
 
-struct GemmShape {
-  int k_blocks_per_tap, taps, k_tap;
-  int tap_shift[8];
-  int rows, n;
-  long long lda, a_batch_stride, ldb;
-  const bf16* a;
-  const bf16* b;
-};
 
 namespace {
 constexpr int LBM = 128, LBN = 128, LBK = 32;
@@ -125,7 +117,7 @@ __global__ void __launch_bounds__(256) gemm_legacy_kernel(const __grid_constant_
   __syncthreads();
   if (tid < LBM) {
     SmemLoader L{sC + tid * C_LD};
-    run_epilogue<LBN, EPI>(P, L, batch, m0 + tid, n0);
+    run_epilogue<EPI>(LBN, P, L, batch, m0 + tid, n0);
   }
 }
 }  // namespace

@@ -11,7 +11,10 @@ import torch
 from . import _lib as L
 
 BF16, F32 = torch.bfloat16, torch.float32
-GEMM_IMPL = 0   # 0 = tcgen05/TMEM/TMA (product path); 1 = legacy mma.sync (A/B baseline, tests only)
+import os as _os
+# 2 = CTA-pair persistent tcgen05 kernel (product path); 0 = single-CTA tcgen05 kernel; 1 = legacy mma.sync
+# (A/B baselines, tests only).  ECHO_GEMM_IMPL overrides for A/B measurements.
+GEMM_IMPL = int(_os.environ.get("ECHO_GEMM_IMPL", "2"))
 
 
 def _need(t: torch.Tensor, dtype, name: str):
