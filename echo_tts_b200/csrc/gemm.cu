@@ -198,6 +198,15 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
     P.sec[i].type = d->sections[i].type; P.sec[i].out = (bf16*)d->sections[i].out;
     P.sec[i].norm_w = d->sections[i].norm_weight;
   }
+  if (d->impl == 2) {   // vectorised epilogue: 16-byte loads of the per-column vectors
+    auto al16 = [](const void* p) { return ((uintptr_t)p % 16) == 0; };
+    ECHO_CHECK_ARG(al16(d->bias) && al16(d->gate) && al16(d->snake_alpha) && al16(d->resid) && al16(d->out_f32) &&
+                   d->gate_ld % 4 == 0, "gemm: bias/gate/alpha/resid/out_f32 must be 16-byte aligned (gate_ld %% 4)");
+    ECHO_CHECK_ARG(((uintptr_t)d->out_bf16 % 8) == 0 && ((uintptr_t)d->out2_bf16 % 8) == 0 &&
+                   ((uintptr_t)d->rope_cos % 8) == 0 && ((uintptr_t)d->rope_sin % 8) == 0, "gemm: bf16 outputs / rope tables must be 8-byte aligned");
+    for (int i = 0; i < 4; ++i)
+      ECHO_CHECK_ARG(al16(d->sections[i].norm_weight) && ((uintptr_t)d->sections[i].out % 8) == 0, "gemm: section pointers misaligned");
+  }
   if (d->epilogue == ECHO_EPI_GENERIC) {
     ECHO_CHECK_ARG(d->out_f32 || d->out_bf16 || d->out2_bf16, "gemm: no output");
     ECHO_CHECK_ARG(!d->out2_bf16 || d->snake_alpha, "gemm: out2 needs snake_alpha");
@@ -276,7 +285,10 @@ static int pick_block_n_pair(const echo_gemm_desc* d) {
     if (d->epilogue == ECHO_EPI_SWIGLU && bn % 128 != 0) continue;
     const long long tiles = tm * ceil_div(d->n, bn);
     const long long rounds = (tiles + npairs - 1) / npairs;
-    const long long cost = rounds * (bn + 24);          // +24: per-tile fixed cost (pipeline refill) in column units
+    // measured (tools/gemm_trace.py): a k-block costs ~600 clocks whether the tile is 128 or 256 columns wide (operand
+    // feed, not MMA issue, is the floor), so narrow tiles only pay off when they remove a whole round or shorten the
+    // exposed epilogue of a single-round launch.
+    const long long cost = rounds * (bn > 240 ? bn : 240) + bn / 2;
     if (!best || cost < best_cost) { best = bn; best_cost = cost; }
   }
   return best;

@@ -7,10 +7,12 @@
 //   * two TMEM accumulator stages (2 x 256 columns): the fused epilogue of tile i runs while the MMAs of
 //     tile i+1 are issued;
 //   * warp roles per CTA: 0 = TMA producer (its CTA's halves; bytes land on the leader's mbarrier),
-//     1 = TMEM owner (+ MMA issuer in the leader CTA), 2..5 = epilogue (one TMEM lane quarter each).
+//     1 = TMEM owner (+ MMA issuer in the leader CTA), 2..9 = epilogue (two warps per TMEM lane quarter taking
+//     alternate 32-column chunks; coalesced vector stores via a per-warp 32x32 shared-memory transpose and
+//     auxiliary loads issued one chunk ahead, gemm_epilogue_t.cuh).
 #include "common.cuh"
 #include "ptx_sm100.cuh"
-#include "gemm_epilogue.cuh"
+#include "gemm_epilogue_t.cuh"
 
 namespace {
 constexpr int BM = 128;            // rows per CTA (256 per pair)
@@ -21,9 +23,16 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;
 constexpr int STAGES = 6;
 constexpr int ACC_STAGES = 2;
 constexpr int ACC_COLS = 256;
-constexpr int SMEM2 = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int EPI_WARPS = 8;       // two per TMEM lane quarter
+constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
+constexpr int SCRATCH_BYTES = EPI_WARPS * EPI_SC_FLOATS * 4;   // per-epilogue-warp 32x32 fp32 transpose scratch
+constexpr int SMEM2 = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
+
+// optional in-kernel timeline (32 clock64 slots per CTA), enabled with echo_debug_gemm_trace(ptr)
+static long long* g_trace_ptr = nullptr;
 
 struct Tiling {
+  long long* trace;       // nullptr unless tracing: [cta][32] SM-clock stamps
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
   int num_tiles;          // tiles_m * tiles_n * batch
@@ -35,7 +44,7 @@ struct TmemLoader2 {
 };
 
 template <int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P,
                  const __grid_constant__ Tiling T) {
@@ -46,6 +55,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+  float* scratch = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
@@ -53,6 +63,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int total_kb = G.k_blocks_per_tap * G.taps;
   const int half_n = T.bn >> 1;
   const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_n * BK * 2);
+  long long* const trace = T.trace ? T.trace + (long long)blockIdx.x * 32 : nullptr;
+  if (trace && threadIdx.x == 0) trace[0] = clock64();
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
@@ -63,7 +75,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     for (int a = 0; a < ACC_STAGES; ++a) {
       ptx::mbar_init(&tmem_full_bar[a], 1);   // tcgen05.commit multicast to both CTAs
-      ptx::mbar_init(&tmem_empty_bar[a], 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's barrier
+      ptx::mbar_init(&tmem_empty_bar[a], 2 * EPI_WARPS);  // every epilogue warp of both CTAs arrives on the leader's barrier
     }
     ptx::fence_barrier_init();
   }
@@ -75,6 +87,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   ptx::cluster_sync_all();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (trace && threadIdx.x == 0) trace[1] = clock64();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -108,12 +121,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
         ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
         ptx::tc_fence_after();
+        if (trace && tc < 6) trace[8 + tc * 4 + 0] = clock64();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
         for (int kb = 0; kb < total_kb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           ptx::mbar_wait(&full_bar[s], ph);
           ptx::tc_fence_after();
+          if (trace && it == 0) trace[2] = clock64();
           const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
           const uint64_t da = ptx::umma_desc_sw128(sa);
           const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
@@ -123,6 +138,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
         }
         ptx::umma_commit_cg2_mc(&tmem_full_bar[as], 0b11);
+        if (trace && tc < 6) trace[8 + tc * 4 + 1] = clock64();
       }
     }
     __syncwarp();
@@ -137,16 +153,21 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
+      if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
       TmemLoader2 L{tmem_base + as * ACC_COLS + ((uint32_t)(q * 32) << 16)};
-      run_epilogue<EPI>(T.bn, P, L, batch, m0 + q * 32 + lane, nt * T.bn);
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + (warp - 2) * EPI_SC_FLOATS, lane, (warp - 2) >> 2, batch, m0 + q * 32,
+                          nt * T.bn);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
+      if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
   }
   ptx::tc_fence_before();
+  if (trace && threadIdx.x == 0) trace[6] = clock64();
   ptx::cluster_sync_all();
   if (warp == 1) ptx::tmem_dealloc_cg2(tmem_base, ACC_STAGES * ACC_COLS);
+  if (trace && threadIdx.x == 0) trace[7] = clock64();
 }
 
 int num_sms() {
@@ -187,16 +208,23 @@ static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int bat
     attr_set = true;
   }
   Tiling T;
+  T.trace = g_trace_ptr;
   T.bn = bn;
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
   T.num_tiles = T.tiles_m * T.tiles_n * batch;
   const int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
-  gemm_pair_kernel<EPI><<<dim3(2 * pairs), 192, SMEM2, st>>>(ta, tb, G, P, T);
+  gemm_pair_kernel<EPI><<<dim3(2 * pairs), NTHREADS, SMEM2, st>>>(ta, tb, G, P, T);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
 }
+
+// Debug aid: device buffer of >= 32 * grid int64 that the next pair-GEMM launches fill with clock64 stamps:
+// [0] start, [1] setup done, [2] first operands landed, [6] all roles done, [7] exit, and for the CTA's first six
+// tiles t: [8+4t] accumulator stage free (MMA thread), [9+4t] MMAs issued, [10+4t] accumulator ready (epilogue
+// warp 2), [11+4t] epilogue done.  Pass NULL to switch tracing off.
+extern "C" void echo_debug_gemm_trace(long long* device_buf) { g_trace_ptr = device_buf; }
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
 int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {

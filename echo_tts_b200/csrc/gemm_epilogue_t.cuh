@@ -1,0 +1,297 @@
+// Coalesced, vectorised, latency-tolerant fused epilogues for the CTA-pair GEMM.
+//
+// The accumulator arrives from TMEM "row per thread" (tcgen05.ld 32x32b: lane r holds 32 consecutive columns of
+// row r).  Math that needs a whole row (per-head sum of squares, sigmoid, SwiGLU pairing) is done in that layout.
+// Everything that touches global memory (bias / gate / residual / RoPE table / outputs) is done after a 32x32
+// transpose through an XOR-swizzled per-warp shared-memory scratch in a "4 columns x 8 row-groups per lane"
+// layout: lane l owns columns 4*(l&7)..+3 of rows (l>>3) + 4*i, i = 0..7, so that each warp-wide 128-bit access
+// covers four complete 128-byte row segments (fully used sectors, 8 instructions per 32x32 chunk).
+//
+// While the GEMM main loop saturates the L2 fabric a global load takes 2-3 k cycles, so no load may sit on the
+// per-chunk critical path: each of the EIGHT epilogue warps (two per TMEM lane quarter, alternating 32-column
+// chunks) issues the auxiliary loads of its NEXT chunk (residual rows, RoPE rows, per-column vectors) before it
+// starts on the current one.  The residual may alias the output, so the compiler cannot do this hoisting itself.
+#pragma once
+#include "gemm_epilogue.cuh"
+
+constexpr int EPI_SC_FLOATS = 32 * 32;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
+
+__device__ __forceinline__ void sc_store_row(float* sc, int lane, const float* v) {
+  float* row = sc + lane * 32;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    *reinterpret_cast<float4*>(row + ((k ^ (lane & 7)) << 2)) = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+  __syncwarp();
+}
+__device__ __forceinline__ float4 sc_load4(const float* sc, int row, int cg) {
+  return *reinterpret_cast<const float4*>(sc + row * 32 + ((cg ^ (row & 7)) << 2));
+}
+__device__ __forceinline__ void store_bf16x4(bf16* p, float4 x) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
+}
+
+// Rows handled by this warp: m_in_batch = mb0 + r, r = 0..31 (lane r owns row r in TMEM layout).
+struct EpiRows {
+  int batch_idx, mb0, n0;
+  int nrows;            // valid rows among the 32 (0..32), warp-uniform
+  int half;             // 0/1: which of the two warps of this lane quarter (chunk parity it owns)
+  long long mg0;        // global row index of row 0
+};
+
+// ---- GENERIC ------------------------------------------------------------------------------
+struct GenAux {
+  float4 bias, alpha, glo, ghi;
+  float4 rv[8];
+};
+
+struct GenCtx {
+  const EpiParams& P;
+  const EpiRows& R;
+  int cg, rsub, rpg, rem0;
+  long long g0;
+  bool gate_fast;
+
+  __device__ __forceinline__ void load(int c, GenAux& A) const {
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f), one4 = make_float4(1.f, 1.f, 1.f, 1.f);
+    const int n = R.n0 + c + 4 * cg;
+    const bool nok = n < P.n;                            // n % 8 == 0: a 4-column group is all in or all out
+    A.bias = (P.bias && nok) ? __ldg(reinterpret_cast<const float4*>(P.bias + n)) : zero4;
+    A.alpha = (P.out2_bf16 && nok) ? __ldg(reinterpret_cast<const float4*>(P.snake_alpha + n)) : one4;
+    A.glo = one4; A.ghi = one4;
+    if (P.gate && nok && gate_fast) {
+      A.glo = __ldg(reinterpret_cast<const float4*>(P.gate + g0 * P.gate_ld + n));
+      if (rem0 + 31 >= rpg) A.ghi = __ldg(reinterpret_cast<const float4*>(P.gate + (g0 + 1) * P.gate_ld + n));
+    }
+    const float* rp = P.resid ? P.resid + R.mg0 * P.ld_resid + n : nullptr;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rsub;
+      A.rv[i] = (rp && nok && r < R.nrows) ? *reinterpret_cast<const float4*>(rp + (long long)r * P.ld_resid) : zero4;
+    }
+  }
+
+  template <class Loader>
+  __device__ __forceinline__ void process(int c, const GenAux& A, Loader& L, float* sc, int lane) const {
+    float v[32];
+    L.load32(c, v);
+    sc_store_row(sc, lane, v);
+    const int n = R.n0 + c + 4 * cg;
+    const bool nok = n < P.n;
+    float4 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      x[i] = sc_load4(sc, 4 * i + rsub, cg);
+      x[i].x += A.bias.x; x[i].y += A.bias.y; x[i].z += A.bias.z; x[i].w += A.bias.w;
+    }
+    if (P.act == ECHO_ACT_GELU) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { x[i].x = geluf_(x[i].x); x[i].y = geluf_(x[i].y); x[i].z = geluf_(x[i].z); x[i].w = geluf_(x[i].w); }
+    } else if (P.act == ECHO_ACT_SILU) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { x[i].x = siluf_(x[i].x); x[i].y = siluf_(x[i].y); x[i].z = siluf_(x[i].z); x[i].w = siluf_(x[i].w); }
+    }
+    if (P.gate) {
+      if (gate_fast) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 g = (rem0 + 4 * i + rsub >= rpg) ? A.ghi : A.glo;
+          x[i].x *= g.x; x[i].y *= g.y; x[i].z *= g.z; x[i].w *= g.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = 4 * i + rsub;
+          if (nok && r < R.nrows) {
+            const float4 g = __ldg(reinterpret_cast<const float4*>(P.gate + ((R.mg0 + r) / rpg) * P.gate_ld + n));
+            x[i].x *= g.x; x[i].y *= g.y; x[i].z *= g.z; x[i].w *= g.w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { x[i].x += A.rv[i].x; x[i].y += A.rv[i].y; x[i].z += A.rv[i].z; x[i].w += A.rv[i].w; }
+    if (P.out_f32) {
+      float* o = P.out_f32 + R.mg0 * P.ld_out_f32 + n;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (nok && 4 * i + rsub < R.nrows) *reinterpret_cast<float4*>(o + (long long)(4 * i + rsub) * P.ld_out_f32) = x[i];
+    }
+    if (P.out_bf16) {
+      bf16* o = P.out_bf16 + R.mg0 * P.ld_out_bf16 + n;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (nok && 4 * i + rsub < R.nrows) store_bf16x4(o + (long long)(4 * i + rsub) * P.ld_out_bf16, x[i]);
+    }
+    if (P.out2_bf16) {
+      bf16* o = P.out2_bf16 + R.mg0 * P.ld_out2_bf16 + n;
+      const float4 ia = make_float4(__fdividef(1.f, A.alpha.x + 1e-9f), __fdividef(1.f, A.alpha.y + 1e-9f),
+                                    __fdividef(1.f, A.alpha.z + 1e-9f), __fdividef(1.f, A.alpha.w + 1e-9f));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float4 s;
+        s.x = __sinf(A.alpha.x * x[i].x); s.y = __sinf(A.alpha.y * x[i].y);
+        s.z = __sinf(A.alpha.z * x[i].z); s.w = __sinf(A.alpha.w * x[i].w);
+        s.x = fmaf(s.x * s.x, ia.x, x[i].x); s.y = fmaf(s.y * s.y, ia.y, x[i].y);
+        s.z = fmaf(s.z * s.z, ia.z, x[i].z); s.w = fmaf(s.w * s.w, ia.w, x[i].w);
+        if (nok && 4 * i + rsub < R.nrows) store_bf16x4(o + (long long)(4 * i + rsub) * P.ld_out2_bf16, s);
+      }
+    }
+    __syncwarp();
+  }
+};
+
+template <class Loader>
+__device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
+                                              const EpiRows& R) {
+  if (R.nrows <= 0) return;                               // warp-uniform; nothing was promised to TMEM readers
+  // gate row of local row r is g0 + ((rem0 + r) >= rows_per_gate) when rows_per_gate >= 32
+  const int rpg = P.rows_per_gate;
+  const long long g0 = R.mg0 / rpg;
+  GenCtx C{P, R, lane & 7, lane >> 3, rpg, (int)(R.mg0 - g0 * rpg), g0, rpg >= 32};
+  const int cend = min(BN, P.n - R.n0);                   // columns of this tile that exist (multiple of 8)
+  // this warp's chunks: half*32, +64, ...; two aux buffers alternate so that chunk k+1's loads fly during chunk k
+  GenAux A, B;
+  int c = R.half * 32;
+  if (c < cend) C.load(c, A);
+#pragma unroll 1
+  for (; c < cend; c += 128) {
+    const bool has_b = c + 64 < cend;
+    if (has_b) C.load(c + 64, B);
+    C.process(c, A, L, sc, lane);
+    if (c + 128 < cend) C.load(c + 128, A);
+    if (has_b) C.process(c + 64, B, L, sc, lane);
+  }
+}
+
+// ---- SECTIONS (q/k/v/gate style) ------------------------------------------------------------
+struct SecAux {
+  float4 w;
+  float2 co[8], si[8];
+};
+
+template <class Loader>
+__device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
+                                               const EpiRows& R) {
+  if (R.nrows <= 0) return;
+  const int cg = lane & 7, rsub = lane >> 3;
+  const int sec_idx = R.n0 / P.section_width;
+  const EpiSection S = P.sec[sec_idx];
+  const int sec_col0 = R.n0 - sec_idx * P.section_width;   // column of the tile inside its section
+  const int hd = P.head_dim;
+  const int seq0 = R.mb0 % P.rows_per_seq;                 // sequence index of local row 0
+  const long long ld = P.ld_sec_out;
+  const bool norm = S.type == ECHO_SEC_NORM_ROPE;
+
+  auto load_aux = [&](int h0, int c, bool do_rope, SecAux& A) {
+    const int col = sec_col0 + h0 + c + 4 * cg;             // first of this lane's 4 columns inside the section
+    A.w = norm ? __ldg(reinterpret_cast<const float4*>(S.norm_w + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
+    if (do_rope) {                                          // lane's columns = rotary pairs p0, p0 + 1 of the head
+      const int p0 = (c + 4 * cg) >> 1;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = 4 * i + rsub;
+        int sq = seq0 + r;
+        if (sq >= P.rows_per_seq) sq %= P.rows_per_seq;
+        const long long off = (long long)(P.pos_offset + sq * P.pos_stride) * (hd / 2) + p0;
+        const bool ok = r < R.nrows;
+        A.co[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_cos + off)) : make_float2(1.f, 1.f);
+        A.si[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_sin + off)) : make_float2(0.f, 0.f);
+      }
+    }
+  };
+  auto process = [&](int h0, int c, bool do_rope, float rstd, const SecAux& A) {
+    float v[32];
+    L.load32(h0 + c, v);
+    if (norm) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] *= rstd;
+    } else if (S.type == ECHO_SEC_SIGMOID) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __fdividef(1.f, 1.f + __expf(-v[j]));
+    }
+    sc_store_row(sc, lane, v);
+    bf16* out = S.out + R.mg0 * ld + sec_col0 + h0 + c + 4 * cg;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rsub;
+      float4 x = sc_load4(sc, r, cg);
+      x.x *= A.w.x; x.y *= A.w.y; x.z *= A.w.z; x.w *= A.w.w;
+      if (do_rope) {
+        float4 y;
+        y.x = x.x * A.co[i].x - x.y * A.si[i].x;
+        y.y = x.x * A.si[i].x + x.y * A.co[i].x;
+        y.z = x.z * A.co[i].y - x.w * A.si[i].y;
+        y.w = x.z * A.si[i].y + x.w * A.co[i].y;
+        x = y;
+      }
+      if (r < R.nrows) store_bf16x4(out + (long long)r * ld, x);
+    }
+    __syncwarp();
+  };
+
+#pragma unroll 1
+  for (int h0 = 0; h0 < BN; h0 += hd) {                    // one head at a time; both warps of the quarter visit it
+    if (R.n0 + h0 >= P.n) break;
+    const int head = (sec_col0 + h0) / hd;
+    const bool do_rope = (norm || S.type == ECHO_SEC_ROPE) && head < P.rope_heads;
+    // this warp's chunks of the head: c = half*32 (+64 when the head is 128 wide); their aux loads go out first
+    const int c0 = R.half * 32, c1 = c0 + 64;
+    SecAux A0, A1;
+    load_aux(h0, c0, do_rope, A0);
+    if (c1 < hd) load_aux(h0, c1, do_rope, A1);
+    float rstd = 1.f;
+    if (norm) {                                            // row-per-thread: sum of squares over the whole head
+      float ssq = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < hd; c += 32) {
+        float v[32];
+        L.load32(h0 + c, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) ssq = fmaf(v[j], v[j], ssq);
+      }
+      rstd = rsqrtf(ssq / (float)hd + P.eps);
+    }
+    process(h0, c0, do_rope, rstd, A0);
+    if (c1 < hd) process(h0, c1, do_rope, rstd, A1);
+  }
+}
+
+// ---- SWIGLU ---------------------------------------------------------------------------------
+template <class Loader>
+__device__ __forceinline__ void epi_t_swiglu(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
+                                             const EpiRows& R) {
+  if (R.nrows <= 0) return;
+  const int cg = lane & 7, rsub = lane >> 3;
+  const long long ld = P.ld_out_bf16;
+  const int c = R.half * 32;                               // this warp's 32 of the 64 (w1 | w3) column pairs per group
+#pragma unroll 1
+  for (int g0 = 0; g0 < BN; g0 += 128) {
+    if (R.n0 + g0 >= P.n) break;
+    const int out_col0 = (R.n0 + g0) / 2;
+    float a[32], b[32];
+    L.load32(g0 + c, a);
+    L.load32(g0 + 64 + c, b);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) a[j] = __fdividef(a[j], 1.f + __expf(-a[j])) * b[j];
+    sc_store_row(sc, lane, a);
+    bf16* out = P.out_bf16 + R.mg0 * ld + out_col0 + c + 4 * cg;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rsub;
+      if (r < R.nrows) store_bf16x4(out + (long long)r * ld, sc_load4(sc, r, cg));
+    }
+    __syncwarp();
+  }
+}
+
+template <int EPI, class Loader>
+__device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
+                                               int batch_idx, int mb0, int n0) {
+  EpiRows R;
+  R.batch_idx = batch_idx; R.mb0 = mb0; R.n0 = n0; R.half = half;
+  R.nrows = min(32, max(0, P.rows - mb0));
+  R.mg0 = (long long)batch_idx * P.rows + mb0;
+  if (EPI == ECHO_EPI_GENERIC) epi_t_generic(BN, P, L, sc, lane, R);
+  else if (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
+  else epi_t_swiglu(BN, P, L, sc, lane, R);
+}

@@ -84,6 +84,12 @@ typedef struct echo_gemm_desc {
 
 int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
 
+/* Debug aid (no reference counterpart): while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every
+ * impl-2 GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles
+ * done, [7] exit, and for its first six tiles t: [8+4t] accumulator stage free, [9+4t] MMAs issued, [10+4t]
+ * accumulator ready, [11+4t] epilogue done.  Pass NULL to switch it off. */
+void echo_debug_gemm_trace(long long* device_buf);
+
 /* ------------------------------------------------------------------------------------------
  * fp32 CUDA-core GEMM for the accuracy-critical small projections:
  *   out[z, m, n] = post( sum_k pre(A[z, m, k]) * W[z, n, k] + bias[z, n] + addend[m, n] )

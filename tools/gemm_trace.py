@@ -1,0 +1,75 @@
+#!/usr/bin/env python
+"""In-kernel timeline of the CTA-pair GEMM (clock64 stamps, see echo_debug_gemm_trace in include/echo_b200.h).
+
+    python tools/gemm_trace.py [--m 1920] [--case wo]
+"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+BF16 = torch.bfloat16
+NAMES = ["setup", "first operands", "tile-0 MMAs issued", "tile-0 accumulator ready (epilogue view)",
+         "tile-0 epilogue", "all roles done", "teardown"]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--m", type=int, default=1920)
+    ap.add_argument("--case", default="wo,w2,qkvg,w13")
+    args = ap.parse_args()
+    from echo_tts_b200 import ops, _lib as L
+    from echo_tts_b200.model import rope_table
+    lib = L.load()
+    D, F_, H, S = 2048, 5888, 16, 640
+    M = args.m
+    g = torch.Generator(device="cuda").manual_seed(0)
+    rnd = lambda *s, sc=1.0: (torch.randn(s, device="cuda", generator=g) * sc)
+    xn, hm, x, gate = rnd(M, D).to(BF16), rnd(M, F_).to(BF16), rnd(M, D), rnd(M // S, D)
+    qkvg = torch.empty((4, M, D), device="cuda", dtype=BF16)
+    hmid = torch.empty((M, F_), device="cuda", dtype=BF16)
+    qn = torch.ones(D, device="cuda")
+    rope = rope_table(128, 4096, "cuda")
+    W = dict(qkvg=rnd(4 * D, D, sc=D ** -0.5).to(BF16), wo=rnd(D, D, sc=D ** -0.5).to(BF16),
+             w13=rnd(2 * F_, D, sc=D ** -0.5).to(BF16), w2=rnd(D, F_, sc=F_ ** -0.5).to(BF16))
+    fns = dict(
+        qkvg=lambda: ops.gemm_sections(xn, W["qkvg"], [(L.SEC_NORM_ROPE, qkvg[0], qn), (L.SEC_NORM_ROPE, qkvg[1], qn),
+                                                       (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
+                                       head_dim=128, rope_heads=H // 2, rope=rope, rows_per_seq=S, eps=1e-5),
+        wo=lambda: ops.gemm_generic(xn, W["wo"], gate=gate, rows_per_gate=S, resid=x, out_f32=x),
+        w13=lambda: ops.gemm_swiglu(xn, W["w13"], hmid),
+        w2=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, resid=x, out_f32=x))
+    buf = torch.zeros((512, 32), device="cuda", dtype=torch.int64)
+    for name in args.case.split(","):
+        fn = fns[name]
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        buf.zero_()
+        lib.echo_debug_gemm_trace(buf.data_ptr())
+        fn()
+        torch.cuda.synchronize()
+        lib.echo_debug_gemm_trace(None)
+        t = buf.cpu()
+        t = t[t[:, 0] != 0]
+        ld, fo = t[0::2], t[1::2]          # leader / follower CTA of each pair
+        med = lambda v: float(v.float().median())
+        print(f"== {name} M={M}: {t.shape[0]} CTAs; SM clocks, median over pairs")
+        print(f"   setup {med(ld[:, 1] - ld[:, 0]):8.0f}   first operands after setup {med(ld[:, 2] - ld[:, 1]):8.0f}   "
+              f"whole CTA {med(ld[:, 6] - ld[:, 0]):8.0f}   teardown {med(ld[:, 7] - ld[:, 6]):8.0f}")
+        for tc in range(6):
+            b = 8 + 4 * tc
+            ok = ld[:, b + 1] != 0
+            if not bool(ok.any()):
+                break
+            l, f = ld[ok], fo[ok]
+            print(f"   tile {tc} ({int(ok.sum())} pairs): acc free @{med(l[:, b] - l[:, 0]):8.0f}  MMAs issued @{med(l[:, b + 1] - l[:, 0]):8.0f} "
+                  f"(issue span {med(l[:, b + 1] - l[:, b]):8.0f})  epilogue start @{med(l[:, b + 2] - l[:, 0]):8.0f}  "
+                  f"duration leader {med(l[:, b + 3] - l[:, b + 2]):8.0f} follower {med(f[:, b + 3] - f[:, b + 2]):8.0f}")
+
+
+if __name__ == "__main__":
+    main()
