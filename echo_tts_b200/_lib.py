@@ -63,7 +63,7 @@ class AttnDesc(C.Structure):
     _fields_ = [
         ("q", c_p), ("q_row_stride", i64), ("q_batch_stride", i64), ("gate", c_p), ("out", c_p),
         ("rows", i32), ("seq", i32), ("heads", i32), ("head_dim", i32),
-        ("n_seg", i32), ("_pad", i32), ("softmax_scale", f32), ("_pad1", f32),
+        ("n_seg", i32), ("impl", i32), ("softmax_scale", f32), ("_pad1", f32),
         ("seg", AttnSegment * 4),
     ]
 

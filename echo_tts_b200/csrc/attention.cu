@@ -227,6 +227,8 @@ __global__ void __launch_bounds__(128) attention_kernel(const __grid_constant__ 
 }
 }  // namespace
 
+int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st);   // attention2.cu (tcgen05 kernel)
+
 extern "C" int echo_attention(const echo_attn_desc* d, echo_stream_t stream) {
   ECHO_CHECK_ARG(d && d->q && d->out, "attention: null argument");
   ECHO_CHECK_ARG(d->head_dim == 64 || d->head_dim == 128, "attention: head_dim must be 64 or 128");
@@ -237,8 +239,12 @@ extern "C" int echo_attention(const echo_attn_desc* d, echo_stream_t stream) {
     ECHO_CHECK_ARG(d->seg[i].len == 0 || (d->seg[i].k && d->seg[i].v), "attention: segment %d has no K/V", i);
     ECHO_CHECK_ARG(d->seg[i].row_stride % 8 == 0 && d->seg[i].batch_stride % 8 == 0, "attention: segment strides %%8");
   }
-  dim3 grid(ceil_div(d->seq, ABM), d->heads, d->rows);
   cudaStream_t st = (cudaStream_t)stream;
+  if (d->impl == 0) {   // tcgen05 kernel when the shape is in its domain (head_dim 128, no causal/window segment)
+    const int rc = echo_attention_tc(d, st);
+    if (rc != ECHO_ERR_UNSUPPORTED) return rc;
+  }
+  dim3 grid(ceil_div(d->seq, ABM), d->heads, d->rows);
   if (d->head_dim == 128) {
     const int smem = 4 * ABN * 128 * 2;
     static bool set = false;

@@ -1,0 +1,400 @@
+// Joint attention for the DiT decoder on tcgen05 (head_dim 128, non-causal, up to four KV segments walked in
+// place: self | latent prefix | text | speaker).  Replaces torch.cat + F.scaled_dot_product_attention + the sigmoid
+// gating of model.py:246-264 and the cache replication / scaling helpers of inference.py:409-428.
+//
+// One CTA = 128 queries of one (row, head).  Per 64-key tile:
+//     S = Q K^T   tcgen05.mma  (A = Q from smem, B = K from smem, both K-major SW128; D = S in TMEM, 64 fp32 columns)
+//     softmax     128 threads, one query row each: tcgen05.ld S -> registers, masks / extents / speaker_kv_scale,
+//                 online max with LAZY rescale of O (only when the running max grows by > 8 in the exp2 domain),
+//                 P = exp2(s - m) as bf16 written back to TMEM over the first 32 columns of S (tcgen05.st)
+//     O += P V    tcgen05.mma  (A = P from TMEM, B = V from smem as an MN-major SW128 operand: no transpose copy)
+// S is double-buffered in TMEM so the QK^T of tile j+1 is issued while the softmax of tile j runs; K and V travel
+// in separate 2-stage TMA rings (K is needed one iteration earlier than V).  A CTA needs 96 KB of shared memory
+// and 256 TMEM columns, so two CTAs are co-resident per SM and fill each other's bubbles.  Warp roles: 0..3 softmax
+// + epilogue (sigmoid gate, 1/l, bf16 store), 4 = TMA producer, 5 = TMEM owner + MMA issuer.
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "../../include/echo_b200.h"
+
+int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                        const cuuint32_t* box);   // gemm.cu
+
+namespace {
+constexpr int QT = 128, KT = 64, HD = 128;
+constexpr int Q_BYTES = QT * HD * 2;          // 32 KB: two [128 x 64] SW128 blocks
+constexpr int KV_BYTES = KT * HD * 2;         // 16 KB: two [64 x 64] SW128 blocks
+constexpr int MAX_TILES = 128;                // <= 8192 keys in total
+constexpr int SMEM_ATTN = Q_BYTES + 4 * KV_BYTES + 1024 /*align*/ + 256 /*barriers*/ + MAX_TILES * 16;
+constexpr int TM_S0 = 0, TM_S1 = 64, TM_O = 128, TM_COLS = 256;
+constexpr float RESCALE_TAU = 8.f;            // lazy-rescale threshold (log2 domain): P <= 2^8
+
+struct AttnSeg {
+  int len, kv_batch_mod;
+  const uint8_t* mask; long long mask_stride;
+  const int* extent;
+  const float* kv_scale;
+};
+struct AttnParams {
+  int rows, seq, heads, n_seg;
+  float softmax_scale;
+  const bf16* gate;
+  bf16* out;
+  AttnSeg seg[4];
+};
+struct TileInfo { int seg, key0; unsigned long long valid; };   // 16 bytes
+
+__device__ __forceinline__ void tma_load_4d(void* dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// MN-major SW128 operand ([k rows][64 elements = 128 B] blocks; 8-row groups 1024 B apart; next 64-column block `lbo` B on)
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+        "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+        "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+struct Maps { CUtensorMap q, k[4], v[4]; };
+
+__global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_constant__ Maps M,
+                                                              const __grid_constant__ AttnParams A) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + Q_BYTES;                     // 2 stages
+  uint8_t* sV = sK + 2 * KV_BYTES;                  // 2 stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * KV_BYTES);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* k_full = bars + 1;        // 2
+  uint64_t* k_empty = bars + 3;       // 2
+  uint64_t* v_full = bars + 5;        // 2
+  uint64_t* v_empty = bars + 7;       // 2
+  uint64_t* s_full = bars + 9;        // 2
+  uint64_t* p_full = bars + 11;       // 2
+  uint64_t* pv_done = bars + 13;      // 2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  int* s_ntiles = reinterpret_cast<int*>(bars + 16);
+  TileInfo* tiles = reinterpret_cast<TileInfo*>(reinterpret_cast<uint8_t*>(bars) + 256);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q0 = blockIdx.x * QT, head = blockIdx.y, row = blockIdx.z;
+
+  // ---- tile list: every 64-key tile any query of this row can see, with its key-valid bits -------------------
+  if (warp == 0) {
+    int nt = 0;
+    for (int sgi = 0; sgi < A.n_seg; ++sgi) {
+      const AttnSeg& sg = A.seg[sgi];
+      const int ext = sg.extent ? min(sg.extent[row], sg.len) : sg.len;
+      for (int key0 = 0; key0 < ext && nt < MAX_TILES; key0 += KT, ++nt) {
+        // lane handles keys key0 + lane and key0 + 32 + lane
+        bool v0 = key0 + lane < ext, v1 = key0 + 32 + lane < ext;
+        if (sg.mask) {
+          const uint8_t* mrow = sg.mask + (long long)row * sg.mask_stride + key0;
+          if (v0) v0 = mrow[lane] != 0;
+          if (v1) v1 = mrow[32 + lane] != 0;
+        }
+        const unsigned lo = __ballot_sync(0xffffffffu, v0), hi = __ballot_sync(0xffffffffu, v1);
+        if (lane == 0) {
+          tiles[nt].seg = sgi; tiles[nt].key0 = key0;
+          tiles[nt].valid = ((unsigned long long)hi << 32) | lo;
+        }
+      }
+    }
+    if (lane == 0) *s_ntiles = nt;
+  }
+  if (warp == 4 && lane == 0) {
+    ptx::prefetch_tensormap(&M.q);
+    ptx::mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&k_empty[i], 1);
+      ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&v_empty[i], 1);
+      ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 128); ptx::mbar_init(&pv_done[i], 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 5) {
+    ptx::tmem_alloc(tmem_slot, TM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int ntiles = *s_ntiles;
+
+  if (warp == 4) {
+    // ===== TMA producer =====
+    if (lane == 0 && ntiles > 0) {
+      ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+      tma_load_4d(sQ, &M.q, q_full, 0, head, q0, row);
+      tma_load_4d(sQ + Q_BYTES / 2, &M.q, q_full, 64, head, q0, row);
+      auto load_k = [&](int j) {
+        const int s = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const TileInfo t = tiles[j];
+        const int kvrow = A.seg[t.seg].kv_batch_mod > 0 ? row % A.seg[t.seg].kv_batch_mod : row;
+        ptx::mbar_wait(&k_empty[s], ph ^ 1);
+        ptx::mbar_arrive_expect_tx(&k_full[s], KV_BYTES);
+        tma_load_4d(sK + s * KV_BYTES, &M.k[t.seg], &k_full[s], 0, head, t.key0, kvrow);
+        tma_load_4d(sK + s * KV_BYTES + KV_BYTES / 2, &M.k[t.seg], &k_full[s], 64, head, t.key0, kvrow);
+      };
+      auto load_v = [&](int j) {
+        const int s = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const TileInfo t = tiles[j];
+        const int kvrow = A.seg[t.seg].kv_batch_mod > 0 ? row % A.seg[t.seg].kv_batch_mod : row;
+        ptx::mbar_wait(&v_empty[s], ph ^ 1);
+        ptx::mbar_arrive_expect_tx(&v_full[s], KV_BYTES);
+        tma_load_4d(sV + s * KV_BYTES, &M.v[t.seg], &v_full[s], 0, head, t.key0, kvrow);
+        tma_load_4d(sV + s * KV_BYTES + KV_BYTES / 2, &M.v[t.seg], &v_full[s], 64, head, t.key0, kvrow);
+      };
+      if (ntiles > 0) load_k(0);
+      for (int j = 0; j < ntiles; ++j) {      // K runs one tile ahead of V
+        if (j + 1 < ntiles) load_k(j + 1);
+        load_v(j);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    // ===== MMA issuer =====
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(QT, KT);                    // 128 x 64, both K-major
+      constexpr uint32_t idesc_o = ptx::umma_idesc_bf16(QT, HD) | (1u << 16);       // 128 x 128, B (= V) MN-major
+      const uint32_t q_addr = smem_u32(sQ);
+      auto issue_s = [&](int j) {
+        const int s = j & 1;
+        ptx::mbar_wait(&k_full[s], (j >> 1) & 1);
+        ptx::tc_fence_after();
+        const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
+        const uint32_t d = tmem_base + (s ? TM_S1 : TM_S0);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2)) + 2 * (kk & 3);
+          const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_BYTES / 2)) + 2 * (kk & 3);
+          ptx::umma_bf16(d, da, db, idesc_s, kk != 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(&k_empty[s]);
+        ptx::umma_commit(&s_full[s]);
+      };
+      ptx::mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        if (j + 1 < ntiles) issue_s(j + 1);
+        ptx::mbar_wait(&p_full[s], ph);
+        ptx::mbar_wait(&v_full[s], ph);
+        ptx::tc_fence_after();
+        const uint32_t v_addr = smem_u32(sV + s * KV_BYTES);
+        const uint32_t p_tmem = tmem_base + (s ? TM_S1 : TM_S0);
+#pragma unroll
+        for (int kk = 0; kk < KT / 16; ++kk) {
+          const uint64_t db = umma_desc_sw128_mn(v_addr + kk * 16 * 128, KV_BYTES / 2);
+          umma_bf16_ts(tmem_base + TM_O, p_tmem + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(&v_empty[s]);
+        ptx::umma_commit(&pv_done[s]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== softmax + epilogue: thread = query row =====
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    const int qi = q0 + tid;
+    const float sl2 = A.softmax_scale * 1.4426950408889634f;
+    float m = -INFINITY, l = 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int b = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      const TileInfo t = tiles[j];
+      const float f = A.seg[t.seg].kv_scale ? __ldg(A.seg[t.seg].kv_scale) : 1.f;
+      const float sc = sl2 * f;
+      ptx::mbar_wait(&s_full[b], ph);
+      ptx::tc_fence_after();
+      float s[64];
+      const uint32_t s_addr = tmem_base + (b ? TM_S1 : TM_S0) + lane_off;
+      tmem_ld32_nowait(s_addr, s);
+      tmem_ld32_nowait(s_addr + 32, s + 32);
+      tmem_ld_wait();
+      float mt = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        const bool ok = (t.valid >> c) & 1ull;
+        s[c] = ok ? s[c] * sc : -INFINITY;
+        mt = fmaxf(mt, s[c]);
+      }
+      // the PV of the previous tile must have landed before O may be rescaled (and is long done by now)
+      if (j > 0) ptx::mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+      const bool grow = mt > m + RESCALE_TAU;            // also true for the first finite max (m = -inf)
+      if (__any_sync(0xffffffffu, grow)) {
+        const float mnew = grow ? mt : m;
+        const float alpha = (m == -INFINITY) ? 0.f : exp2f(m - mnew);
+        m = mnew;
+        l *= alpha;
+        if (j > 0) {
+          ptx::tc_fence_after();
+#pragma unroll 1
+          for (int c = 0; c < HD; c += 32) {
+            float o[32];
+            ptx::tmem_ld32(tmem_base + TM_O + lane_off + c, o);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] *= alpha;
+            tmem_st32(tmem_base + TM_O + lane_off + c, reinterpret_cast<const uint32_t*>(o));
+          }
+          tmem_st_wait();
+        }
+      }
+      const float muse = (m == -INFINITY) ? 0.f : m;
+      uint32_t p[32];
+      float ls = 0.f;
+#pragma unroll
+      for (int c = 0; c < 64; c += 2) {
+        const float p0 = exp2f(s[c] - muse), p1 = exp2f(s[c + 1] - muse);
+        ls += p0 + p1;
+        p[c >> 1] = pack_bf16x2(p0 * f, p1 * f);
+      }
+      l += ls;
+      tmem_st32(s_addr, p);
+      tmem_st_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&p_full[b]);
+    }
+    // ---- epilogue: O / l * sigmoid-gate -> bf16 ------------------------------------------------------------
+    const int width = A.heads * HD;
+    const long long o_off = ((long long)row * A.seq + qi) * width + (long long)head * HD;
+    const bool q_ok = qi < A.seq;
+    if (ntiles > 0) {
+      ptx::mbar_wait(&pv_done[(ntiles - 1) & 1], ((ntiles - 1) >> 1) & 1);
+      ptx::tc_fence_after();
+    }
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll 1
+    for (int c = 0; c < HD; c += 32) {
+      float o[32];
+      if (ntiles > 0) {
+        ptx::tmem_ld32(tmem_base + TM_O + lane_off + c, o);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0.f;
+      }
+      if (q_ok) {
+#pragma unroll
+        for (int g = 0; g < 32; g += 8) {
+          float w[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w[i] = o[g + i] * inv;
+          if (A.gate) {
+            const uint4 gv = *reinterpret_cast<const uint4*>(A.gate + o_off + c + g);
+            const float2 g0 = unpack_bf16x2(gv.x), g1 = unpack_bf16x2(gv.y), g2 = unpack_bf16x2(gv.z), g3 = unpack_bf16x2(gv.w);
+            w[0] *= g0.x; w[1] *= g0.y; w[2] *= g1.x; w[3] *= g1.y; w[4] *= g2.x; w[5] *= g2.y; w[6] *= g3.x; w[7] *= g3.y;
+          }
+          uint4 u;
+          u.x = pack_bf16x2(w[0], w[1]); u.y = pack_bf16x2(w[2], w[3]);
+          u.z = pack_bf16x2(w[4], w[5]); u.w = pack_bf16x2(w[6], w[7]);
+          *reinterpret_cast<uint4*>(A.out + o_off + c + g) = u;
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 5) ptx::tmem_dealloc(tmem_base, TM_COLS);
+}
+}  // namespace
+
+// Returns ECHO_ERR_UNSUPPORTED (without setting an error) when the descriptor is outside this kernel's domain so
+// that echo_attention() can fall back to the generic mma.sync kernel (causal / windowed / head_dim 64 encoders).
+int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
+  if (d->head_dim != HD) return ECHO_ERR_UNSUPPORTED;
+  long long total_tiles = 0;
+  for (int i = 0; i < d->n_seg; ++i) {
+    if (d->seg[i].causal || d->seg[i].window > 0) return ECHO_ERR_UNSUPPORTED;
+    total_tiles += ceil_div(d->seg[i].len, KT);
+  }
+  if (total_tiles > MAX_TILES) return ECHO_ERR_UNSUPPORTED;
+  if (((uintptr_t)d->q % 16) || ((uintptr_t)d->out % 16) || ((uintptr_t)d->gate % 16) || (d->heads * HD) % 8)
+    return ECHO_ERR_UNSUPPORTED;
+  Maps M;
+  AttnParams A;
+  memset(&A, 0, sizeof(A));
+  memset(&M, 0, sizeof(M));
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)HD, (cuuint64_t)d->heads, (cuuint64_t)d->seq, (cuuint64_t)d->rows};
+    cuuint64_t str[3] = {(cuuint64_t)HD * 2, (cuuint64_t)d->q_row_stride * 2, (cuuint64_t)d->q_batch_stride * 2};
+    cuuint32_t box[4] = {64, 1, QT, 1};
+    int rc = echo_make_tmap_bf16(&M.q, d->q, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  A.rows = d->rows; A.seq = d->seq; A.heads = d->heads; A.n_seg = d->n_seg;
+  A.softmax_scale = d->softmax_scale;
+  A.gate = (const bf16*)d->gate; A.out = (bf16*)d->out;
+  for (int i = 0; i < d->n_seg; ++i) {
+    const echo_attn_segment& s = d->seg[i];
+    A.seg[i].len = s.len; A.seg[i].kv_batch_mod = s.kv_batch_mod;
+    A.seg[i].mask = s.mask; A.seg[i].mask_stride = s.mask_stride;
+    A.seg[i].extent = s.extent; A.seg[i].kv_scale = s.kv_scale;
+    if (s.len <= 0) { M.k[i] = M.q; M.v[i] = M.q; continue; }
+    if (((uintptr_t)s.k % 16) || ((uintptr_t)s.v % 16)) return ECHO_ERR_UNSUPPORTED;
+    const int kv_rows = s.kv_batch_mod > 0 ? s.kv_batch_mod : d->rows;
+    cuuint64_t dims[4] = {(cuuint64_t)HD, (cuuint64_t)d->heads, (cuuint64_t)s.len, (cuuint64_t)kv_rows};
+    cuuint64_t str[3] = {(cuuint64_t)HD * 2, (cuuint64_t)s.row_stride * 2,
+                         (cuuint64_t)(kv_rows > 1 ? s.batch_stride : (long long)s.len * s.row_stride) * 2};
+    cuuint32_t box[4] = {64, 1, KT, 1};
+    int rc = echo_make_tmap_bf16(&M.k[i], s.k, 4, dims, str, box);
+    if (rc) return rc;
+    rc = echo_make_tmap_bf16(&M.v[i], s.v, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    ECHO_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ATTN));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(d->seq, QT), d->heads, d->rows);
+  attention_tc_kernel<<<grid, 192, SMEM_ATTN, st>>>(M, A);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}

@@ -128,7 +128,7 @@ int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint
                         const cuuint32_t* box) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { echo_set_error("cuTensorMapEncodeTiled entry point unavailable"); return ECHO_ERR_CUDA; }
-  cuuint32_t estr[3] = {1, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_b, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

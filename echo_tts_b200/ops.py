@@ -189,8 +189,11 @@ class Segment:
         self.length = k.shape[1] if length is None else length
 
 
+ATTN_IMPL = int(_os.environ.get("ECHO_ATTN_IMPL", "0"))   # 0 = tcgen05 kernel when eligible; 1 = mma.sync kernel (A/B)
+
+
 def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate: Optional[torch.Tensor] = None,
-              softmax_scale: Optional[float] = None) -> None:
+              softmax_scale: Optional[float] = None, impl: Optional[int] = None) -> None:
     """q bf16 [R, S, H, Dh] (last two dims contiguous); out bf16 [R*S, H*Dh]."""
     _need(q, BF16, "q"); _need(out, BF16, "out")
     R, S, H, Dh = q.shape
@@ -204,6 +207,7 @@ def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate:
     d.rows, d.seq, d.heads, d.head_dim = R, S, H, Dh
     d.softmax_scale = softmax_scale if softmax_scale is not None else Dh ** -0.5
     d.n_seg = len(segs)
+    d.impl = ATTN_IMPL if impl is None else impl
     for i, s in enumerate(segs):
         sg = d.seg[i]
         sg.len = s.length

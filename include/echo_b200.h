@@ -151,7 +151,8 @@ typedef struct echo_attn_desc {
   const void* gate;         /* bf16 sigmoid(gate) [rows*seq, heads*head_dim] or NULL */
   void* out;                /* bf16 [rows*seq, heads*head_dim] */
   int32_t rows, seq, heads, head_dim;
-  int32_t n_seg, _pad;
+  int32_t n_seg;
+  int32_t impl;             /* 0 = tcgen05 kernel when eligible (head_dim 128, non-causal), else mma.sync kernel; 1 = force mma.sync */
   float softmax_scale, _pad1;
   echo_attn_segment seg[4];
 } echo_attn_desc;

@@ -70,6 +70,32 @@ def test_joint_attention_segments(ops):
     assert rel_l2(out.float(), ref) < 6e-3
 
 
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("R,S,Lt,valid_t,Ls", [(3, 640, 768, 256, 53), (1, 640, 768, 300, 53), (2, 128, 64, 64, 8),
+                                                (3, 320, 768, 1, 1600)])
+def test_joint_attention_dit_shapes(ops, impl, R, S, Lt, valid_t, Ls):
+    """BASELINE config-2/4 shapes: self + text (768-padded) + speaker segments, CFG rows dropping a modality,
+    tcgen05 kernel (impl 0) and mma.sync kernel (impl 1) against the dense fp32 reference."""
+    H, Dh = 16, 128
+    qkv = _rand((3, R, S, H, Dh), 31, dtype=BF16)
+    kt, vt = _rand((1, Lt, H, Dh), 32, dtype=BF16), _rand((1, Lt, H, Dh), 33, dtype=BF16)
+    ksp, vsp = _rand((1, Ls, H, Dh), 34, dtype=BF16), _rand((1, Ls, H, Dh), 35, dtype=BF16)
+    gate = torch.sigmoid(_rand((R * S, H * Dh), 36)).to(BF16)
+    tm = torch.zeros(R, Lt, dtype=torch.uint8, device="cuda"); tm[:, :valid_t] = 1
+    sm = torch.ones(R, Ls, dtype=torch.uint8, device="cuda")
+    if R == 3:
+        tm[1] = 0; sm[2] = 0
+    scale = torch.tensor([1.5], device="cuda")
+    out = torch.full((R * S, H * Dh), float("nan"), device="cuda", dtype=BF16)
+    ops.attention(qkv[0], [ops.Segment(qkv[1], qkv[2]),
+                           ops.Segment(kt, vt, kv_batch_mod=1, mask=tm, extent=ops.mask_extent(tm)),
+                           ops.Segment(ksp, vsp, kv_batch_mod=1, mask=sm, extent=ops.mask_extent(sm), kv_scale=scale)],
+                  out, gate=gate, impl=impl)
+    ref = _ref_attention(qkv[0], [dict(k=qkv[1], v=qkv[2]), dict(k=kt, v=vt, mask=tm), dict(k=ksp, v=vsp, mask=sm, scale=1.5)],
+                         gate)
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
 @pytest.mark.parametrize("Dh,window", [(128, 0), (64, 16), (64, 128)])
 def test_causal_window_attention(ops, Dh, window):
     B, S, H = 2, 333, 4

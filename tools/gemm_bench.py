@@ -93,10 +93,21 @@ def main():
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             n = reps * nw
-            e0.record()
-            for i in range(n):
-                fn(i)
-            e1.record()
+            if args.quick:
+                e0.record()
+                for i in range(n):
+                    fn(i)
+                e1.record()
+            else:   # replay the launches from a CUDA graph: no Python/ctypes launch overhead between kernels
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr):
+                    for i in range(n):
+                        fn(i)
+                gr.replay()
+                torch.cuda.synchronize()
+                e0.record()
+                gr.replay()
+                e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / n
             tot_us += us; tot_fl += fl
