@@ -82,6 +82,11 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, float* v) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ float ex2_approx(float x) {   // 2^x, -inf -> 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
   asm volatile(
@@ -258,13 +263,19 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       tmem_ld32_nowait(s_addr, s);
       tmem_ld32_nowait(s_addr + 32, s + 32);
       tmem_ld_wait();
+      // raw maximum first (sc > 0), masked only on partial tiles (warp-uniform branch: most tiles are full)
       float mt = -INFINITY;
+      if (t.valid != ~0ull) {
+        const unsigned lo = (unsigned)t.valid, hi = (unsigned)(t.valid >> 32);
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const bool ok = (t.valid >> c) & 1ull;
-        s[c] = ok ? s[c] * sc : -INFINITY;
-        mt = fmaxf(mt, s[c]);
+        for (int c = 0; c < 32; ++c) {
+          if (!((lo >> c) & 1u)) s[c] = -INFINITY;
+          if (!((hi >> c) & 1u)) s[c + 32] = -INFINITY;
+        }
       }
+#pragma unroll
+      for (int c = 0; c < 64; ++c) mt = fmaxf(mt, s[c]);
+      mt *= sc;
       // the PV of the previous tile must have landed before O may be rescaled (and is long done by now)
       if (j > 0) ptx::mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
       const bool grow = mt > m + RESCALE_TAU;            // also true for the first finite max (m = -inf)
@@ -286,16 +297,25 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
           tmem_st_wait();
         }
       }
-      const float muse = (m == -INFINITY) ? 0.f : m;
+      const float nmuse = (m == -INFINITY) ? 0.f : -m;
       uint32_t p[32];
-      float ls = 0.f;
+      float ls0 = 0.f, ls1 = 0.f;
+      if (f == 1.f) {
 #pragma unroll
-      for (int c = 0; c < 64; c += 2) {
-        const float p0 = exp2f(s[c] - muse), p1 = exp2f(s[c + 1] - muse);
-        ls += p0 + p1;
-        p[c >> 1] = pack_bf16x2(p0 * f, p1 * f);
+        for (int c = 0; c < 64; c += 2) {
+          const float p0 = ex2_approx(fmaf(s[c], sc, nmuse)), p1 = ex2_approx(fmaf(s[c + 1], sc, nmuse));
+          ls0 += p0; ls1 += p1;
+          p[c >> 1] = pack_bf16x2(p0, p1);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 64; c += 2) {
+          const float p0 = ex2_approx(fmaf(s[c], sc, nmuse)), p1 = ex2_approx(fmaf(s[c + 1], sc, nmuse));
+          ls0 += p0; ls1 += p1;
+          p[c >> 1] = pack_bf16x2(p0 * f, p1 * f);
+        }
       }
-      l += ls;
+      l += ls0 + ls1;
       tmem_st32(s_addr, p);
       tmem_st_wait();
       ptx::tc_fence_before();
