@@ -125,9 +125,11 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * QT, head = blockIdx.y, row = blockIdx.z;
+  pdl_launch_dependents();
 
   // ---- tile list: every 64-key tile any query of this row can see, with its key-valid bits -------------------
   if (warp == 0) {
+    pdl_wait();            // extents / masks may come from the previous kernel
     int nt = 0;
     for (int sgi = 0; sgi < A.n_seg; ++sgi) {
       const AttnSeg& sg = A.seg[sgi];
@@ -168,6 +170,7 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int ntiles = *s_ntiles;
+  pdl_wait();
 
   if (warp == 4) {
     // ===== TMA producer =====
@@ -413,7 +416,7 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid(ceil_div(d->seq, QT), d->heads, d->rows);
-  attention_tc_kernel<<<grid, 192, SMEM_ATTN, st>>>(M, A);
+  ECHO_CUDA(echo_launch(attention_tc_kernel, grid, dim3(192), SMEM_ATTN, st, M, A));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

@@ -39,6 +39,28 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 extern unsigned long long g_echo_launches;
 #define ECHO_COUNT_LAUNCH() (++g_echo_launches)
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------------
+// Hot-path kernels are launched with cudaLaunchAttributeProgrammaticStreamSerialization: the next kernel of the
+// stream (or CUDA graph) may start its prologue (barrier init, TMEM alloc, tensor-map prefetch) while this one
+// drains; it must call pdl_wait() before its first dependent global access.  ECHO_PDL=0 switches it off (A/B).
+int echo_pdl_enabled();
+#ifdef __CUDACC__
+#include <utility>
+template <typename... KArgs, typename... Args>
+static inline cudaError_t echo_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                      Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = echo_pdl_enabled();
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
 typedef __nv_bfloat16 bf16;
 
 __device__ __forceinline__ float bf2f(bf16 v) { return __bfloat162float(v); }

@@ -1,7 +1,8 @@
 // bf16 GEMM / implicit causal conv, CTA-pair edition (impl 2, the product path):
 //   * cluster of 2 CTAs = one 256 x BN output tile; tcgen05.mma.cta_group::2 issued by one thread of the leader
 //     CTA reads A (128 rows per CTA) and B (BN/2 rows per CTA) from BOTH CTAs' shared memory, so every SM
-//     stages half as many B bytes per MMA (64 B/clk/SM from L2 instead of 96) and the ring gets 6 stages;
+//     stages half as many B bytes per MMA (64 B/clk/SM from L2 instead of 96) and the 192 KB ring holds 6 stages of a
+//     256-wide tile (8 of a 128-wide one: operand latency, not MMA issue, bounds narrow tiles);
 //   * persistent: grid = min(#pair tiles, #SM/2) clusters, static round-robin tile order with the M index
 //     fastest so that the pairs working concurrently share one weight (B) tile through L2;
 //   * two TMEM accumulator stages (2 x 256 columns): the fused epilogue of tile i runs while the MMAs of
@@ -10,6 +11,7 @@
 //     1 = TMEM owner (+ MMA issuer in the leader CTA), 2..9 = epilogue (two warps per TMEM lane quarter taking
 //     alternate 32-column chunks; coalesced vector stores via a per-warp 32x32 shared-memory transpose and
 //     auxiliary loads issued one chunk ahead, gemm_epilogue_t.cuh).
+#include <stdlib.h>
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 #include "gemm_epilogue_t.cuh"
@@ -20,19 +22,23 @@ constexpr int BK = 64;
 constexpr int A_BYTES = BM * BK * 2;
 constexpr int B_BYTES_MAX = 128 * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;
-constexpr int STAGES = 6;
+constexpr int RING_BYTES = 6 * STAGE_BYTES;       // 192 KB of operand ring; narrower tiles get more, smaller stages
+constexpr int MAX_STAGES = 10;
 constexpr int ACC_STAGES = 2;
 constexpr int ACC_COLS = 256;
 constexpr int EPI_WARPS = 8;       // two per TMEM lane quarter
 constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
 constexpr int SCRATCH_BYTES = EPI_WARPS * EPI_SC_FLOATS * 4;   // per-epilogue-warp 32x32 fp32 transpose scratch
-constexpr int SMEM2 = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
+constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
 
 // optional in-kernel timeline (32 clock64 slots per CTA), enabled with echo_debug_gemm_trace(ptr)
 static long long* g_trace_ptr = nullptr;
+static int g_debug_noload = 0;   // debug: MMAs re-use whatever is in the ring (no TMA after the first fill): isolates MMA issue rate
 
 struct Tiling {
   long long* trace;       // nullptr unless tracing: [cta][32] SM-clock stamps
+  int noload;             // debug only
+  int stages, stage_bytes; // operand ring: stage = A (16 KB) + this CTA's half of B (bn/2 rows x 128 B)
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
   int num_tiles;          // tiles_m * tiles_n * batch
@@ -50,12 +56,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                  const __grid_constant__ Tiling T) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + RING_BYTES);
+  uint64_t* empty_bar = full_bar + MAX_STAGES;
+  uint64_t* tmem_full_bar = empty_bar + MAX_STAGES;
   uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
-  float* scratch = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
+  float* scratch = reinterpret_cast<float*>(smem + RING_BYTES + 256);
+  const int STAGES = T.stages, STAGE_SZ = T.stage_bytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
@@ -88,27 +95,30 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (trace && threadIdx.x == 0) trace[1] = clock64();
+  pdl_launch_dependents();    // the next kernel may begin its own setup
+  pdl_wait();                 // everything below reads / writes memory the previous kernel may still be producing
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t it = 0;
+      int s = 0;
+      uint32_t ph = 0;
       for (int tile = pair; tile < T.num_tiles; tile += npairs) {
         const int mt = tile % T.tiles_m;
         const int rest = tile / T.tiles_m;
         const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
         const int m0 = mt * (2 * BM) + (int)rank * BM;
         const int n0 = nt * T.bn + (int)rank * half_n;
-        for (int kb = 0; kb < total_kb; ++kb, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
+        for (int kb = 0; kb < total_kb; ++kb) {
+          if (T.noload && (kb >= STAGES || tile != pair)) break;
           ptx::mbar_wait(&empty_bar[s], ph ^ 1);
           const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
-          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sa = smem + s * STAGE_SZ;
           uint8_t* sb = sa + A_BYTES;
           if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], stage_tx);
           const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
           ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
           ptx::tma_load_2d_cg2(sb, &tmap_b, lbar, tap * G.k_tap + kk * BK, n0);
+          if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -116,26 +126,27 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp == 1) {
     if (rank == 0 && lane == 0) {
       const uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, T.bn);
-      uint32_t it = 0, tc = 0;
+      uint32_t tc = 0, ph = 0;
+      int s = 0;
+      bool first = true;
       for (int tile = pair; tile < T.num_tiles; tile += npairs, ++tc) {
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
         ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
         ptx::tc_fence_after();
         if (trace && tc < 6) trace[8 + tc * 4 + 0] = clock64();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
-        for (int kb = 0; kb < total_kb; ++kb, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          ptx::mbar_wait(&full_bar[s], ph);
+        for (int kb = 0; kb < total_kb; ++kb) {
+          if (!(T.noload && (kb >= STAGES || tile != pair))) ptx::mbar_wait(&full_bar[s], ph);
           ptx::tc_fence_after();
-          if (trace && it == 0) trace[2] = clock64();
-          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          if (trace && first) { trace[2] = clock64(); first = false; }
+          const uint32_t sa = smem_u32(smem + s * STAGE_SZ);
           const uint64_t da = ptx::umma_desc_sw128(sa);
           const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
             ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
+          if (!T.noload) ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
+          if (++s == STAGES) { s = 0; ph ^= 1; }
         }
         ptx::umma_commit_cg2_mc(&tmem_full_bar[as], 0b11);
         if (trace && tc < 6) trace[8 + tc * 4 + 1] = clock64();
@@ -209,12 +220,15 @@ static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int bat
   }
   Tiling T;
   T.trace = g_trace_ptr;
+  T.noload = g_debug_noload;
   T.bn = bn;
+  T.stage_bytes = A_BYTES + (bn / 2) * BK * 2;
+  T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
   T.num_tiles = T.tiles_m * T.tiles_n * batch;
   const int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
-  gemm_pair_kernel<EPI><<<dim3(2 * pairs), NTHREADS, SMEM2, st>>>(ta, tb, G, P, T);
+  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, G, P, T));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
@@ -224,7 +238,11 @@ static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int bat
 // [0] start, [1] setup done, [2] first operands landed, [6] all roles done, [7] exit, and for the CTA's first six
 // tiles t: [8+4t] accumulator stage free (MMA thread), [9+4t] MMAs issued, [10+4t] accumulator ready (epilogue
 // warp 2), [11+4t] epilogue done.  Pass NULL to switch tracing off.
-extern "C" void echo_debug_gemm_trace(long long* device_buf) { g_trace_ptr = device_buf; }
+extern "C" void echo_debug_gemm_trace(long long* device_buf) {
+  g_trace_ptr = device_buf;
+  const char* e = getenv("ECHO_GEMM_NOLOAD");    // results are garbage in this mode; timing experiments only
+  g_debug_noload = (device_buf && e && e[0] == '1') ? 1 : 0;
+}
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
 int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "../../include/echo_b200.h"
 #include <stdarg.h>
+#include <stdlib.h>
 
 static thread_local char g_err[512] = "";
 unsigned long long g_echo_launches = 0;
@@ -13,6 +14,14 @@ void echo_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 extern "C" const char* echo_last_error(void) { return g_err; }
+int echo_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("ECHO_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
+}
 extern "C" int echo_version(void) { return 100; }
 extern "C" unsigned long long echo_launch_count(void) { return g_echo_launches; }
 extern "C" void echo_reset_launch_count(void) { g_echo_launches = 0; }
@@ -30,6 +39,8 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
                                                           long long ldy) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   if (row >= m) return;
   const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
   float4 v[VEC_ITERS];
@@ -74,11 +85,11 @@ extern "C" int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float
   dim3 grid(ceil_div(m, 8));
   cudaStream_t st = (cudaStream_t)stream;
   if (d <= 1024)
-    rmsnorm_mod_kernel<8><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<8>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else if (d <= 2048)
-    rmsnorm_mod_kernel<16><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<16>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else
-    rmsnorm_mod_kernel<32><<<grid, 256, 0, st>>>(x, ldx, m, d, eps, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride, (bf16*)y, ldy);
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<32>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
@@ -91,6 +102,8 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo
   __shared__ float sA[16][64 + 4];
   __shared__ float sW[16][64 + 4];
   const int z = blockIdx.z;
+  pdl_launch_dependents();
+  pdl_wait();
   const float* A = D.a + z * D.a_zstride;
   const float* W = D.w + z * D.w_zstride;
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
@@ -149,7 +162,7 @@ extern "C" int echo_sgemm_f32(const echo_sgemm_desc* d, echo_stream_t stream) {
   ECHO_CHECK_ARG(d && d->a && d->w && (d->out || d->out_bf16), "sgemm: null argument");
   ECHO_CHECK_ARG(d->m > 0 && d->n > 0 && d->k > 0 && d->nz > 0, "sgemm: bad shape");
   dim3 grid(ceil_div(d->n, 64), ceil_div(d->m, 64), d->nz);
-  sgemm_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*d);
+  ECHO_CUDA(echo_launch(sgemm_kernel, grid, dim3(256), 0, (cudaStream_t)stream, *d));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

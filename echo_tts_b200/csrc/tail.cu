@@ -16,6 +16,8 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int pos0 = blockIdx.x * PP;
   const int nvec = D.d >> 2;
+  pdl_launch_dependents();
+  pdl_wait();
 
   for (int r = warp; r < nrows; r += 8) {
     const int br = r / PP, p = pos0 + (r % PP);
@@ -113,7 +115,7 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
     ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  cfg_euler_tail_kernel<<<ceil_div(d->positions, PP), 256, smem, (cudaStream_t)stream>>>(*d);
+  ECHO_CUDA(echo_launch(cfg_euler_tail_kernel, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
