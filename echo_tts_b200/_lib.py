@@ -27,14 +27,14 @@ class GemmDesc(C.Structure):
         ("a", c_p), ("b", c_p), ("lda", i64), ("a_batch_stride", i64), ("ldb", i64),
         ("rows", i32), ("batch", i32), ("n", i32), ("k_tap", i32), ("taps", i32),
         ("tap_shift", i32 * 8), ("epilogue", i32), ("impl", i32), ("block_n", i32), ("act", i32),
-        ("bias", c_p), ("gate", c_p), ("gate_ld", i64), ("rows_per_gate", i32), ("_pad0", i32),
+        ("bias", c_p), ("gate", c_p), ("gate_ld", i64), ("rows_per_gate", i32), ("k_splits", i32),
         ("resid", c_p), ("ld_resid", i64), ("out_f32", c_p), ("ld_out_f32", i64),
         ("out_bf16", c_p), ("ld_out_bf16", i64), ("out2_bf16", c_p), ("ld_out2_bf16", i64),
         ("snake_alpha", c_p),
         ("n_sections", i32), ("section_width", i32), ("head_dim", i32), ("rope_heads", i32),
         ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("_pad1", i32),
         ("eps", f32), ("_pad2", f32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
-        ("sections", GemmSection * 4),
+        ("sections", GemmSection * 4), ("split_stride", i64),
     ]
 
 
@@ -74,7 +74,7 @@ class TailDesc(C.Structure):
         ("x_t", c_p), ("v_out", c_p), ("v_comb_out", c_p), ("sched", c_p), ("step", c_p),
         ("positions", i32), ("d", i32), ("latent", i32), ("branches", i32),
         ("eps", f32), ("cfg_text", f32), ("cfg_speaker", f32), ("rescale_k", f32), ("rescale_sigma", f32),
-        ("use_rescale", i32), ("update_x", i32), ("_pad", i32),
+        ("use_rescale", i32), ("update_x", i32), ("n_delta", i32), ("delta", c_p), ("delta_stride", i64),
     ]
 
 
@@ -93,6 +93,7 @@ EXPORTS = {
     "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),
     "echo_timestep_embedding": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p]),
     "echo_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, C.c_int, c_p, i64, c_p, i64, c_p]),
+    "echo_add_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, C.c_int, i64, c_p, c_p, i64, C.c_int, c_p, i64, c_p]),
     "echo_attention": (C.c_int, [C.POINTER(AttnDesc), c_p]),
     "echo_mask_extent": (C.c_int, [c_p, C.c_int, C.c_int, i64, c_p, c_p]),
     "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),

@@ -168,7 +168,8 @@ static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStre
 
 template <int EPI>
 int launch_legacy(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm_legacy.cu
-int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm2.cu
+int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P,
+                          int batch, cudaStream_t st);  // gemm2.cu
 
 static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
@@ -265,6 +266,7 @@ static int dispatch_bn(int bn, const GemmShape& G, const EpiParams& P, int batch
 // Tile width for the CTA-pair kernel: fewest (rounds x tile cost) over the 74 pairs; ties go to the wider tile.
 static int pick_block_n_pair(const echo_gemm_desc* d) {
   if (d->block_n) return d->block_n;
+  if (d->k_splits > 1) return d->n >= 256 ? 256 : ((d->n + 31) / 32) * 32;   // split-K callers size splits for 256-wide tiles
   static int npairs = 0;
   if (!npairs) {
     int dev = 0, sms = 0;
@@ -314,8 +316,12 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
     if (d->epilogue == ECHO_EPI_SECTIONS)
       ECHO_CHECK_ARG(d->section_width % bn == 0 && bn % d->head_dim == 0, "gemm: block_n %d does not tile sections", bn);
     if (d->epilogue == ECHO_EPI_SWIGLU) ECHO_CHECK_ARG(bn % 128 == 0, "gemm: swiglu needs block_n %% 128 == 0");
-    return echo_launch_gemm_pair(d->epilogue, bn, G, P, d->batch, st);
+    if (d->k_splits > 1)
+      ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
+                     !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
+    return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, G, P, d->batch, st);
   }
+  ECHO_CHECK_ARG(d->k_splits <= 1, "gemm: k_splits is an impl-2 feature");
   ECHO_CHECK_ARG(d->impl == 0, "gemm: unknown impl %d", d->impl);
   const int bn = pick_block_n(d);
   if (d->epilogue == ECHO_EPI_SECTIONS)

@@ -41,7 +41,9 @@ struct Tiling {
   int stages, stage_bytes; // operand ring: stage = A (16 KB) + this CTA's half of B (bn/2 rows x 128 B)
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
-  int num_tiles;          // tiles_m * tiles_n * batch
+  int num_tiles;          // work units: tiles_m * tiles_n * batch * splits
+  int splits;             // split-K: units per tile (unit index = tile * splits + split)
+  long long split_stride; // elements between the partial outputs
 };
 
 struct TmemLoader2 {
@@ -102,14 +104,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = pair; tile < T.num_tiles; tile += npairs) {
+      for (int unit = pair; unit < T.num_tiles; unit += npairs) {
+        const int tile = unit / T.splits, split = unit - tile * T.splits;
         const int mt = tile % T.tiles_m;
         const int rest = tile / T.tiles_m;
         const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
         const int m0 = mt * (2 * BM) + (int)rank * BM;
         const int n0 = nt * T.bn + (int)rank * half_n;
-        for (int kb = 0; kb < total_kb; ++kb) {
-          if (T.noload && (kb >= STAGES || tile != pair)) break;
+        const int kb0 = (int)((long long)total_kb * split / T.splits), kb1 = (int)((long long)total_kb * (split + 1) / T.splits);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          if (T.noload && (kb - kb0 >= STAGES || unit != pair)) break;
           ptx::mbar_wait(&empty_bar[s], ph ^ 1);
           const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
           uint8_t* sa = smem + s * STAGE_SZ;
@@ -129,14 +133,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       uint32_t tc = 0, ph = 0;
       int s = 0;
       bool first = true;
-      for (int tile = pair; tile < T.num_tiles; tile += npairs, ++tc) {
+      for (int unit = pair; unit < T.num_tiles; unit += npairs, ++tc) {
+        const int split = unit % T.splits;
+        const int kb0 = (int)((long long)total_kb * split / T.splits), kb1 = (int)((long long)total_kb * (split + 1) / T.splits);
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
         ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
         ptx::tc_fence_after();
         if (trace && tc < 6) trace[8 + tc * 4 + 0] = clock64();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
-        for (int kb = 0; kb < total_kb; ++kb) {
-          if (!(T.noload && (kb >= STAGES || tile != pair))) ptx::mbar_wait(&full_bar[s], ph);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          if (!(T.noload && (kb - kb0 >= STAGES || unit != pair))) ptx::mbar_wait(&full_bar[s], ph);
           ptx::tc_fence_after();
           if (trace && first) { trace[2] = clock64(); first = false; }
           const uint32_t sa = smem_u32(smem + s * STAGE_SZ);
@@ -144,7 +150,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
           if (!T.noload) ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
@@ -156,7 +162,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else {
     const int q = warp & 3;                  // TMEM lane quarter this warp may read
     uint32_t tc = 0;
-    for (int tile = pair; tile < T.num_tiles; tile += npairs, ++tc) {
+    for (int unit = pair; unit < T.num_tiles; unit += npairs, ++tc) {
+      const int tile = unit / T.splits, split = unit - tile * T.splits;
       const int mt = tile % T.tiles_m;
       const int rest = tile / T.tiles_m;
       const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
@@ -167,7 +174,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
       TmemLoader2 L{tmem_base + as * ACC_COLS + ((uint32_t)(q * 32) << 16)};
       run_epilogue_t<EPI>(T.bn, P, L, scratch + (warp - 2) * EPI_SC_FLOATS, lane, (warp - 2) >> 2, batch, m0 + q * 32,
-                          nt * T.bn);
+                          nt * T.bn, split, split * T.split_stride);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
@@ -197,7 +204,8 @@ int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint
                         const cuuint32_t* box);   // gemm.cu
 
 template <int EPI>
-static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+static int launch_pair_t(int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P, int batch,
+                         cudaStream_t st) {
   CUtensorMap ta, tb;
   {
     cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
@@ -226,7 +234,9 @@ static int launch_pair_t(int bn, const GemmShape& G, const EpiParams& P, int bat
   T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
-  T.num_tiles = T.tiles_m * T.tiles_n * batch;
+  T.splits = splits;
+  T.split_stride = split_stride;
+  T.num_tiles = T.tiles_m * T.tiles_n * batch * splits;
   const int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
   ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, G, P, T));
   ECHO_COUNT_LAUNCH();
@@ -245,14 +255,20 @@ extern "C" void echo_debug_gemm_trace(long long* device_buf) {
 }
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
-int echo_launch_gemm_pair(int epi, int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P,
+                          int batch, cudaStream_t st) {
+  if (splits < 1) splits = 1;
+  if (splits > 1 && (epi != ECHO_EPI_GENERIC || splits > G.k_blocks_per_tap * G.taps)) {
+    echo_set_error("pair gemm: k_splits %d needs the GENERIC epilogue and at least one k-block per split", splits);
+    return ECHO_ERR_UNSUPPORTED;
+  }
   if (bn < 64 || bn > 256 || bn % 32 != 0) {
     echo_set_error("pair gemm: block_n %d must be a multiple of 32 in [64, 256]", bn);
     return ECHO_ERR_UNSUPPORTED;
   }
   switch (epi) {
-    case ECHO_EPI_GENERIC: return launch_pair_t<ECHO_EPI_GENERIC>(bn, G, P, batch, st);
-    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, G, P, batch, st);
-    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, G, P, batch, st);
+    case ECHO_EPI_GENERIC: return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, G, P, batch, st);
+    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, G, P, batch, st);
+    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, G, P, batch, st);
   }
 }

@@ -35,6 +35,8 @@ struct EpiRows {
   int batch_idx, mb0, n0;
   int nrows;            // valid rows among the 32 (0..32), warp-uniform
   int half;             // 0/1: which of the two warps of this lane quarter (chunk parity it owns)
+  int split;            // split-K unit index (bias only in unit 0)
+  long long out_off;    // split * split_stride: offset of this unit's partial output
   long long mg0;        // global row index of row 0
 };
 
@@ -55,7 +57,7 @@ struct GenCtx {
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f), one4 = make_float4(1.f, 1.f, 1.f, 1.f);
     const int n = R.n0 + c + 4 * cg;
     const bool nok = n < P.n;                            // n % 8 == 0: a 4-column group is all in or all out
-    A.bias = (P.bias && nok) ? __ldg(reinterpret_cast<const float4*>(P.bias + n)) : zero4;
+    A.bias = (P.bias && nok && R.split == 0) ? __ldg(reinterpret_cast<const float4*>(P.bias + n)) : zero4;
     A.alpha = (P.out2_bf16 && nok) ? __ldg(reinterpret_cast<const float4*>(P.snake_alpha + n)) : one4;
     A.glo = one4; A.ghi = one4;
     if (P.gate && nok && gate_fast) {
@@ -111,7 +113,7 @@ struct GenCtx {
 #pragma unroll
     for (int i = 0; i < 8; ++i) { x[i].x += A.rv[i].x; x[i].y += A.rv[i].y; x[i].z += A.rv[i].z; x[i].w += A.rv[i].w; }
     if (P.out_f32) {
-      float* o = P.out_f32 + R.mg0 * P.ld_out_f32 + n;
+      float* o = P.out_f32 + R.out_off + R.mg0 * P.ld_out_f32 + n;
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         if (nok && 4 * i + rsub < R.nrows) *reinterpret_cast<float4*>(o + (long long)(4 * i + rsub) * P.ld_out_f32) = x[i];
@@ -286,9 +288,9 @@ __device__ __forceinline__ void epi_t_swiglu(const int BN, const EpiParams& P, L
 
 template <int EPI, class Loader>
 __device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
-                                               int batch_idx, int mb0, int n0) {
+                                               int batch_idx, int mb0, int n0, int split = 0, long long out_off = 0) {
   EpiRows R;
-  R.batch_idx = batch_idx; R.mb0 = mb0; R.n0 = n0; R.half = half;
+  R.batch_idx = batch_idx; R.mb0 = mb0; R.n0 = n0; R.half = half; R.split = split; R.out_off = out_off;
   R.nrows = min(32, max(0, P.rows - mb0));
   R.mg0 = (long long)batch_idx * P.rows + mb0;
   if (EPI == ECHO_EPI_GENERIC) epi_t_generic(BN, P, L, sc, lane, R);

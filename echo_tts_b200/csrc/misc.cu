@@ -32,7 +32,9 @@ extern "C" void echo_reset_launch_count(void) { g_echo_launches = 0; }
 // ---------------------------------------------------------------------------------------------
 template <int VEC_ITERS>
 __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restrict__ x, long long ldx, int m, int d,
-                                                          float eps, const float* __restrict__ scale1,
+                                                          float eps, const float* __restrict__ delta, int n_delta,
+                                                          long long delta_stride, float* __restrict__ x_out,
+                                                          const float* __restrict__ scale1,
                                                           const float* __restrict__ shift, long long mod_ld,
                                                           int rows_per_mod, const int* __restrict__ step,
                                                           long long mod_step_stride, bf16* __restrict__ y,
@@ -49,10 +51,31 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
 #pragma unroll
   for (int i = 0; i < VEC_ITERS; ++i) {
     const int c = lane + i * 32;
-    if (c < nvec) {
-      v[i] = xr[c];
-      ssq += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+    if (c < nvec) v[i] = xr[c];
+  }
+  if (n_delta > 0) {   // deferred residual update: x += sum of the split-K partial outputs (fixed order), written back
+    for (int s = 0; s < n_delta; ++s) {
+      const float4* dr = reinterpret_cast<const float4*>(delta + s * delta_stride + (long long)row * ldx);
+#pragma unroll
+      for (int i = 0; i < VEC_ITERS; ++i) {
+        const int c = lane + i * 32;
+        if (c < nvec) {
+          const float4 dv = dr[c];
+          v[i].x += dv.x; v[i].y += dv.y; v[i].z += dv.z; v[i].w += dv.w;
+        }
+      }
     }
+    float4* xo = reinterpret_cast<float4*>(x_out + (long long)row * ldx);
+#pragma unroll
+    for (int i = 0; i < VEC_ITERS; ++i) {
+      const int c = lane + i * 32;
+      if (c < nvec) xo[c] = v[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < VEC_ITERS; ++i) {
+    const int c = lane + i * 32;
+    if (c < nvec) ssq += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
   }
   ssq = warp_sum(ssq);
   const float rstd = rsqrtf(ssq / (float)d + eps);
@@ -76,23 +99,38 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
   }
 }
 
-extern "C" int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float eps, const float* scale1,
-                                const float* shift, int64_t mod_ld, int rows_per_mod, const int32_t* step,
-                                int64_t mod_step_stride, void* y, int64_t ldy, echo_stream_t stream) {
+static int launch_rmsnorm(const float* x, int64_t ldx, int m, int d, float eps, const float* delta, int n_delta,
+                          int64_t delta_stride, float* x_out, const float* scale1, const float* shift, int64_t mod_ld,
+                          int rows_per_mod, const int32_t* step, int64_t mod_step_stride, void* y, int64_t ldy,
+                          echo_stream_t stream) {
   ECHO_CHECK_ARG(x && scale1 && y && m > 0, "rmsnorm: null argument");
+  ECHO_CHECK_ARG(n_delta >= 0 && (n_delta == 0 || (delta && x_out && delta_stride % 4 == 0)), "rmsnorm: bad delta arguments");
   ECHO_CHECK_ARG(d % 4 == 0 && d <= 4096 && ldx % 4 == 0 && ldy % 4 == 0 && mod_ld % 4 == 0, "rmsnorm: d must be <=4096, %%4");
   if (rows_per_mod <= 0) rows_per_mod = 1 << 30;
   dim3 grid(ceil_div(m, 8));
   cudaStream_t st = (cudaStream_t)stream;
   if (d <= 1024)
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<8>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<8>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else if (d <= 2048)
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<16>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<16>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<32>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<32>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
+}
+
+extern "C" int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float eps, const float* scale1,
+                                const float* shift, int64_t mod_ld, int rows_per_mod, const int32_t* step,
+                                int64_t mod_step_stride, void* y, int64_t ldy, echo_stream_t stream) {
+  return launch_rmsnorm(x, ldx, m, d, eps, nullptr, 0, 0, nullptr, scale1, shift, mod_ld, rows_per_mod, step, mod_step_stride,
+                        y, ldy, stream);
+}
+extern "C" int echo_add_rmsnorm_mod(float* x, int64_t ldx, int m, int d, float eps, const float* delta, int n_delta,
+                                    int64_t delta_stride, const float* scale1, const float* shift, int64_t mod_ld,
+                                    int rows_per_mod, void* y, int64_t ldy, echo_stream_t stream) {
+  return launch_rmsnorm(x, ldx, m, d, eps, delta, n_delta, delta_stride, x, scale1, shift, mod_ld, rows_per_mod, nullptr, 0, y,
+                        ldy, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -26,17 +26,23 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
       for (int c = lane; c < nvec; c += 32) dst[c] = make_float4(0.f, 0.f, 0.f, 0.f);
       continue;
     }
-    const float4* src = reinterpret_cast<const float4*>(D.h + ((long long)br * D.positions + p) * D.ldh);
+    const long long roff = ((long long)br * D.positions + p) * D.ldh;
+    const float4* src = reinterpret_cast<const float4*>(D.h + roff);
     float ssq = 0.f;
     for (int c = lane; c < nvec; c += 32) {
-      const float4 v = src[c];
+      float4 v = src[c];
+      for (int s = 0; s < D.n_delta; ++s) {   // deferred residual update of the last projection (fixed order)
+        const float4 dv = reinterpret_cast<const float4*>(D.delta + s * D.delta_stride + roff)[c];
+        v.x += dv.x; v.y += dv.y; v.z += dv.z; v.w += dv.w;
+      }
+      dst[c] = v;
       ssq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     ssq = warp_sum(ssq);
     const float rstd = rsqrtf(ssq / (float)D.d + D.eps);
     const float4* nw = reinterpret_cast<const float4*>(D.norm_w);
     for (int c = lane; c < nvec; c += 32) {
-      const float4 v = src[c], w = __ldg(nw + c);
+      const float4 v = dst[c], w = __ldg(nw + c);
       dst[c] = make_float4(v.x * rstd * w.x, v.y * rstd * w.y, v.z * rstd * w.z, v.w * rstd * w.w);
     }
   }
@@ -109,6 +115,7 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
   ECHO_CHECK_ARG(d->d % 4 == 0 && d->ldh % 4 == 0 && d->positions > 0 && d->latent > 0, "tail: bad shape");
   ECHO_CHECK_ARG(!d->update_x || (d->x_t && d->sched), "tail: x_t/sched required when update_x");
   ECHO_CHECK_ARG(d->update_x || d->v_out || d->v_comb_out, "tail: nothing to write");
+  ECHO_CHECK_ARG(d->n_delta >= 0 && (d->n_delta == 0 || (d->delta && d->delta_stride % 4 == 0)), "tail: bad delta arguments");
   const size_t smem = ((size_t)d->branches * PP * (d->d + d->latent)) * sizeof(float);
   static size_t configured = 0;
   if (smem > configured) {

@@ -272,17 +272,28 @@ class EchoDiT:
         if ws is None:
             cfg, dev = self.cfg, self._device
             M, D = rows * S, cfg.model_size
+            ns = self.k_splits(M)
             ws = dict(x=torch.empty((M, D), device=dev, dtype=F32), xn=torch.empty((M, D), device=dev, dtype=BF16),
+                      delta=(torch.empty((ns, M, D), device=dev, dtype=F32) if ns > 1 else None),
                       qkvg=torch.empty((4, M, D), device=dev, dtype=BF16), ao=torch.empty((M, D), device=dev, dtype=BF16),
                       h=torch.empty((M, cfg.intermediate_size), device=dev, dtype=BF16))
             self._ws[key] = ws
         return ws
 
+    def k_splits(self, M: int) -> int:
+        """Split-K factor for the two N = model_size projections (wo, w2) of a forward over M tokens: with few tokens
+        (one un-guided row of 640) a 256 x 256 tiling leaves most of the 74 CTA pairs idle, so the K loop is split
+        over enough work units to fill them; the partial products are summed by the next norm kernel."""
+        tiles = -(-M // 256) * -(-self.cfg.model_size // 256)
+        return max(1, min(4, 74 // tiles, self.cfg.model_size // 64))
+
     def forward_hidden(self, x_in: torch.Tensor, mod: torch.Tensor, B: int, *, text_mask, text_extent, spk_mask,
                        spk_extent, kv_text: KVCache, kv_speaker: KVCache, kv_latent: Optional[KVCache] = None,
                        start_pos: int = 0, n_prefix: int = 0, spk_scale: Optional[torch.Tensor] = None,
-                       x_rows: Optional[int] = None) -> torch.Tensor:
-        """x_in fp32 [x_rows*S... see below] -> final residual stream fp32 [R*S, D].
+                       x_rows: Optional[int] = None):
+        """x_in fp32 [x_rows*S... see below] -> (final residual stream fp32 [R*S, D], pending delta or None): when
+        the forward runs split-K the last w2's partial products [splits, R*S, D] are still to be added to the stream
+        (the sampler tail does it).
 
         x_in: [Bx, S, latent] fp32 with Bx == R (one input per row) or Bx == B (CFG: the three branches
         share x_t, inference.py:516 -- in_proj is evaluated once per prompt and broadcast).
@@ -296,7 +307,8 @@ class EchoDiT:
         R = text_mask.shape[0]
         M = R * S
         ws = self.workspace(R, S)
-        x, xn, qkvg, ao, hmid = ws["x"], ws["xn"], ws["qkvg"], ws["ao"], ws["h"]
+        x, xn, qkvg, ao, hmid, delta = ws["x"], ws["xn"], ws["qkvg"], ws["ao"], ws["h"], ws["delta"]
+        pending = None          # split-K partial products not yet added to x
         # in_proj (fp32, model.py:586); for CFG rows the same [B*S, D] result is written to all three branches
         xin2 = x_in.reshape(Bx * S, lat)
         reps = R // Bx
@@ -308,7 +320,7 @@ class EchoDiT:
         mod_ld = mod.stride(0)
         kv_mod = lambda c: (B if c[0][0].shape[0] != R else 0)
         for l, lw in enumerate(self.layers):
-            ops.rmsnorm_mod(x, mod[0, l, 0, 1], mod[0, l, 0, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
+            ops.rmsnorm_mod(x, mod[0, l, 0, 1], mod[0, l, 0, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld, delta=pending)
             ops.gemm_sections(xn, lw["qkvg"],
                               [(L.SEC_NORM_ROPE, qkvg[0], lw["qn"]), (L.SEC_NORM_ROPE, qkvg[1], lw["kn"]),
                                (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
@@ -323,11 +335,18 @@ class EchoDiT:
             segs.append(ops.Segment(kv_speaker[l][0], kv_speaker[l][1], kv_batch_mod=kv_mod(kv_speaker), mask=spk_mask,
                                     extent=spk_extent, kv_scale=(spk_scale[l:l + 1] if spk_scale is not None else None)))
             ops.attention(qkvg[0].view(R, S, H, 128), segs, ao, gate=qkvg[3])
-            ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
-            ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
-            ops.gemm_swiglu(xn, lw["w13"], hmid)
-            ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
-        return x
+            if delta is None:
+                ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
+                ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
+                ops.gemm_swiglu(xn, lw["w13"], hmid)
+                ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
+            else:   # few tokens: split-K projections, residual update deferred into the next norm kernel
+                ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, split_out=delta)
+                ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld, delta=delta)
+                ops.gemm_swiglu(xn, lw["w13"], hmid)
+                ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, split_out=delta)
+                pending = delta
+        return x, pending
 
     @torch.inference_mode()
     def __call__(self, x, t, text_mask, speaker_mask, kv_cache_text, kv_cache_speaker, start_pos=None,
@@ -344,13 +363,13 @@ class EchoDiT:
         if kv_cache_latent is not None and kv_cache_latent[0][0].shape[1] > 0:
             n_prefix = min(kv_cache_latent[0][0].shape[1], -(-start_pos // cfg.speaker_patch_size))
         Bkv = kv_cache_text[0][0].shape[0]
-        h = self.forward_hidden(x.to(dev).float().contiguous(), mod, Bkv, text_mask=tm, text_extent=ops.mask_extent(tm),
+        h, pending = self.forward_hidden(x.to(dev).float().contiguous(), mod, Bkv, text_mask=tm, text_extent=ops.mask_extent(tm),
                                 spk_mask=sm, spk_extent=ops.mask_extent(sm), kv_text=kv_cache_text,
                                 kv_speaker=kv_cache_speaker, kv_latent=kv_cache_latent, start_pos=start_pos,
                                 n_prefix=n_prefix)
         v = torch.empty((R * S, lat), device=dev, dtype=F32)
         ops.cfg_euler_tail(h, self.out_norm, self.out_w, self.out_b, positions=R * S, branches=1, eps=cfg.norm_eps,
-                           v_out=v, update_x=False)
+                           v_out=v, update_x=False, delta=pending)
         return v.view(R, S, lat)
 
     forward = __call__

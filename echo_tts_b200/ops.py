@@ -48,10 +48,18 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
 
 def gemm_generic(a, w, *, taps=(0,), batch=1, bias=None, act=L.ACT_NONE, gate=None, rows_per_gate=0,
                  resid=None, out_f32=None, out_bf16=None, out2_bf16=None, snake_alpha=None,
-                 impl=None, block_n=0) -> None:
+                 impl=None, block_n=0, split_out=None) -> None:
+    """``split_out``: fp32 [S, M, N] -> split-K over S work units per tile; unit s writes its partial (gated) product to
+    split_out[s]; the consumer (rmsnorm_mod / cfg_euler_tail ``delta=``) adds them to the residual stream."""
     d = _base_gemm(a, w, taps, batch, impl, block_n)
     d.epilogue, d.act = L.EPI_GENERIC, act
     M, N = a.shape[0], w.shape[0]
+    if split_out is not None:
+        _need(split_out, F32, "split_out")
+        assert split_out.dim() == 3 and split_out.shape[1:] == (M, N) and split_out.is_contiguous()
+        assert resid is None and out_f32 is None and out_bf16 is None and out2_bf16 is None and act == L.ACT_NONE
+        d.k_splits, d.split_stride = split_out.shape[0], split_out.stride(0)
+        out_f32 = split_out[0]
     if bias is not None:
         _need(bias, F32, "bias"); assert bias.numel() == N
         d.bias = bias.data_ptr()
@@ -170,10 +178,18 @@ def timestep_embedding(t: torch.Tensor, size: int) -> torch.Tensor:
 
 def rmsnorm_mod(x: torch.Tensor, scale1: torch.Tensor, shift: Optional[torch.Tensor], y: torch.Tensor, eps: float,
                 rows_per_mod: int = 0, mod_ld: int = 0, step: Optional[torch.Tensor] = None,
-                mod_step_stride: int = 0) -> None:
-    """x fp32 [M, d] -> y bf16 [M, d]; scale1/shift point at table row 0 (row g at g*mod_ld)."""
+                mod_step_stride: int = 0, delta: Optional[torch.Tensor] = None) -> None:
+    """x fp32 [M, d] -> y bf16 [M, d]; scale1/shift point at table row 0 (row g at g*mod_ld).
+    ``delta`` fp32 [S, M, d]: x += delta.sum(0) first (deferred residual update, x written back)."""
     _need(x, F32, "x"); _need(y, BF16, "y"); _need(scale1, F32, "scale1")
     M, d = x.shape
+    if delta is not None:
+        _need(delta, F32, "delta")
+        assert delta.dim() == 3 and delta.shape[1:] == (M, d) and delta.is_contiguous() and x.stride(0) == d and step is None
+        L.check(L.load().echo_add_rmsnorm_mod(x.data_ptr(), x.stride(0), M, d, eps, delta.data_ptr(), delta.shape[0],
+                                              delta.stride(0), scale1.data_ptr(), L.ptr(shift), mod_ld, rows_per_mod,
+                                              y.data_ptr(), y.stride(0), L.stream()))
+        return
     L.check(L.load().echo_rmsnorm_mod(x.data_ptr(), x.stride(0), M, d, eps, scale1.data_ptr(), L.ptr(shift), mod_ld,
                                       rows_per_mod, L.ptr(step), mod_step_stride, y.data_ptr(), y.stride(0),
                                       L.stream()))
@@ -242,9 +258,13 @@ def mask_extent(mask: torch.Tensor) -> torch.Tensor:
 
 def cfg_euler_tail(h, norm_w, w_out, b_out, *, positions, branches, eps, x_t=None, sched=None, step=None,
                    cfg_text=0.0, cfg_speaker=0.0, rescale_k=None, rescale_sigma=None, v_out=None, v_comb_out=None,
-                   update_x=True) -> None:
+                   update_x=True, delta=None) -> None:
     _need(h, F32, "h")
     d = L.TailDesc()
+    if delta is not None:
+        _need(delta, F32, "delta")
+        assert delta.dim() == 3 and delta.shape[1:] == h.shape and delta.is_contiguous() and h.is_contiguous()
+        d.delta, d.n_delta, d.delta_stride = delta.data_ptr(), delta.shape[0], delta.stride(0)
     d.h, d.ldh = h.data_ptr(), h.stride(0)
     d.norm_w, d.w_out, d.b_out = norm_w.data_ptr(), w_out.data_ptr(), b_out.data_ptr()
     d.x_t, d.v_out, d.v_comb_out = L.ptr(x_t), L.ptr(v_out), L.ptr(v_comb_out)

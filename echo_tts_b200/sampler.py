@@ -77,7 +77,7 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
     use_rescale = p["rescale_k"] is not None and p["rescale_sigma"] is not None
     for i, has_cfg in enumerate(plan.has_cfg):
         R = 3 * B if has_cfg else B
-        h = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[:R], text_extent=te3[:R], spk_mask=sm3[:R],
+        h, pending = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[:R], text_extent=te3[:R], spk_mask=sm3[:R],
                                  spk_extent=se3[:R], kv_text=kv_text, kv_speaker=kv_spk, kv_latent=kv_latent,
                                  start_pos=start_pos, n_prefix=n_prefix,
                                  spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
@@ -89,7 +89,8 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
         ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=(3 if has_cfg else 1),
                            eps=cfg.norm_eps, x_t=x_t, sched=plan.sched[i], cfg_text=p["cfg_scale_text"],
                            cfg_speaker=p["cfg_scale_speaker"], rescale_k=p["rescale_k"] if use_rescale else None,
-                           rescale_sigma=p["rescale_sigma"] if use_rescale else None, v_out=v_out, v_comb_out=v_comb)
+                           rescale_sigma=p["rescale_sigma"] if use_rescale else None, v_out=v_out, v_comb_out=v_comb,
+                           delta=pending)
         if trace is not None:
             trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
 

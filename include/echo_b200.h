@@ -58,7 +58,10 @@ typedef struct echo_gemm_desc {
   const float* gate;
   int64_t gate_ld;
   int32_t rows_per_gate;
-  int32_t _pad0;
+  int32_t k_splits;         /* impl 2, GENERIC only: > 1 splits the K loop over k_splits work units per tile; unit s writes
+                             * its partial result (bias only in unit 0; act must be NONE, resid NULL) to
+                             * out_f32 + s * split_stride -- the consumer (echo_rmsnorm_mod / echo_cfg_euler_tail `delta`
+                             * arguments) sums them in a fixed order, so the result is deterministic.  0 or 1 = off. */
   const float* resid;
   int64_t ld_resid;
   float* out_f32;
@@ -79,6 +82,7 @@ typedef struct echo_gemm_desc {
   const float* rope_sin;
   int64_t ld_sec_out;
   echo_gemm_section sections[4];
+  int64_t split_stride;     /* elements between the k_splits partial outputs */
   /* SWIGLU: B rows interleaved in groups of 64 (w1 | w3); out_bf16[m, j] = silu(a)*b (model.py:308) */
 } echo_gemm_desc;
 
@@ -124,6 +128,12 @@ int echo_timestep_embedding(const float* t, int n, int size, float* out, echo_st
 int echo_rmsnorm_mod(const float* x, int64_t ldx, int m, int d, float eps, const float* scale1,
                      const float* shift, int64_t mod_ld, int rows_per_mod, const int32_t* step,
                      int64_t mod_step_stride, void* y_bf16, int64_t ldy, echo_stream_t stream);
+/* Same, preceded by the deferred residual update x[m, :] += sum_s delta[s * delta_stride + m * ldx + :] (the split-K
+ * partial outputs of the previous projection, already multiplied by the AdaLN gate: model.py:385, 388); x is
+ * updated in place.  n_delta = 0 is echo_rmsnorm_mod. */
+int echo_add_rmsnorm_mod(float* x, int64_t ldx, int m, int d, float eps, const float* delta, int n_delta,
+                         int64_t delta_stride, const float* scale1, const float* shift, int64_t mod_ld,
+                         int rows_per_mod, void* y_bf16, int64_t ldy, echo_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Flash-style attention over up to four KV segments walked in place (no concat):
@@ -182,7 +192,9 @@ typedef struct echo_tail_desc {
   float eps, cfg_text, cfg_speaker, rescale_k, rescale_sigma;
   int32_t use_rescale;
   int32_t update_x;         /* 0: only write velocities (model.__call__ compatibility path) */
-  int32_t _pad;
+  int32_t n_delta;          /* deferred residual update of the last projection: h += sum_s delta[s * delta_stride + ...] */
+  const float* delta;       /* fp32 [n_delta][rows][ldh] or NULL */
+  int64_t delta_stride;
 } echo_tail_desc;
 int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream);
 int echo_step_advance(int32_t* step, echo_stream_t stream); /* step[0] += 1 */

@@ -127,6 +127,25 @@ def test_gemm_sections_norm_rope(ops, L, impl, hd, H, rope_heads):
         assert rel_l2(got.float().cpu(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("M,N,K,S", [(640, 2048, 5888, 3), (640, 2048, 2048, 3), (100, 256, 256, 4), (300, 512, 1024, 2)])
+def test_gemm_split_k_deferred_residual(ops, M, N, K, S):
+    """split-K partial products (gated) + the fused add-norm that consumes them == the one-pass residual GEMM."""
+    a, w = _rand((M, K), 40, dtype=BF16), _rand((N, K), 41, K ** -0.5, BF16)
+    gate, x0 = _rand((1, N), 42), _rand((M, N), 43)
+    sc1, sh = _rand((N,), 44) + 1.0, _rand((N,), 45)
+    parts = torch.full((S, M, N), float("nan"), device="cuda", dtype=F32)
+    ops.gemm_generic(a, w, gate=gate, split_out=parts)
+    ref_delta = (a.float() @ w.float().t()) * gate
+    assert rel_l2(parts.sum(0), ref_delta) < 2e-5
+    x = x0.clone()
+    y = torch.empty((M, N), device="cuda", dtype=BF16)
+    ops.rmsnorm_mod(x, sc1, sh, y, 1e-5, delta=parts)
+    xr = x0 + ref_delta
+    assert rel_l2(x, xr) < 2e-5
+    ref = xr * torch.rsqrt(xr.pow(2).mean(-1, keepdim=True) + 1e-5) * sc1 + sh
+    assert rel_l2(y.float(), ref) < 3e-3
+
+
 def test_sgemm_and_batched(ops, L):
     a, w, b, add = _rand((70, 100), 21), _rand((90, 100), 22), _rand((90,), 23), _rand((70, 90), 24)
     out = torch.empty((70, 90), device="cuda")

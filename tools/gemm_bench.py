@@ -63,6 +63,18 @@ def main():
         def f_wo(i):
             ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x)
 
+        ns = max(1, min(4, 74 // (-(-M // 256) * 8)))
+        parts = torch.empty((ns, M, D), device="cuda")
+
+        def f_wo_split(i):
+            ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, split_out=parts)
+
+        def f_w2_split(i):
+            ops.gemm_generic(hm, W["w2"][i % nw], gate=gate, rows_per_gate=S, split_out=parts)
+
+        def f_addnorm(i):
+            ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0), delta=parts)
+
         def f_w13(i):
             ops.gemm_swiglu(xn, W["w13"][i % nw], hmid)
 
@@ -83,6 +95,9 @@ def main():
         cases = [("qkvg", f_qkvg, 2.0 * M * 4 * D * D), ("wo", f_wo, 2.0 * M * D * D), ("w13", f_w13, 2.0 * M * 2 * F_ * D),
                  ("w2", f_w2, 2.0 * M * D * F_), ("attn", f_attn, sum(4.0 * S * lv * D for lv in valid)),
                  ("norm", f_norm, 0.0)]
+        if ns > 1:
+            cases += [(f"wo/s{ns}", f_wo_split, 2.0 * M * D * D), (f"w2/s{ns}", f_w2_split, 2.0 * M * D * F_),
+                      ("addnorm", f_addnorm, 0.0)]
         tot_us, tot_fl = 0.0, 0.0
         for name, fn, fl in cases:
             if args.only and name not in args.only.split(","):

@@ -41,7 +41,10 @@ def main():
                                        head_dim=128, rope_heads=H // 2, rope=rope, rows_per_seq=S, eps=1e-5),
         wo=lambda: ops.gemm_generic(xn, W["wo"], gate=gate, rows_per_gate=S, resid=x, out_f32=x),
         w13=lambda: ops.gemm_swiglu(xn, W["w13"], hmid),
-        w2=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, resid=x, out_f32=x))
+        w2=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, resid=x, out_f32=x),
+        wo_split=lambda: ops.gemm_generic(xn, W["wo"], gate=gate, rows_per_gate=S, split_out=parts),
+        w2_split=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, split_out=parts))
+    parts = torch.empty((3, M, D), device="cuda")
     buf = torch.zeros((512, 32), device="cuda", dtype=torch.int64)
     for name in args.case.split(","):
         fn = fns[name]
