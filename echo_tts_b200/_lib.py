@@ -90,6 +90,7 @@ EXPORTS = {
     "echo_reset_launch_count": (None, []),
     "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
     "echo_debug_gemm_trace": (None, [c_p]),
+    "echo_debug_attn_trace": (None, [c_p]),
     "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),
     "echo_timestep_embedding": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p]),
     "echo_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, C.c_int, c_p, i64, c_p, i64, c_p]),

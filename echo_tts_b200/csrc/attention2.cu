@@ -35,7 +35,9 @@ struct AttnSeg {
   const float* kv_scale;
 };
 struct AttnParams {
+  long long* trace;      // nullptr unless tracing: [cta][64] clock64 stamps
   int rows, seq, heads, n_seg;
+  int static_first;      // segment 0 has no mask / extent and len > 0: tile 0 is known before the tile list is built
   float softmax_scale;
   const bf16* gate;
   bf16* out;
@@ -100,8 +102,18 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_4d(const void* tmap, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit_wait() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
 
-struct Maps { CUtensorMap q, k[4], v[4]; };
+struct Maps { CUtensorMap q, k[4], v[4], gate, out; };
+static long long* g_attn_trace = nullptr;   // debug timeline, see echo_debug_attn_trace
 
 __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_constant__ Maps M,
                                                               const __grid_constant__ AttnParams A) {
@@ -119,47 +131,100 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   uint64_t* s_full = bars + 9;        // 2
   uint64_t* p_full = bars + 11;       // 2
   uint64_t* pv_done = bars + 13;      // 2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
-  int* s_ntiles = reinterpret_cast<int*>(bars + 16);
+  uint64_t* g_full = bars + 15;       // 1: gate tile landed in the (drained) K ring
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  int* s_ntiles = reinterpret_cast<int*>(bars + 17);
   TileInfo* tiles = reinterpret_cast<TileInfo*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * QT, head = blockIdx.y, row = blockIdx.z;
+  long long* const trace = A.trace ? A.trace + ((long long)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 64 : nullptr;
+  if (trace && tid == 0) trace[0] = clock64();
   pdl_launch_dependents();
 
-  // ---- tile list: every 64-key tile any query of this row can see, with its key-valid bits -------------------
+  // ---- tile list: every 64-key tile any query of this row can see, with its key-valid bits.  Two memory round
+  //      trips for the whole CTA: all extents, then one tile per lane with 16-byte mask loads. ---------------------
   if (warp == 0) {
     pdl_wait();            // extents / masks may come from the previous kernel
-    int nt = 0;
-    for (int sgi = 0; sgi < A.n_seg; ++sgi) {
+    if (trace && tid == 0) trace[2] = clock64();
+    // extents and mask bytes are loaded together: lanes walk the POTENTIAL tiles (from the static segment lengths),
+    // then tiles with no visible key are squeezed out with a ballot (order preserved)
+    int ext_l = 0x7fffffff;
+    if (lane < A.n_seg && A.seg[lane].extent) ext_l = A.seg[lane].extent[row];
+    int pbase[5];
+    pbase[0] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pbase[i + 1] = pbase[i] + (i < A.n_seg ? (max(A.seg[i].len, 0) + KT - 1) / KT : 0);
+    int nkept = 0;
+    if (trace && tid == 0) trace[56] = clock64() + (ext_l & 1) - (ext_l & 1);
+    for (int g0 = 0; g0 < pbase[4]; g0 += 32) {
+      const int g = g0 + lane;
+      const bool in = g < pbase[4];
+      const int sgi = in ? (g >= pbase[1]) + (g >= pbase[2]) + (g >= pbase[3]) : 0;
+      const int b0 = sgi == 0 ? 0 : (sgi == 1 ? pbase[1] : (sgi == 2 ? pbase[2] : pbase[3]));
       const AttnSeg& sg = A.seg[sgi];
-      const int ext = sg.extent ? min(sg.extent[row], sg.len) : sg.len;
-      for (int key0 = 0; key0 < ext && nt < MAX_TILES; key0 += KT, ++nt) {
-        // lane handles keys key0 + lane and key0 + 32 + lane
-        bool v0 = key0 + lane < ext, v1 = key0 + 32 + lane < ext;
-        if (sg.mask) {
-          const uint8_t* mrow = sg.mask + (long long)row * sg.mask_stride + key0;
-          if (v0) v0 = mrow[lane] != 0;
-          if (v1) v1 = mrow[32 + lane] != 0;
+      const int key0 = (g - b0) * KT;
+      unsigned long long mbits = ~0ull;
+      if (in && sg.mask) {
+        // 64 mask bytes -> 64 bits.  One path for aligned and ragged rows (the 53-key speaker segment): 17 aligned
+        // 32-bit loads, all in flight together, realigned with funnel shifts; words wholly outside the row are not
+        // read (an aligned word holding one valid byte cannot leave the allocation).
+        const uint8_t* mrow = sg.mask + (long long)row * sg.mask_stride + key0;
+        const int nvalid = min(sg.len - key0, 64);
+        const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(mrow) & 3);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(mrow - mis);
+        uint32_t w[17];
+#pragma unroll
+        for (int i = 0; i < 17; ++i) w[i] = (i * 4 < (int)mis + nvalid) ? wp[i] : 0u;
+        uint32_t bits[2] = {0u, 0u};
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const uint32_t v = __funnelshift_r(w[i], w[i + 1], mis * 8);
+          const uint32_t nz = (((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v) & 0x80808080u;   // bit 7 of every non-zero byte
+          bits[i >> 3] |= ((((nz >> 7) * 0x01020408u) >> 24) & 0xfu) << ((i & 7) * 4);
         }
-        const unsigned lo = __ballot_sync(0xffffffffu, v0), hi = __ballot_sync(0xffffffffu, v1);
-        if (lane == 0) {
-          tiles[nt].seg = sgi; tiles[nt].key0 = key0;
-          tiles[nt].valid = ((unsigned long long)hi << 32) | lo;
-        }
+        mbits = ((unsigned long long)bits[1] << 32) | bits[0];
+        if (nvalid < 64) mbits &= (1ull << nvalid) - 1ull;
       }
+      const int e = min(__shfl_sync(0xffffffffu, ext_l, sgi), sg.len);
+      const unsigned long long valid =
+          (!in || e <= key0) ? 0ull : (mbits & ((e - key0 >= 64) ? ~0ull : ((1ull << (e - key0)) - 1ull)));
+      const unsigned keep = __ballot_sync(0xffffffffu, valid != 0ull);
+      if (valid != 0ull) {
+        const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
+        tiles[pos].seg = sgi; tiles[pos].key0 = key0; tiles[pos].valid = valid;
+      }
+      nkept += __popc(keep);
     }
-    if (lane == 0) *s_ntiles = nt;
+    if (lane == 0) *s_ntiles = nkept;
+    if (trace && tid == 0) trace[3] = clock64();
   }
   if (warp == 4 && lane == 0) {
     ptx::prefetch_tensormap(&M.q);
+    ptx::prefetch_tensormap(&M.k[0]);
+    ptx::prefetch_tensormap(&M.v[0]);
     ptx::mbar_init(q_full, 1);
+    ptx::mbar_init(g_full, 1);
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&k_empty[i], 1);
       ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&v_empty[i], 1);
       ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 128); ptx::mbar_init(&pv_done[i], 1);
     }
     ptx::fence_barrier_init();
+    if (A.static_first) {
+      // Q and the first K / V tile do not depend on the tile list: put them in flight under the rest of the set-up.
+      pdl_wait();
+      const int kvrow = A.seg[0].kv_batch_mod > 0 ? row % A.seg[0].kv_batch_mod : row;
+      ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+      tma_load_4d(sQ, &M.q, q_full, 0, head, q0, row);
+      tma_load_4d(sQ + Q_BYTES / 2, &M.q, q_full, 64, head, q0, row);
+      ptx::mbar_arrive_expect_tx(&k_full[0], KV_BYTES);
+      tma_load_4d(sK, &M.k[0], &k_full[0], 0, head, 0, kvrow);
+      tma_load_4d(sK + KV_BYTES / 2, &M.k[0], &k_full[0], 64, head, 0, kvrow);
+      ptx::mbar_arrive_expect_tx(&v_full[0], KV_BYTES);
+      tma_load_4d(sV, &M.v[0], &v_full[0], 0, head, 0, kvrow);
+      tma_load_4d(sV + KV_BYTES / 2, &M.v[0], &v_full[0], 64, head, 0, kvrow);
+    }
   }
   if (warp == 5) {
     ptx::tmem_alloc(tmem_slot, TM_COLS);
@@ -171,13 +236,17 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   const uint32_t tmem_base = *tmem_slot;
   const int ntiles = *s_ntiles;
   pdl_wait();
+  if (trace && tid == 0) trace[1] = clock64();
 
   if (warp == 4) {
     // ===== TMA producer =====
     if (lane == 0 && ntiles > 0) {
-      ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
-      tma_load_4d(sQ, &M.q, q_full, 0, head, q0, row);
-      tma_load_4d(sQ + Q_BYTES / 2, &M.q, q_full, 64, head, q0, row);
+      const bool early = A.static_first != 0;     // Q, K(0), V(0) already in flight
+      if (!early) {
+        ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
+        tma_load_4d(sQ, &M.q, q_full, 0, head, q0, row);
+        tma_load_4d(sQ + Q_BYTES / 2, &M.q, q_full, 64, head, q0, row);
+      }
       auto load_k = [&](int j) {
         const int s = j & 1;
         const uint32_t ph = (j >> 1) & 1;
@@ -198,77 +267,104 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
         tma_load_4d(sV + s * KV_BYTES, &M.v[t.seg], &v_full[s], 0, head, t.key0, kvrow);
         tma_load_4d(sV + s * KV_BYTES + KV_BYTES / 2, &M.v[t.seg], &v_full[s], 64, head, t.key0, kvrow);
       };
-      if (ntiles > 0) load_k(0);
+      if (!early) load_k(0);
       for (int j = 0; j < ntiles; ++j) {      // K runs one tile ahead of V
         if (j + 1 < ntiles) load_k(j + 1);
-        load_v(j);
+        if (j > 0 || !early) load_v(j);
+      }
+      if (A.gate) {
+        // every QK^T has been issued: once the last one per stage retires, the K ring (32 KB) is free to take this
+        // CTA's [128 x 128] gate tile, which then doubles as the staging buffer of the output TMA store
+        const int jl = ntiles - 1;
+        ptx::mbar_wait(&k_empty[jl & 1], (jl >> 1) & 1);
+        if (jl > 0) ptx::mbar_wait(&k_empty[(jl - 1) & 1], ((jl - 1) >> 1) & 1);
+        ptx::mbar_arrive_expect_tx(g_full, Q_BYTES);
+        tma_load_4d(sK, &M.gate, g_full, 0, head, q0, row);
+        tma_load_4d(sK + Q_BYTES / 2, &M.gate, g_full, 64, head, q0, row);
       }
     }
     __syncwarp();
   } else if (warp == 5) {
-    // ===== MMA issuer =====
-    if (lane == 0 && ntiles > 0) {
+    // ===== MMA issuer: whole warp converged, one elected lane waits and issues =====
+    if (ntiles > 0) {
       constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(QT, KT);                    // 128 x 64, both K-major
       constexpr uint32_t idesc_o = ptx::umma_idesc_bf16(QT, HD) | (1u << 16);       // 128 x 128, B (= V) MN-major
       const uint32_t q_addr = smem_u32(sQ);
       auto issue_s = [&](int j) {
         const int s = j & 1;
-        ptx::mbar_wait(&k_full[s], (j >> 1) & 1);
-        ptx::tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + s * KV_BYTES);
         const uint32_t d = tmem_base + (s ? TM_S1 : TM_S0);
+        if (ptx::elect_one()) {
+          ptx::mbar_wait(&k_full[s], (j >> 1) & 1);
+          ptx::tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2)) + 2 * (kk & 3);
-          const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_BYTES / 2)) + 2 * (kk & 3);
-          ptx::umma_bf16(d, da, db, idesc_s, kk != 0 ? 1u : 0u);
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint64_t da = ptx::umma_desc_sw128(q_addr + (kk >> 2) * (Q_BYTES / 2)) + 2 * (kk & 3);
+            const uint64_t db = ptx::umma_desc_sw128(k_addr + (kk >> 2) * (KV_BYTES / 2)) + 2 * (kk & 3);
+            ptx::umma_bf16(d, da, db, idesc_s, kk != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&k_empty[s]);
+          ptx::umma_commit(&s_full[s]);
         }
-        ptx::umma_commit(&k_empty[s]);
-        ptx::umma_commit(&s_full[s]);
+        __syncwarp();
       };
-      ptx::mbar_wait(q_full, 0);
+      if (ptx::elect_one()) {
+        if (trace) trace[52] = clock64();
+        ptx::mbar_wait(q_full, 0);
+        if (trace) trace[53] = clock64();
+        ptx::mbar_wait(&k_full[0], 0);
+        if (trace) trace[54] = clock64();
+      }
+      __syncwarp();
       issue_s(0);
+      if (trace && ptx::elect_one()) trace[55] = clock64();
+      __syncwarp();
       for (int j = 0; j < ntiles; ++j) {
         const int s = j & 1;
         const uint32_t ph = (j >> 1) & 1;
         if (j + 1 < ntiles) issue_s(j + 1);
-        ptx::mbar_wait(&p_full[s], ph);
-        ptx::mbar_wait(&v_full[s], ph);
-        ptx::tc_fence_after();
         const uint32_t v_addr = smem_u32(sV + s * KV_BYTES);
         const uint32_t p_tmem = tmem_base + (s ? TM_S1 : TM_S0);
+        if (ptx::elect_one()) {
+          ptx::mbar_wait(&p_full[s], ph);
+          ptx::mbar_wait(&v_full[s], ph);
+          ptx::tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < KT / 16; ++kk) {
-          const uint64_t db = umma_desc_sw128_mn(v_addr + kk * 16 * 128, KV_BYTES / 2);
-          umma_bf16_ts(tmem_base + TM_O, p_tmem + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+          for (int kk = 0; kk < KT / 16; ++kk) {
+            const uint64_t db = umma_desc_sw128_mn(v_addr + kk * 16 * 128, KV_BYTES / 2);
+            umma_bf16_ts(tmem_base + TM_O, p_tmem + kk * 8, db, idesc_o, (j | kk) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&v_empty[s]);
+          ptx::umma_commit(&pv_done[s]);
+          if (trace && j < 12) trace[4 + 4 * j + 3] = clock64();
         }
-        ptx::umma_commit(&v_empty[s]);
-        ptx::umma_commit(&pv_done[s]);
+        __syncwarp();
       }
     }
     __syncwarp();
   } else {
     // ===== softmax + epilogue: thread = query row =====
     const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    const int qi = q0 + tid;
     const float sl2 = A.softmax_scale * 1.4426950408889634f;
     float m = -INFINITY, l = 0.f;
+    float fseg[4];                                         // per-segment K/V multiplier (speaker_kv_scale), loaded once
+#pragma unroll
+    for (int i = 0; i < 4; ++i) fseg[i] = (i < A.n_seg && A.seg[i].kv_scale) ? __ldg(A.seg[i].kv_scale) : 1.f;
     for (int j = 0; j < ntiles; ++j) {
       const int b = j & 1;
       const uint32_t ph = (j >> 1) & 1;
       const TileInfo t = tiles[j];
-      const float f = A.seg[t.seg].kv_scale ? __ldg(A.seg[t.seg].kv_scale) : 1.f;
+      const float f = t.seg == 0 ? fseg[0] : (t.seg == 1 ? fseg[1] : (t.seg == 2 ? fseg[2] : fseg[3]));
       const float sc = sl2 * f;
       ptx::mbar_wait(&s_full[b], ph);
       ptx::tc_fence_after();
+      if (trace && tid == 0 && j < 12) trace[4 + 4 * j + 0] = clock64();
       float s[64];
       const uint32_t s_addr = tmem_base + (b ? TM_S1 : TM_S0) + lane_off;
       tmem_ld32_nowait(s_addr, s);
       tmem_ld32_nowait(s_addr + 32, s + 32);
       tmem_ld_wait();
-      // raw maximum first (sc > 0), masked only on partial tiles (warp-uniform branch: most tiles are full)
-      float mt = -INFINITY;
-      if (t.valid != ~0ull) {
+      if (t.valid != ~0ull) {                              // partial tile (warp-uniform; most tiles are full)
         const unsigned lo = (unsigned)t.valid, hi = (unsigned)(t.valid >> 32);
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
@@ -276,13 +372,42 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
           if (!((hi >> c) & 1u)) s[c + 32] = -INFINITY;
         }
       }
+      uint32_t p[32];
+      float lsum = 0.f, mt;
+      // P = 2^(s*sc - m) [* f], its row sum and the raw row maximum in ONE pass (the max instructions hide under the
+      // MUFU-bound exponentials)
+      auto pass = [&](float nm, bool scaled) {
+        float x0 = -INFINITY, x1 = -INFINITY, x2 = -INFINITY, x3 = -INFINITY, l0 = 0.f, l1 = 0.f;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) mt = fmaxf(mt, s[c]);
-      mt *= sc;
-      // the PV of the previous tile must have landed before O may be rescaled (and is long done by now)
-      if (j > 0) ptx::mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        for (int c = 0; c < 64; c += 4) {
+          x0 = fmaxf(x0, s[c]); x1 = fmaxf(x1, s[c + 1]); x2 = fmaxf(x2, s[c + 2]); x3 = fmaxf(x3, s[c + 3]);
+          const float p0 = ex2_approx(fmaf(s[c], sc, nm)), p1 = ex2_approx(fmaf(s[c + 1], sc, nm));
+          const float p2 = ex2_approx(fmaf(s[c + 2], sc, nm)), p3 = ex2_approx(fmaf(s[c + 3], sc, nm));
+          l0 += p0 + p1; l1 += p2 + p3;
+          p[c >> 1] = scaled ? pack_bf16x2(p0 * f, p1 * f) : pack_bf16x2(p0, p1);
+          p[(c >> 1) + 1] = scaled ? pack_bf16x2(p2 * f, p3 * f) : pack_bf16x2(p2, p3);
+        }
+        lsum = l0 + l1;
+        mt = fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)) * sc;
+      };
+      // Speculate that the running maximum still covers this tile (true for almost every tile after the first): the
+      // exponentials then do not wait for the row maximum.  Rows that have not seen a valid key yet (m = -inf) and
+      // tiles whose maximum outgrows m by more than 2^8 take the exact path below and redo the pass.
+      const bool fresh = __any_sync(0xffffffffu, m == -INFINITY);
+      if (!fresh) {
+        if (f == 1.f) pass(-m, false); else pass(-m, true);
+      } else {
+        float x0 = -INFINITY, x1 = -INFINITY, x2 = -INFINITY, x3 = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 64; c += 4) {
+          x0 = fmaxf(x0, s[c]); x1 = fmaxf(x1, s[c + 1]); x2 = fmaxf(x2, s[c + 2]); x3 = fmaxf(x3, s[c + 3]);
+        }
+        mt = fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)) * sc;
+      }
       const bool grow = mt > m + RESCALE_TAU;            // also true for the first finite max (m = -inf)
-      if (__any_sync(0xffffffffu, grow)) {
+      if (fresh || __any_sync(0xffffffffu, grow)) {
+        // the PV of the previous tile must have landed before O may be rescaled
+        if (j > 0) ptx::mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
         const float mnew = grow ? mt : m;
         const float alpha = (m == -INFINITY) ? 0.f : exp2f(m - mnew);
         m = mnew;
@@ -299,40 +424,26 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
           }
           tmem_st_wait();
         }
+        pass((m == -INFINITY) ? 0.f : -m, true);
       }
-      const float nmuse = (m == -INFINITY) ? 0.f : -m;
-      uint32_t p[32];
-      float ls0 = 0.f, ls1 = 0.f;
-      if (f == 1.f) {
-#pragma unroll
-        for (int c = 0; c < 64; c += 2) {
-          const float p0 = ex2_approx(fmaf(s[c], sc, nmuse)), p1 = ex2_approx(fmaf(s[c + 1], sc, nmuse));
-          ls0 += p0; ls1 += p1;
-          p[c >> 1] = pack_bf16x2(p0, p1);
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < 64; c += 2) {
-          const float p0 = ex2_approx(fmaf(s[c], sc, nmuse)), p1 = ex2_approx(fmaf(s[c + 1], sc, nmuse));
-          ls0 += p0; ls1 += p1;
-          p[c >> 1] = pack_bf16x2(p0 * f, p1 * f);
-        }
-      }
-      l += ls0 + ls1;
+      if (trace && tid == 0 && j < 12) trace[4 + 4 * j + 1] = clock64();
+      l += lsum;
       tmem_st32(s_addr, p);
       tmem_st_wait();
       ptx::tc_fence_before();
       ptx::mbar_arrive(&p_full[b]);
+      if (trace && tid == 0 && j < 12) trace[4 + 4 * j + 2] = clock64();
     }
-    // ---- epilogue: O / l * sigmoid-gate -> bf16 ------------------------------------------------------------
-    const int width = A.heads * HD;
-    const long long o_off = ((long long)row * A.seq + qi) * width + (long long)head * HD;
-    const bool q_ok = qi < A.seq;
+    // ---- epilogue: O / l * sigmoid-gate -> bf16, staged in the K ring (SW128 rows: conflict-free 16-byte accesses
+    //      for a thread-per-row pattern) and written with two TMA stores (rows past `seq` are clipped by the map) ----
     if (ntiles > 0) {
       ptx::mbar_wait(&pv_done[(ntiles - 1) & 1], ((ntiles - 1) >> 1) & 1);
       ptx::tc_fence_after();
+      if (A.gate) ptx::mbar_wait(g_full, 0);
     }
+    if (trace && tid == 0) trace[60] = clock64();
     const float inv = l > 0.f ? 1.f / l : 0.f;
+    uint8_t* const stage_row = sK + tid * 128;
 #pragma unroll 1
     for (int c = 0; c < HD; c += 32) {
       float o[32];
@@ -342,30 +453,44 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
 #pragma unroll
         for (int i = 0; i < 32; ++i) o[i] = 0.f;
       }
-      if (q_ok) {
 #pragma unroll
-        for (int g = 0; g < 32; g += 8) {
-          float w[8];
+      for (int g = 0; g < 32; g += 8) {
+        const int col = c + g;
+        uint4* cell = reinterpret_cast<uint4*>(stage_row + (col >> 6) * (Q_BYTES / 2) + ((((col & 63) >> 3) ^ (tid & 7)) << 4));
+        float w[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) w[i] = o[g + i] * inv;
-          if (A.gate) {
-            const uint4 gv = *reinterpret_cast<const uint4*>(A.gate + o_off + c + g);
-            const float2 g0 = unpack_bf16x2(gv.x), g1 = unpack_bf16x2(gv.y), g2 = unpack_bf16x2(gv.z), g3 = unpack_bf16x2(gv.w);
-            w[0] *= g0.x; w[1] *= g0.y; w[2] *= g1.x; w[3] *= g1.y; w[4] *= g2.x; w[5] *= g2.y; w[6] *= g3.x; w[7] *= g3.y;
-          }
-          uint4 u;
-          u.x = pack_bf16x2(w[0], w[1]); u.y = pack_bf16x2(w[2], w[3]);
-          u.z = pack_bf16x2(w[4], w[5]); u.w = pack_bf16x2(w[6], w[7]);
-          *reinterpret_cast<uint4*>(A.out + o_off + c + g) = u;
+        for (int i = 0; i < 8; ++i) w[i] = o[g + i] * inv;
+        if (A.gate && ntiles > 0) {
+          const uint4 gv = *cell;
+          const float2 g0 = unpack_bf16x2(gv.x), g1 = unpack_bf16x2(gv.y), g2 = unpack_bf16x2(gv.z), g3 = unpack_bf16x2(gv.w);
+          w[0] *= g0.x; w[1] *= g0.y; w[2] *= g1.x; w[3] *= g1.y; w[4] *= g2.x; w[5] *= g2.y; w[6] *= g3.x; w[7] *= g3.y;
         }
+        uint4 u;
+        u.x = pack_bf16x2(w[0], w[1]); u.y = pack_bf16x2(w[2], w[3]);
+        u.z = pack_bf16x2(w[4], w[5]); u.w = pack_bf16x2(w[6], w[7]);
+        *cell = u;
       }
     }
+    ptx::fence_proxy_async();                              // generic-proxy writes -> visible to the TMA store
+    asm volatile("bar.sync 1, 128;" ::: "memory");         // the four softmax warps only
+    if (tid == 0) {
+      tma_store_4d(&M.out, sK, 0, head, q0, row);
+      tma_store_4d(&M.out, sK + Q_BYTES / 2, 64, head, q0, row);
+      tma_store_commit_wait();
+    }
   }
+  if (trace && tid == 0) trace[61] = clock64();
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 5) ptx::tmem_dealloc(tmem_base, TM_COLS);
+  if (trace && tid == 0) { trace[62] = clock64(); trace[63] = ntiles; }
 }
 }  // namespace
+
+// Debug aid: >= 64 int64 per CTA; [0] start, [1] setup done, per tile j < 12: [4+4j] S(j) ready, [5+4j] PV(j-1) done,
+// [6+4j] P(j) published, [7+4j] PV(j) issued (MMA lane); [2] warp 0 past the PDL wait, [3] tile list built,
+// [60] last PV done (+ gate tile landed), [61] epilogue done, [62] exit, [63] #tiles.
+extern "C" void echo_debug_attn_trace(long long* device_buf) { g_attn_trace = device_buf; }
 
 // Returns ECHO_ERR_UNSUPPORTED (without setting an error) when the descriptor is outside this kernel's domain so
 // that echo_attention() can fall back to the generic mma.sync kernel (causal / windowed / head_dim 64 encoders).
@@ -390,6 +515,22 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
     int rc = echo_make_tmap_bf16(&M.q, d->q, 4, dims, str, box);
     if (rc) return rc;
   }
+  {
+    const long long width = (long long)d->heads * HD;
+    cuuint64_t dims[4] = {(cuuint64_t)HD, (cuuint64_t)d->heads, (cuuint64_t)d->seq, (cuuint64_t)d->rows};
+    cuuint64_t str[3] = {(cuuint64_t)HD * 2, (cuuint64_t)width * 2, (cuuint64_t)d->seq * width * 2};
+    cuuint32_t box[4] = {64, 1, QT, 1};
+    int rc = echo_make_tmap_bf16(&M.out, d->out, 4, dims, str, box);
+    if (rc) return rc;
+    if (d->gate) {
+      rc = echo_make_tmap_bf16(&M.gate, d->gate, 4, dims, str, box);
+      if (rc) return rc;
+    } else {
+      M.gate = M.out;
+    }
+  }
+  A.trace = g_attn_trace;
+  A.static_first = (d->n_seg > 0 && d->seg[0].len > 0 && !d->seg[0].mask && !d->seg[0].extent) ? 1 : 0;
   A.rows = d->rows; A.seq = d->seq; A.heads = d->heads; A.n_seg = d->n_seg;
   A.softmax_scale = d->softmax_scale;
   A.gate = (const bf16*)d->gate; A.out = (bf16*)d->out;

@@ -128,7 +128,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (rank == 0 && lane == 0) {
+    if (rank == 0) {   // whole warp converged; one elected lane issues (keeps UTCHMMA free of election loops)
       const uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, T.bn);
       uint32_t tc = 0, ph = 0;
       int s = 0;
@@ -137,25 +137,31 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int split = unit % T.splits;
         const int kb0 = (int)((long long)total_kb * split / T.splits), kb1 = (int)((long long)total_kb * (split + 1) / T.splits);
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
-        ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
+        if (lane == 0) ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
+        __syncwarp();
         ptx::tc_fence_after();
-        if (trace && tc < 6) trace[8 + tc * 4 + 0] = clock64();
+        if (trace && tc < 6 && lane == 0) trace[8 + tc * 4 + 0] = clock64();
         const uint32_t tacc = tmem_base + as * ACC_COLS;
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (!(T.noload && (kb - kb0 >= STAGES || unit != pair))) ptx::mbar_wait(&full_bar[s], ph);
-          ptx::tc_fence_after();
-          if (trace && first) { trace[2] = clock64(); first = false; }
           const uint32_t sa = smem_u32(smem + s * STAGE_SZ);
           const uint64_t da = ptx::umma_desc_sw128(sa);
           const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
+          if (ptx::elect_one()) {      // the elected lane alone polls the barrier (31 spinning lanes only steal issue slots)
+            if (!(T.noload && (kb - kb0 >= STAGES || unit != pair))) ptx::mbar_wait(&full_bar[s], ph);
+            ptx::tc_fence_after();
+            if (trace && first) trace[2] = clock64();
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
-          if (!T.noload) ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::umma_bf16_cg2(tacc, da + 2 * k, db + 2 * k, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+            if (!T.noload) ptx::umma_commit_cg2_mc(&empty_bar[s], 0b11);   // both CTAs may refill this slot
+          }
+          __syncwarp();
+          first = false;
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
-        ptx::umma_commit_cg2_mc(&tmem_full_bar[as], 0b11);
-        if (trace && tc < 6) trace[8 + tc * 4 + 1] = clock64();
+        if (ptx::elect_one()) ptx::umma_commit_cg2_mc(&tmem_full_bar[as], 0b11);
+        __syncwarp();
+        if (trace && tc < 6 && lane == 0) trace[8 + tc * 4 + 1] = clock64();
       }
     }
     __syncwarp();

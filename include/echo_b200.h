@@ -167,6 +167,9 @@ typedef struct echo_attn_desc {
   echo_attn_segment seg[4];
 } echo_attn_desc;
 int echo_attention(const echo_attn_desc* d, echo_stream_t stream);
+/* Debug aid (no reference counterpart): while non-NULL, every tcgen05 attention launch records 64 clock64() stamps per
+ * CTA (layout documented at the definition in csrc/attention2.cu).  Pass NULL to switch it off. */
+void echo_debug_attn_trace(long long* device_buf);
 
 /* extent[r] = 1 + index of last non-zero byte of mask[r, :len] (0 if none) */
 int echo_mask_extent(const uint8_t* mask, int rows, int len, int64_t stride, int32_t* extent,
