@@ -144,7 +144,7 @@ def workload_config(B):
 
 
 def gemm_roofline(model, pk):
-    """Dominant kernel: the tcgen05 GEMM.  Timed live with CUDA events on the launch stream over all 24 layers'
+    """Dominant kernel: the CTA-pair tcgen05 GEMM (csrc/gemm2.cu).  Timed live with CUDA events on the launch stream over all 24 layers'
     w1|w3 operands (24 x 48 MB > L2) at the CFG-step shape M=1920, N=11776, K=2048 (43 % of step FLOPs)."""
     from echo_tts_b200 import ops
     M, D, F2 = 3 * S_LAT, 2048, 2 * 5888
@@ -165,9 +165,12 @@ def gemm_roofline(model, pk):
     sec = e0.elapsed_time(e1) / 1e3 / n
     flops = 2.0 * M * F2 * D
     ach = flops / sec / 1e12
-    return dict(bound="tensor", kernel="gemm_tcgen05_kernel<256,SWIGLU> M=1920 N=11776 K=2048", achieved=ach,
-                peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=None, peak_source=pk["src"] + " burst",
-                launches_timed=n, us_per_launch=sec * 1e6)
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full` capture
+    # (profiles/r1_ncu_hot_kernels.md: 56.13 MB + 5.90 MB), per launch like `achieved`
+    return dict(bound="tensor", kernel="gemm_pair_kernel<SWIGLU> (tcgen05 cta_group::2, 256x256 tiles) M=1920 N=11776 K=2048",
+                achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=62.03e6,
+                traffic_unit="bytes/launch (ncu dram read+write)", flop_per_launch=flops,
+                peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6)
 
 
 def run_gpu(args):
