@@ -35,6 +35,7 @@ class GemmDesc(C.Structure):
         ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("_pad1", i32),
         ("eps", f32), ("_pad2", f32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
         ("sections", GemmSection * 4), ("split_stride", i64),
+        ("workspace", c_p), ("workspace_bytes", i64),
     ]
 
 
@@ -89,6 +90,7 @@ EXPORTS = {
     "echo_launch_count": (C.c_ulonglong, []),
     "echo_reset_launch_count": (None, []),
     "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
+    "echo_gemm_workspace_bytes": (C.c_longlong, []),
     "echo_debug_gemm_trace": (None, [c_p]),
     "echo_debug_attn_trace": (None, [c_p]),
     "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),

@@ -168,8 +168,8 @@ static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStre
 
 template <int EPI>
 int launch_legacy(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm_legacy.cu
-int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P,
-                          int batch, cudaStream_t st);  // gemm2.cu
+int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
+                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm2.cu
 
 static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
@@ -319,7 +319,8 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
     if (d->k_splits > 1)
       ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
                      !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
-    return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, G, P, d->batch, st);
+    return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
+                                 d->batch, st);
   }
   ECHO_CHECK_ARG(d->k_splits <= 1, "gemm: k_splits is an impl-2 feature");
   ECHO_CHECK_ARG(d->impl == 0, "gemm: unknown impl %d", d->impl);

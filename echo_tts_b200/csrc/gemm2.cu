@@ -5,6 +5,11 @@
 //     256-wide tile (8 of a 128-wide one: operand latency, not MMA issue, bounds narrow tiles);
 //   * persistent: grid = min(#pair tiles, #SM/2) clusters, static round-robin tile order with the M index
 //     fastest so that the pairs working concurrently share one weight (B) tile through L2;
+//   * stream-K (when the caller lends a workspace and the tile count leaves the last round ragged): the K loops of
+//     all tiles form one line of k-blocks cut into equal contiguous ranges, one per pair.  A pair whose range starts
+//     inside a tile dumps that raw fp32 partial accumulator to the workspace (always its FIRST unit, so it never waits
+//     before publishing); the pair that owns the tile's k = 0 part (always its LAST unit) adds the partials in a
+//     fixed order into its TMEM accumulator and runs the fused epilogue: deterministic, no extra kernel;
 //   * two TMEM accumulator stages (2 x 256 columns): the fused epilogue of tile i runs while the MMAs of
 //     tile i+1 are issued;
 //   * warp roles per CTA: 0 = TMA producer (its CTA's halves; bytes land on the leader's mbarrier),
@@ -44,12 +49,143 @@ struct Tiling {
   int num_tiles;          // work units: tiles_m * tiles_n * batch * splits
   int splits;             // split-K: units per tile (unit index = tile * splits + split)
   long long split_stride; // elements between the partial outputs
+  int stream_k;           // 1: contiguous k-block ranges per pair (num_tiles = plain tile count, splits = 1)
+  int* sk_flags;          // [pairs][2 CTAs][EPI_WARPS] 0/1, self-resetting
+  float* sk_partials;     // [pairs][2 CTAs][128 x 256] fp32 in the exchange layout of sk_cell()
 };
+
+constexpr int SK_FLAG_BYTES = 16384;
+constexpr long long SK_SLOT_FLOATS = 2LL * BM * ACC_COLS;      // one pair's partial accumulator (256 KB)
+
+// One work unit: k-blocks [kb0, kb1) of `tile`.  All three warp roles walk the same sequence.
+struct Unit { int tile, split, kb0, kb1; };
+struct Sched {
+  int sk, total_kb, splits, unit, step, end;
+  long long u, e;
+  __device__ Sched(const Tiling& T, int pair, int npairs, int total_kb_) {
+    sk = T.stream_k; total_kb = total_kb_; splits = T.splits;
+    unit = pair; step = npairs; end = T.num_tiles;
+    const long long U = (long long)T.num_tiles * total_kb;
+    u = U * pair / npairs; e = U * (pair + 1) / npairs;
+  }
+  __device__ bool next(Unit& w) {
+    if (sk) {
+      if (u >= e) return false;
+      w.tile = (int)(u / total_kb); w.split = 0;
+      w.kb0 = (int)(u - (long long)w.tile * total_kb);
+      const long long rem = e - u;
+      w.kb1 = rem < (long long)(total_kb - w.kb0) ? w.kb0 + (int)rem : total_kb;
+      u += w.kb1 - w.kb0;
+      return true;
+    }
+    if (unit >= end) return false;
+    w.tile = unit / splits; w.split = unit - w.tile * splits;
+    w.kb0 = (int)((long long)total_kb * w.split / splits); w.kb1 = (int)((long long)total_kb * (w.split + 1) / splits);
+    unit += step;
+    return true;
+  }
+};
+
+// Exchange layout of a partial accumulator: [32-column chunk][lane quarter][4-column group][lane] float4 -- a warp
+// writes / reads 512 contiguous bytes per instruction, and the reader thread is the thread position that wrote.
+__device__ __forceinline__ float4* sk_cell(float* slot_cta, int chunk, int q, int c4, int lane) {
+  return reinterpret_cast<float4*>(slot_cta) + (((chunk * 4 + q) * 8 + c4) * 32 + lane);
+}
+__device__ __forceinline__ void sk_dump(int bn, uint32_t taddr, float* slot_cta, int* flag, int q, int half, int lane) {
+  for (int c = half; c < bn / 32; c += 2) {
+    float v[32];
+    ptx::tmem_ld32(taddr + (uint32_t)(c * 32), v);
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4)
+      __stcg(sk_cell(slot_cta, c, q, c4, lane), make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]));
+  }
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(1) : "memory");
+}
+__device__ __forceinline__ void sk_wait_flag(int* flag, int lane) {
+  if (lane == 0) {
+    int v = 0;
+    const long long t0 = clock64();
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+      if (!v && clock64() - t0 > 4000000000LL) { printf("echo gemm: stream-K partial never arrived\n"); __trap(); }
+    } while (!v);
+  }
+  __syncwarp();
+  __threadfence();
+}
+// Sum of the partial accumulators of the pairs that continue tile `w.tile` (fixed pair order) -> the idle TMEM
+// accumulator stage `tside`.  Runs on the epilogue warps while the MMAs of the owner's head unit are still in flight;
+// the epilogue then reads accumulator + side stage (TmemLoader2).
+__device__ __forceinline__ void sk_sideload(const Tiling& T, const Unit& w, int total_kb, int pair, int npairs, uint32_t rank,
+                                            uint32_t tside, int q, int half, int lane, int ew) {
+  const long long U = (long long)T.num_tiles * total_kb, tile_end = (long long)(w.tile + 1) * total_kb;
+  int last = pair;
+  for (int p2 = pair + 1; p2 < npairs && U * p2 / npairs < tile_end; ++p2) {
+    sk_wait_flag(T.sk_flags + (p2 * 2 + (int)rank) * EPI_WARPS + ew, lane);
+    last = p2;
+  }
+  float* const slot0 = T.sk_partials + (long long)rank * (BM * ACC_COLS);
+  const int nch = T.bn / 32;
+  // two chunks (64 registers) of every contributor are requested before anything is consumed: two memory round trips
+  // per warp instead of one per chunk (the asm statements around TMEM accesses are compiler barriers)
+#pragma unroll 1
+  for (int i0 = 0; i0 < 4; i0 += 2) {
+    float4 d[2][8];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int c = half + 2 * (i0 + i);
+      if (c < nch) {
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) d[i][c4] = __ldcg(sk_cell(slot0 + (long long)(pair + 1) * SK_SLOT_FLOATS, c, q, c4, lane));
+      }
+    }
+    for (int p2 = pair + 2; p2 <= last; ++p2) {
+      float* slot = slot0 + (long long)p2 * SK_SLOT_FLOATS;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int c = half + 2 * (i0 + i);
+        if (c < nch) {
+          float4 t[8];
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) t[c4] = __ldcg(sk_cell(slot, c, q, c4, lane));
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            d[i][c4].x += t[c4].x; d[i][c4].y += t[c4].y; d[i][c4].z += t[c4].z; d[i][c4].w += t[c4].w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int c = half + 2 * (i0 + i);
+      if (c < nch) ptx::tmem_st32(tside + (uint32_t)(c * 32), reinterpret_cast<const float*>(d[i]));
+    }
+  }
+  ptx::tmem_st_wait();
+  __syncwarp();
+  if (lane == 0)
+    for (int p2 = pair + 1; p2 <= last; ++p2)        // consumed: ready for the next launch
+      *reinterpret_cast<volatile int*>(T.sk_flags + (p2 * 2 + (int)rank) * EPI_WARPS + ew) = 0;
+}
 
 struct TmemLoader2 {
   uint32_t taddr;
   __device__ __forceinline__ void load32(int col, float* v) { ptx::tmem_ld32(taddr + (uint32_t)col, v); }
 };
+// accumulator += side stage (TMEM -> registers -> TMEM), this warp's chunks
+__device__ __forceinline__ void sk_merge(int bn, uint32_t tacc, uint32_t tside, int half) {
+  for (int c = half; c < bn / 32; c += 2) {
+    float v[32], s[32];
+    ptx::tmem_ld32(tacc + (uint32_t)(c * 32), v);
+    ptx::tmem_ld32(tside + (uint32_t)(c * 32), s);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += s[i];
+    ptx::tmem_st32(tacc + (uint32_t)(c * 32), v);
+  }
+  ptx::tmem_st_wait();
+}
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
@@ -104,16 +240,21 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int unit = pair; unit < T.num_tiles; unit += npairs) {
-        const int tile = unit / T.splits, split = unit - tile * T.splits;
+      Sched sch(T, pair, npairs, total_kb);
+      Unit w;
+      bool first_unit = true;
+      while (sch.next(w)) {
+        const int tile = w.tile;
         const int mt = tile % T.tiles_m;
         const int rest = tile / T.tiles_m;
         const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
         const int m0 = mt * (2 * BM) + (int)rank * BM;
         const int n0 = nt * T.bn + (int)rank * half_n;
-        const int kb0 = (int)((long long)total_kb * split / T.splits), kb1 = (int)((long long)total_kb * (split + 1) / T.splits);
+        const int kb0 = w.kb0, kb1 = w.kb1;
+        const bool first_u = first_unit;
+        first_unit = false;
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (T.noload && (kb - kb0 >= STAGES || unit != pair)) break;
+          if (T.noload && (kb - kb0 >= STAGES || !first_u)) break;
           ptx::mbar_wait(&empty_bar[s], ph ^ 1);
           const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
           uint8_t* sa = smem + s * STAGE_SZ;
@@ -132,10 +273,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, T.bn);
       uint32_t tc = 0, ph = 0;
       int s = 0;
-      bool first = true;
-      for (int unit = pair; unit < T.num_tiles; unit += npairs, ++tc) {
-        const int split = unit % T.splits;
-        const int kb0 = (int)((long long)total_kb * split / T.splits), kb1 = (int)((long long)total_kb * (split + 1) / T.splits);
+      bool first = true, first_unit = true;
+      Sched sch(T, pair, npairs, total_kb);
+      Unit w;
+      for (; sch.next(w); ++tc) {
+        const int kb0 = w.kb0, kb1 = w.kb1;
+        const bool first_u = first_unit;
+        first_unit = false;
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
         if (lane == 0) ptx::mbar_wait(&tmem_empty_bar[as], aph ^ 1);     // epilogues of both CTAs drained this accumulator
         __syncwarp();
@@ -147,7 +291,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const uint64_t da = ptx::umma_desc_sw128(sa);
           const uint64_t db = ptx::umma_desc_sw128(sa + A_BYTES);
           if (ptx::elect_one()) {      // the elected lane alone polls the barrier (31 spinning lanes only steal issue slots)
-            if (!(T.noload && (kb - kb0 >= STAGES || unit != pair))) ptx::mbar_wait(&full_bar[s], ph);
+            if (!(T.noload && (kb - kb0 >= STAGES || !first_u))) ptx::mbar_wait(&full_bar[s], ph);
             ptx::tc_fence_after();
             if (trace && first) trace[2] = clock64();
 #pragma unroll
@@ -167,9 +311,33 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncwarp();
   } else {
     const int q = warp & 3;                  // TMEM lane quarter this warp may read
+    const int ew = warp - 2, half = ew >> 2;
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     uint32_t tc = 0;
-    for (int unit = pair; unit < T.num_tiles; unit += npairs, ++tc) {
-      const int tile = unit / T.splits, split = unit - tile * T.splits;
+    Sched sch(T, pair, npairs, total_kb);
+    Unit w;
+    bool have = sch.next(w);
+    auto release_acc = [&](uint32_t as) {
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
+    };
+    // The stream-K special cases are peeled off the steady-state loop (first unit = dump, last unit = head) so that
+    // their register needs do not lengthen live ranges inside it.
+    if (have && T.stream_k && w.kb0 > 0) {
+      // the tile's k = 0 part belongs to an earlier pair: publish this partial accumulator, no epilogue
+      ptx::mbar_wait(&tmem_full_bar[0], 0);
+      ptx::tc_fence_after();
+      if (trace && warp == 2 && lane == 0) trace[10] = clock64();
+      sk_dump(T.bn, tmem_base + lane_base, T.sk_partials + (long long)pair * SK_SLOT_FLOATS + (long long)rank * (BM * ACC_COLS),
+              T.sk_flags + (pair * 2 + (int)rank) * EPI_WARPS + ew, q, half, lane);
+      release_acc(0);
+      if (trace && warp == 2 && lane == 0) trace[11] = clock64();
+      ++tc;
+      have = sch.next(w);
+    }
+    for (; have && !(T.stream_k && w.kb1 < total_kb); have = sch.next(w), ++tc) {
+      const int tile = w.tile, split = w.split;
       const int mt = tile % T.tiles_m;
       const int rest = tile / T.tiles_m;
       const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
@@ -178,12 +346,37 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
-      TmemLoader2 L{tmem_base + as * ACC_COLS + ((uint32_t)(q * 32) << 16)};
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + (warp - 2) * EPI_SC_FLOATS, lane, (warp - 2) >> 2, batch, m0 + q * 32,
-                          nt * T.bn, split, split * T.split_stride);
+      TmemLoader2 L{tmem_base + as * ACC_COLS + lane_base};
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, split,
+                          split * T.split_stride);
+      release_acc(as);
+      if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
+    }
+    if (have) {
+      // stream-K head: k-blocks [0, kb1) of a tile that later pairs continue (always this pair's last unit).  The other
+      // accumulator stage is idle from here on: fill it with their partial sum while our MMAs still run, merge, then
+      // run the fused epilogue on the complete accumulator.
+      const int tile = w.tile;
+      const int mt = tile % T.tiles_m;
+      const int rest = tile / T.tiles_m;
+      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
+      const int m0 = mt * (2 * BM) + (int)rank * BM;
+      const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
+      const uint32_t tacc = tmem_base + as * ACC_COLS + lane_base, tside = tmem_base + (as ^ 1u) * ACC_COLS + lane_base;
+      if (trace && warp == 2 && lane == 0) trace[3] = clock64();
+      sk_sideload(T, w, total_kb, pair, npairs, rank, tside, q, half, lane, ew);
+      if (trace && warp == 2 && lane == 0) trace[4] = clock64();
+      ptx::mbar_wait(&tmem_full_bar[as], aph);
+      ptx::tc_fence_after();
+      if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
+      sk_merge(T.bn, tacc, tside, half);
       ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
+      asm volatile("bar.sync 2, %0;" ::"n"(32 * EPI_WARPS) : "memory");   // fused epilogues read neighbouring chunks
+      ptx::tc_fence_after();
+      if (trace && warp == 2 && lane == 0) trace[5] = clock64();
+      TmemLoader2 L{tacc};
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, 0, 0);
+      release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
   }
@@ -194,6 +387,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (trace && threadIdx.x == 0) trace[7] = clock64();
 }
 
+int getenv_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e && e[0] ? atoi(e) : dflt;
+}
 int num_sms() {
   static int n = 0;
   if (!n) {
@@ -209,9 +406,15 @@ int num_sms() {
 int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                         const cuuint32_t* box);   // gemm.cu
 
+// Bytes of the optional stream-K workspace (echo_gemm_desc.workspace): flags + one partial accumulator per CTA pair.
+// The caller zeroes it once after allocation and must not share it between streams that run GEMMs concurrently.
+extern "C" long long echo_gemm_workspace_bytes(void) {
+  return SK_FLAG_BYTES + (long long)(num_sms() / 2) * SK_SLOT_FLOATS * (long long)sizeof(float);
+}
+
 template <int EPI>
-static int launch_pair_t(int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P, int batch,
-                         cudaStream_t st) {
+static int launch_pair_t(int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
+                         const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
   CUtensorMap ta, tb;
   {
     cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
@@ -243,7 +446,21 @@ static int launch_pair_t(int bn, int splits, long long split_stride, const GemmS
   T.splits = splits;
   T.split_stride = split_stride;
   T.num_tiles = T.tiles_m * T.tiles_n * batch * splits;
-  const int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
+  int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
+  T.stream_k = 0; T.sk_flags = nullptr; T.sk_partials = nullptr;
+  if (splits == 1 && workspace && workspace_bytes >= echo_gemm_workspace_bytes() && !g_debug_noload) {
+    // stream-K when whole-tile scheduling would idle more than ~8 % of the machine in its last round and every pair
+    // still gets a few k-blocks of work
+    const int P2 = num_sms() / 2, total_kb = G.k_blocks_per_tap * G.taps;
+    const long long tiles = T.num_tiles, rounds = (tiles + P2 - 1) / P2;
+    const bool ragged = tiles * 100 < rounds * P2 * 92;
+    if (ragged && total_kb >= 8 && tiles * total_kb >= 4LL * P2 && getenv_int("ECHO_STREAM_K", 0)) {
+      T.stream_k = 1;
+      T.sk_flags = reinterpret_cast<int*>(workspace);
+      T.sk_partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_FLAG_BYTES);
+      pairs = P2;
+    }
+  }
   ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, G, P, T));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
@@ -261,8 +478,8 @@ extern "C" void echo_debug_gemm_trace(long long* device_buf) {
 }
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
-int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, const GemmShape& G, const EpiParams& P,
-                          int batch, cudaStream_t st) {
+int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
+                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
   if (splits < 1) splits = 1;
   if (splits > 1 && (epi != ECHO_EPI_GENERIC || splits > G.k_blocks_per_tap * G.taps)) {
     echo_set_error("pair gemm: k_splits %d needs the GENERIC epilogue and at least one k-block per split", splits);
@@ -273,8 +490,9 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, c
     return ECHO_ERR_UNSUPPORTED;
   }
   switch (epi) {
-    case ECHO_EPI_GENERIC: return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, G, P, batch, st);
-    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, G, P, batch, st);
-    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, G, P, batch, st);
+    case ECHO_EPI_GENERIC:
+      return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
+    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);
+    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);
   }
 }

@@ -16,15 +16,24 @@
 
 constexpr int EPI_SC_FLOATS = 32 * 32;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
 
+// The scratch is addressed in the shared state space explicitly: through a generic pointer the compiler emits
+// generic LD/ST (address translation, long-scoreboard latency) instead of LDS/STS.
 __device__ __forceinline__ void sc_store_row(float* sc, int lane, const float* v) {
-  float* row = sc + lane * 32;
+  const uint32_t row = smem_u32(sc) + (uint32_t)lane * 128u;
 #pragma unroll
   for (int k = 0; k < 8; ++k)
-    *reinterpret_cast<float4*>(row + ((k ^ (lane & 7)) << 2)) = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row + (uint32_t)((k ^ (lane & 7)) << 4)), "f"(v[4 * k]),
+                 "f"(v[4 * k + 1]), "f"(v[4 * k + 2]), "f"(v[4 * k + 3])
+                 : "memory");
   __syncwarp();
 }
 __device__ __forceinline__ float4 sc_load4(const float* sc, int row, int cg) {
-  return *reinterpret_cast<const float4*>(sc + row * 32 + ((cg ^ (row & 7)) << 2));
+  float4 x;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
+               : "r"(smem_u32(sc) + (uint32_t)(row * 128 + ((cg ^ (row & 7)) << 4)))
+               : "memory");
+  return x;
 }
 __device__ __forceinline__ void store_bf16x4(bf16* p, float4 x) {
   *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
@@ -41,8 +50,10 @@ struct EpiRows {
 };
 
 // ---- GENERIC ------------------------------------------------------------------------------
+// Only the residual rows (one 128-byte segment of 32 different rows: L2 latency) are fetched a chunk ahead; the
+// per-column vectors (bias / gate / snake alpha: a few KB shared by every row, L1 hits after the first touch) are
+// requested at the top of process(), under the TMEM load and the transpose.
 struct GenAux {
-  float4 bias, alpha, glo, ghi;
   float4 rv[8];
 };
 
@@ -54,16 +65,9 @@ struct GenCtx {
   bool gate_fast;
 
   __device__ __forceinline__ void load(int c, GenAux& A) const {
-    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f), one4 = make_float4(1.f, 1.f, 1.f, 1.f);
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     const int n = R.n0 + c + 4 * cg;
     const bool nok = n < P.n;                            // n % 8 == 0: a 4-column group is all in or all out
-    A.bias = (P.bias && nok && R.split == 0) ? __ldg(reinterpret_cast<const float4*>(P.bias + n)) : zero4;
-    A.alpha = (P.out2_bf16 && nok) ? __ldg(reinterpret_cast<const float4*>(P.snake_alpha + n)) : one4;
-    A.glo = one4; A.ghi = one4;
-    if (P.gate && nok && gate_fast) {
-      A.glo = __ldg(reinterpret_cast<const float4*>(P.gate + g0 * P.gate_ld + n));
-      if (rem0 + 31 >= rpg) A.ghi = __ldg(reinterpret_cast<const float4*>(P.gate + (g0 + 1) * P.gate_ld + n));
-    }
     const float* rp = P.resid ? P.resid + R.mg0 * P.ld_resid + n : nullptr;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -74,44 +78,61 @@ struct GenCtx {
 
   template <class Loader>
   __device__ __forceinline__ void process(int c, const GenAux& A, Loader& L, float* sc, int lane) const {
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f), one4 = make_float4(1.f, 1.f, 1.f, 1.f);
+    const int n = R.n0 + c + 4 * cg;
+    const bool nok = n < P.n;
+    const bool two_gates = rem0 + 31 >= rpg;             // warp-uniform: the 32 rows straddle a gate-row boundary
+    const float4 bias = (P.bias && nok && R.split == 0) ? __ldg(reinterpret_cast<const float4*>(P.bias + n)) : zero4;
+    float4 glo = one4, ghi = one4;
+    if (P.gate && nok && gate_fast) {
+      glo = __ldg(reinterpret_cast<const float4*>(P.gate + g0 * P.gate_ld + n));
+      if (two_gates) ghi = __ldg(reinterpret_cast<const float4*>(P.gate + (g0 + 1) * P.gate_ld + n));
+    }
     float v[32];
     L.load32(c, v);
     sc_store_row(sc, lane, v);
-    const int n = R.n0 + c + 4 * cg;
-    const bool nok = n < P.n;
     float4 x[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      x[i] = sc_load4(sc, 4 * i + rsub, cg);
-      x[i].x += A.bias.x; x[i].y += A.bias.y; x[i].z += A.bias.z; x[i].w += A.bias.w;
-    }
-    if (P.act == ECHO_ACT_GELU) {
+    for (int i = 0; i < 8; ++i) x[i] = sc_load4(sc, 4 * i + rsub, cg);
+    if (P.act == ECHO_ACT_NONE && (!P.gate || (gate_fast && !two_gates))) {
+      // the DiT projections: x = (acc + bias) * g + resid as one FMA per element
+      const float4 bg = make_float4(bias.x * glo.x, bias.y * glo.y, bias.z * glo.z, bias.w * glo.w);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { x[i].x = geluf_(x[i].x); x[i].y = geluf_(x[i].y); x[i].z = geluf_(x[i].z); x[i].w = geluf_(x[i].w); }
-    } else if (P.act == ECHO_ACT_SILU) {
+      for (int i = 0; i < 8; ++i) {
+        x[i].x = fmaf(x[i].x, glo.x, bg.x + A.rv[i].x); x[i].y = fmaf(x[i].y, glo.y, bg.y + A.rv[i].y);
+        x[i].z = fmaf(x[i].z, glo.z, bg.z + A.rv[i].z); x[i].w = fmaf(x[i].w, glo.w, bg.w + A.rv[i].w);
+      }
+    } else {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { x[i].x = siluf_(x[i].x); x[i].y = siluf_(x[i].y); x[i].z = siluf_(x[i].z); x[i].w = siluf_(x[i].w); }
-    }
-    if (P.gate) {
-      if (gate_fast) {
+      for (int i = 0; i < 8; ++i) { x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w; }
+      if (P.act == ECHO_ACT_GELU) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float4 g = (rem0 + 4 * i + rsub >= rpg) ? A.ghi : A.glo;
-          x[i].x *= g.x; x[i].y *= g.y; x[i].z *= g.z; x[i].w *= g.w;
-        }
-      } else {
+        for (int i = 0; i < 8; ++i) { x[i].x = geluf_(x[i].x); x[i].y = geluf_(x[i].y); x[i].z = geluf_(x[i].z); x[i].w = geluf_(x[i].w); }
+      } else if (P.act == ECHO_ACT_SILU) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = 4 * i + rsub;
-          if (nok && r < R.nrows) {
-            const float4 g = __ldg(reinterpret_cast<const float4*>(P.gate + ((R.mg0 + r) / rpg) * P.gate_ld + n));
+        for (int i = 0; i < 8; ++i) { x[i].x = siluf_(x[i].x); x[i].y = siluf_(x[i].y); x[i].z = siluf_(x[i].z); x[i].w = siluf_(x[i].w); }
+      }
+      if (P.gate) {
+        if (gate_fast) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 g = (rem0 + 4 * i + rsub >= rpg) ? ghi : glo;
             x[i].x *= g.x; x[i].y *= g.y; x[i].z *= g.z; x[i].w *= g.w;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = 4 * i + rsub;
+            if (nok && r < R.nrows) {
+              const float4 g = __ldg(reinterpret_cast<const float4*>(P.gate + ((R.mg0 + r) / rpg) * P.gate_ld + n));
+              x[i].x *= g.x; x[i].y *= g.y; x[i].z *= g.z; x[i].w *= g.w;
+            }
           }
         }
       }
-    }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { x[i].x += A.rv[i].x; x[i].y += A.rv[i].y; x[i].z += A.rv[i].z; x[i].w += A.rv[i].w; }
+      for (int i = 0; i < 8; ++i) { x[i].x += A.rv[i].x; x[i].y += A.rv[i].y; x[i].z += A.rv[i].z; x[i].w += A.rv[i].w; }
+    }
     if (P.out_f32) {
       float* o = P.out_f32 + R.out_off + R.mg0 * P.ld_out_f32 + n;
 #pragma unroll
@@ -126,13 +147,14 @@ struct GenCtx {
     }
     if (P.out2_bf16) {
       bf16* o = P.out2_bf16 + R.mg0 * P.ld_out2_bf16 + n;
-      const float4 ia = make_float4(__fdividef(1.f, A.alpha.x + 1e-9f), __fdividef(1.f, A.alpha.y + 1e-9f),
-                                    __fdividef(1.f, A.alpha.z + 1e-9f), __fdividef(1.f, A.alpha.w + 1e-9f));
+      const float4 alpha = nok ? __ldg(reinterpret_cast<const float4*>(P.snake_alpha + n)) : one4;
+      const float4 ia = make_float4(__fdividef(1.f, alpha.x + 1e-9f), __fdividef(1.f, alpha.y + 1e-9f),
+                                    __fdividef(1.f, alpha.z + 1e-9f), __fdividef(1.f, alpha.w + 1e-9f));
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float4 s;
-        s.x = __sinf(A.alpha.x * x[i].x); s.y = __sinf(A.alpha.y * x[i].y);
-        s.z = __sinf(A.alpha.z * x[i].z); s.w = __sinf(A.alpha.w * x[i].w);
+        s.x = __sinf(alpha.x * x[i].x); s.y = __sinf(alpha.y * x[i].y);
+        s.z = __sinf(alpha.z * x[i].z); s.w = __sinf(alpha.w * x[i].w);
         s.x = fmaf(s.x * s.x, ia.x, x[i].x); s.y = fmaf(s.y * s.y, ia.y, x[i].y);
         s.z = fmaf(s.z * s.z, ia.z, x[i].z); s.w = fmaf(s.w * s.w, ia.w, x[i].w);
         if (nok && 4 * i + rsub < R.nrows) store_bf16x4(o + (long long)(4 * i + rsub) * P.ld_out2_bf16, s);

@@ -14,6 +14,7 @@ BF16, F32 = torch.bfloat16, torch.float32
 import os as _os
 # 2 = CTA-pair persistent tcgen05 kernel (product path); 0 = single-CTA tcgen05 kernel; 1 = legacy mma.sync
 # (A/B baselines, tests only).  ECHO_GEMM_IMPL overrides for A/B measurements.
+STREAM_K = True   # lend the stream-K workspace; the library decides (ECHO_STREAM_K=1 enables it, default off)
 GEMM_IMPL = int(_os.environ.get("ECHO_GEMM_IMPL", "2"))
 
 
@@ -22,6 +23,20 @@ def _need(t: torch.Tensor, dtype, name: str):
         raise RuntimeError(f"{name}: CUDA tensor required (no CPU fallback)")
     if t.dtype != dtype:
         raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+
+
+_GEMM_WS = {}
+
+
+def gemm_workspace(device: torch.device) -> torch.Tensor:
+    """Stream-K scratch lent to every impl-2 GEMM on ``device`` (flags + one partial accumulator per CTA pair, zeroed
+    once).  One buffer per device: GEMMs of this package run on one stream at a time per device."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _GEMM_WS.get(key)
+    if ws is None:
+        ws = torch.zeros(int(L.load().echo_gemm_workspace_bytes()), device=device, dtype=torch.uint8)
+        _GEMM_WS[key] = ws
+    return ws
 
 
 def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), batch: int = 1,
@@ -43,6 +58,9 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
     d.impl = GEMM_IMPL if impl is None else impl
     d.block_n = block_n
     d.rows_per_gate = 1
+    if d.impl == 2 and STREAM_K:
+        ws = gemm_workspace(a.device)
+        d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
     return d
 
 

@@ -49,7 +49,7 @@ typedef struct echo_gemm_desc {
   int32_t rows, batch, n, k_tap, taps;
   int32_t tap_shift[8];
   int32_t epilogue;         /* ECHO_EPI_* */
-  int32_t impl;             /* 0 tcgen05, 1 legacy mma.sync */
+  int32_t impl;             /* 2 = CTA-pair tcgen05 kernel (product path); 0 = single-CTA tcgen05; 1 = legacy mma.sync */
   int32_t block_n;          /* 0 = auto; 64 / 128 / 256 */
   int32_t act;              /* GENERIC: activation applied after bias */
   /* GENERIC: v = act(acc + bias[n]) * gate[(m / rows_per_gate) * gate_ld + n] + resid[m, n]
@@ -84,9 +84,15 @@ typedef struct echo_gemm_desc {
   echo_gemm_section sections[4];
   int64_t split_stride;     /* elements between the k_splits partial outputs */
   /* SWIGLU: B rows interleaved in groups of 64 (w1 | w3); out_bf16[m, j] = silu(a)*b (model.py:308) */
+  void* workspace;          /* optional, impl 2: device scratch of >= echo_gemm_workspace_bytes(), zeroed once by the
+                             * caller, not shared between concurrently running streams.  When present the library may
+                             * schedule the launch stream-K (equal k-block ranges per CTA pair, partial accumulators
+                             * exchanged through this buffer in a fixed order: deterministic, same epilogues). */
+  int64_t workspace_bytes;
 } echo_gemm_desc;
 
 int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
+long long echo_gemm_workspace_bytes(void);
 
 /* Debug aid (no reference counterpart): while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every
  * impl-2 GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles

@@ -127,6 +127,58 @@ def test_gemm_sections_norm_rope(ops, L, impl, hd, H, rope_heads):
         assert rel_l2(got.float().cpu(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(1920, 2048, 2048), (1920, 2048, 5888), (640, 2048, 2048), (640, 8192, 2048), (2304, 768, 1024)])
+def test_gemm_stream_k_generic(ops, M, N, K, monkeypatch):
+    """Ragged tile counts are scheduled stream-K (partial accumulators exchanged through the lent workspace): same
+    result as whole-tile scheduling up to fp32 summation order, identical from run to run (self-resetting flags)."""
+    a, w = _rand((M, K), 41, dtype=BF16), _rand((N, K), 42, K ** -0.5, BF16)
+    bias, gate, resid = _rand((N,), 43), _rand((3, N), 44), _rand((M, N), 45)
+    rpg = (M + 2) // 3
+    ref = (a.float() @ w.float().t() + bias) * gate[torch.arange(M, device="cuda") // rpg] + resid
+    outs = []
+    for sk in ("1", "1", "0"):
+        monkeypatch.setenv("ECHO_STREAM_K", sk)
+        x = resid.clone()
+        ops.gemm_generic(a, w, bias=bias, gate=gate, rows_per_gate=rpg, resid=x, out_f32=x, impl=2)
+        outs.append(x)
+    assert torch.equal(outs[0], outs[1])
+    assert rel_l2(outs[0], ref) < 2e-5 and rel_l2(outs[2], ref) < 2e-5
+    assert rel_l2(outs[0], outs[2]) < 5e-6
+
+
+def test_gemm_stream_k_fused_epilogues(ops, L, monkeypatch):
+    """SECTIONS (per-head norm needs the whole fixed-up accumulator row) and SWIGLU epilogues on stream-K tiles."""
+    from oracle import echo_oracle as O
+    R, S, K, H, hd = 1, 640, 2048, 16, 128
+    D, M = H * hd, R * S
+    a = _rand((M, K), 46, dtype=BF16)
+    w = _rand((4 * D, K), 47, K ** -0.5, BF16)
+    qn, kn = _rand((D,), 48).abs() + 0.5, _rand((D,), 49).abs() + 0.5
+    cos, sin = O.rope_table(hd, 4096)
+    rope = (cos.cuda().contiguous(), sin.cuda().contiguous())
+    res = {}
+    for sk in ("1", "0"):
+        monkeypatch.setenv("ECHO_STREAM_K", sk)
+        outs = torch.empty((4, M, D), device="cuda", dtype=BF16)
+        ops.gemm_sections(a, w, [(L.SEC_NORM_ROPE, outs[0], qn), (L.SEC_NORM_ROPE, outs[1], kn), (L.SEC_PLAIN, outs[2], None),
+                                 (L.SEC_SIGMOID, outs[3], None)], head_dim=hd, rope_heads=8, rope=rope, pos_offset=0,
+                          rows_per_seq=S, eps=1e-5, impl=2)
+        res[sk] = outs.float()
+    assert rel_l2(res["1"], res["0"]) < 2e-3          # bf16 outputs: an fp32 reordering flips a few roundings
+    acc = (a.float() @ w.float().t())
+    assert rel_l2(res["1"][2], acc[:, 2 * D:3 * D]) < 4e-3 and rel_l2(res["1"][3], torch.sigmoid(acc[:, 3 * D:])) < 4e-3
+    F_ = 5888
+    w1, w3 = _rand((F_, K), 50, K ** -0.5, BF16), _rand((F_, K), 51, K ** -0.5, BF16)
+    w13 = ops.pack_w13(w1, w3)
+    a2 = _rand((896, K), 52, dtype=BF16)               # 4 x 46 = 184 tiles on 74 pairs: ragged
+    ref = torch.nn.functional.silu(a2.float() @ w1.float().t()) * (a2.float() @ w3.float().t())
+    for sk in ("1", "0"):
+        monkeypatch.setenv("ECHO_STREAM_K", sk)
+        out = torch.empty((896, F_), device="cuda", dtype=BF16)
+        ops.gemm_swiglu(a2, w13, out, impl=2)
+        assert rel_l2(out.float(), ref) < 4e-3, sk
+
+
 @pytest.mark.parametrize("M,N,K,S", [(640, 2048, 5888, 3), (640, 2048, 2048, 3), (100, 256, 256, 4), (300, 512, 1024, 2)])
 def test_gemm_split_k_deferred_residual(ops, M, N, K, S):
     """split-K partial products (gated) + the fused add-norm that consumes them == the one-pass residual GEMM."""

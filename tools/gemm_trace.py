@@ -63,6 +63,15 @@ def main():
         print(f"== {name} M={M}: {t.shape[0]} CTAs; SM clocks, median over pairs")
         print(f"   setup {med(ld[:, 1] - ld[:, 0]):8.0f}   first operands after setup {med(ld[:, 2] - ld[:, 1]):8.0f}   "
               f"whole CTA {med(ld[:, 6] - ld[:, 0]):8.0f}   teardown {med(ld[:, 7] - ld[:, 6]):8.0f}")
+        mx = lambda v: float(v.float().max())
+        sk = ld[ld[:, 3] != 0]
+        if sk.shape[0]:
+            last = torch.stack([sk[i, 8 + 4 * tc + 2: 8 + 4 * tc + 4] for i in range(sk.shape[0])
+                                for tc in [max(k for k in range(6) if sk[i, 9 + 4 * k] != 0)]])
+            print(f"   stream-K head units ({sk.shape[0]} pairs): sideload start @{med(sk[:, 3] - sk[:, 0]):8.0f}  took "
+                  f"{med(sk[:, 4] - sk[:, 3]):8.0f} (max {mx(sk[:, 4] - sk[:, 3]):8.0f})  own MMAs done @{med(last[:, 0] - sk[:, 0]):8.0f}  "
+                  f"merge+barrier {med(sk[:, 5] - last[:, 0]):8.0f}  epilogue {med(last[:, 1] - sk[:, 5]):8.0f}  end @{med(last[:, 1] - sk[:, 0]):8.0f} "
+                  f"(max {mx(last[:, 1] - sk[:, 0]):8.0f})")
         for tc in range(6):
             b = 8 + 4 * tc
             ok = ld[:, b + 1] != 0
