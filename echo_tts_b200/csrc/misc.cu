@@ -30,7 +30,11 @@ extern "C" void echo_reset_launch_count(void) { g_echo_launches = 0; }
 // RMS-normalise (+ AdaLN modulate) fp32 rows -> bf16.  One warp per row, float4 loads, row kept
 // in registers (d <= 4096).  HBM-bound: 4 B in + 2 B out per element.
 // ---------------------------------------------------------------------------------------------
-template <int VEC_ITERS>
+// Four warps per row, two rows per CTA: every load a row needs (x, up to four split-K partials, scale, shift) is in
+// flight before the first use -- one memory round trip per row, and 4x the CTAs of a warp-per-row layout when only
+// a few hundred rows exist (the single-branch Euler steps).
+constexpr int NORM_MAX_DELTA = 4;
+template <int VEC>
 __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restrict__ x, long long ldx, int m, int d,
                                                           float eps, const float* __restrict__ delta, int n_delta,
                                                           long long delta_stride, float* __restrict__ x_out,
@@ -39,61 +43,83 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
                                                           int rows_per_mod, const int* __restrict__ step,
                                                           long long mod_step_stride, bf16* __restrict__ y,
                                                           long long ldy) {
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
+  __shared__ float s_part[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 2 + (warp >> 2);
+  const int t = (warp & 3) * 32 + lane;           // 0..127 inside the row
+  const int nvec = d >> 2;
+  const bool live = row < m;
   pdl_launch_dependents();
   pdl_wait();
-  if (row >= m) return;
-  const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
-  float4 v[VEC_ITERS];
-  float ssq = 0.f;
-  const int nvec = d >> 2;
+  float4 v[VEC], dl[NORM_MAX_DELTA][VEC], sc[VEC], sh[VEC];
+  if (live) {
+    const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
 #pragma unroll
-  for (int i = 0; i < VEC_ITERS; ++i) {
-    const int c = lane + i * 32;
-    if (c < nvec) v[i] = xr[c];
-  }
-  if (n_delta > 0) {   // deferred residual update: x += sum of the split-K partial outputs (fixed order), written back
-    for (int s = 0; s < n_delta; ++s) {
-      const float4* dr = reinterpret_cast<const float4*>(delta + s * delta_stride + (long long)row * ldx);
+    for (int i = 0; i < VEC; ++i) {
+      const int c = t + i * 128;
+      if (c < nvec) v[i] = xr[c];
+    }
 #pragma unroll
-      for (int i = 0; i < VEC_ITERS; ++i) {
-        const int c = lane + i * 32;
-        if (c < nvec) {
-          const float4 dv = dr[c];
-          v[i].x += dv.x; v[i].y += dv.y; v[i].z += dv.z; v[i].w += dv.w;
+    for (int s = 0; s < NORM_MAX_DELTA; ++s) {
+      if (s < n_delta) {
+        const float4* dr = reinterpret_cast<const float4*>(delta + s * delta_stride + (long long)row * ldx);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+          const int c = t + i * 128;
+          if (c < nvec) dl[s][i] = dr[c];
         }
       }
     }
-    float4* xo = reinterpret_cast<float4*>(x_out + (long long)row * ldx);
+    long long g = row / rows_per_mod;
+    if (step) g += (long long)step[0] * mod_step_stride;
+    const float4* scp = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
+    const float4* shp = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
 #pragma unroll
-    for (int i = 0; i < VEC_ITERS; ++i) {
-      const int c = lane + i * 32;
-      if (c < nvec) xo[c] = v[i];
+    for (int i = 0; i < VEC; ++i) {
+      const int c = t + i * 128;
+      if (c < nvec) {
+        sc[i] = __ldg(scp + c);
+        sh[i] = shp ? __ldg(shp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
     }
   }
+  float ssq = 0.f;
+  if (live) {
+    if (n_delta > 0) {   // deferred residual update: x += sum of the split-K partial outputs (fixed order), written back
 #pragma unroll
-  for (int i = 0; i < VEC_ITERS; ++i) {
-    const int c = lane + i * 32;
-    if (c < nvec) ssq += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      for (int s = 0; s < NORM_MAX_DELTA; ++s) {
+        if (s < n_delta) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) {
+            if (t + i * 128 < nvec) { v[i].x += dl[s][i].x; v[i].y += dl[s][i].y; v[i].z += dl[s][i].z; v[i].w += dl[s][i].w; }
+          }
+        }
+      }
+      float4* xo = reinterpret_cast<float4*>(x_out + (long long)row * ldx);
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) {
+        const int c = t + i * 128;
+        if (c < nvec) xo[c] = v[i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < VEC; ++i)
+      if (t + i * 128 < nvec) ssq += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
   }
   ssq = warp_sum(ssq);
-  const float rstd = rsqrtf(ssq / (float)d + eps);
-  long long g = row / rows_per_mod;
-  if (step) g += (long long)step[0] * mod_step_stride;
-  const float4* sc = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
-  const float4* sh = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
+  if (lane == 0) s_part[warp] = ssq;
+  __syncthreads();
+  if (!live) return;
+  const int w0 = warp & ~3;
+  const float tot = (s_part[w0] + s_part[w0 + 1]) + (s_part[w0 + 2] + s_part[w0 + 3]);
+  const float rstd = rsqrtf(tot / (float)d + eps);
   uint2* yr = reinterpret_cast<uint2*>(y + (long long)row * ldy);
 #pragma unroll
-  for (int i = 0; i < VEC_ITERS; ++i) {
-    const int c = lane + i * 32;
+  for (int i = 0; i < VEC; ++i) {
+    const int c = t + i * 128;
     if (c < nvec) {
-      const float4 s = __ldg(sc + c);
-      float4 o = make_float4(v[i].x * rstd * s.x, v[i].y * rstd * s.y, v[i].z * rstd * s.z, v[i].w * rstd * s.w);
-      if (sh) {
-        const float4 b = __ldg(sh + c);
-        o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-      }
+      const float4 o = make_float4(fmaf(v[i].x * rstd, sc[i].x, sh[i].x), fmaf(v[i].y * rstd, sc[i].y, sh[i].y),
+                                   fmaf(v[i].z * rstd, sc[i].z, sh[i].z), fmaf(v[i].w * rstd, sc[i].w, sh[i].w));
       yr[c] = make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
     }
   }
@@ -104,17 +130,18 @@ static int launch_rmsnorm(const float* x, int64_t ldx, int m, int d, float eps, 
                           int rows_per_mod, const int32_t* step, int64_t mod_step_stride, void* y, int64_t ldy,
                           echo_stream_t stream) {
   ECHO_CHECK_ARG(x && scale1 && y && m > 0, "rmsnorm: null argument");
-  ECHO_CHECK_ARG(n_delta >= 0 && (n_delta == 0 || (delta && x_out && delta_stride % 4 == 0)), "rmsnorm: bad delta arguments");
+  ECHO_CHECK_ARG(n_delta >= 0 && n_delta <= NORM_MAX_DELTA && (n_delta == 0 || (delta && x_out && delta_stride % 4 == 0)),
+                 "rmsnorm: bad delta arguments (at most %d partials)", NORM_MAX_DELTA);
   ECHO_CHECK_ARG(d % 4 == 0 && d <= 4096 && ldx % 4 == 0 && ldy % 4 == 0 && mod_ld % 4 == 0, "rmsnorm: d must be <=4096, %%4");
   if (rows_per_mod <= 0) rows_per_mod = 1 << 30;
-  dim3 grid(ceil_div(m, 8));
+  dim3 grid(ceil_div(m, 2));
   cudaStream_t st = (cudaStream_t)stream;
   if (d <= 1024)
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<8>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<2>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else if (d <= 2048)
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<16>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<4>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   else
-    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<32>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
+    ECHO_CUDA(echo_launch(rmsnorm_mod_kernel<8>, grid, dim3(256), 0, st, x, (long long)ldx, m, d, eps, delta, n_delta, (long long)delta_stride, x_out, scale1, shift, (long long)mod_ld, rows_per_mod, step, (long long)mod_step_stride, (bf16*)y, (long long)ldy));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
