@@ -1,13 +1,15 @@
 // Fused sampler tail (fp32): out_norm -> out_proj -> CFG combine -> temporal score rescale -> Euler.
-// One CTA owns PP latent positions x all CFG branches: the normalised rows live in shared memory,
-// each warp streams one out_proj weight row at a time (L2-resident, 80 x d fp32) and reduces it
-// against every row with warp shuffles; the combine/update happens in registers.
+// One CTA owns PP latent positions x all CFG branches: the normalised rows live in shared memory; each warp streams
+// CW out_proj weight rows at a time (L2-resident, 80 x d fp32) against every row -- a [BR*PP x CW] register tile per
+// lane, lanes splitting K, so one weight float4 and one row float4 feed CW and BR*PP FMAs x 4 respectively -- and
+// reduces with warp shuffles; the combine/update happens in registers.  128 CTAs for 640 positions: one wave.
 #include "common.cuh"
 #include "../../include/echo_b200.h"
 
 namespace {
-constexpr int PP = 2;
+constexpr int PP = 5, CW = 5;
 
+template <int BR>
 __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_constant__ echo_tail_desc D) {
   extern __shared__ float sm[];
   const int nrows = D.branches * PP;
@@ -48,27 +50,32 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
   }
   __syncthreads();
 
-  for (int o = warp; o < D.latent; o += 8) {
-    const float4* w = reinterpret_cast<const float4*>(D.w_out + (long long)o * D.d);
-    float acc[3 * PP];
+  for (int o0 = warp * CW; o0 < D.latent; o0 += 8 * CW) {
+    float acc[BR * PP][CW];
 #pragma unroll
-    for (int r = 0; r < 3 * PP; ++r) acc[r] = 0.f;
+    for (int r = 0; r < BR * PP; ++r)
+#pragma unroll
+      for (int j = 0; j < CW; ++j) acc[r][j] = 0.f;
+    const float4* w = reinterpret_cast<const float4*>(D.w_out + (long long)o0 * D.d);
     for (int c = lane; c < nvec; c += 32) {
-      const float4 wv = __ldg(w + c);
+      float4 wv[CW];
 #pragma unroll
-      for (int r = 0; r < 3 * PP; ++r) {
-        if (r < nrows) {
-          const float4 xv = reinterpret_cast<const float4*>(srow + (size_t)r * D.d)[c];
-          acc[r] = fmaf(wv.x, xv.x, fmaf(wv.y, xv.y, fmaf(wv.z, xv.z, fmaf(wv.w, xv.w, acc[r]))));
-        }
+      for (int j = 0; j < CW; ++j) wv[j] = (o0 + j < D.latent) ? __ldg(w + (long long)j * nvec + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < BR * PP; ++r) {
+        const float4 xv = reinterpret_cast<const float4*>(srow + (size_t)r * D.d)[c];
+#pragma unroll
+        for (int j = 0; j < CW; ++j)
+          acc[r][j] = fmaf(wv[j].x, xv.x, fmaf(wv[j].y, xv.y, fmaf(wv[j].z, xv.z, fmaf(wv[j].w, xv.w, acc[r][j]))));
       }
     }
-    const float b = __ldg(D.b_out + o);
 #pragma unroll
-    for (int r = 0; r < 3 * PP; ++r) {
-      if (r < nrows) {
-        const float s = warp_sum(acc[r]);
-        if (lane == 0) sv[r * D.latent + o] = s + b;
+    for (int j = 0; j < CW; ++j) {
+      const float b = (o0 + j < D.latent) ? __ldg(D.b_out + o0 + j) : 0.f;
+#pragma unroll
+      for (int r = 0; r < BR * PP; ++r) {
+        const float sum = warp_sum(acc[r][j]);
+        if (lane == 0 && o0 + j < D.latent) sv[r * D.latent + o0 + j] = sum + b;
       }
     }
   }
@@ -117,12 +124,17 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
   ECHO_CHECK_ARG(d->update_x || d->v_out || d->v_comb_out, "tail: nothing to write");
   ECHO_CHECK_ARG(d->n_delta >= 0 && (d->n_delta == 0 || (d->delta && d->delta_stride % 4 == 0)), "tail: bad delta arguments");
   const size_t smem = ((size_t)d->branches * PP * (d->d + d->latent)) * sizeof(float);
+  ECHO_CHECK_ARG(smem <= 220 * 1024, "tail: d = %d too wide for the shared-memory row cache", d->d);
   static size_t configured = 0;
   if (smem > configured) {
-    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  ECHO_CUDA(echo_launch(cfg_euler_tail_kernel, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
+  if (d->branches == 3)
+    ECHO_CUDA(echo_launch(cfg_euler_tail_kernel<3>, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
+  else
+    ECHO_CUDA(echo_launch(cfg_euler_tail_kernel<1>, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
