@@ -81,6 +81,36 @@ def test_model_call_compat_vs_oracle(tiny_model):
     assert rel_l2(got.cpu(), ref) < V_TOL
 
 
+def test_long_reference_force_speaker_batch_vs_oracle(tiny_model):
+    """BASELINE.json configs[3] in miniature (tiny architecture so the CPU oracle finishes in seconds): 5-minute speaker
+    reference = 6400 latents = 1600 cached speaker keys (25 key tiles per row, ragged valid lengths per prompt), text
+    padded to 768 with different valid lengths, Force-Speaker speaker_kv_scale 1.5 on the first layer for t >= 0.9, B = 3."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    cfg = S.ECHO_TINY
+    sd = S.synth_state_dict(S.dit_schema(cfg))
+    g = torch.Generator().manual_seed(21)
+    ids, mask, _ = O.text_ids_and_mask(["first prompt, the longest of the three by some margin", "second", "a third one"], 768)
+    spk = torch.randn(3, 6400, 80, generator=g)
+    smask = torch.ones(3, 6400, dtype=torch.bool)
+    smask[1, 3000:] = False
+    smask[2, 215:] = False
+    noise = torch.randn(3, 96, 80, generator=g)
+    kw = dict(num_steps=6, cfg_scale_text=3.0, cfg_scale_speaker=8.0, cfg_min_t=0.5, cfg_max_t=1.0, truncation_factor=None,
+              rescale_k=None, rescale_sigma=None, speaker_kv_scale=1.5, speaker_kv_max_layers=1, speaker_kv_min_t=0.9,
+              sequence_length=96)
+    otrace, trace = [], []
+    ref = O.sample_euler_cfg_independent_guidances(sd, cfg, spk, smask, ids, mask, 0, noise=noise, trace=otrace, **kw)
+    out = sample(tiny_model, spk.cuda(), smask.cuda(), ids.cuda(), mask.cuda(), 0, _noise=noise, _trace=trace, **kw).cpu()
+    assert len(trace) == len(otrace) == 6
+    for a, b in zip(trace, otrace):
+        assert a["has_cfg"] == b["has_cfg"]
+        for br_a, br_b in zip(a["v_branches"].cpu().chunk(3 if a["has_cfg"] else 1, 0),
+                              b["v_branches"].chunk(3 if b["has_cfg"] else 1, 0)):
+            assert rel_l2(br_a, br_b) < V_TOL
+    assert rel_l2(out, ref) < X_TOL
+
+
 def test_blockwise_vs_reference_fixture(tiny_model):
     from echo_tts_b200.inference_blockwise import sample_blockwise_euler_cfg_independent_guidances as sample
     g = torch.load(os.path.join(GOLDEN, "dit_tiny_blockwise.pt"))
