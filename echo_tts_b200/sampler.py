@@ -126,9 +126,6 @@ def sample_euler_cfg_independent_guidances(
              rescale_sigma=rescale_sigma)
     plan = StepPlan(dev, num_steps, cfg_min_t, cfg_max_t, speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t,
                     cfg.num_layers)
-    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)                           # inference.py:482
-    kv_spk = model.get_kv_cache_speaker(speaker_latent)                                    # inference.py:483
-    masks = _prep_masks(model, text_mask, speaker_mask)
     if _noise is not None:
         x_t = _noise.to(dev, F32).clone()
     else:
@@ -137,39 +134,46 @@ def sample_euler_cfg_independent_guidances(
     if truncation_factor is not None:
         x_t = x_t * truncation_factor
 
-    if _trace is not None or not _use_graphs():
-        mod = model.build_mod_table(plan.t_dev)
-        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, trace=_trace)
-        return x_t.view(B, S, cfg.latent_size)
+    def conditioning(ids, tmask, spk, smask):
+        kv_t = model.get_kv_cache_text(ids, tmask)                                         # inference.py:482
+        kv_s = model.get_kv_cache_speaker(spk)                                             # inference.py:483
+        return kv_t, kv_s, _prep_masks(model, tmask, smask)
 
-    # ---- CUDA-graph path: static buffers keyed by everything baked into the captured launches ----
-    key = ("euler", B, S, text_input_ids.shape[1], kv_spk[0][0].shape[1], num_steps, tuple(plan.has_cfg),
+    key = ("euler", B, S, text_input_ids.shape[1], speaker_latent.shape[1], num_steps, tuple(plan.has_cfg),
            p["cfg_scale_text"], p["cfg_scale_speaker"], rescale_k, rescale_sigma, plan.uses_kv_scale)
     cache = model.__dict__.setdefault("_graphs", {})
     ent: _GraphEntry = cache.setdefault(key, _GraphEntry())
     ent.calls += 1
-    if ent.calls == 1:                      # first request with this shape: plain launches (also warms kernels up)
+    if _trace is not None or not _use_graphs() or ent.calls == 1:
+        # plain launches: parity traces, ECHO_CUDA_GRAPH=0, and the first request with a new shape (warms kernels up)
+        if _trace is not None or not _use_graphs():
+            ent.calls -= 1
+        kv_text, kv_spk, masks = conditioning(text_input_ids, text_mask, speaker_latent, speaker_mask)
         mod = model.build_mod_table(plan.t_dev)
-        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p)
+        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, trace=_trace)
         return x_t.view(B, S, cfg.latent_size)
+
+    # ---- CUDA-graph path: conditioning encoders + all Euler steps are ONE captured graph over static input buffers,
+    #      keyed by everything baked into the captured launches (shapes, schedule, guidance constants) ----
     st = ent.static
     if ent.graph is None:
+        st["ids"] = text_input_ids.to(dev, torch.int32).contiguous().clone()
+        st["tmask"] = text_mask.to(dev).contiguous().clone()
+        st["spk"] = speaker_latent.to(dev, F32).contiguous().clone()
+        st["smask"] = speaker_mask.to(dev).contiguous().clone()
         st["x_t"] = x_t.clone()
-        st["mod"] = model.build_mod_table(plan.t_dev)
-        st["masks"] = tuple(m.clone() for m in masks)
-        H = cfg.num_heads
-        st["kv_text"] = KVList.from_buffer(kv_text.buf.clone(), B, kv_text[0][0].shape[1], H)
-        st["kv_spk"] = KVList.from_buffer(kv_spk.buf.clone(), B, kv_spk[0][0].shape[1], H)
+        st["mod"] = model.build_mod_table(plan.t_dev)     # depends on the schedule only (part of the key)
         st["plan"] = plan
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            run_steps(model, st["x_t"], plan, st["mod"], B, st["masks"], st["kv_text"], st["kv_spk"], p)
+            kv_text, kv_spk, masks = conditioning(st["ids"], st["tmask"], st["spk"], st["smask"])
+            run_steps(model, st["x_t"], plan, st["mod"], B, masks, kv_text, kv_spk, p)
         ent.graph = g
+    st["ids"].copy_(text_input_ids)
+    st["tmask"].copy_(text_mask)
+    st["spk"].copy_(speaker_latent)
+    st["smask"].copy_(speaker_mask)
     st["x_t"].copy_(x_t)
-    for dst, src in zip(st["masks"], masks):
-        dst.copy_(src)
-    st["kv_text"].buf.copy_(kv_text.buf)
-    st["kv_spk"].buf.copy_(kv_spk.buf)
     if plan.uses_kv_scale:
         st["plan"].kv_mult.copy_(plan.kv_mult)
     st["plan"].sched.copy_(plan.sched)
