@@ -343,11 +343,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
       const int m0 = mt * (2 * BM) + (int)rank * BM;
       const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
+      EpiPre<EPI> pre;
+      epilogue_prefetch_t<EPI>(T.bn, P, lane, half, batch, m0 + q * 32, nt * T.bn, pre);
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
       TmemLoader2 L{tmem_base + as * ACC_COLS + lane_base};
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, split,
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre, split,
                           split * T.split_stride);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
@@ -375,7 +377,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::tc_fence_after();
       if (trace && warp == 2 && lane == 0) trace[5] = clock64();
       TmemLoader2 L{tacc};
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, 0, 0);
+      EpiPre<EPI> pre;
+      epilogue_prefetch_t<EPI>(T.bn, P, lane, half, batch, m0 + q * 32, nt * T.bn, pre);
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre, 0, 0);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }

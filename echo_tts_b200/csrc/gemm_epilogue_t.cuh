@@ -164,19 +164,30 @@ struct GenCtx {
   }
 };
 
-template <class Loader>
-__device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
-                                              const EpiRows& R) {
-  if (R.nrows <= 0) return;                               // warp-uniform; nothing was promised to TMEM readers
+__device__ __forceinline__ GenCtx gen_ctx(const EpiParams& P, const EpiRows& R, int lane) {
   // gate row of local row r is g0 + ((rem0 + r) >= rows_per_gate) when rows_per_gate >= 32
   const int rpg = P.rows_per_gate;
   const long long g0 = R.mg0 / rpg;
-  GenCtx C{P, R, lane & 7, lane >> 3, rpg, (int)(R.mg0 - g0 * rpg), g0, rpg >= 32};
+  return GenCtx{P, R, lane & 7, lane >> 3, rpg, (int)(R.mg0 - g0 * rpg), g0, rpg >= 32};
+}
+// The first chunk's residual rows do not depend on the accumulator: they are requested BEFORE the warp waits for the
+// tile's MMAs, so their latency is off the exposed epilogue of the last tile (and of every other one).
+__device__ __forceinline__ void epi_t_generic_prefetch(const int BN, const EpiParams& P, int lane, const EpiRows& R,
+                                                       GenAux& A) {
+  if (R.nrows <= 0) return;
+  const GenCtx C = gen_ctx(P, R, lane);
+  if (R.half * 32 < min(BN, P.n - R.n0)) C.load(R.half * 32, A);
+}
+template <class Loader>
+__device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
+                                              const EpiRows& R, GenAux& A) {
+  if (R.nrows <= 0) return;                               // warp-uniform; nothing was promised to TMEM readers
+  const GenCtx C = gen_ctx(P, R, lane);
   const int cend = min(BN, P.n - R.n0);                   // columns of this tile that exist (multiple of 8)
   // this warp's chunks: half*32, +64, ...; two aux buffers alternate so that chunk k+1's loads fly during chunk k
-  GenAux A, B;
+  // (A arrives pre-loaded with the first chunk's rows: epi_t_generic_prefetch)
+  GenAux B;
   int c = R.half * 32;
-  if (c < cend) C.load(c, A);
 #pragma unroll 1
   for (; c < cend; c += 128) {
     const bool has_b = c + 64 < cend;
@@ -193,6 +204,32 @@ struct SecAux {
   float2 co[8], si[8];
 };
 
+// norm weight + RoPE rows of one 32-column chunk (columns h0 + c .. of the tile) for this lane's 4 columns x 8 rows
+__device__ __forceinline__ void sec_load_aux(const EpiParams& P, const EpiRows& R, int lane, int h0, int c, SecAux& A) {
+  const int cg = lane & 7, rsub = lane >> 3;
+  const int sec_idx = R.n0 / P.section_width;
+  const EpiSection& S = P.sec[sec_idx];
+  const int sec_col0 = R.n0 - sec_idx * P.section_width;
+  const int hd = P.head_dim;
+  const bool norm = S.type == ECHO_SEC_NORM_ROPE;
+  const bool do_rope = (norm || S.type == ECHO_SEC_ROPE) && (sec_col0 + h0) / hd < P.rope_heads;
+  const int col = sec_col0 + h0 + c + 4 * cg;               // first of this lane's 4 columns inside the section
+  A.w = norm ? __ldg(reinterpret_cast<const float4*>(S.norm_w + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
+  if (do_rope) {                                            // lane's columns = rotary pairs p0, p0 + 1 of the head
+    const int seq0 = R.mb0 % P.rows_per_seq;                // sequence index of local row 0
+    const int p0 = (c + 4 * cg) >> 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = 4 * i + rsub;
+      int sq = seq0 + r;
+      if (sq >= P.rows_per_seq) sq %= P.rows_per_seq;
+      const long long off = (long long)(P.pos_offset + sq * P.pos_stride) * (hd / 2) + p0;
+      const bool ok = r < R.nrows;
+      A.co[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_cos + off)) : make_float2(1.f, 1.f);
+      A.si[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_sin + off)) : make_float2(0.f, 0.f);
+    }
+  }
+}
 template <class Loader>
 __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
                                                const EpiRows& R) {
@@ -202,27 +239,9 @@ __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P,
   const EpiSection S = P.sec[sec_idx];
   const int sec_col0 = R.n0 - sec_idx * P.section_width;   // column of the tile inside its section
   const int hd = P.head_dim;
-  const int seq0 = R.mb0 % P.rows_per_seq;                 // sequence index of local row 0
   const long long ld = P.ld_sec_out;
   const bool norm = S.type == ECHO_SEC_NORM_ROPE;
 
-  auto load_aux = [&](int h0, int c, bool do_rope, SecAux& A) {
-    const int col = sec_col0 + h0 + c + 4 * cg;             // first of this lane's 4 columns inside the section
-    A.w = norm ? __ldg(reinterpret_cast<const float4*>(S.norm_w + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
-    if (do_rope) {                                          // lane's columns = rotary pairs p0, p0 + 1 of the head
-      const int p0 = (c + 4 * cg) >> 1;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int r = 4 * i + rsub;
-        int sq = seq0 + r;
-        if (sq >= P.rows_per_seq) sq %= P.rows_per_seq;
-        const long long off = (long long)(P.pos_offset + sq * P.pos_stride) * (hd / 2) + p0;
-        const bool ok = r < R.nrows;
-        A.co[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_cos + off)) : make_float2(1.f, 1.f);
-        A.si[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_sin + off)) : make_float2(0.f, 0.f);
-      }
-    }
-  };
   auto process = [&](int h0, int c, bool do_rope, float rstd, const SecAux& A) {
     float v[32];
     L.load32(h0 + c, v);
@@ -261,8 +280,8 @@ __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P,
     // this warp's chunks of the head: c = half*32 (+64 when the head is 128 wide); their aux loads go out first
     const int c0 = R.half * 32, c1 = c0 + 64;
     SecAux A0, A1;
-    load_aux(h0, c0, do_rope, A0);
-    if (c1 < hd) load_aux(h0, c1, do_rope, A1);
+    sec_load_aux(P, R, lane, h0, c0, A0);
+    if (c1 < hd) sec_load_aux(P, R, lane, h0, c1, A1);
     float rstd = 1.f;
     if (norm) {                                            // row-per-thread: sum of squares over the whole head
       float ssq = 0.f;
@@ -308,14 +327,31 @@ __device__ __forceinline__ void epi_t_swiglu(const int BN, const EpiParams& P, L
   }
 }
 
-template <int EPI, class Loader>
-__device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
-                                               int batch_idx, int mb0, int n0, int split = 0, long long out_off = 0) {
+// What an epilogue can fetch before its accumulator exists (kept in registers across the wait for the MMAs).
+template <int EPI> struct EpiPre {};
+template <> struct EpiPre<ECHO_EPI_GENERIC> { GenAux a; };
+// (SECTIONS: holding the RoPE rows of the first chunk across the wait costs 36 registers and spills; measured slower)
+
+__device__ __forceinline__ EpiRows epi_rows(const EpiParams& P, int half, int batch_idx, int mb0, int n0, int split,
+                                            long long out_off) {
   EpiRows R;
   R.batch_idx = batch_idx; R.mb0 = mb0; R.n0 = n0; R.half = half; R.split = split; R.out_off = out_off;
   R.nrows = min(32, max(0, P.rows - mb0));
   R.mg0 = (long long)batch_idx * P.rows + mb0;
-  if (EPI == ECHO_EPI_GENERIC) epi_t_generic(BN, P, L, sc, lane, R);
-  else if (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
+  return R;
+}
+template <int EPI>
+__device__ __forceinline__ void epilogue_prefetch_t(const int BN, const EpiParams& P, int lane, int half, int batch_idx,
+                                                    int mb0, int n0, EpiPre<EPI>& pre) {
+  const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, 0, 0);
+  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic_prefetch(BN, P, lane, R, pre.a);
+}
+template <int EPI, class Loader>
+__device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
+                                               int batch_idx, int mb0, int n0, EpiPre<EPI>& pre, int split = 0,
+                                               long long out_off = 0) {
+  const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, split, out_off);
+  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic(BN, P, L, sc, lane, R, pre.a);
+  else if constexpr (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
   else epi_t_swiglu(BN, P, L, sc, lane, R);
 }
