@@ -100,6 +100,7 @@ EXPORTS = {
     "echo_attention": (C.c_int, [C.POINTER(AttnDesc), c_p]),
     "echo_mask_extent": (C.c_int, [c_p, C.c_int, C.c_int, i64, c_p, c_p]),
     "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),
+    "echo_cfg_combine_euler": (C.c_int, [C.POINTER(TailDesc), c_p]),
     "echo_step_advance": (C.c_int, [c_p, c_p]),
     "echo_embedding": (C.c_int, [c_p, C.c_int, c_p, C.c_int, c_p, c_p]),
     "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),

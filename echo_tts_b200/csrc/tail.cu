@@ -9,6 +9,39 @@
 namespace {
 constexpr int PP = 5, CW = 5;
 
+// v = v_c + a (v_c - v_ut) + b (v_c - v_us)  (inference.py:526-530), optional temporal score rescale (inference.py:431-443),
+// x += v dt (inference.py:558)
+__device__ __forceinline__ float combine3(const echo_tail_desc& D, float vc, float vt, float vs) {
+  return vc + D.cfg_text * (vc - vt) + D.cfg_speaker * (vc - vs);
+}
+__device__ __forceinline__ float rescale_and_step(const echo_tail_desc& D, float v, float t, float dt, long long xi) {
+  if (D.update_x) {
+    const float x = D.x_t[xi];
+    if (D.use_rescale && t < 1.f) {
+      const float omt = 1.f - t;
+      const float snr = (omt * omt) / (t * t);
+      const float sg2 = D.rescale_sigma * D.rescale_sigma;
+      const float ratio = (snr * sg2 + 1.f) / (snr * sg2 / D.rescale_k + 1.f);
+      v = 1.f / omt * (ratio * (omt * v + x) - x);
+    }
+    D.x_t[xi] = x + v * dt;
+  }
+  if (D.v_comb_out) D.v_comb_out[xi] = v;
+  return v;
+}
+
+// Combine-only variant for the multi-GPU CFG-branch split: v_out holds the three gathered branch velocities
+// fp32 [3][positions][latent] (INPUT); everything else as in the fused tail.
+__global__ void __launch_bounds__(256) cfg_combine_euler_kernel(const __grid_constant__ echo_tail_desc D) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int s = D.step ? D.step[0] : 0;
+  const float t = D.sched[s * 4 + 0], dt = D.sched[s * 4 + 1];
+  const long long n = (long long)D.positions * D.latent;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    rescale_and_step(D, combine3(D, D.v_out[i], D.v_out[n + i], D.v_out[2 * n + i]), t, dt, i);
+}
+
 template <int BR>
 __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_constant__ echo_tail_desc D) {
   extern __shared__ float sm[];
@@ -97,21 +130,9 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
         D.v_out[((long long)1 * D.positions + p) * D.latent + c] = vt;
         D.v_out[((long long)2 * D.positions + p) * D.latent + c] = vs;
       }
-      v = vc + D.cfg_text * (vc - vt) + D.cfg_speaker * (vc - vs);   // inference.py:526-530
+      v = combine3(D, vc, vt, vs);
     }
-    const long long xi = (long long)p * D.latent + c;
-    if (D.update_x) {
-      const float x = D.x_t[xi];
-      if (D.use_rescale && t < 1.f) {                                  // inference.py:431-443
-        const float omt = 1.f - t;
-        const float snr = (omt * omt) / (t * t);
-        const float sg2 = D.rescale_sigma * D.rescale_sigma;
-        const float ratio = (snr * sg2 + 1.f) / (snr * sg2 / D.rescale_k + 1.f);
-        v = 1.f / omt * (ratio * (omt * v + x) - x);
-      }
-      D.x_t[xi] = x + v * dt;                                          // inference.py:558
-    }
-    if (D.v_comb_out) D.v_comb_out[xi] = v;
+    rescale_and_step(D, v, t, dt, (long long)p * D.latent + c);
   }
 }
 }  // namespace
@@ -135,6 +156,17 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
     ECHO_CUDA(echo_launch(cfg_euler_tail_kernel<3>, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
   else
     ECHO_CUDA(echo_launch(cfg_euler_tail_kernel<1>, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t stream) {
+  ECHO_CHECK_ARG(d && d->v_out && d->sched && d->positions > 0 && d->latent > 0, "combine: null argument");
+  ECHO_CHECK_ARG(!d->update_x || d->x_t, "combine: x_t required when update_x");
+  const long long n = (long long)d->positions * d->latent;
+  const int grid = (int)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
+  ECHO_CUDA(echo_launch(cfg_combine_euler_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, *d));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

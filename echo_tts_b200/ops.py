@@ -296,6 +296,22 @@ def cfg_euler_tail(h, norm_w, w_out, b_out, *, positions, branches, eps, x_t=Non
     L.check(L.load().echo_cfg_euler_tail(C.byref(d), L.stream()))
 
 
+def cfg_combine_euler(v3: torch.Tensor, x_t: torch.Tensor, sched: torch.Tensor, *, cfg_text: float, cfg_speaker: float,
+                      rescale_k=None, rescale_sigma=None, v_comb_out=None) -> None:
+    """v3 fp32 [3, positions, latent] (cond | text-dropped | speaker-dropped) -> x_t fp32 [positions, latent] += v dt."""
+    _need(v3, F32, "v3"); _need(x_t, F32, "x_t"); _need(sched, F32, "sched")
+    assert v3.dim() == 3 and v3.shape[0] == 3 and v3.is_contiguous() and x_t.is_contiguous()
+    d = L.TailDesc()
+    d.v_out, d.x_t, d.v_comb_out, d.sched = v3.data_ptr(), x_t.data_ptr(), L.ptr(v_comb_out), sched.data_ptr()
+    d.positions, d.latent, d.branches = v3.shape[1], v3.shape[2], 3
+    assert x_t.numel() == v3.shape[1] * v3.shape[2]
+    d.cfg_text, d.cfg_speaker = cfg_text, cfg_speaker
+    d.use_rescale = int(rescale_k is not None and rescale_sigma is not None)
+    d.rescale_k, d.rescale_sigma = (rescale_k or 1.0), (rescale_sigma or 0.0)
+    d.update_x = 1
+    L.check(L.load().echo_cfg_combine_euler(C.byref(d), L.stream()))
+
+
 def step_advance(step: torch.Tensor) -> None:
     L.check(L.load().echo_step_advance(step.data_ptr(), L.stream()))
 

@@ -206,6 +206,10 @@ typedef struct echo_tail_desc {
   int64_t delta_stride;
 } echo_tail_desc;
 int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream);
+/* Combine-only variant for the multi-GPU CFG-branch split: d->v_out is INPUT, the three branch
+ * velocities fp32 [3][positions][latent] gathered from the branch ranks; h / norm_w / w_out / b_out are ignored.
+ * Same combine, rescale and Euler arithmetic as echo_cfg_euler_tail (inference.py:526-530, 431-443, 558). */
+int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t stream);
 int echo_step_advance(int32_t* step, echo_stream_t stream); /* step[0] += 1 */
 
 /* text embedding lookup (model.py:420): ids int32 [n] -> out fp32 [n, d] */

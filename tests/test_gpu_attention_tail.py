@@ -146,6 +146,26 @@ def test_cfg_euler_tail(ops, branches, rescale):
     assert rel_l2(x.cpu(), x0.cpu() + v * tt[1]) < 1e-5
 
 
+@pytest.mark.parametrize("rescale", [False, True])
+def test_cfg_combine_euler_equals_fused_tail(ops, rescale):
+    """The combine-only kernel of the multi-GPU CFG-branch split = the fused tail fed with the same branch velocities."""
+    B, S, D, lat = 2, 41, 256, 80
+    P = B * S
+    h = _rand((3 * P, D), 30, 2.0)
+    nw, w, b = _rand((D,), 31).abs() + 0.5, _rand((lat, D), 32, D ** -0.5), _rand((lat,), 33)
+    x0 = _rand((P, lat), 34)
+    sched = torch.tensor([0.61, -0.025, 0, 0], device="cuda", dtype=F32)
+    kw = dict(cfg_text=3.0, cfg_speaker=8.0, rescale_k=1.2 if rescale else None, rescale_sigma=3.0 if rescale else None)
+    x_fused, v3 = x0.clone(), torch.empty((3 * P, lat), device="cuda")
+    ops.cfg_euler_tail(h, nw, w, b, positions=P, branches=3, eps=1e-5, x_t=x_fused, sched=sched, v_out=v3, **kw)
+    x_split, vcomb = x0.clone(), torch.empty((P, lat), device="cuda")
+    ops.cfg_combine_euler(v3.view(3, P, lat), x_split, sched, v_comb_out=vcomb, **kw)
+    assert rel_l2(x_split, x_fused) < 1e-6
+    a, bb, c = v3.chunk(3, 0)
+    if not rescale:
+        assert rel_l2(vcomb, a + 3.0 * (a - bb) + 8.0 * (a - c)) < 1e-6
+
+
 def test_small_kernels(ops):
     from oracle import echo_oracle as O
     t = torch.tensor([0.999, 0.5, 0.0123], device="cuda")

@@ -21,6 +21,13 @@ def test_shard_indices_cover_exactly_once():
         serving.shard_indices(4, 2, 2)
 
 
+def test_branch_rows_follow_reference_mask_layout():
+    """cond | text-dropped | speaker-dropped blocks of B rows (reference inference.py:494-497)."""
+    assert [serving.branch_rows(r, 4) for r in range(3)] == [slice(0, 4), slice(4, 8), slice(8, 12)]
+    with pytest.raises(ValueError):
+        serving.branch_rows(3, 4)
+
+
 def test_run_sharded_without_process_group():
     assert serving.run_sharded(["a", "bb"], lambda s, i: (i, len(s))) == [(0, 1), (1, 2)]
 
