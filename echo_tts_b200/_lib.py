@@ -76,6 +76,7 @@ class TailDesc(C.Structure):
         ("positions", i32), ("d", i32), ("latent", i32), ("branches", i32),
         ("eps", f32), ("cfg_text", f32), ("cfg_speaker", f32), ("rescale_k", f32), ("rescale_sigma", f32),
         ("use_rescale", i32), ("update_x", i32), ("n_delta", i32), ("delta", c_p), ("delta_stride", i64),
+        ("v_peer", c_p * 2), ("flag_peer", c_p * 2), ("wait_flag", c_p * 2), ("wait_value", i32), ("_pad_tail", i32),
     ]
 
 
@@ -101,6 +102,7 @@ EXPORTS = {
     "echo_mask_extent": (C.c_int, [c_p, C.c_int, C.c_int, i64, c_p, c_p]),
     "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),
     "echo_cfg_combine_euler": (C.c_int, [C.POINTER(TailDesc), c_p]),
+    "echo_cfg_tail_ctas": (C.c_int, [C.c_int]),
     "echo_step_advance": (C.c_int, [c_p, c_p]),
     "echo_embedding": (C.c_int, [c_p, C.c_int, c_p, C.c_int, c_p, c_p]),
     "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),

@@ -35,6 +35,20 @@ __device__ __forceinline__ float rescale_and_step(const echo_tail_desc& D, float
 __global__ void __launch_bounds__(256) cfg_combine_euler_kernel(const __grid_constant__ echo_tail_desc D) {
   pdl_launch_dependents();
   pdl_wait();
+  if (D.wait_flag[0]) {
+    // fused exchange: the other two ranks' tail kernels pushed their branch velocities into our v_out over NVLink and
+    // then bumped these counters (release, system scope).  Bounded wait: a lost peer traps instead of hanging the GPU.
+    if (threadIdx.x < 2) {
+      const int32_t* f = D.wait_flag[threadIdx.x];
+      int v = 0;
+      const long long t0 = clock64();
+      do {
+        asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if (v < D.wait_value && clock64() - t0 > 6000000000LL) { printf("echo: CFG-split peer never arrived\n"); __trap(); }
+      } while (v < D.wait_value);
+    }
+    __syncthreads();
+  }
   const int s = D.step ? D.step[0] : 0;
   const float t = D.sched[s * 4 + 0], dt = D.sched[s * 4 + 1];
   const long long n = (long long)D.positions * D.latent;
@@ -123,6 +137,10 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
     const float vc = sv[(0 * PP + pl) * D.latent + c];
     float v = vc;
     if (D.v_out) D.v_out[((long long)0 * D.positions + p) * D.latent + c] = vc;
+    if (D.v_peer[0]) {      // branches == 1: push this rank's branch velocity into the two other ranks' gather buffers
+      D.v_peer[0][(long long)p * D.latent + c] = vc;
+      D.v_peer[1][(long long)p * D.latent + c] = vc;
+    }
     if (D.branches == 3) {
       const float vt = sv[(1 * PP + pl) * D.latent + c];
       const float vs = sv[(2 * PP + pl) * D.latent + c];
@@ -134,6 +152,12 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
     }
     rescale_and_step(D, v, t, dt, (long long)p * D.latent + c);
   }
+  if (D.flag_peer[0]) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < 2)
+      asm volatile("red.release.sys.global.add.s32 [%0], %1;" ::"l"(D.flag_peer[threadIdx.x]), "r"(1) : "memory");
+  }
 }
 }  // namespace
 
@@ -144,6 +168,8 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
   ECHO_CHECK_ARG(!d->update_x || (d->x_t && d->sched), "tail: x_t/sched required when update_x");
   ECHO_CHECK_ARG(d->update_x || d->v_out || d->v_comb_out, "tail: nothing to write");
   ECHO_CHECK_ARG(d->n_delta >= 0 && (d->n_delta == 0 || (d->delta && d->delta_stride % 4 == 0)), "tail: bad delta arguments");
+  ECHO_CHECK_ARG(!d->v_peer[0] || (d->branches == 1 && d->v_peer[1] && d->flag_peer[0] && d->flag_peer[1]),
+                 "tail: the fused exchange needs branches == 1, two peer buffers and two peer counters");
   const size_t smem = ((size_t)d->branches * PP * (d->d + d->latent)) * sizeof(float);
   ECHO_CHECK_ARG(smem <= 220 * 1024, "tail: d = %d too wide for the shared-memory row cache", d->d);
   static size_t configured = 0;
@@ -164,6 +190,7 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
 extern "C" int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t stream) {
   ECHO_CHECK_ARG(d && d->v_out && d->sched && d->positions > 0 && d->latent > 0, "combine: null argument");
   ECHO_CHECK_ARG(!d->update_x || d->x_t, "combine: x_t required when update_x");
+  ECHO_CHECK_ARG(!d->wait_flag[0] || d->wait_flag[1], "combine: two wait counters or none");
   const long long n = (long long)d->positions * d->latent;
   const int grid = (int)((n + 255) / 256 < 1184 ? (n + 255) / 256 : 1184);
   ECHO_CUDA(echo_launch(cfg_combine_euler_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, *d));
@@ -171,3 +198,6 @@ extern "C" int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t str
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
 }
+
+/* CTAs echo_cfg_euler_tail launches for `positions` rows (each adds 1 to the peer counters of the fused exchange). */
+extern "C" int echo_cfg_tail_ctas(int positions) { return ceil_div(positions, PP); }

@@ -276,9 +276,14 @@ def mask_extent(mask: torch.Tensor) -> torch.Tensor:
 
 def cfg_euler_tail(h, norm_w, w_out, b_out, *, positions, branches, eps, x_t=None, sched=None, step=None,
                    cfg_text=0.0, cfg_speaker=0.0, rescale_k=None, rescale_sigma=None, v_out=None, v_comb_out=None,
-                   update_x=True, delta=None) -> None:
+                   update_x=True, delta=None, push_to=None) -> None:
+    """``push_to``: ((v_peer0, flag_peer0), (v_peer1, flag_peer1)) P2P-mapped tensors on the two other ranks of a
+    CFG-branch split (branches == 1): the kernel stores its velocities there too and bumps the counters."""
     _need(h, F32, "h")
     d = L.TailDesc()
+    if push_to is not None:
+        for k, (vp, fp) in enumerate(push_to):
+            d.v_peer[k], d.flag_peer[k] = vp.data_ptr(), fp.data_ptr()
     if delta is not None:
         _need(delta, F32, "delta")
         assert delta.dim() == 3 and delta.shape[1:] == h.shape and delta.is_contiguous() and h.is_contiguous()
@@ -297,8 +302,10 @@ def cfg_euler_tail(h, norm_w, w_out, b_out, *, positions, branches, eps, x_t=Non
 
 
 def cfg_combine_euler(v3: torch.Tensor, x_t: torch.Tensor, sched: torch.Tensor, *, cfg_text: float, cfg_speaker: float,
-                      rescale_k=None, rescale_sigma=None, v_comb_out=None) -> None:
-    """v3 fp32 [3, positions, latent] (cond | text-dropped | speaker-dropped) -> x_t fp32 [positions, latent] += v dt."""
+                      rescale_k=None, rescale_sigma=None, v_comb_out=None, wait=None) -> None:
+    """v3 fp32 [3, positions, latent] (cond | text-dropped | speaker-dropped) -> x_t fp32 [positions, latent] += v dt.
+    ``wait``: (counter0, counter1, value): spin until both int32 device counters (bumped by the peers' tail kernels)
+    reach ``value`` before reading v3."""
     _need(v3, F32, "v3"); _need(x_t, F32, "x_t"); _need(sched, F32, "sched")
     assert v3.dim() == 3 and v3.shape[0] == 3 and v3.is_contiguous() and x_t.is_contiguous()
     d = L.TailDesc()
@@ -309,6 +316,8 @@ def cfg_combine_euler(v3: torch.Tensor, x_t: torch.Tensor, sched: torch.Tensor, 
     d.use_rescale = int(rescale_k is not None and rescale_sigma is not None)
     d.rescale_k, d.rescale_sigma = (rescale_k or 1.0), (rescale_sigma or 0.0)
     d.update_x = 1
+    if wait is not None:
+        d.wait_flag[0], d.wait_flag[1], d.wait_value = wait[0].data_ptr(), wait[1].data_ptr(), int(wait[2])
     L.check(L.load().echo_cfg_combine_euler(C.byref(d), L.stream()))
 
 

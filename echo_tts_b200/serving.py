@@ -56,6 +56,27 @@ def max_over_ranks_ms(ms: float, device: Optional[torch.device] = None, group=No
 # ----------------------------------------------------------------------------------------------------------------
 # Optional latency mode: CFG-branch split over three GPUs.
 # ----------------------------------------------------------------------------------------------------------------
+_P2P_CACHE: dict = {}
+
+
+def _p2p_buffers(group, rank: int, P: int, latent: int, dev):
+    """Symmetric (peer-mapped) gather buffers of the fused exchange, one rendezvous per (group, shape)."""
+    import torch.distributed._symmetric_memory as symm
+    key = (id(group), P, latent)
+    ent = _P2P_CACHE.get(key)
+    if ent is None:
+        F32 = torch.float32
+        v3_all = symm.empty((2, 3, P, latent), dtype=F32, device=dev)            # double-buffered by guided-step parity
+        flags = symm.empty((4,), dtype=torch.int32, device=dev)                  # counter s: CTAs of sender s seen so far
+        hv, hf = symm.rendezvous(v3_all, group), symm.rendezvous(flags, group)
+        others = [r for r in range(3) if r != rank]
+        peer_v = [hv.get_buffer(r, (2, 3, P, latent), F32) for r in others]
+        peer_f = [hf.get_buffer(r, (4,), torch.int32) for r in others]
+        ent = (v3_all, flags, hf, peer_v, peer_f, hv)
+        _P2P_CACHE[key] = ent
+    return ent[:5]
+
+
 def branch_rows(rank: int, B: int) -> slice:
     """Rows of the (cond | text-dropped | speaker-dropped) mask layout (reference ``inference.py:494-497``) that branch
     rank ``rank`` (0, 1, 2) evaluates."""
@@ -69,13 +90,15 @@ def sample_euler_cfg_split(model, speaker_latent, speaker_mask, text_input_ids, 
                            cfg_scale_text: float, cfg_scale_speaker: float, cfg_min_t: float, cfg_max_t: float,
                            truncation_factor, rescale_k, rescale_sigma, speaker_kv_scale, speaker_kv_max_layers,
                            speaker_kv_min_t, sequence_length: Optional[int] = None, *, group=None,
-                           _noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+                           exchange: str = "nccl", _noise: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``sample_euler_cfg_independent_guidances`` with the three guidance branches of every CFG step evaluated on
     three GPUs (ranks 0/1/2 of ``group`` = cond / text-dropped / speaker-dropped; every rank holds the full model and
     receives the same inputs and seed).  Per CFG step: one forward over B rows instead of 3B, ONE all-gather of the
     branch velocities ([B, S, 80] fp32 per rank) over NCCL/NVLink, then the combine + rescale + Euler update
     redundantly on every rank, so x_t stays bit-identical across ranks without a broadcast.  Un-guided steps run
-    replicated.  A latency feature for few prompts (about 3x fewer tokens per GPU on guided steps); for throughput
+    replicated.  ``exchange="p2p"`` fuses the exchange into the kernels instead of calling NCCL: the tail kernel of
+    every rank stores its velocities straight into the other two ranks' gather buffers (symmetric memory, NVLink peer
+    stores) and bumps a counter there; the combine kernel waits on its two counters.  No collective launch at all.  A latency feature for few prompts (about 3x fewer tokens per GPU on guided steps); for throughput
     use ``run_sharded`` instead."""
     from . import ops
     from .sampler import StepPlan, _prep_masks, INIT_SCALE  # noqa: F401
@@ -102,21 +125,45 @@ def sample_euler_cfg_split(model, speaker_latent, speaker_mask, text_input_ids, 
     mod = model.build_mod_table(plan.t_dev)
     use_rescale = rescale_k is not None and rescale_sigma is not None
     mine = branch_rows(rank, B)
-    v3 = torch.empty((3, B * S, cfg.latent_size), device=dev, dtype=F32)
+    P = B * S
+    if exchange == "p2p":
+        lib = __import__("echo_tts_b200._lib", fromlist=["load"]).load()
+        v3_all, flags, hf, peer_v, peer_f = _p2p_buffers(group, rank, P, cfg.latent_size, dev)
+        others = [r for r in range(3) if r != rank]
+        flags.zero_()
+        torch.cuda.synchronize()
+        hf.barrier()                                                             # nobody pushes before everyone zeroed
+        ctas, n_guided = int(lib.echo_cfg_tail_ctas(P)), 0
+    elif exchange == "nccl":
+        v3 = torch.empty((3, P, cfg.latent_size), device=dev, dtype=F32)
+    else:
+        raise ValueError(f"exchange must be 'nccl' or 'p2p', got {exchange!r}")
     for i, has_cfg in enumerate(plan.has_cfg):
         rows = mine if has_cfg else slice(0, B)
         h, pending = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[rows], text_extent=te3[rows],
                                           spk_mask=sm3[rows], spk_extent=se3[rows], kv_text=kv_text, kv_speaker=kv_spk,
                                           spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
-        if has_cfg:
-            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=1, eps=cfg.norm_eps,
+        if has_cfg and exchange == "p2p":
+            par, n_guided = n_guided & 1, n_guided + 1
+            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
+                               v_out=v3_all[par, rank], update_x=False, delta=pending,
+                               push_to=[(pv[par, rank], pf[rank:rank + 1]) for pv, pf in zip(peer_v, peer_f)])
+            ops.cfg_combine_euler(v3_all[par], x_t.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
+                                  cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
+                                  rescale_sigma=rescale_sigma if use_rescale else None,
+                                  wait=(flags[others[0]:others[0] + 1], flags[others[1]:others[1] + 1], ctas * n_guided))
+        elif has_cfg:
+            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
                                v_out=v3[rank], update_x=False, delta=pending)
             dist.all_gather_into_tensor(v3.view(-1), v3[rank].view(-1), group=group)
-            ops.cfg_combine_euler(v3, x_t.view(B * S, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
+            ops.cfg_combine_euler(v3, x_t.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
                                   cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
                                   rescale_sigma=rescale_sigma if use_rescale else None)
         else:
             ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=1, eps=cfg.norm_eps,
                                x_t=x_t, sched=plan.sched[i], rescale_k=rescale_k if use_rescale else None,
                                rescale_sigma=rescale_sigma if use_rescale else None, delta=pending)
+    if exchange == "p2p":
+        torch.cuda.synchronize()
+        hf.barrier()               # peers may still be reading / writing our symmetric buffers: free them together
     return x_t.view(B, S, cfg.latent_size)

@@ -204,12 +204,23 @@ typedef struct echo_tail_desc {
   int32_t n_delta;          /* deferred residual update of the last projection: h += sum_s delta[s * delta_stride + ...] */
   const float* delta;       /* fp32 [n_delta][rows][ldh] or NULL */
   int64_t delta_stride;
+  /* Multi-GPU CFG-branch split with the exchange fused into the kernels (peer memory over NVLink, no NCCL call):
+   * echo_cfg_euler_tail with branches = 1 additionally stores its velocities at v_peer[0..1] (the same slot of the two
+   * other ranks' gather buffers, P2P-mapped) and then adds 1 per CTA to flag_peer[0..1] (system-scope release);
+   * echo_cfg_combine_euler first waits until wait_flag[0..1] (this rank's counters for the two other senders) reach
+   * wait_value.  All NULL / 0 = off. */
+  float* v_peer[2];
+  int32_t* flag_peer[2];
+  const int32_t* wait_flag[2];
+  int32_t wait_value, _pad_tail;
 } echo_tail_desc;
 int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream);
 /* Combine-only variant for the multi-GPU CFG-branch split: d->v_out is INPUT, the three branch
  * velocities fp32 [3][positions][latent] gathered from the branch ranks; h / norm_w / w_out / b_out are ignored.
  * Same combine, rescale and Euler arithmetic as echo_cfg_euler_tail (inference.py:526-530, 431-443, 558). */
 int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t stream);
+/* CTAs one echo_cfg_euler_tail launch uses for `positions` rows = increments per launch of each flag_peer counter. */
+int echo_cfg_tail_ctas(int positions);
 int echo_step_advance(int32_t* step, echo_stream_t stream); /* step[0] += 1 */
 
 /* text embedding lookup (model.py:420): ids int32 [n] -> out fp32 [n, d] */

@@ -49,6 +49,8 @@ def main():
             return r, serving.max_over_ranks_ms(e0.elapsed_time(e1) / args.reps, torch.device("cuda", local), group)
         split, ms_split = timed(lambda: serving.sample_euler_cfg_split(model, spk, smask, ids, mask, 0, group=group,
                                                                         _noise=noise, **kw))
+        split_p2p, ms_p2p = timed(lambda: serving.sample_euler_cfg_split(model, spk, smask, ids, mask, 0, group=group,
+                                                                          exchange="p2p", _noise=noise, **kw))
         os.environ["ECHO_CUDA_GRAPH"] = "0"
         single_eager, ms_eager = timed(lambda: sample(model, spk, smask, ids, mask, 0, _noise=noise, **kw))
         os.environ["ECHO_CUDA_GRAPH"] = "1"
@@ -60,8 +62,9 @@ def main():
             same = all(torch.equal(gathered[0], g) for g in gathered[1:])
             out = dict(check="cfg_split", arch="tiny" if args.tiny else "base", steps=kw["num_steps"], S=kw["sequence_length"],
                        rel_l2_vs_single_gpu=rel, ranks_bit_identical=same, ms_split_3gpu=ms_split,
+                       p2p_equals_nccl=bool(torch.equal(split_p2p, split)), ms_split_3gpu_p2p=ms_p2p,
                        ms_single_gpu_eager=ms_eager, ms_single_gpu_graph=ms_graph)
-            assert rel < 1e-2 and same, out      # bf16 paths with different GEMM summation splits
+            assert rel < 1e-2 and same and out["p2p_equals_nccl"], out      # bf16 paths with different GEMM summation splits
     dist.barrier()
     if rank == 0:
         print(json.dumps(out), flush=True)
