@@ -50,8 +50,21 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
   const int nvec = d >> 2;
   const bool live = row < m;
   pdl_launch_dependents();
-  pdl_wait();
   float4 v[VEC], dl[NORM_MAX_DELTA][VEC], sc[VEC], sh[VEC];
+  if (live && !step) {   // the modulation table is not produced by the previous kernel: request it before waiting
+    const long long g = row / rows_per_mod;
+    const float4* scp = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
+    const float4* shp = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      const int c = t + i * 128;
+      if (c < nvec) {
+        sc[i] = __ldg(scp + c);
+        sh[i] = shp ? __ldg(shp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  pdl_wait();
   if (live) {
     const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
 #pragma unroll
@@ -70,16 +83,17 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
         }
       }
     }
-    long long g = row / rows_per_mod;
-    if (step) g += (long long)step[0] * mod_step_stride;
-    const float4* scp = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
-    const float4* shp = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
+    if (step) {            // table row depends on a device-side step counter the previous kernel may have advanced
+      const long long g = row / rows_per_mod + (long long)step[0] * mod_step_stride;
+      const float4* scp = reinterpret_cast<const float4*>(scale1 + g * mod_ld);
+      const float4* shp = shift ? reinterpret_cast<const float4*>(shift + g * mod_ld) : nullptr;
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) {
-      const int c = t + i * 128;
-      if (c < nvec) {
-        sc[i] = __ldg(scp + c);
-        sh[i] = shp ? __ldg(shp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = 0; i < VEC; ++i) {
+        const int c = t + i * 128;
+        if (c < nvec) {
+          sc[i] = __ldg(scp + c);
+          sh[i] = shp ? __ldg(shp + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
     }
   }
