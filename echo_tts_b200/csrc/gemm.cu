@@ -189,6 +189,8 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   P.kind = d->epilogue; P.rows = d->rows; P.n = d->n; P.act = d->act;
   P.bias = d->bias; P.gate = d->gate; P.gate_ld = d->gate_ld; P.rows_per_gate = d->rows_per_gate > 0 ? d->rows_per_gate : 1;
   P.resid = d->resid; P.ld_resid = d->ld_resid; P.out_f32 = d->out_f32; P.ld_out_f32 = d->ld_out_f32;
+  P.red_resid = (d->impl == 2 && d->resid && d->resid == d->out_f32 && d->ld_resid == d->ld_out_f32 && !d->out_bf16 &&
+                 !d->out2_bf16 && d->k_splits <= 1) ? 1 : 0;
   P.out_bf16 = (bf16*)d->out_bf16; P.ld_out_bf16 = d->ld_out_bf16;
   P.out2_bf16 = (bf16*)d->out2_bf16; P.ld_out2_bf16 = d->ld_out2_bf16; P.snake_alpha = d->snake_alpha;
   P.n_sections = d->n_sections; P.section_width = d->section_width; P.head_dim = d->head_dim;

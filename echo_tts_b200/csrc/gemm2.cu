@@ -173,6 +173,8 @@ __device__ __forceinline__ void sk_sideload(const Tiling& T, const Unit& w, int 
 struct TmemLoader2 {
   uint32_t taddr;
   __device__ __forceinline__ void load32(int col, float* v) { ptx::tmem_ld32(taddr + (uint32_t)col, v); }
+  __device__ __forceinline__ void issue32(int col, float* v) { ptx::tmem_ld32_issue(taddr + (uint32_t)col, v); }
+  __device__ __forceinline__ void wait() { ptx::tmem_ld_wait(); }
 };
 // accumulator += side stage (TMEM -> registers -> TMEM), this warp's chunks
 __device__ __forceinline__ void sk_merge(int bn, uint32_t tacc, uint32_t tside, int half) {

@@ -28,6 +28,8 @@ struct EpiParams {
   const float* bias;
   const float* gate; long long gate_ld; int rows_per_gate;
   const float* resid; long long ld_resid;
+  int red_resid;             // resid aliases out_f32 and nothing else consumes the sum: the pair kernel issues
+                             // x += delta as a vector reduction (no residual load on the epilogue's critical path)
   float* out_f32; long long ld_out_f32;
   bf16* out_bf16; long long ld_out_bf16;
   bf16* out2_bf16; long long ld_out2_bf16;

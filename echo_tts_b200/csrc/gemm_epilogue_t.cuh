@@ -35,6 +35,12 @@ __device__ __forceinline__ float4 sc_load4(const float* sc, int row, int cg) {
                : "memory");
   return x;
 }
+// x[0..3] += v as ONE fire-and-forget vector reduction executed in the L2 (sm_90+): the in-place residual update
+// without reading the residual in the epilogue (its rows are usually back in DRAM by then: ~3 k clocks per chunk on
+// the exposed last epilogue of every launch)
+__device__ __forceinline__ void red_add_f32x4(float* p, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ void store_bf16x4(bf16* p, float4 x) {
   *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(x.x, x.y), pack_bf16x2(x.z, x.w));
 }
@@ -68,7 +74,7 @@ struct GenCtx {
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     const int n = R.n0 + c + 4 * cg;
     const bool nok = n < P.n;                            // n % 8 == 0: a 4-column group is all in or all out
-    const float* rp = P.resid ? P.resid + R.mg0 * P.ld_resid + n : nullptr;
+    const float* rp = (P.resid && !P.red_resid) ? P.resid + R.mg0 * P.ld_resid + n : nullptr;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = 4 * i + rsub;
@@ -133,7 +139,12 @@ struct GenCtx {
 #pragma unroll
       for (int i = 0; i < 8; ++i) { x[i].x += A.rv[i].x; x[i].y += A.rv[i].y; x[i].z += A.rv[i].z; x[i].w += A.rv[i].w; }
     }
-    if (P.out_f32) {
+    if (P.red_resid) {       // x[i] holds the update only (A.rv is zero): out_f32 += x
+      float* o = P.out_f32 + R.mg0 * P.ld_out_f32 + n;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (nok && 4 * i + rsub < R.nrows) red_add_f32x4(o + (long long)(4 * i + rsub) * P.ld_out_f32, x[i]);
+    } else if (P.out_f32) {
       float* o = P.out_f32 + R.out_off + R.mg0 * P.ld_out_f32 + n;
 #pragma unroll
       for (int i = 0; i < 8; ++i)
