@@ -195,17 +195,25 @@ __device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, 
   if (R.nrows <= 0) return;                               // warp-uniform; nothing was promised to TMEM readers
   const GenCtx C = gen_ctx(P, R, lane);
   const int cend = min(BN, P.n - R.n0);                   // columns of this tile that exist (multiple of 8)
-  // this warp's chunks: half*32, +64, ...; two aux buffers alternate so that chunk k+1's loads fly during chunk k
-  // (A arrives pre-loaded with the first chunk's rows: epi_t_generic_prefetch)
-  GenAux B;
+  // this warp's chunks: half*32, +64, ...  ONE rolled call site of process(): the ~300-instruction body then stays in
+  // the instruction cache from the second chunk on (the unrolled two-site version spent 20 % of the exposed epilogue on
+  // instruction fetch).  A arrives pre-loaded with the first chunk's residual rows (epi_t_generic_prefetch); chunk
+  // k+1's rows are requested into B before chunk k is processed.
   int c = R.half * 32;
+  if (P.red_resid) {                                     // nothing to fetch ahead: x += update goes out as reductions
+#pragma unroll
+    for (int i = 0; i < 8; ++i) A.rv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
-  for (; c < cend; c += 128) {
-    const bool has_b = c + 64 < cend;
-    if (has_b) C.load(c + 64, B);
+    for (; c < cend; c += 64) C.process(c, A, L, sc, lane);
+    return;
+  }
+#pragma unroll 1
+  for (; c < cend; c += 64) {
+    GenAux B;
+    const bool has_next = c + 64 < cend;
+    if (has_next) C.load(c + 64, B);
     C.process(c, A, L, sc, lane);
-    if (c + 128 < cend) C.load(c + 128, A);
-    if (has_b) C.process(c + 64, B, L, sc, lane);
+    if (has_next) A = B;
   }
 }
 

@@ -90,11 +90,29 @@ def main():
         def f_norm(i):
             ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0))
 
+        def f_seq(i):      # one decoder layer in launch order: cross-kernel effects (instruction cache, L2 state, PDL hand-offs)
+            f_norm(i); f_qkvg(i); f_attn(i)
+            if ns > 1:
+                f_wo_split(i); f_addnorm(i)
+            else:
+                f_wo(i); f_norm(i)
+            f_w13(i)
+            if ns > 1:
+                f_w2_split(i)
+            else:
+                f_w2(i)
+
+        def f_seq2(i):     # the same launches, each kernel twice in a row (2 layers' worth): isolates per-kernel cold-start cost
+            for f in ([f_norm, f_qkvg, f_attn] + ([f_wo_split, f_addnorm] if ns > 1 else [f_wo, f_norm]) + [f_w13] +
+                      ([f_w2_split] if ns > 1 else [f_w2])):
+                f(2 * i); f(2 * i + 1)
+
         keys = 640 + 256 + 53
         valid = [keys, 640 + 53, 640 + 256][:R] if R == 3 else [keys] * R
         cases = [("qkvg", f_qkvg, 2.0 * M * 4 * D * D), ("wo", f_wo, 2.0 * M * D * D), ("w13", f_w13, 2.0 * M * 2 * F_ * D),
                  ("w2", f_w2, 2.0 * M * D * F_), ("attn", f_attn, sum(4.0 * S * lv * D for lv in valid)),
                  ("norm", f_norm, 0.0)]
+        cases += [("seq", f_seq, 0.0), ("seq2", f_seq2, 0.0)]
         if ns > 1:
             cases += [(f"wo/s{ns}", f_wo_split, 2.0 * M * D * D), (f"w2/s{ns}", f_w2_split, 2.0 * M * D * F_),
                       ("addnorm", f_addnorm, 0.0)]
@@ -125,10 +143,12 @@ def main():
                 e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / n
-            tot_us += us; tot_fl += fl
+            if name not in ("seq", "seq2"):
+                tot_us += us; tot_fl += fl
             extra = f"{fl / us / 1e6:8.1f} TFLOP/s" if fl else f"{M * D * 6 / us / 1e3:8.1f} GB/s"
             print(f"M={M:5d} {name:5s} {us:8.2f} us  {extra}", flush=True)
-        print(f"M={M:5d} layer {tot_us:8.2f} us  {tot_fl / tot_us / 1e6:8.1f} TFLOP/s  (x24 = {tot_us * 24 / 1e3:.2f} ms/step)", flush=True)
+        if tot_us > 0:
+            print(f"M={M:5d} layer {tot_us:8.2f} us  {tot_fl / tot_us / 1e6:8.1f} TFLOP/s  (x24 = {tot_us * 24 / 1e3:.2f} ms/step)", flush=True)
 
 
 if __name__ == "__main__":
