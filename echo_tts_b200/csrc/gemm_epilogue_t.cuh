@@ -313,8 +313,11 @@ __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P,
       }
       rstd = rsqrtf(ssq / (float)hd + P.eps);
     }
-    process(h0, c0, do_rope, rstd, A0);
-    if (c1 < hd) process(h0, c1, do_rope, rstd, A1);
+#pragma unroll 1
+    for (int c = c0; c < hd; c += 64) {                   // one rolled call site (instruction-cache footprint)
+      process(h0, c, do_rope, rstd, A0);
+      A0 = A1;
+    }
   }
 }
 
