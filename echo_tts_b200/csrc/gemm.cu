@@ -186,6 +186,7 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   for (int i = 0; i < 8; ++i) G.tap_shift[i] = d->tap_shift[i];
   G.rows = d->rows; G.n = d->n; G.lda = d->lda; G.a_batch_stride = d->a_batch_stride; G.ldb = d->ldb;
   G.a = (const bf16*)d->a; G.b = (const bf16*)d->b;
+  ECHO_CHECK_ARG((long long)d->rows * d->batch < (1LL << 31), "gemm: rows * batch must fit 31 bits");
   P.kind = d->epilogue; P.rows = d->rows; P.n = d->n; P.act = d->act;
   P.bias = d->bias; P.gate = d->gate; P.gate_ld = d->gate_ld; P.rows_per_gate = d->rows_per_gate > 0 ? d->rows_per_gate : 1;
   P.resid = d->resid; P.ld_resid = d->ld_resid; P.out_f32 = d->out_f32; P.ld_out_f32 = d->ld_out_f32;

@@ -80,7 +80,7 @@ struct Sched {
     }
     if (unit >= end) return false;
     w.tile = unit / splits; w.split = unit - w.tile * splits;
-    w.kb0 = (int)((long long)total_kb * w.split / splits); w.kb1 = (int)((long long)total_kb * (w.split + 1) / splits);
+    w.kb0 = total_kb * w.split / splits; w.kb1 = total_kb * (w.split + 1) / splits;      // 32-bit: k-blocks x splits is tiny
     unit += step;
     return true;
   }

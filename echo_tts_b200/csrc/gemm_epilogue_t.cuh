@@ -178,8 +178,8 @@ struct GenCtx {
 __device__ __forceinline__ GenCtx gen_ctx(const EpiParams& P, const EpiRows& R, int lane) {
   // gate row of local row r is g0 + ((rem0 + r) >= rows_per_gate) when rows_per_gate >= 32
   const int rpg = P.rows_per_gate;
-  const long long g0 = R.mg0 / rpg;
-  return GenCtx{P, R, lane & 7, lane >> 3, rpg, (int)(R.mg0 - g0 * rpg), g0, rpg >= 32};
+  const unsigned g0 = (unsigned)R.mg0 / (unsigned)rpg;    // rows fit 32 bits (checked at launch); avoids the 64-bit divide routine
+  return GenCtx{P, R, lane & 7, lane >> 3, rpg, (int)((unsigned)R.mg0 - g0 * (unsigned)rpg), (long long)g0, rpg >= 32};
 }
 // The first chunk's residual rows do not depend on the accumulator: they are requested BEFORE the warp waits for the
 // tile's MMAs, so their latency is off the exposed epilogue of the last tile (and of every other one).
