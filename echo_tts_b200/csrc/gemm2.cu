@@ -497,6 +497,8 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, v
   }
   switch (epi) {
     case ECHO_EPI_GENERIC:
+      if (P.act == ECHO_ACT_NONE && !P.out_bf16 && !P.out2_bf16)
+        return launch_pair_t<EPI_GENERIC_LEAN>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
       return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
     case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);
     default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);

@@ -14,7 +14,10 @@
 #pragma once
 #include "gemm_epilogue.cuh"
 
-constexpr int EPI_SC_FLOATS = 32 * 32;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
+constexpr int EPI_SC_FLOATS = 32 * 32;
+// Kernel-internal epilogue id: GENERIC without activation / bf16 / Snake outputs (the DiT's two residual projections
+// and their split-K form).  Same arithmetic as GENERIC; the point is a small, contiguous instruction footprint.
+constexpr int EPI_GENERIC_LEAN = 3;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
 
 // The scratch is addressed in the shared state space explicitly: through a generic pointer the compiler emits
 // generic LD/ST (address translation, long-scoreboard latency) instead of LDS/STS.
@@ -82,7 +85,7 @@ struct GenCtx {
     }
   }
 
-  template <class Loader>
+  template <bool LEAN, class Loader>
   __device__ __forceinline__ void process(int c, const GenAux& A, Loader& L, float* sc, int lane) const {
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f), one4 = make_float4(1.f, 1.f, 1.f, 1.f);
     const int n = R.n0 + c + 4 * cg;
@@ -100,7 +103,7 @@ struct GenCtx {
     float4 x[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) x[i] = sc_load4(sc, 4 * i + rsub, cg);
-    if (P.act == ECHO_ACT_NONE && (!P.gate || (gate_fast && !two_gates))) {
+    if ((LEAN || P.act == ECHO_ACT_NONE) && (!P.gate || (gate_fast && !two_gates))) {
       // the DiT projections: x = (acc + bias) * g + resid as one FMA per element
       const float4 bg = make_float4(bias.x * glo.x, bias.y * glo.y, bias.z * glo.z, bias.w * glo.w);
 #pragma unroll
@@ -111,10 +114,10 @@ struct GenCtx {
     } else {
 #pragma unroll
       for (int i = 0; i < 8; ++i) { x[i].x += bias.x; x[i].y += bias.y; x[i].z += bias.z; x[i].w += bias.w; }
-      if (P.act == ECHO_ACT_GELU) {
+      if (!LEAN && P.act == ECHO_ACT_GELU) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) { x[i].x = geluf_(x[i].x); x[i].y = geluf_(x[i].y); x[i].z = geluf_(x[i].z); x[i].w = geluf_(x[i].w); }
-      } else if (P.act == ECHO_ACT_SILU) {
+      } else if (!LEAN && P.act == ECHO_ACT_SILU) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) { x[i].x = siluf_(x[i].x); x[i].y = siluf_(x[i].y); x[i].z = siluf_(x[i].z); x[i].w = siluf_(x[i].w); }
       }
@@ -150,13 +153,13 @@ struct GenCtx {
       for (int i = 0; i < 8; ++i)
         if (nok && 4 * i + rsub < R.nrows) *reinterpret_cast<float4*>(o + (long long)(4 * i + rsub) * P.ld_out_f32) = x[i];
     }
-    if (P.out_bf16) {
+    if (!LEAN && P.out_bf16) {
       bf16* o = P.out_bf16 + R.mg0 * P.ld_out_bf16 + n;
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         if (nok && 4 * i + rsub < R.nrows) store_bf16x4(o + (long long)(4 * i + rsub) * P.ld_out_bf16, x[i]);
     }
-    if (P.out2_bf16) {
+    if (!LEAN && P.out2_bf16) {
       bf16* o = P.out2_bf16 + R.mg0 * P.ld_out2_bf16 + n;
       const float4 alpha = nok ? __ldg(reinterpret_cast<const float4*>(P.snake_alpha + n)) : one4;
       const float4 ia = make_float4(__fdividef(1.f, alpha.x + 1e-9f), __fdividef(1.f, alpha.y + 1e-9f),
@@ -189,7 +192,7 @@ __device__ __forceinline__ void epi_t_generic_prefetch(const int BN, const EpiPa
   const GenCtx C = gen_ctx(P, R, lane);
   if (R.half * 32 < min(BN, P.n - R.n0)) C.load(R.half * 32, A);
 }
-template <class Loader>
+template <bool LEAN, class Loader>
 __device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
                                               const EpiRows& R, GenAux& A) {
   if (R.nrows <= 0) return;                               // warp-uniform; nothing was promised to TMEM readers
@@ -204,7 +207,7 @@ __device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, 
 #pragma unroll
     for (int i = 0; i < 8; ++i) A.rv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
-    for (; c < cend; c += 64) C.process(c, A, L, sc, lane);
+    for (; c < cend; c += 64) C.template process<LEAN>(c, A, L, sc, lane);
     return;
   }
 #pragma unroll 1
@@ -212,7 +215,7 @@ __device__ __forceinline__ void epi_t_generic(const int BN, const EpiParams& P, 
     GenAux B;
     const bool has_next = c + 64 < cend;
     if (has_next) C.load(c + 64, B);
-    C.process(c, A, L, sc, lane);
+    C.template process<LEAN>(c, A, L, sc, lane);
     if (has_next) A = B;
   }
 }
@@ -352,6 +355,7 @@ __device__ __forceinline__ void epi_t_swiglu(const int BN, const EpiParams& P, L
 // What an epilogue can fetch before its accumulator exists (kept in registers across the wait for the MMAs).
 template <int EPI> struct EpiPre {};
 template <> struct EpiPre<ECHO_EPI_GENERIC> { GenAux a; };
+template <> struct EpiPre<EPI_GENERIC_LEAN> { GenAux a; };
 // (SECTIONS: holding the RoPE rows of the first chunk across the wait costs 36 registers and spills; measured slower)
 
 __device__ __forceinline__ EpiRows epi_rows(const EpiParams& P, int half, int batch_idx, int mb0, int n0, int split,
@@ -366,14 +370,15 @@ template <int EPI>
 __device__ __forceinline__ void epilogue_prefetch_t(const int BN, const EpiParams& P, int lane, int half, int batch_idx,
                                                     int mb0, int n0, EpiPre<EPI>& pre) {
   const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, 0, 0);
-  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic_prefetch(BN, P, lane, R, pre.a);
+  if constexpr (EPI == ECHO_EPI_GENERIC || EPI == EPI_GENERIC_LEAN) epi_t_generic_prefetch(BN, P, lane, R, pre.a);
 }
 template <int EPI, class Loader>
 __device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
                                                int batch_idx, int mb0, int n0, EpiPre<EPI>& pre, int split = 0,
                                                long long out_off = 0) {
   const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, split, out_off);
-  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic(BN, P, L, sc, lane, R, pre.a);
+  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic<false>(BN, P, L, sc, lane, R, pre.a);
+  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_generic<true>(BN, P, L, sc, lane, R, pre.a);
   else if constexpr (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
   else epi_t_swiglu(BN, P, L, sc, lane, R);
 }
