@@ -80,6 +80,31 @@ class TailDesc(C.Structure):
     ]
 
 
+class DitLayer(C.Structure):
+    _fields_ = [("w_qkvg", c_p), ("w_o", c_p), ("w13", c_p), ("w2", c_p), ("q_norm", c_p), ("k_norm", c_p)]
+
+
+class DitKV(C.Structure):
+    _fields_ = [
+        ("k", C.POINTER(c_p)), ("v", C.POINTER(c_p)), ("row_stride", i64), ("batch_stride", i64),
+        ("len", i32), ("kv_batch_mod", i32), ("mask", c_p), ("mask_stride", i64), ("extent", c_p), ("kv_scale", c_p),
+    ]
+
+
+class DitStepDesc(C.Structure):
+    _fields_ = [
+        ("n_layers", i32), ("d", i32), ("heads", i32), ("head_dim", i32), ("ffn", i32), ("latent", i32),
+        ("eps", f32), ("rope_len", i32),
+        ("layers", C.POINTER(DitLayer)), ("in_w", c_p), ("in_b", c_p), ("rope_cos", c_p), ("rope_sin", c_p),
+        ("x_in", c_p), ("x_rows", i32), ("rows", i32), ("seq", i32), ("pos_offset", i32),
+        ("mod", c_p), ("mod_row_stride", i64), ("mod_rows", i32), ("k_splits", i32),
+        ("prefix", DitKV), ("text", DitKV), ("speaker", DitKV),
+        ("x", c_p), ("xn", c_p), ("qkvg", c_p), ("ao", c_p), ("hmid", c_p), ("delta", c_p),
+        ("gemm_workspace", c_p), ("gemm_workspace_bytes", i64), ("gemm_impl", i32), ("attn_impl", i32),
+        ("tail", C.POINTER(TailDesc)), ("pending_out", C.POINTER(i32)),
+    ]
+
+
 EPI_GENERIC, EPI_SECTIONS, EPI_SWIGLU = 0, 1, 2
 ACT_NONE, ACT_GELU, ACT_SILU = 0, 1, 2
 SEC_PLAIN, SEC_NORM_ROPE, SEC_SIGMOID, SEC_ROPE = 0, 1, 2, 3
@@ -103,6 +128,8 @@ EXPORTS = {
     "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),
     "echo_cfg_combine_euler": (C.c_int, [C.POINTER(TailDesc), c_p]),
     "echo_cfg_tail_ctas": (C.c_int, [C.c_int]),
+    "echo_dit_step": (C.c_int, [C.POINTER(DitStepDesc), c_p]),
+    "echo_dit_sample": (C.c_int, [C.POINTER(DitStepDesc), C.POINTER(DitStepDesc), C.c_int, c_p, i64, i64, i64, c_p]),
     "echo_step_advance": (C.c_int, [c_p, c_p]),
     "echo_embedding": (C.c_int, [c_p, C.c_int, c_p, C.c_int, c_p, c_p]),
     "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),

@@ -11,6 +11,7 @@ bf16 tensor-core operands with fp32 accumulation, fp32 softmax statistics.
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -287,66 +288,103 @@ class EchoDiT:
         tiles = -(-M // 256) * -(-self.cfg.model_size // 256)
         return max(1, min(4, 74 // tiles, self.cfg.model_size // 64))
 
-    def forward_hidden(self, x_in: torch.Tensor, mod: torch.Tensor, B: int, *, text_mask, text_extent, spk_mask,
-                       spk_extent, kv_text: KVCache, kv_speaker: KVCache, kv_latent: Optional[KVCache] = None,
-                       start_pos: int = 0, n_prefix: int = 0, spk_scale: Optional[torch.Tensor] = None,
-                       x_rows: Optional[int] = None):
-        """x_in fp32 [x_rows*S... see below] -> (final residual stream fp32 [R*S, D], pending delta or None): when
-        the forward runs split-K the last w2's partial products [splits, R*S, D] are still to be added to the stream
-        (the sampler tail does it).
+    def _layer_array(self):
+        """HOST array of per-layer weight pointers for echo_dit_step (built once; the tensors live in self.layers)."""
+        arr = self.__dict__.get("_c_layers")
+        if arr is None:
+            arr = (L.DitLayer * len(self.layers))()
+            for l, lw in enumerate(self.layers):
+                arr[l].w_qkvg, arr[l].w_o = lw["qkvg"].data_ptr(), lw["wo"].data_ptr()
+                arr[l].w13, arr[l].w2 = lw["w13"].data_ptr(), lw["w2"].data_ptr()
+                arr[l].q_norm, arr[l].k_norm = lw["qn"].data_ptr(), lw["kn"].data_ptr()
+            self._c_layers = arr
+        return arr
 
-        x_in: [Bx, S, latent] fp32 with Bx == R (one input per row) or Bx == B (CFG: the three branches
-        share x_t, inference.py:516 -- in_proj is evaluated once per prompt and broadcast).
-        mod:  fp32 [R or 1, L, 2, 3, D] modulation rows (row g serves rows g*S..); text_mask/spk_mask
-        uint8/bool [R, L_t] / [R, L_s] (patch rate) with their extents; spk_scale: fp32 [L] per-layer
-        speaker K/V multiplier (speaker_kv_scale, inference.py:420-428) or None.
-        """
+    def _fill_kv(self, dst: "L.DitKV", cache: KVCache, R: int, B: int, keep: list, *, length=None, mask=None,
+                 extent=None, kv_scale=None) -> None:
         cfg = self.cfg
-        D, H, Lr = cfg.model_size, cfg.num_heads, cfg.num_layers
+        H, Dh = cfg.num_heads, cfg.head_dim
+        assert len(cache) == cfg.num_layers
+        k0 = cache[0][0]
+        dst.len = k0.shape[1] if length is None else length
+        if dst.len > 0:
+            for k, v in cache:
+                for t in (k, v):
+                    if not t.is_cuda or t.dtype != BF16:
+                        raise RuntimeError("kv cache: bf16 CUDA tensors required (no CPU fallback)")
+                    assert t.shape == k0.shape and t.stride() == k0.stride()
+            assert k0.shape[2:] == (H, Dh) and k0.stride(3) == 1 and k0.stride(2) == Dh and dst.len <= k0.shape[1]
+            ka = (C.c_void_p * len(cache))(*[k.data_ptr() for k, _ in cache])
+            va = (C.c_void_p * len(cache))(*[v.data_ptr() for _, v in cache])
+            keep += [ka, va]
+            dst.k, dst.v = C.cast(ka, C.POINTER(C.c_void_p)), C.cast(va, C.POINTER(C.c_void_p))
+            dst.row_stride, dst.batch_stride = k0.stride(1), k0.stride(0)
+        dst.kv_batch_mod = B if k0.shape[0] != R else 0
+        if mask is not None:
+            assert mask.is_cuda and mask.dtype in (torch.bool, torch.uint8) and mask.shape[0] >= R
+            assert mask.stride(1) == 1 and mask.shape[1] >= dst.len
+            dst.mask, dst.mask_stride = mask.data_ptr(), mask.stride(0)
+        if extent is not None:
+            assert extent.is_cuda and extent.dtype == torch.int32 and extent.numel() >= R and extent.is_contiguous()
+            dst.extent = extent.data_ptr()
+        if kv_scale is not None:
+            assert kv_scale.is_cuda and kv_scale.dtype == F32 and kv_scale.numel() >= cfg.num_layers and kv_scale.is_contiguous()
+            dst.kv_scale = kv_scale.data_ptr()
+
+    def step_desc(self, x_in: torch.Tensor, mod: torch.Tensor, B: int, R: int, *, text_mask, text_extent, spk_mask,
+                  spk_extent, kv_text: KVCache, kv_speaker: KVCache, kv_latent: Optional[KVCache] = None,
+                  start_pos: int = 0, n_prefix: int = 0, spk_scale: Optional[torch.Tensor] = None,
+                  tail: Optional["L.TailDesc"] = None):
+        """Descriptor of one velocity evaluation for ``echo_dit_step`` (+ the objects it points into, to be kept alive
+        by the caller until the launch calls have returned).
+
+        x_in: fp32 [Bx, S, latent] with Bx == R (one input per row) or R % Bx == 0 (CFG: the three branches share x_t,
+        inference.py:516 -- in_proj is evaluated once per prompt and written to every branch).
+        mod: fp32 [R or 1, L, 2, 3, D] modulation rows (row g serves rows g*S..); text_mask/spk_mask uint8/bool
+        [>= R, L_t] / [>= R, L_s] (patch rate) with their extents; spk_scale: fp32 [L] per-layer speaker K/V multiplier
+        (speaker_kv_scale, inference.py:420-428) or None; ``tail``: ops.tail_desc(...) to fuse out_norm / out_proj /
+        CFG combine / Euler behind the forward."""
+        cfg = self.cfg
+        for t, name in ((x_in, "x_in"), (mod, "mod")):
+            if not t.is_cuda or t.dtype != F32:
+                raise RuntimeError(f"{name}: fp32 CUDA tensor required (no CPU fallback)")
         Bx, S, lat = x_in.shape
-        R = text_mask.shape[0]
-        M = R * S
+        assert x_in.is_contiguous() and lat == cfg.latent_size and R % Bx == 0
+        assert mod.dim() == 5 and mod.shape[1:] == (cfg.num_layers, 2, 3, cfg.model_size) and mod[0].is_contiguous()
+        assert mod.shape[0] in (1, R)
         ws = self.workspace(R, S)
-        x, xn, qkvg, ao, hmid, delta = ws["x"], ws["xn"], ws["qkvg"], ws["ao"], ws["h"], ws["delta"]
-        pending = None          # split-K partial products not yet added to x
-        # in_proj (fp32, model.py:586); for CFG rows the same [B*S, D] result is written to all three branches
-        xin2 = x_in.reshape(Bx * S, lat)
-        reps = R // Bx
-        ops.sgemm(xin2.unsqueeze(0).expand(reps, -1, -1) if reps > 1 else xin2,
-                  self.in_w.unsqueeze(0).expand(reps, -1, -1) if reps > 1 else self.in_w,
-                  bias=self.in_b, out=x.view(reps, Bx * S, D) if reps > 1 else x)
-        mod_rows = mod.shape[0]
-        rows_per_mod = S if mod_rows > 1 else 0
-        mod_ld = mod.stride(0)
-        kv_mod = lambda c: (B if c[0][0].shape[0] != R else 0)
-        for l, lw in enumerate(self.layers):
-            ops.rmsnorm_mod(x, mod[0, l, 0, 1], mod[0, l, 0, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld, delta=pending)
-            ops.gemm_sections(xn, lw["qkvg"],
-                              [(L.SEC_NORM_ROPE, qkvg[0], lw["qn"]), (L.SEC_NORM_ROPE, qkvg[1], lw["kn"]),
-                               (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
-                              head_dim=128, rope_heads=H // 2, rope=self.rope, pos_offset=start_pos, rows_per_seq=S,
-                              eps=cfg.norm_eps)
-            segs = [ops.Segment(qkvg[1].view(R, S, H, 128), qkvg[2].view(R, S, H, 128))]
-            if kv_latent is not None and n_prefix > 0:
-                segs.append(ops.Segment(kv_latent[l][0], kv_latent[l][1], kv_batch_mod=kv_mod(kv_latent),
-                                        length=n_prefix))
-            segs.append(ops.Segment(kv_text[l][0], kv_text[l][1], kv_batch_mod=kv_mod(kv_text), mask=text_mask,
-                                    extent=text_extent))
-            segs.append(ops.Segment(kv_speaker[l][0], kv_speaker[l][1], kv_batch_mod=kv_mod(kv_speaker), mask=spk_mask,
-                                    extent=spk_extent, kv_scale=(spk_scale[l:l + 1] if spk_scale is not None else None)))
-            ops.attention(qkvg[0].view(R, S, H, 128), segs, ao, gate=qkvg[3])
-            if delta is None:
-                ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
-                ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld)
-                ops.gemm_swiglu(xn, lw["w13"], hmid)
-                ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, resid=x, out_f32=x)
-            else:   # few tokens: split-K projections, residual update deferred into the next norm kernel
-                ops.gemm_generic(ao, lw["wo"], gate=mod[:, l, 0, 2], rows_per_gate=rows_per_mod, split_out=delta)
-                ops.rmsnorm_mod(x, mod[0, l, 1, 1], mod[0, l, 1, 0], xn, cfg.norm_eps, rows_per_mod, mod_ld, delta=delta)
-                ops.gemm_swiglu(xn, lw["w13"], hmid)
-                ops.gemm_generic(hmid, lw["w2"], gate=mod[:, l, 1, 2], rows_per_gate=rows_per_mod, split_out=delta)
-                pending = delta
-        return x, pending
+        keep = [x_in, mod, ws, tail, text_mask, text_extent, spk_mask, spk_extent, spk_scale, kv_text, kv_speaker, kv_latent]
+        d = L.DitStepDesc()
+        d.n_layers, d.d, d.heads, d.head_dim = cfg.num_layers, cfg.model_size, cfg.num_heads, cfg.head_dim
+        d.ffn, d.latent, d.eps = cfg.intermediate_size, cfg.latent_size, cfg.norm_eps
+        d.layers = self._layer_array()
+        d.in_w, d.in_b = self.in_w.data_ptr(), self.in_b.data_ptr()
+        d.rope_cos, d.rope_sin, d.rope_len = self.rope[0].data_ptr(), self.rope[1].data_ptr(), self.rope[0].shape[0]
+        d.x_in, d.x_rows, d.rows, d.seq, d.pos_offset = x_in.data_ptr(), Bx, R, S, start_pos
+        d.mod, d.mod_row_stride, d.mod_rows = mod.data_ptr(), mod.stride(0), mod.shape[0]
+        d.k_splits = self.k_splits(R * S)
+        if kv_latent is not None and n_prefix > 0:
+            self._fill_kv(d.prefix, kv_latent, R, B, keep, length=n_prefix)
+        self._fill_kv(d.text, kv_text, R, B, keep, mask=text_mask, extent=text_extent)
+        self._fill_kv(d.speaker, kv_speaker, R, B, keep, mask=spk_mask, extent=spk_extent, kv_scale=spk_scale)
+        d.x, d.xn, d.qkvg, d.ao, d.hmid = (ws[k].data_ptr() for k in ("x", "xn", "qkvg", "ao", "h"))
+        d.delta = L.ptr(ws["delta"])
+        gws = ops.gemm_workspace(self._device)
+        d.gemm_workspace, d.gemm_workspace_bytes = gws.data_ptr(), gws.numel()
+        d.gemm_impl, d.attn_impl = ops.GEMM_IMPL, ops.ATTN_IMPL
+        if tail is not None:
+            d.tail = C.pointer(tail)
+        return d, keep
+
+    def forward_hidden(self, x_in: torch.Tensor, mod: torch.Tensor, B: int, *, text_mask, **kw):
+        """x_in fp32 [Bx, S, latent] -> (final residual stream fp32 [R*S, D], pending delta or None): when the forward
+        runs split-K the last w2's partial products [splits, R*S, D] are still to be added to the stream (the sampler
+        tail does it).  One native call (``echo_dit_step``); arguments as in step_desc."""
+        R = text_mask.shape[0]
+        d, keep = self.step_desc(x_in, mod, B, R, text_mask=text_mask, **kw)
+        L.check(L.load().echo_dit_step(C.byref(d), L.stream()))
+        ws = self.workspace(R, x_in.shape[1])
+        return ws["x"], ws["delta"]
 
     @torch.inference_mode()
     def __call__(self, x, t, text_mask, speaker_mask, kv_cache_text, kv_cache_speaker, start_pos=None,

@@ -274,30 +274,46 @@ def mask_extent(mask: torch.Tensor) -> torch.Tensor:
     return ext
 
 
-def cfg_euler_tail(h, norm_w, w_out, b_out, *, positions, branches, eps, x_t=None, sched=None, step=None,
-                   cfg_text=0.0, cfg_speaker=0.0, rescale_k=None, rescale_sigma=None, v_out=None, v_comb_out=None,
-                   update_x=True, delta=None, push_to=None) -> None:
-    """``push_to``: ((v_peer0, flag_peer0), (v_peer1, flag_peer1)) P2P-mapped tensors on the two other ranks of a
-    CFG-branch split (branches == 1): the kernel stores its velocities there too and bumps the counters."""
-    _need(h, F32, "h")
+def tail_desc(norm_w, w_out, b_out, *, positions, branches, eps, h=None, x_t=None, sched=None, step=None,
+              cfg_text=0.0, cfg_speaker=0.0, rescale_k=None, rescale_sigma=None, v_out=None, v_comb_out=None,
+              update_x=True, delta=None, push_to=None) -> L.TailDesc:
+    """Descriptor of the fused sampler tail.  ``h`` (final residual stream) may be left out when the descriptor rides
+    on ``echo_dit_step``, which fills it in.  ``push_to``: ((v_peer0, flag_peer0), (v_peer1, flag_peer1)) P2P-mapped
+    tensors on the two other ranks of a CFG-branch split (branches == 1): the kernel stores its velocities there too
+    and bumps the counters."""
     d = L.TailDesc()
     if push_to is not None:
         for k, (vp, fp) in enumerate(push_to):
             d.v_peer[k], d.flag_peer[k] = vp.data_ptr(), fp.data_ptr()
-    if delta is not None:
-        _need(delta, F32, "delta")
-        assert delta.dim() == 3 and delta.shape[1:] == h.shape and delta.is_contiguous() and h.is_contiguous()
-        d.delta, d.n_delta, d.delta_stride = delta.data_ptr(), delta.shape[0], delta.stride(0)
-    d.h, d.ldh = h.data_ptr(), h.stride(0)
+    for t, name in ((norm_w, "norm_w"), (w_out, "w_out"), (b_out, "b_out")):
+        _need(t, F32, name); assert t.is_contiguous()
     d.norm_w, d.w_out, d.b_out = norm_w.data_ptr(), w_out.data_ptr(), b_out.data_ptr()
+    d.positions, d.d, d.latent, d.branches = positions, w_out.shape[1], w_out.shape[0], branches
+    if h is not None:
+        _need(h, F32, "h")
+        assert h.shape == (positions * branches, d.d)
+        d.h, d.ldh = h.data_ptr(), h.stride(0)
+        if delta is not None:
+            _need(delta, F32, "delta")
+            assert delta.dim() == 3 and delta.shape[1:] == h.shape and delta.is_contiguous() and h.is_contiguous()
+            d.delta, d.n_delta, d.delta_stride = delta.data_ptr(), delta.shape[0], delta.stride(0)
+    for t, name, n in ((x_t, "x_t", positions), (v_out, "v_out", positions * branches), (v_comb_out, "v_comb_out", positions)):
+        if t is not None:
+            _need(t, F32, name); assert t.is_contiguous() and t.numel() == n * d.latent
+    if sched is not None:
+        _need(sched, F32, "sched")
     d.x_t, d.v_out, d.v_comb_out = L.ptr(x_t), L.ptr(v_out), L.ptr(v_comb_out)
     d.sched, d.step = L.ptr(sched), L.ptr(step)
-    d.positions, d.d, d.latent, d.branches = positions, h.shape[1], w_out.shape[0], branches
-    assert h.shape[0] == positions * branches
     d.eps, d.cfg_text, d.cfg_speaker = eps, cfg_text, cfg_speaker
     d.use_rescale = int(rescale_k is not None and rescale_sigma is not None)
     d.rescale_k, d.rescale_sigma = (rescale_k or 1.0), (rescale_sigma or 0.0)
     d.update_x = int(update_x)
+    return d
+
+
+def cfg_euler_tail(h, norm_w, w_out, b_out, **kw) -> None:
+    """Stand-alone launch of the fused tail on a given residual stream ``h`` (see tail_desc for the arguments)."""
+    d = tail_desc(norm_w, w_out, b_out, h=h, **kw)
     L.check(L.load().echo_cfg_euler_tail(C.byref(d), L.stream()))
 
 

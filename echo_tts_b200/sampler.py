@@ -8,11 +8,13 @@ the loop, and the whole 40-step loop replays as a single CUDA graph.
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
 
+from . import _lib as L
 from . import ops
 from .model import EchoDiT, KVCache, KVList, BF16, F32
 
@@ -70,29 +72,44 @@ def _prep_masks(model: EchoDiT, text_mask: torch.Tensor, speaker_mask: torch.Ten
 def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tensor, B: int, masks, kv_text: KVCache,
               kv_spk: KVCache, p: dict, *, start_pos: int = 0, kv_latent: Optional[KVCache] = None, n_prefix: int = 0,
               trace: Optional[list] = None) -> None:
-    """The hot loop (inference.py:508-558): x_t fp32 [B, S, latent] updated in place; launches only."""
+    """The hot loop (inference.py:508-558): x_t fp32 [B, S, latent] updated in place; launches only.  Without a trace
+    the whole loop is ONE native call (``echo_dit_sample``: per step the DiT forward over 3B or B rows + the fused
+    out-projection / CFG combine / rescale / Euler tail); with a trace, one ``echo_dit_step`` per step."""
     cfg = model.cfg
     tm3, te3, sm3, se3 = masks
     S = x_t.shape[1]
     use_rescale = p["rescale_k"] is not None and p["rescale_sigma"] is not None
+    n = len(plan.has_cfg)
+    lib = L.load()
+
+    def step(R: int, i: int, **tail_kw):
+        tail = ops.tail_desc(model.out_norm, model.out_w, model.out_b, positions=B * S, branches=R // B,
+                             eps=cfg.norm_eps, x_t=x_t, sched=plan.sched[i:], cfg_text=p["cfg_scale_text"],
+                             cfg_speaker=p["cfg_scale_speaker"], rescale_k=p["rescale_k"] if use_rescale else None,
+                             rescale_sigma=p["rescale_sigma"] if use_rescale else None, **tail_kw)
+        return model.step_desc(x_t, mod[i:i + 1], B, R, text_mask=tm3, text_extent=te3, spk_mask=sm3, spk_extent=se3,
+                               kv_text=kv_text, kv_speaker=kv_spk, kv_latent=kv_latent, start_pos=start_pos,
+                               n_prefix=n_prefix, spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None),
+                               tail=tail)
+
+    if trace is None:
+        assert mod.shape[0] >= n and plan.sched.is_contiguous()
+        d3, keep3 = step(3 * B, 0) if any(plan.has_cfg) else (None, None)
+        d1, keep1 = step(B, 0) if not all(plan.has_cfg) else (None, None)
+        flags = (C.c_uint8 * max(n, 1))(*[int(f) for f in plan.has_cfg])
+        L.check(lib.echo_dit_sample(C.byref(d3) if d3 is not None else None, C.byref(d1) if d1 is not None else None,
+                                    n, C.cast(flags, C.c_void_p), mod.stride(0),
+                                    plan.kv_mult.stride(0) if plan.uses_kv_scale else 0, plan.sched.stride(0),
+                                    L.stream()))
+        return
     for i, has_cfg in enumerate(plan.has_cfg):
         R = 3 * B if has_cfg else B
-        h, pending = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[:R], text_extent=te3[:R], spk_mask=sm3[:R],
-                                 spk_extent=se3[:R], kv_text=kv_text, kv_speaker=kv_spk, kv_latent=kv_latent,
-                                 start_pos=start_pos, n_prefix=n_prefix,
-                                 spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
-        v_out = v_comb = None
-        if trace is not None:
-            v_out = torch.empty((R * S, cfg.latent_size), device=x_t.device, dtype=F32)
-            v_comb = torch.empty((B * S, cfg.latent_size), device=x_t.device, dtype=F32)
-            x_in = x_t.clone()
-        ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=(3 if has_cfg else 1),
-                           eps=cfg.norm_eps, x_t=x_t, sched=plan.sched[i], cfg_text=p["cfg_scale_text"],
-                           cfg_speaker=p["cfg_scale_speaker"], rescale_k=p["rescale_k"] if use_rescale else None,
-                           rescale_sigma=p["rescale_sigma"] if use_rescale else None, v_out=v_out, v_comb_out=v_comb,
-                           delta=pending)
-        if trace is not None:
-            trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
+        v_out = torch.empty((R * S, cfg.latent_size), device=x_t.device, dtype=F32)
+        v_comb = torch.empty((B * S, cfg.latent_size), device=x_t.device, dtype=F32)
+        x_in = x_t.clone()
+        d, keep = step(R, i, v_out=v_out, v_comb_out=v_comb)
+        L.check(lib.echo_dit_step(C.byref(d), L.stream()))
+        trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
 
 
 class _GraphEntry:

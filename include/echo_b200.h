@@ -26,8 +26,9 @@ void echo_reset_launch_count(void);
  * bf16 tensor-core GEMM with implicit-conv taps and fused epilogues.
  *   acc[b, m, n] = sum_t sum_k A[b, m + tap_shift[t], k] * B[n, t*k_tap + k]     (fp32 accumulate)
  * Rows outside [0, rows) read as zero (causal left padding of CausalConvNet,
- * autoencoder.py:285-289).  impl 0 = tcgen05.mma + TMEM accumulators + TMA loads (the product
- * path); impl 1 = legacy mma.sync kernel kept as an A/B baseline and debugging aid.
+ * autoencoder.py:285-289).  impl 2 = persistent CTA-pair tcgen05.mma kernel with TMEM accumulators
+ * and TMA loads (the product path); impl 0 = single-CTA tcgen05 kernel, impl 1 = legacy mma.sync
+ * kernel, both kept as A/B baselines and debugging aids.
  * Replaces every nn.Linear / Conv1d / ConvTranspose1d on the path: model.py:217-224, 266, 308;
  * autoencoder.py:285-316, 365-367, 667, 704, 717.
  * ------------------------------------------------------------------------------------------ */
@@ -222,6 +223,70 @@ int echo_cfg_combine_euler(const echo_tail_desc* d, echo_stream_t stream);
 /* CTAs one echo_cfg_euler_tail launch uses for `positions` rows = increments per launch of each flag_peer counter. */
 int echo_cfg_tail_ctas(int positions);
 int echo_step_advance(int32_t* step, echo_stream_t stream); /* step[0] += 1 */
+
+/* ------------------------------------------------------------------------------------------
+ * Whole-step entry points: one velocity evaluation of the DiT (EchoDiT.forward, model.py:563-604: in_proj, n_layers x
+ * [AdaLN norm -> q|k|v|gate projection + head RMSNorm + RoPE -> joint attention over self / latent-prefix / text /
+ * speaker keys -> gated wo residual -> AdaLN norm -> SwiGLU -> gated w2 residual]) followed, when `tail` is given, by
+ * the fused out_norm + out_proj + CFG combine + rescale + Euler update (inference.py:514-558); and the whole Euler
+ * loop (inference.py:508-558).  Pure launch sequences over the entry points above (about 7 launches per layer), on
+ * `stream`, CUDA-graph capturable; `layers`, `k`/`v` pointer arrays and `has_cfg` are HOST arrays read at call time,
+ * everything else is device memory lent by the caller.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct echo_dit_layer {
+  const void* w_qkvg;       /* bf16 [4*d, d]: wq | wk | wv | gate rows (model.py:215-224) */
+  const void* w_o;          /* bf16 [d, d] (model.py:266) */
+  const void* w13;          /* bf16 [2*ffn, d], w1 / w3 rows interleaved in groups of 64 (model.py:296-308) */
+  const void* w2;           /* bf16 [d, ffn] */
+  const float* q_norm;      /* fp32 [heads*head_dim] per-head RMSNorm weights (model.py:192-193) */
+  const float* k_norm;
+} echo_dit_layer;
+
+typedef struct echo_dit_kv { /* cached keys / values of one conditioning modality, all layers */
+  const void* const* k;     /* HOST array [n_layers] of device pointers, bf16 [kv_rows, >= len, heads, head_dim] */
+  const void* const* v;
+  int64_t row_stride, batch_stride;
+  int32_t len;              /* keys visible to this forward (0 = none: a latent prefix that does not exist yet) */
+  int32_t kv_batch_mod;     /* as echo_attn_segment */
+  const uint8_t* mask; int64_t mask_stride;
+  const int32_t* extent;
+  const float* kv_scale;    /* device fp32 [n_layers] per-layer multiplier (speaker_kv_scale, inference.py:420-428) or NULL */
+} echo_dit_kv;
+
+typedef struct echo_dit_step_desc {
+  int32_t n_layers, d, heads, head_dim, ffn, latent;
+  float eps;
+  int32_t rope_len;         /* positions in rope_cos / rope_sin */
+  const echo_dit_layer* layers; /* HOST array [n_layers] */
+  const float* in_w;        /* fp32 [d, latent] */
+  const float* in_b;        /* fp32 [d] */
+  const float* rope_cos; const float* rope_sin; /* fp32 [rope_len, head_dim/2] */
+  const float* x_in;        /* fp32 [x_rows, seq, latent]; x_rows == rows, or rows % x_rows == 0: CFG branches share x_t */
+  int32_t x_rows, rows, seq;
+  int32_t pos_offset;       /* RoPE position of the first latent (start_pos, model.py:573-579) */
+  const float* mod;         /* fp32 [mod_rows][n_layers][2][3][d] = {shift, 1 + scale, tanh-ed gate} (model.py:60-83) */
+  int64_t mod_row_stride;
+  int32_t mod_rows;         /* 1 (one t for all rows) or rows */
+  int32_t k_splits;         /* > 1: wo / w2 run split-K into `delta`, summed by the next norm / the tail */
+  echo_dit_kv prefix, text, speaker;
+  float* x;                 /* workspace: residual stream fp32 [rows*seq, d] (result when tail == NULL) */
+  void* xn;                 /* bf16 [rows*seq, d] */
+  void* qkvg;               /* bf16 [4][rows*seq, d] */
+  void* ao;                 /* bf16 [rows*seq, d] */
+  void* hmid;               /* bf16 [rows*seq, ffn] */
+  float* delta;             /* fp32 [k_splits][rows*seq, d] when k_splits > 1 */
+  void* gemm_workspace; int64_t gemm_workspace_bytes; /* as echo_gemm_desc.workspace */
+  int32_t gemm_impl, attn_impl; /* echo_gemm_desc.impl / echo_attn_desc.impl for every launch (2 / 0 = product path) */
+  const echo_tail_desc* tail;   /* nullable; h, ldh, delta, n_delta, delta_stride are filled in by the library */
+  int32_t* pending_out;     /* HOST, nullable: set to 1 when tail == NULL and `delta` still has to be added to x */
+} echo_dit_step_desc;
+int echo_dit_step(const echo_dit_step_desc* d, echo_stream_t stream);
+
+/* The Euler loop (inference.py:508-558): step i runs *cfg_step (three-branch rows) when has_cfg[i] else *plain_step,
+ * with mod, speaker.kv_scale (when non-NULL) and tail->sched advanced by i * the given element strides. */
+int echo_dit_sample(const echo_dit_step_desc* cfg_step, const echo_dit_step_desc* plain_step, int n_steps,
+                    const uint8_t* has_cfg, int64_t mod_step_stride, int64_t kv_scale_step_stride,
+                    int64_t sched_step_stride, echo_stream_t stream);
 
 /* text embedding lookup (model.py:420): ids int32 [n] -> out fp32 [n, d] */
 int echo_embedding(const int32_t* ids, int n, const float* table, int d, float* out, echo_stream_t stream);

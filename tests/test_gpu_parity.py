@@ -64,6 +64,50 @@ def test_graph_replay_equals_eager(tiny_model):
     assert rel_l2(outs[2], g["x_final"]) < X_TOL
 
 
+def test_native_loop_equals_stepwise(tiny_model, monkeypatch):
+    """echo_dit_sample (the whole Euler loop as one C-ABI call) == one echo_dit_step per step, bit for bit."""
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    monkeypatch.setenv("ECHO_CUDA_GRAPH", "0")
+    g = torch.load(os.path.join(GOLDEN, "dit_tiny_sampler_opts.pt"))
+    args = (tiny_model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0)
+    trace = []
+    stepwise = sample(*args, _noise=g["noise"], _trace=trace, **g["kwargs"])
+    looped = sample(*args, _noise=g["noise"], **g["kwargs"])
+    assert len(trace) == g["kwargs"]["num_steps"] and torch.equal(stepwise, looped)
+
+
+def test_dit_step_rejects_bad_arguments(tiny_model):
+    """Error behaviour of the whole-step entry point: negative status + message, nothing launched on garbage."""
+    import ctypes as C
+    from echo_tts_b200 import _lib as L
+    cfg = S.ECHO_TINY
+    gen = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, 255, (1, 12), generator=gen, dtype=torch.int32).cuda()
+    tmask = torch.ones(1, 12, dtype=torch.bool).cuda()
+    spk = torch.randn(1, 16, 80, generator=gen).cuda()
+    kt, ks = tiny_model.get_kv_cache_text(ids, tmask), tiny_model.get_kv_cache_speaker(spk)
+    x = torch.randn(1, 24, 80, generator=gen).cuda()
+    mod = tiny_model.build_mod_table(torch.tensor([0.5]).cuda())
+    tm = tmask.to(torch.uint8)
+    sm = torch.ones(1, 4, dtype=torch.uint8).cuda()
+    from echo_tts_b200 import ops
+    kw = dict(text_mask=tm, text_extent=ops.mask_extent(tm), spk_mask=sm, spk_extent=ops.mask_extent(sm), kv_text=kt,
+              kv_speaker=ks)
+    lib = L.load()
+    d, keep = tiny_model.step_desc(x, mod, 1, 1, **kw)
+    assert lib.echo_dit_step(C.byref(d), L.stream()) == 0
+    for field, value, msg in (("x_rows", 2, "multiple of x_rows"), ("pos_offset", 1 << 20, "rope table too short"),
+                              ("xn", None, "null input"), ("mod_rows", 3, "mod_rows"), ("heads", 3, "heads * head_dim")):
+        d, keep = tiny_model.step_desc(x, mod, 1, 1, **kw)
+        setattr(d, field, value)
+        assert lib.echo_dit_step(C.byref(d), L.stream()) < 0
+        assert msg in lib.echo_last_error().decode()
+    assert lib.echo_dit_sample(None, None, 2, None, 0, 0, 0, L.stream()) < 0
+    with pytest.raises(RuntimeError):
+        tiny_model.step_desc(x.cpu(), mod, 1, 1, **kw)            # no CPU fallback
+    torch.cuda.synchronize()
+
+
 def test_model_call_compat_vs_oracle(tiny_model):
     """The reference-shaped ``model(x, t, masks, caches)`` surface (third-party samplers)."""
     from oracle import echo_oracle as O
