@@ -252,6 +252,25 @@ def run_gpu(args):
         return
     audio = world * B * AUDIO_SEC_PER_PROMPT * args.steps
     value, e2e = audio / (ms / 1e3), audio / (ms_e2e / 1e3)
+
+    def sampler_ms_median(kw, n=5):
+        """median device time of one graph-replayed sample() call under schedule `kw`"""
+        for _ in range(3):                                             # eager, capture, replay
+            sample(model, dev[2], dev[3], dev[0], dev[1], 0, **kw)
+        ts = []
+        for _ in range(n):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            a.record(); sample(model, dev[2], dev[3], dev[0], dev[1], 0, **kw); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return sorted(ts)[n // 2]
+
+    # per-step latency (SURVEY 8d): slope between 40- and 20-step schedules, all steps guided / none guided
+    all_cfg, no_cfg = dict(KW, cfg_min_t=0.0, cfg_max_t=1.0), dict(KW, cfg_min_t=2.0, cfg_max_t=3.0)
+    step_ms = {name: (sampler_ms_median(dict(kw, num_steps=40)) - sampler_ms_median(dict(kw, num_steps=20))) / 20
+               for name, kw in (("cfg_step", all_cfg), ("plain_step", no_cfg))}
+    step_ms["method"] = "(40-step - 20-step sample() graph replay, median of 5) / 20, all steps guided / none guided"
     roof = gemm_roofline(model, pk)
     step_tflops = B * FLOP_GEN / (ms / 1e3 / args.steps) / 1e12
     line = dict(metric="audio-sec generated per GPU-sec, 640-latent 40-step CFG", value=value, unit="audio-sec/sec",
@@ -266,7 +285,8 @@ def run_gpu(args):
                 generation_roofline=dict(bound="tensor", achieved=step_tflops, peak=pk["bf16_sustained"], unit="TFLOP/s",
                                          frac=step_tflops / pk["bf16_sustained"], flop_per_generation=B * FLOP_GEN,
                                          peak_source=pk["src"] + " sustained"),
-                breakdown_ms=dict(conditioning_plus_sampler=sampler_ms, decode=decode_ms), load_seconds=load_s)
+                breakdown_ms=dict(conditioning_plus_sampler=sampler_ms, decode=decode_ms), step_latency_ms=step_ms,
+                load_seconds=load_s)
     if not args.no_cpu_baseline:
         del model, ae
         torch.cuda.empty_cache()

@@ -529,3 +529,16 @@ def synth_pca(latent_size: int = 80, latent_dim: int = 1024, seed: int = 99):
     g = torch.Generator().manual_seed(seed)
     q, _ = torch.linalg.qr(torch.randn(latent_dim, latent_size, generator=g))
     return q.t().contiguous(), 0.05 * torch.randn(latent_dim, generator=g), 0.5
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# LoRA adapters: the un-merged forward of a wrapped layer, lora.py:55-64, and the merge lora.py:66-82
+# ---------------------------------------------------------------------------------------------------------------------
+def lora_linear(x: torch.Tensor, w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, alpha: float, rank: int) -> torch.Tensor:
+    """y = x W^T + (alpha / rank) * (x A^T) B^T   (LoRALinear.forward, lora.py:55-64; dropout is identity at inference)"""
+    return x @ w.T + ((x @ a.T) @ b.T) * (alpha / rank)
+
+
+def lora_merged_weight(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, alpha: float, rank: int) -> torch.Tensor:
+    """W' = W + (alpha / rank) * B A   (LoRALinear.merge_weights, lora.py:77-78)"""
+    return w + (b @ a) * (alpha / rank)
