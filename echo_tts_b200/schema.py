@@ -73,6 +73,24 @@ class AEConfig:
     convnext_ratio: int = 4
     decoder_dim: int = 1536
     decoder_rates: Tuple[int, ...] = (8, 8, 4, 2)
+    # encode half (Encoder autoencoder.py:903-929, DownsampleResidualVectorQuantize :376-447, build_ae :1144-1192)
+    encoder_dim: int = 64
+    encoder_rates: Tuple[int, ...] = (2, 4, 8, 8)
+    enc_tr_layers: int = 4                  # WindowLimitedTransformer after the last encoder block only
+    enc_tr_window: int = 512                # fixed by EncoderBlock (autoencoder.py:858), not a build_ae() parameter
+    enc_tr_block_size: int = 16384
+    n_codebooks: int = 9
+    codebook_size: int = 1024
+    codebook_dim: int = 8
+    semantic_codebook_size: int = 4096
+
+    @property
+    def enc_out_dim(self) -> int:
+        return self.encoder_dim * 2 ** len(self.encoder_rates)
+
+    @property
+    def enc_tr_heads(self) -> int:
+        return self.enc_out_dim // 64
 
     @property
     def hop(self) -> int:
@@ -87,7 +105,9 @@ class AEConfig:
 AE_BASE = AEConfig()
 # Small AE for fast oracle-vs-kernel tests (not constructible by the reference's build_ae()).
 AE_TINY = AEConfig(latent_dim=128, tr_layers=2, tr_heads=2, tr_head_dim=64, tr_ffn=256,
-                   tr_window=16, tr_block_size=512, decoder_dim=256, decoder_rates=(4, 2, 2, 2))
+                   tr_window=16, tr_block_size=512, decoder_dim=256, decoder_rates=(4, 2, 2, 2),
+                   encoder_dim=16, encoder_rates=(2, 2, 2, 4), enc_tr_layers=2, enc_tr_block_size=1024,
+                   n_codebooks=3, codebook_size=32, semantic_codebook_size=64)
 
 
 # --------------------------------------------------------------------------------------
@@ -225,6 +245,75 @@ def ae_decode_schema(cfg: AEConfig = AE_BASE) -> Dict[str, Tuple[int, ...]]:
     return s
 
 
+def _transformer_keys(s, pm: str, layers: int, D: int, heads: int, head_dim: int, ffn: int) -> None:
+    for i in range(layers):
+        p = f"{pm}.layers.{i}"
+        s[f"{p}.attention.wqkv.weight"] = (3 * heads * head_dim, D)
+        s[f"{p}.attention.wo.weight"] = (D, heads * head_dim)
+        s[f"{p}.feed_forward.w1.weight"] = (ffn, D)
+        s[f"{p}.feed_forward.w3.weight"] = (ffn, D)
+        s[f"{p}.feed_forward.w2.weight"] = (D, ffn)
+        s[f"{p}.ffn_norm.weight"] = (D,)
+        s[f"{p}.attention_norm.weight"] = (D,)
+        s[f"{p}.attention_layer_scale.gamma"] = (D,)
+        s[f"{p}.ffn_layer_scale.gamma"] = (D,)
+    s[f"{pm}.norm.weight"] = (D,)
+
+
+def ae_encode_schema(cfg: AEConfig = AE_BASE) -> Dict[str, Tuple[int, ...]]:
+    """Parameters on the ``DAC.encode_zq`` path (reference ``autoencoder.py:1080-1126``): Encoder, quantizer.downsample,
+    quantizer.pre_module and the 1 + n_codebooks vector quantizers (key names as the reference's ``state_dict``)."""
+    s: Dict[str, Tuple[int, ...]] = {}
+
+    def wnconv(prefix: str, cout: int, cin: int, k: int, conv: str = ".conv"):
+        s[f"{prefix}{conv}.bias"] = (cout,)
+        s[f"{prefix}{conv}.parametrizations.weight.original0"] = (cout, 1, 1)
+        s[f"{prefix}{conv}.parametrizations.weight.original1"] = (cout, cin, k)
+
+    eb = "encoder.block"
+    c = cfg.encoder_dim
+    wnconv(f"{eb}.0", c, 1, 7)
+    n = len(cfg.encoder_rates)
+    for i, r in enumerate(cfg.encoder_rates):
+        b = f"{eb}.{i + 1}.block"
+        for j in range(3):
+            ru = f"{b}.{j}.block"
+            s[f"{ru}.0.alpha"] = (1, c, 1)
+            wnconv(f"{ru}.1", c, c, 7)
+            s[f"{ru}.2.alpha"] = (1, c, 1)
+            wnconv(f"{ru}.3", c, c, 1)
+        s[f"{b}.3.alpha"] = (1, c, 1)
+        wnconv(f"{b}.4", 2 * c, c, 2 * r)
+        c *= 2
+        if i == n - 1 and cfg.enc_tr_layers > 0:
+            _transformer_keys(s, f"{b}.5", cfg.enc_tr_layers, c, c // 64, 64, 3 * c)
+    s[f"{eb}.{n + 1}.alpha"] = (1, c, 1)
+    wnconv(f"{eb}.{n + 2}", cfg.latent_dim, c, 3)
+    D = cfg.latent_dim
+    for u, f in enumerate(cfg.up_factors):
+        p = f"quantizer.downsample.{u}"
+        s[f"{p}.0.conv.weight"] = (D, D, f)
+        s[f"{p}.0.conv.bias"] = (D,)
+        s[f"{p}.1.gamma"] = (D,)
+        s[f"{p}.1.dwconv.conv.weight"] = (D, 1, 7)
+        s[f"{p}.1.dwconv.conv.bias"] = (D,)
+        s[f"{p}.1.norm.weight"] = (D,)
+        s[f"{p}.1.norm.bias"] = (D,)
+        s[f"{p}.1.pwconv1.weight"] = (cfg.convnext_ratio * D, D)
+        s[f"{p}.1.pwconv1.bias"] = (cfg.convnext_ratio * D,)
+        s[f"{p}.1.pwconv2.weight"] = (D, cfg.convnext_ratio * D)
+        s[f"{p}.1.pwconv2.bias"] = (D,)
+    _transformer_keys(s, "quantizer.pre_module", cfg.tr_layers, D, cfg.tr_heads, cfg.tr_head_dim, cfg.tr_ffn)
+    for name, n_q, size in (("quantizer.semantic_quantizer", 1, cfg.semantic_codebook_size),
+                            ("quantizer.quantizer", cfg.n_codebooks, cfg.codebook_size)):
+        for q in range(n_q):
+            p = f"{name}.quantizers.{q}"
+            wnconv(f"{p}.in_proj", cfg.codebook_dim, D, 1, conv="")
+            wnconv(f"{p}.out_proj", D, cfg.codebook_dim, 1, conv="")
+            s[f"{p}.codebook.weight"] = (size, cfg.codebook_dim)
+    return s
+
+
 # --------------------------------------------------------------------------------------
 # deterministic synthetic weights
 # --------------------------------------------------------------------------------------
@@ -270,7 +359,7 @@ def synth_tensor(key: str, shape: Tuple[int, ...], seed: int, init: str = "unit"
         return 1.0 + 0.2 * (torch.rand(shape, generator=g) - 0.5)
     if leaf == "bias":
         return 0.1 * (torch.rand(shape, generator=g) - 0.5)
-    if "text_embedding" in key:
+    if "text_embedding" in key or key.endswith("codebook.weight"):
         return torch.randn(shape, generator=g)
     bound = (3.0 / _fan_in(shape)) ** 0.5     # unit-gain uniform
     if init == "torch":
@@ -286,18 +375,24 @@ def synth_state_dict(schema: Dict[str, Tuple[int, ...]], seed: int = 1234, init:
     return {k: synth_tensor(k, shp, seed, init) for k, shp in schema.items()}
 
 
-def ae_rope_table(cfg: AEConfig = AE_BASE) -> torch.Tensor:
+def ae_rope_table(cfg: AEConfig = AE_BASE, block_size: int = 0, head_dim: int = 0) -> torch.Tensor:
     """``quantizer.post_module.freqs_cis`` buffer: [block_size, head_dim/2, 2] rounded to
     **bf16** exactly as the reference builds it (``autoencoder.py:805-813``)."""
-    n = cfg.tr_head_dim
+    n = head_dim or cfg.tr_head_dim
     freqs = 1.0 / (10000 ** (torch.arange(0, n, 2)[: n // 2].float() / n))
-    t = torch.arange(cfg.tr_block_size)
+    t = torch.arange(block_size or cfg.tr_block_size)
     freqs = torch.outer(t, freqs)
     fc = torch.polar(torch.ones_like(freqs), freqs)
     return torch.stack([fc.real, fc.imag], dim=-1).to(torch.bfloat16)
 
 
-def synth_ae_state_dict(cfg: AEConfig = AE_BASE, seed: int = 4321) -> Dict[str, torch.Tensor]:
+def synth_ae_state_dict(cfg: AEConfig = AE_BASE, seed: int = 4321, encode: bool = False) -> Dict[str, torch.Tensor]:
+    """Decode-path tensors (+ the encode path's with ``encode=True``; the decode tensors do not change)."""
     sd = synth_state_dict(ae_decode_schema(cfg), seed)
     sd["quantizer.post_module.freqs_cis"] = ae_rope_table(cfg)
+    if encode:
+        sd.update(synth_state_dict(ae_encode_schema(cfg), seed))
+        sd["quantizer.pre_module.freqs_cis"] = ae_rope_table(cfg)
+        if cfg.enc_tr_layers > 0:
+            sd[f"encoder.block.{len(cfg.encoder_rates)}.block.5.freqs_cis"] = ae_rope_table(cfg, cfg.enc_tr_block_size, 64)
     return sd

@@ -417,8 +417,10 @@ def find_flattening_point(data: torch.Tensor, target_value=0.0, window_size=20, 
 def wn_weight(sd: SD, prefix: str) -> torch.Tensor:
     """weight_norm parametrization (autoencoder.py:90-94, 291-293): w = g * v / ||v||, the norm
     taken over every dim but 0."""
-    g = sd[f"{prefix}.conv.parametrizations.weight.original0"]
-    v = sd[f"{prefix}.conv.parametrizations.weight.original1"]
+    if f"{prefix}.conv.parametrizations.weight.original0" in sd:
+        prefix = f"{prefix}.conv"                         # CausalConvNet wrapper; VectorQuantize's WNConv1d has none
+    g = sd[f"{prefix}.parametrizations.weight.original0"]
+    v = sd[f"{prefix}.parametrizations.weight.original1"]
     return g * v / v.flatten(1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
 
 
@@ -446,18 +448,20 @@ def ae_rms_norm(x, w, eps):
     return (xf * torch.rsqrt((xf * xf).mean(-1, keepdim=True) + eps)).type_as(x) * w
 
 
-def ae_window_transformer(sd: SD, cfg, x: torch.Tensor, pm: str = "quantizer.post_module") -> torch.Tensor:
+def ae_window_transformer(sd: SD, cfg, x: torch.Tensor, pm: str = "quantizer.post_module", layers: Optional[int] = None,
+                          heads: Optional[int] = None, window: Optional[int] = None) -> torch.Tensor:
     """WindowLimitedTransformer.forward, autoencoder.py:786-802 (channels-first in/out) with
     Transformer/TransformerBlock/Attention/FeedForward 590-717 and the window mask 762-773.
     RoPE table is the module's bf16 buffer (autoencoder.py:805-826), applied to ALL heads."""
     h = x.transpose(1, 2)                                     # [B, T, D]
     B, T, D = h.shape
-    H, Dh = cfg.tr_heads, cfg.tr_head_dim
+    H, Dh = heads or cfg.tr_heads, cfg.tr_head_dim
+    window = window or cfg.tr_window
     fc = sd[f"{pm}.freqs_cis"][:T].float()                    # [T, Dh/2, 2]
     cos, sin = fc[..., 0], fc[..., 1]
     i = torch.arange(T)
-    win = (i[None, :] <= i[:, None]) & (i[None, :] >= (i[:, None] - cfg.tr_window + 1).clamp(min=0))
-    for l in range(cfg.tr_layers):
+    win = (i[None, :] <= i[:, None]) & (i[None, :] >= (i[:, None] - window + 1).clamp(min=0))
+    for l in range(cfg.tr_layers if layers is None else layers):
         p = f"{pm}.layers.{l}"
         a = ae_rms_norm(h, sd[f"{p}.attention_norm.weight"], cfg.tr_eps)
         q, k, v = F.linear(a, sd[f"{p}.attention.wqkv.weight"]).split(H * Dh, dim=-1)
@@ -476,18 +480,23 @@ def ae_window_transformer(sd: SD, cfg, x: torch.Tensor, pm: str = "quantizer.pos
     return h.transpose(1, 2)
 
 
+def convnext_block(sd: SD, p: str, x: torch.Tensor) -> torch.Tensor:
+    """ConvNeXtBlock.forward, autoencoder.py:360-373: dwconv k7 -> LayerNorm(1e-6) -> Linear -> GELU(erf) -> Linear ->
+    gamma -> + residual."""
+    y = causal_conv1d(x, sd[f"{p}.dwconv.conv.weight"], sd[f"{p}.dwconv.conv.bias"], groups=x.shape[1])
+    y = y.transpose(1, 2)
+    y = F.layer_norm(y, (y.shape[-1],), sd[f"{p}.norm.weight"], sd[f"{p}.norm.bias"], 1e-6)
+    y = F.linear(F.gelu(F.linear(y, sd[f"{p}.pwconv1.weight"], sd[f"{p}.pwconv1.bias"])),
+                 sd[f"{p}.pwconv2.weight"], sd[f"{p}.pwconv2.bias"])
+    return x + (y * sd[f"{p}.gamma"]).transpose(1, 2)
+
+
 def ae_upsample(sd: SD, cfg, x: torch.Tensor) -> torch.Tensor:
-    """quantizer.upsample, autoencoder.py:427-435: per factor, causal transposed conv then ConvNeXt
-    (autoencoder.py:360-373: dwconv k7 -> LayerNorm(1e-6) -> Linear -> GELU(erf) -> Linear -> gamma -> +res)."""
+    """quantizer.upsample, autoencoder.py:427-435: per factor, causal transposed conv then ConvNeXt."""
     for u, f in enumerate(cfg.up_factors):
         p = f"quantizer.upsample.{u}"
         x = causal_conv_transpose1d(x, sd[f"{p}.0.conv.weight"], sd[f"{p}.0.conv.bias"], f)
-        y = causal_conv1d(x, sd[f"{p}.1.dwconv.conv.weight"], sd[f"{p}.1.dwconv.conv.bias"], groups=x.shape[1])
-        y = y.transpose(1, 2)
-        y = F.layer_norm(y, (y.shape[-1],), sd[f"{p}.1.norm.weight"], sd[f"{p}.1.norm.bias"], 1e-6)
-        y = F.linear(F.gelu(F.linear(y, sd[f"{p}.1.pwconv1.weight"], sd[f"{p}.1.pwconv1.bias"])),
-                     sd[f"{p}.1.pwconv2.weight"], sd[f"{p}.1.pwconv2.bias"])
-        x = x + (y * sd[f"{p}.1.gamma"]).transpose(1, 2)
+        x = convnext_block(sd, f"{p}.1", x)
     return x
 
 
@@ -542,3 +551,119 @@ def lora_linear(x: torch.Tensor, w: torch.Tensor, a: torch.Tensor, b: torch.Tens
 def lora_merged_weight(w: torch.Tensor, a: torch.Tensor, b: torch.Tensor, alpha: float, rank: int) -> torch.Tensor:
     """W' = W + (alpha / rank) * B A   (LoRALinear.merge_weights, lora.py:77-78)"""
     return w + (b @ a) * (alpha / rank)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Fish S1-DAC encode (SURVEY 8 f1): DAC.encode_zq, autoencoder.py:1080-1126
+# ---------------------------------------------------------------------------------------------------------------------
+def causal_conv1d_strided(x, w, b, stride: int):
+    """CausalConvNet.forward with stride, autoencoder.py:285-289 + get_extra_padding_for_conv1d :49-56: left pad
+    k - stride zeros, right pad up to a whole number of frames."""
+    k, length = w.shape[-1], x.shape[-1]
+    pad = k - stride
+    n_frames = (length - k + pad) / stride + 1
+    extra = (math.ceil(n_frames) - 1) * stride + (k - pad) - length
+    return F.conv1d(F.pad(x, (pad, extra)), w, b, stride=stride)
+
+
+def residual_unit(sd: SD, ru: str, x: torch.Tensor, dilation: int) -> torch.Tensor:
+    """ResidualUnit.forward (causal), autoencoder.py:879-900."""
+    y = snake(x, sd[f"{ru}.0.alpha"])
+    y = causal_conv1d(y, wn_weight(sd, f"{ru}.1"), sd[f"{ru}.1.conv.bias"], dilation=dilation)
+    y = snake(y, sd[f"{ru}.2.alpha"])
+    y = causal_conv1d(y, wn_weight(sd, f"{ru}.3"), sd[f"{ru}.3.conv.bias"])
+    return x + y
+
+
+def ae_encoder(sd: SD, cfg, audio: torch.Tensor) -> torch.Tensor:
+    """Encoder.forward, autoencoder.py:903-929 with EncoderBlock 839-876: audio [B, 1, n] -> z [B, latent_dim, n / prod(rates)]."""
+    eb = "encoder.block"
+    x = causal_conv1d(audio, wn_weight(sd, f"{eb}.0"), sd[f"{eb}.0.conv.bias"])
+    n = len(cfg.encoder_rates)
+    for i, r in enumerate(cfg.encoder_rates):
+        b = f"{eb}.{i + 1}.block"
+        for j, dil in enumerate((1, 3, 9)):
+            x = residual_unit(sd, f"{b}.{j}.block", x, dil)
+        x = snake(x, sd[f"{b}.3.alpha"])
+        x = causal_conv1d_strided(x, wn_weight(sd, f"{b}.4"), sd[f"{b}.4.conv.bias"], r)
+        if i == n - 1 and cfg.enc_tr_layers > 0:
+            x = ae_window_transformer(sd, cfg, x, f"{b}.5", layers=cfg.enc_tr_layers, heads=cfg.enc_tr_heads,
+                                      window=cfg.enc_tr_window)
+    x = snake(x, sd[f"{eb}.{n + 1}.alpha"])
+    return causal_conv1d(x, wn_weight(sd, f"{eb}.{n + 2}"), sd[f"{eb}.{n + 2}.conv.bias"])
+
+
+def ae_downsample(sd: SD, cfg, z: torch.Tensor) -> torch.Tensor:
+    """quantizer.downsample, autoencoder.py:416-425: per factor, strided causal conv (k = stride) then ConvNeXt."""
+    for u, f in enumerate(cfg.up_factors):
+        p = f"quantizer.downsample.{u}"
+        z = causal_conv1d_strided(z, sd[f"{p}.0.conv.weight"], sd[f"{p}.0.conv.bias"], f)
+        z = convnext_block(sd, f"{p}.1", z)
+    return z
+
+
+def vq_nearest(e: torch.Tensor, codebook: torch.Tensor) -> torch.Tensor:
+    """VectorQuantize.decode_latents, autoencoder.py:145-157: e [B, dim, T] -> indices [B, T] of the nearest
+    l2-normalised code (first index on exact ties, as torch.max)."""
+    B = e.shape[0]
+    enc = F.normalize(e.transpose(1, 2).reshape(-1, e.shape[1]))
+    cb = F.normalize(codebook)
+    dist = enc.pow(2).sum(1, keepdim=True) - 2 * enc @ cb.t() + cb.pow(2).sum(1, keepdim=True).t()
+    return (-dist).max(1)[1].reshape(B, -1)
+
+
+def vq_quantize(sd: SD, p: str, z: torch.Tensor):
+    """VectorQuantize.forward (eval), autoencoder.py:129-136: -> (out_proj(code vectors) [B, D, T], indices [B, T])."""
+    z_e = F.conv1d(z, wn_weight(sd, f"{p}.in_proj"), sd[f"{p}.in_proj.bias"])
+    idx = vq_nearest(z_e, sd[f"{p}.codebook.weight"])
+    z_q = F.embedding(idx, sd[f"{p}.codebook.weight"]).transpose(1, 2)
+    z_q = z_e + (z_q - z_e)                                  # straight-through form the reference evaluates
+    return F.conv1d(z_q, wn_weight(sd, f"{p}.out_proj"), sd[f"{p}.out_proj.bias"]), idx
+
+
+def rvq_codes(sd: SD, cfg, z: torch.Tensor) -> torch.Tensor:
+    """Semantic VQ then the residual stack (DownsampleResidualVectorQuantize.forward :457-468 with
+    ResidualVectorQuantize.forward :185-222, eval mode): z [B, D, T] -> codes [B, 1 + n_codebooks, T] int64."""
+    sem, idx0 = vq_quantize(sd, "quantizer.semantic_quantizer.quantizers.0", z)
+    residual = z - sem
+    codes = [idx0]
+    for q in range(cfg.n_codebooks):
+        z_q, idx = vq_quantize(sd, f"quantizer.quantizer.quantizers.{q}", residual)
+        residual = residual - z_q
+        codes.append(idx)
+    return torch.stack(codes, 1)
+
+
+def zq_from_codes(sd: SD, cfg, codes: torch.Tensor) -> torch.Tensor:
+    """encode_zq's second half, autoencoder.py:1116-1126 with from_codes :224-233: clamp, look up, out_proj, sum."""
+    z_q = 0.0
+    for i in range(codes.shape[1]):
+        p = "quantizer.semantic_quantizer.quantizers.0" if i == 0 else f"quantizer.quantizer.quantizers.{i - 1}"
+        cb = sd[f"{p}.codebook.weight"]
+        v = F.embedding(codes[:, i].clamp(max=cb.shape[0] - 1), cb).transpose(1, 2)
+        z_q = z_q + F.conv1d(v, wn_weight(sd, f"{p}.out_proj"), sd[f"{p}.out_proj.bias"])
+    return z_q
+
+
+def encode_stages(sd: SD, cfg, audio: torch.Tensor) -> dict:
+    """DAC.encode (autoencoder.py:1080-1100) + encode_zq (:1116-1126) with the intermediate tensors the stage-wise
+    parity tests pin: audio [B, 1, n] or [B, n] -> {z_enc, z_pre (quantizer input after pre_module), codes, z_q}."""
+    if audio.dim() == 2:
+        audio = audio.unsqueeze(1)
+    n = audio.shape[-1]
+    audio = F.pad(audio, (0, math.ceil(n / cfg.hop) * cfg.hop - n))
+    z_enc = ae_encoder(sd, cfg, audio)
+    z_pre = ae_window_transformer(sd, cfg, ae_downsample(sd, cfg, z_enc), "quantizer.pre_module")
+    codes = rvq_codes(sd, cfg, z_pre)
+    return dict(z_enc=z_enc, z_pre=z_pre, codes=codes, z_q=zq_from_codes(sd, cfg, codes))
+
+
+def encode_zq(sd: SD, cfg, audio: torch.Tensor) -> torch.Tensor:
+    """DAC.encode_zq, autoencoder.py:1116-1126: audio -> z_q [B, latent_dim, ceil(n / hop)]."""
+    return encode_stages(sd, cfg, audio)["z_q"]
+
+
+def ae_encode(sd: SD, cfg, pca_components, pca_mean, latent_scale: float, audio: torch.Tensor) -> torch.Tensor:
+    """inference.py:223-229: z_q -> PCA projection: ((z_q^T - mean) @ components^T) * latent_scale, [B, T, 80]."""
+    z_q = encode_zq(sd, cfg, audio).float()
+    return ((z_q.transpose(1, 2) - pca_mean) @ pca_components.T) * latent_scale

@@ -79,3 +79,30 @@ def test_ae_decode_matches_reference_fixture():
     # causality identity: decoding a prefix equals the prefix of the decode
     wav6 = O.ae_decode(sd, S.AE_BASE, comp, mean, scale, g["z"][:, :6])
     assert rel_l2(wav6, g["wav"][..., : 6 * 2048]) < 2e-4
+
+
+def _check_encode_fixture(name, cfg, with_pca=False):
+    g = torch.load(os.path.join(GOLDEN, name))
+    sd = S.synth_ae_state_dict(cfg, encode=True)
+    st = O.encode_stages(sd, cfg, g["audio"])
+    n_frames = -(-g["audio"].shape[-1] // cfg.hop)
+    assert st["z_q"].shape == g["z_q"].shape == (g["audio"].shape[0], cfg.latent_dim, n_frames)
+    assert st["codes"].dtype == g["codes"].dtype == torch.int64
+    assert torch.equal(st["codes"], g["codes"])                      # indices: bit-exact
+    for k in ("z_enc", "z_pre", "z_q"):
+        assert rel_l2(st[k], g[k].float()) < 1e-3                    # fixtures are stored in fp16
+    # from_codes alone (autoencoder.py:224-233) given the reference's codes
+    assert rel_l2(O.zq_from_codes(sd, cfg, g["codes"]), g["z_q"].float()) < 1e-3
+    if with_pca:
+        comp, mean, scale = O.synth_pca()
+        lat = O.ae_encode(sd, cfg, comp, mean, scale, g["audio"])
+        assert lat.shape == g["latent"].shape == (1, n_frames, 80) and rel_l2(lat, g["latent"]) < 2e-5
+
+
+def test_ae_encode_tiny_matches_reference_fixture():
+    _check_encode_fixture("ae_encode_tiny.pt", S.AE_TINY)
+
+
+@pytest.mark.slow
+def test_ae_encode_base_matches_reference_fixture():
+    _check_encode_fixture("ae_encode_base.pt", S.AE_BASE, with_pca=True)

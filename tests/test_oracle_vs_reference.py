@@ -81,3 +81,19 @@ def test_sampler_live(ns, tiny):
         out_r = ns.inference.sample_euler_cfg_independent_guidances(ref, spk, smask, ids, mask, 3, **kw)
     out_o = O.sample_euler_cfg_independent_guidances(sd, cfg, spk, smask, ids, mask, 3, **kw)
     assert out_o.shape == out_r.shape and rel_l2(out_o, out_r.float()) < 5e-5
+
+
+def test_ae_encode_live(ns):
+    """S1-DAC encode (autoencoder.py:1080-1126) at AE_TINY dims: stage tensors, bit-exact codes, ragged length,
+    both attention windows active (encoder transformer 512 of 608 frames, pre_module 16 of 152)."""
+    cfg = S.AE_TINY
+    sd = S.synth_ae_state_dict(cfg, encode=True)
+    ae = ref_import.build_ae_cfg(ns, cfg, sd)
+    g = torch.Generator().manual_seed(33)
+    for n in (cfg.hop * 152 - 5, cfg.hop * 3, 17):
+        audio = (torch.rand(1, 1, n, generator=g) * 2 - 1) * 0.7
+        r = ref_import.encode_stages(ae, audio)
+        o = O.encode_stages(sd, cfg, audio)
+        assert torch.equal(o["codes"], r["codes"])
+        for k in ("z_enc", "z_pre", "z_q"):
+            assert o[k].shape == r[k].shape and rel_l2(o[k], r[k].float()) < 1e-5
