@@ -135,6 +135,10 @@ EXPORTS = {
     "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
     "echo_conv_out_tanh": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
     "echo_cast_snake": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
+    "echo_conv_in_snake": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "echo_snake_bf16": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
+    "echo_rmsnorm_f32": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, c_p]),
+    "echo_vq_nearest": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p, C.c_int, c_p, c_p, c_p]),
     "echo_flattening_point": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, f32, f32, c_p, c_p]),
 }
 

@@ -1,4 +1,5 @@
-"""Fish S1-DAC decode engine (``DAC.decode_zq``, reference ``autoencoder.py:1128-1132``) on sm_100a kernels.
+"""Fish S1-DAC engine on sm_100a kernels: ``DAC.decode_zq`` (reference ``autoencoder.py:1128-1132``) and, when the
+checkpoint carries the encoder / quantizer tensors, ``DAC.encode_zq`` (``autoencoder.py:1080-1126``).
 
 Activations are time-major ``[B, T, C]`` so that every convolution is an implicit GEMM over TMA-shifted row
 windows (causal left padding = TMA out-of-bounds zero fill), weight-norm is folded once at load
@@ -30,6 +31,23 @@ def _pack_conv(w: torch.Tensor) -> torch.Tensor:
     return w.permute(0, 2, 1).reshape(w.shape[0], -1).to(BF16).contiguous()
 
 
+def _fold_wn_plain(sd, prefix: str, dev) -> torch.Tensor:
+    """weight-normed conv without the CausalConvNet wrapper (VectorQuantize.in_proj / out_proj, autoencoder.py:126-127)."""
+    g = sd[f"{prefix}.parametrizations.weight.original0"].to(dev).float()
+    v = sd[f"{prefix}.parametrizations.weight.original1"].to(dev).float()
+    return g * v / v.flatten(1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
+
+
+def _pack_conv_strided(w: torch.Tensor, stride: int) -> torch.Tensor:
+    """Strided causal Conv1d weight [Cout, Cin, K], K = taps*stride (left pad K - stride, autoencoder.py:283-289) ->
+    GEMM B operand [Cout, taps * stride*Cin] over the input viewed as [T/stride, stride*Cin] rows:
+    out[t] = sum_tap sum_j sum_ci x[(t - (taps-1) + tap)*stride + j, ci] * w[co, ci, tap*stride + j]."""
+    cout, cin, k = w.shape
+    taps = k // stride
+    assert taps * stride == k
+    return w.reshape(cout, cin, taps, stride).permute(0, 2, 3, 1).reshape(cout, k * cin).to(BF16).contiguous()
+
+
 def _pack_convT(w: torch.Tensor, stride: int) -> torch.Tensor:
     """ConvTranspose1d weight [Cin, Cout, K] (K = stride or 2*stride) -> [stride*Cout, taps*Cin]:
     out[t*stride + j] = sum_tap x[t - tap] . w[:, :, j + tap*stride]   (autoencoder.py:310-316, right trim)."""
@@ -52,20 +70,7 @@ class DAC:
         self._dtype = dtype                     # interface dtype of decode_zq's input/output (reference default fp32)
         dev, sd = self._device, state_dict
         f = lambda k: sd[k].to(dev).float().contiguous()
-        pm = "quantizer.post_module"
-        fc = sd[f"{pm}.freqs_cis"].to(dev).float()              # bf16-rounded table (autoencoder.py:805-813)
-        self.rope = (fc[..., 0].contiguous(), fc[..., 1].contiguous())
-        self.tr_layers = []
-        for i in range(cfg.tr_layers):
-            p = f"{pm}.layers.{i}"
-            self.tr_layers.append(dict(
-                wqkv=sd[f"{p}.attention.wqkv.weight"].to(dev).to(BF16).contiguous(),
-                wo=sd[f"{p}.attention.wo.weight"].to(dev).to(BF16).contiguous(),
-                w13=ops.pack_w13(sd[f"{p}.feed_forward.w1.weight"].to(dev), sd[f"{p}.feed_forward.w3.weight"].to(dev)).to(BF16),
-                w2=sd[f"{p}.feed_forward.w2.weight"].to(dev).to(BF16).contiguous(),
-                an=f(f"{p}.attention_norm.weight"), fn=f(f"{p}.ffn_norm.weight"),
-                ga=f(f"{p}.attention_layer_scale.gamma"), gf=f(f"{p}.ffn_layer_scale.gamma")))
-        self.tr_norm = f(f"{pm}.norm.weight")
+        self.post_tr = self._load_transformer(sd, "quantizer.post_module", cfg.tr_layers)
         self.ups = []
         for u, fac in enumerate(cfg.up_factors):
             p = f"quantizer.upsample.{u}"
@@ -97,6 +102,76 @@ class DAC:
         self.w_last = w_last[0].t().contiguous()                         # [7, C] fp32
         self.b_last = float(sd[f"{dm}.{n + 2}.conv.bias"].float().item())
         self._pca_cache = None
+        self.has_encoder = "encoder.block.0.conv.bias" in sd
+        if self.has_encoder:
+            self._load_encoder(sd)
+
+    def _load_transformer(self, sd, pm: str, n_layers: int) -> dict:
+        """Weights of one WindowLimitedTransformer (autoencoder.py:744-802); its RoPE table is the module's own
+        bf16-rounded buffer (autoencoder.py:805-813)."""
+        dev = self._device
+        f = lambda k: sd[k].to(dev).float().contiguous()
+        fc = sd[f"{pm}.freqs_cis"].to(dev).float()
+        layers = []
+        for i in range(n_layers):
+            p = f"{pm}.layers.{i}"
+            layers.append(dict(
+                wqkv=sd[f"{p}.attention.wqkv.weight"].to(dev).to(BF16).contiguous(),
+                wo=sd[f"{p}.attention.wo.weight"].to(dev).to(BF16).contiguous(),
+                w13=ops.pack_w13(sd[f"{p}.feed_forward.w1.weight"].to(dev), sd[f"{p}.feed_forward.w3.weight"].to(dev)).to(BF16),
+                w2=sd[f"{p}.feed_forward.w2.weight"].to(dev).to(BF16).contiguous(),
+                an=f(f"{p}.attention_norm.weight"), fn=f(f"{p}.ffn_norm.weight"),
+                ga=f(f"{p}.attention_layer_scale.gamma"), gf=f(f"{p}.ffn_layer_scale.gamma")))
+        return dict(layers=layers, norm=f(f"{pm}.norm.weight"), rope=(fc[..., 0].contiguous(), fc[..., 1].contiguous()))
+
+    def _load_convnext(self, sd, p: str) -> dict:
+        dev = self._device
+        f = lambda k: sd[k].to(dev).float().contiguous()
+        return dict(dw=f(f"{p}.dwconv.conv.weight").reshape(-1, 7).contiguous(), dwb=f(f"{p}.dwconv.conv.bias"),
+                    lnw=f(f"{p}.norm.weight"), lnb=f(f"{p}.norm.bias"),
+                    pw1=sd[f"{p}.pwconv1.weight"].to(dev).to(BF16).contiguous(), pb1=f(f"{p}.pwconv1.bias"),
+                    pw2=sd[f"{p}.pwconv2.weight"].to(dev).to(BF16).contiguous(), pb2=f(f"{p}.pwconv2.bias"),
+                    gamma=f(f"{p}.gamma"))
+
+    def _load_encoder(self, sd) -> None:
+        """Encoder (autoencoder.py:903-929), quantizer.downsample / pre_module (:416-425, :1150-1163) and the
+        1 + n_codebooks VectorQuantize layers (:117-157), packed like the decode half."""
+        cfg, dev = self.cfg, self._device
+        f = lambda k: sd[k].to(dev).float().contiguous()
+        eb = "encoder.block"
+        self.enc_in_w = _fold_wn(sd, f"{eb}.0", dev)[:, 0, :].contiguous()          # [C, 7] fp32
+        self.enc_in_b = f(f"{eb}.0.conv.bias")
+        self.enc_blocks = []
+        n = len(cfg.encoder_rates)
+        for i, r in enumerate(cfg.encoder_rates):
+            b = f"{eb}.{i + 1}.block"
+            blk = dict(rate=r, units=[], alpha_out=f(f"{b}.3.alpha").reshape(-1),
+                       wd=_pack_conv_strided(_fold_wn(sd, f"{b}.4", dev), r), bd=f(f"{b}.4.conv.bias"))
+            for j, dil in enumerate((1, 3, 9)):
+                ru = f"{b}.{j}.block"
+                blk["units"].append(dict(dil=dil, a1=f(f"{ru}.0.alpha").reshape(-1), a2=f(f"{ru}.2.alpha").reshape(-1),
+                                         w7=_pack_conv(_fold_wn(sd, f"{ru}.1", dev)), b7=f(f"{ru}.1.conv.bias"),
+                                         w1=_pack_conv(_fold_wn(sd, f"{ru}.3", dev)), b1=f(f"{ru}.3.conv.bias")))
+            self.enc_blocks.append(blk)
+        self.enc_tr = (self._load_transformer(sd, f"{eb}.{n}.block.5", cfg.enc_tr_layers) if cfg.enc_tr_layers > 0 else None)
+        self.enc_alpha_out = f(f"{eb}.{n + 1}.alpha").reshape(-1)
+        self.enc_out_w, self.enc_out_b = _pack_conv(_fold_wn(sd, f"{eb}.{n + 2}", dev)), f(f"{eb}.{n + 2}.conv.bias")
+        self.downs = []
+        for u, fac in enumerate(cfg.up_factors):
+            p = f"quantizer.downsample.{u}"
+            d = self._load_convnext(sd, f"{p}.1")
+            d.update(factor=fac, wd=_pack_conv_strided(sd[f"{p}.0.conv.weight"].to(dev).float(), fac), bd=f(f"{p}.0.conv.bias"))
+            self.downs.append(d)
+        self.pre_tr = self._load_transformer(sd, "quantizer.pre_module", cfg.tr_layers)
+        self.quantizers = []
+        names = ["quantizer.semantic_quantizer.quantizers.0"] + [f"quantizer.quantizer.quantizers.{q}" for q in range(cfg.n_codebooks)]
+        for p in names:
+            w_in = _fold_wn_plain(sd, f"{p}.in_proj", dev)[:, :, 0].contiguous()          # [dim, D] fp32
+            w_out = _fold_wn_plain(sd, f"{p}.out_proj", dev)[:, :, 0].contiguous()        # [D, dim] fp32
+            cb = f(f"{p}.codebook.weight")
+            self.quantizers.append(dict(w_in=w_in, b_in=f(f"{p}.in_proj.bias"), w_out=w_out, b_out=f(f"{p}.out_proj.bias"),
+                                        w_out_neg=(-w_out).contiguous(), b_out_neg=(-f(f"{p}.out_proj.bias")).contiguous(),
+                                        cb=cb, cbn=torch.nn.functional.normalize(cb).contiguous()))   # autoencoder.py:149
 
     @property
     def device(self):
@@ -109,34 +184,177 @@ class DAC:
     def eval(self):
         return self
 
-    def encode_zq(self, audio_data):
-        raise NotImplementedError(
-            "S1-DAC *encode* is not on the accelerated path yet (SURVEY.md section 8 row f1): pass speaker latents "
-            "directly to the sampler, or encode the reference clip once with the upstream model.")
-
     # ------------------------------------------------------------------------------------------
-    def _transformer(self, x: torch.Tensor, B: int, T: int) -> torch.Tensor:
-        """post_module (WindowLimitedTransformer, autoencoder.py:744-802): x fp32 [B*T, D] -> bf16 [B*T, D]."""
+    def _transformer(self, x: torch.Tensor, B: int, T: int, tw: Optional[dict] = None, *, heads: Optional[int] = None,
+                     ffn: Optional[int] = None, window: Optional[int] = None, out_f32: bool = False) -> torch.Tensor:
+        """WindowLimitedTransformer (autoencoder.py:744-802): x fp32 [B*T, D] residual stream (updated in place) ->
+        final RMSNorm as bf16 [B*T, D] (a GEMM operand) or fp32 (the quantizer input)."""
         cfg, dev = self.cfg, self._device
-        D, H, Dh = cfg.latent_dim, cfg.tr_heads, cfg.tr_head_dim
+        tw = self.post_tr if tw is None else tw
+        D = x.shape[1]
+        H, Dh = heads or cfg.tr_heads, cfg.tr_head_dim
+        ffn, window = ffn or cfg.tr_ffn, window or cfg.tr_window
         M = B * T
+        assert T <= tw["rope"][0].shape[0], "sequence longer than the transformer's RoPE table (block_size)"
         xn = torch.empty((M, D), device=dev, dtype=BF16)
         qkv = torch.empty((3, M, H * Dh), device=dev, dtype=BF16)
         ao = torch.empty((M, H * Dh), device=dev, dtype=BF16)
-        hmid = torch.empty((M, cfg.tr_ffn), device=dev, dtype=BF16)
-        for lw in self.tr_layers:
+        hmid = torch.empty((M, ffn), device=dev, dtype=BF16)
+        for lw in tw["layers"]:
             ops.rmsnorm_mod(x, lw["an"], None, xn, cfg.tr_eps)
             ops.gemm_sections(xn, lw["wqkv"], [(L.SEC_ROPE, qkv[0], None), (L.SEC_ROPE, qkv[1], None),
                                                (L.SEC_PLAIN, qkv[2], None)],
-                              head_dim=Dh, rope_heads=H, rope=self.rope, rows_per_seq=T, eps=cfg.tr_eps)
-            seg = ops.Segment(qkv[1].view(B, T, H, Dh), qkv[2].view(B, T, H, Dh), causal=True, window=cfg.tr_window)
+                              head_dim=Dh, rope_heads=H, rope=tw["rope"], rows_per_seq=T, eps=cfg.tr_eps)
+            seg = ops.Segment(qkv[1].view(B, T, H, Dh), qkv[2].view(B, T, H, Dh), causal=True, window=window)
             ops.attention(qkv[0].view(B, T, H, Dh), [seg], ao)
             ops.gemm_generic(ao, lw["wo"], gate=lw["ga"], resid=x, out_f32=x)
             ops.rmsnorm_mod(x, lw["fn"], None, xn, cfg.tr_eps)
             ops.gemm_swiglu(xn, lw["w13"], hmid)
             ops.gemm_generic(hmid, lw["w2"], gate=lw["gf"], resid=x, out_f32=x)
-        ops.rmsnorm_mod(x, self.tr_norm, None, xn, cfg.tr_eps)
+        if out_f32:
+            y = torch.empty((M, D), device=dev, dtype=F32)
+            ops.rmsnorm_f32(x, tw["norm"], y, cfg.tr_eps)
+            return y
+        ops.rmsnorm_mod(x, tw["norm"], None, xn, cfg.tr_eps)
         return xn
+
+    def _convnext(self, x: torch.Tensor, cw: dict, B: int, T: int, *, out_bf16=None, out_f32=None) -> None:
+        """ConvNeXtBlock (autoencoder.py:340-373): x fp32 [B*T, D] -> x + gamma * pw2(gelu(pw1(LN(dwconv(x)))))."""
+        dev = self._device
+        D = x.shape[1]
+        y = torch.empty((B * T, D), device=dev, dtype=BF16)
+        ops.dwconv_layernorm(x.view(B, T, D), cw["dw"], cw["dwb"], cw["lnw"], cw["lnb"], 1e-6, y.view(B, T, D))
+        hmid = torch.empty((B * T, cw["pw1"].shape[0]), device=dev, dtype=BF16)
+        ops.gemm_generic(y, cw["pw1"], bias=cw["pb1"], act=L.ACT_GELU, out_bf16=hmid)
+        ops.gemm_generic(hmid, cw["pw2"], bias=cw["pb2"], gate=cw["gamma"], resid=x, out_bf16=out_bf16, out_f32=out_f32)
+
+    # ------------------------------------------------------------------------------------------
+    # encode half (SURVEY 8 f1)
+    # ------------------------------------------------------------------------------------------
+    def _residual_units(self, units, x, s1, s2, B: int, next_alpha) -> None:
+        """Three ResidualUnits (autoencoder.py:879-900): x fp32 residual stream in place; s1 = snake(x) bf16 on entry,
+        = snake(x_out, next_alpha) on exit."""
+        for j, u in enumerate(units):
+            d = u["dil"]
+            ops.gemm_generic(s1, u["w7"], taps=tuple(-(6 - k) * d for k in range(7)), batch=B, bias=u["b7"],
+                             out2_bf16=s2, snake_alpha=u["a2"])
+            nxt = units[j + 1]["a1"] if j + 1 < len(units) else next_alpha
+            ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out_f32=x, out2_bf16=s1, snake_alpha=nxt)
+
+    def _encoder(self, audio: torch.Tensor):
+        """Encoder.forward (autoencoder.py:903-929): audio fp32 [B, T] (T a multiple of the hop) ->
+        (z fp32 [B*T', latent], z bf16 [B*T', latent], T' = T / prod(encoder_rates))."""
+        cfg, dev = self.cfg, self._device
+        B, T = audio.shape
+        C = self.enc_in_w.shape[0]
+        x = torch.empty((B, T, C), device=dev, dtype=F32)
+        s1 = torch.empty((B, T, C), device=dev, dtype=BF16)
+        ops.conv_in_snake(audio, self.enc_in_w, self.enc_in_b, self.enc_blocks[0]["units"][0]["a1"], x, s1)
+        x, s1 = x.view(B * T, C), s1.view(B * T, C)
+        n = len(self.enc_blocks)
+        for i, blk in enumerate(self.enc_blocks):
+            r = blk["rate"]
+            s2 = torch.empty_like(s1)
+            self._residual_units(blk["units"], x, s1, s2, B, blk["alpha_out"])
+            del s2, x
+            T, C = T // r, 2 * C
+            a = s1.view(B * T, r * C // 2)                   # strided conv = 2-tap conv over [T/r, r*C] rows
+            x = torch.empty((B * T, C), device=dev, dtype=F32)
+            if i + 1 < n:
+                s1 = torch.empty((B * T, C), device=dev, dtype=BF16)
+                ops.gemm_generic(a, blk["wd"], taps=(-1, 0), batch=B, bias=blk["bd"], out_f32=x, out2_bf16=s1,
+                                 snake_alpha=self.enc_blocks[i + 1]["units"][0]["a1"])
+            else:
+                ops.gemm_generic(a, blk["wd"], taps=(-1, 0), batch=B, bias=blk["bd"], out_f32=x)
+        s = torch.empty((B * T, C), device=dev, dtype=BF16)
+        if self.enc_tr is not None:
+            xn = self._transformer(x, B, T, self.enc_tr, heads=cfg.enc_tr_heads, ffn=3 * C, window=cfg.enc_tr_window)
+            ops.snake_bf16(xn, self.enc_alpha_out, s)
+        else:
+            ops.cast_snake(x, self.enc_alpha_out, s)
+        z = torch.empty((B * T, cfg.latent_dim), device=dev, dtype=F32)
+        zb = torch.empty((B * T, cfg.latent_dim), device=dev, dtype=BF16)
+        ops.gemm_generic(s, self.enc_out_w, taps=(-2, -1, 0), batch=B, bias=self.enc_out_b, out_f32=z, out_bf16=zb)
+        return z, zb, T
+
+    def _downsample(self, zb: torch.Tensor, B: int, T: int):
+        """quantizer.downsample (autoencoder.py:416-425): zb bf16 [B*T, D] -> fp32 [B*T/prod(factors), D]."""
+        dev = self._device
+        D = zb.shape[1]
+        x = None
+        for i, dw in enumerate(self.downs):
+            fac = dw["factor"]
+            T //= fac
+            x = torch.empty((B * T, D), device=dev, dtype=F32)
+            ops.gemm_generic(zb.view(B * T, fac * D), dw["wd"], batch=B, bias=dw["bd"], out_f32=x)   # k == stride: one tap
+            if i + 1 < len(self.downs):
+                zb = torch.empty((B * T, D), device=dev, dtype=BF16)
+                self._convnext(x, dw, B, T, out_bf16=zb)
+            else:
+                self._convnext(x, dw, B, T, out_f32=x)
+        return x, T
+
+    def _rvq(self, z: torch.Tensor):
+        """Semantic VQ + residual VQ stack in fp32 (autoencoder.py:457-468, 185-222, 129-157) and from_codes
+        (:224-233): z fp32 [M, D] -> (codes int32 [1 + n_codebooks, M], z_q fp32 [M, D])."""
+        dev = self._device
+        M, D = z.shape
+        residual = z.clone()
+        nq = len(self.quantizers)
+        codes = torch.empty((nq, M), device=dev, dtype=torch.int32)
+        z_q = torch.empty((M, D), device=dev, dtype=F32)
+        dim = self.quantizers[0]["cb"].shape[1]
+        e = torch.empty((M, dim), device=dev, dtype=F32)
+        code = torch.empty((M, dim), device=dev, dtype=F32)
+        for i, q in enumerate(self.quantizers):
+            ops.sgemm(residual, q["w_in"], bias=q["b_in"], out=e)
+            ops.vq_nearest(e, q["cbn"], q["cb"], codes[i], code)
+            ops.sgemm(code, q["w_out"], bias=q["b_out"], addend=(z_q if i > 0 else None), out=z_q)
+            if i + 1 < nq:      # residual -= out_proj(code): exact negation of weights and bias, then add
+                ops.sgemm(code, q["w_out_neg"], bias=q["b_out_neg"], addend=residual, out=residual)
+        return codes, z_q
+
+    @torch.inference_mode()
+    def encode_stages(self, audio_data: torch.Tensor) -> dict:
+        """encode_zq with the stage tensors the parity tests pin (reference layouts: channels-first)."""
+        if not self.has_encoder:
+            raise NotImplementedError("this DAC was loaded from a decode-only checkpoint (no encoder.* / quantizer "
+                                      "tensors): encode_zq needs the full S1-DAC state dict")
+        if not audio_data.is_cuda:
+            audio_data = audio_data.to(self._device)
+        a = audio_data.unsqueeze(1) if audio_data.ndim == 2 else audio_data
+        assert a.ndim == 3 and a.shape[1] == 1
+        cfg, dev = self.cfg, self._device
+        B, _, n = a.shape
+        hop = cfg.hop
+        T = -(-n // hop) * hop                                     # right pad to whole frames (autoencoder.py:1091-1092)
+        audio = torch.zeros((B, T), device=dev, dtype=F32)
+        audio[:, :n] = a[:, 0].to(dev, F32)
+        z_enc, zb, Te = self._encoder(audio)
+        x, Tq = self._downsample(zb, B, Te)
+        z_pre = self._transformer(x, B, Tq, self.pre_tr, out_f32=True)
+        codes, z_q = self._rvq(z_pre)
+        cf = lambda t, Tn: t.view(B, Tn, -1).transpose(1, 2)
+        return dict(z_enc=cf(z_enc, Te), z_pre=cf(z_pre, Tq), z_q=cf(z_q, Tq), z_q_rows=z_q,
+                    codes=codes.view(-1, B, Tq).permute(1, 0, 2).long())
+
+    def encode_zq(self, audio_data: torch.Tensor) -> torch.Tensor:
+        """Reference signature (autoencoder.py:1116-1126): audio [B, 1, n] -> z_q [B, latent_dim, ceil(n / hop)]."""
+        return self.encode_stages(audio_data)["z_q"].to(self._dtype)
+
+    @torch.inference_mode()
+    def encode_latent(self, audio: torch.Tensor, pca_components: torch.Tensor, pca_mean: torch.Tensor,
+                      latent_scale: float) -> torch.Tensor:
+        """ae_encode (inference.py:223-229) fused: the PCA projection reads z_q time-major (no transposes):
+        ((z_q - mean) @ components^T) * scale = (z_q @ components^T - components @ mean) * scale, fp32 [B, T, 80]."""
+        dev = self._device
+        st = self.encode_stages(audio)
+        comp = pca_components.to(dev, F32).contiguous()
+        nb = -(comp @ pca_mean.to(dev, F32)).contiguous()
+        B, _, Tq = st["z_q"].shape
+        out = torch.empty((B * Tq, comp.shape[0]), device=dev, dtype=F32)
+        ops.sgemm(st["z_q_rows"], comp, bias=nb, out=out, out_scale=float(latent_scale))
+        return out.view(B, Tq, -1)
 
     def _upsample(self, a: torch.Tensor, B: int, T: int):
         """quantizer.upsample (autoencoder.py:427-435): a bf16 [B*T, D] -> bf16 [B*T*prod(factors), D]."""

@@ -101,6 +101,88 @@ __global__ void cast_snake_kernel(const float* __restrict__ x, long long n, int 
   *reinterpret_cast<uint2*>(y + i) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
 }
 
+// ---- S1-DAC encode helpers ----------------------------------------------------------------------------
+// Encoder's first layer (autoencoder.py:917): causal conv k=7 from the mono waveform to C channels, fused with the
+// first ResidualUnit's Snake: x fp32 [B, T, C] (residual stream) and snake(x) bf16 (operand of the next conv).
+// HBM-bound on the stores: one thread per (t, 4 channels), the 7 input samples come from L1.
+__global__ void conv_in_snake_kernel(const float* __restrict__ audio, int t_len, int c_len, const float* __restrict__ w,
+                                     const float* __restrict__ bias, const float* __restrict__ alpha,
+                                     float* __restrict__ x, bf16* __restrict__ s) {
+  const int cq = c_len >> 2;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // over t * cq
+  const int bt = blockIdx.y;
+  if (i >= (long long)t_len * cq) return;
+  const int t = (int)(i / cq), c = (int)(i % cq) * 4;
+  const float* a = audio + (long long)bt * t_len;
+  float in[7];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) in[k] = (t - 6 + k >= 0) ? __ldg(a + t - 6 + k) : 0.f;
+  float o[4], sn[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float acc = bias[c + j];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) acc = fmaf(w[(c + j) * 7 + k], in[k], acc);
+    o[j] = acc;
+    sn[j] = snakef_(acc, alpha[c + j]);
+  }
+  const long long off = ((long long)bt * t_len + t) * c_len + c;
+  *reinterpret_cast<float4*>(x + off) = make_float4(o[0], o[1], o[2], o[3]);
+  *reinterpret_cast<uint2*>(s + off) = make_uint2(pack_bf16x2(sn[0], sn[1]), pack_bf16x2(sn[2], sn[3]));
+}
+
+__global__ void snake_bf16_kernel(const bf16* __restrict__ x, long long n, int c_len, const float* __restrict__ alpha,
+                                  bf16* __restrict__ y) {
+  const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const uint2 u = *reinterpret_cast<const uint2*>(x + i);
+  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+  float o[4] = {a.x, a.y, b.x, b.y};
+  const int c = (int)(i % c_len);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) o[j] = snakef_(o[j], alpha[c + j]);
+  *reinterpret_cast<uint2*>(y + i) = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
+}
+
+// VectorQuantize.decode_latents (autoencoder.py:145-157) in fp32: one warp per row; the row is l2-normalised, the
+// codebook arrives normalised (cbn), dist = |e|^2 - 2 e.c + |c|^2 evaluated in the reference's order; smallest
+// distance wins, smallest index on exact ties (torch.max of -dist).  Also gathers the RAW code vector (embed_code).
+template <int DIM>
+__global__ void vq_nearest_kernel(const float* __restrict__ e, int m, const float* __restrict__ cbn,
+                                  const float* __restrict__ cb, int n, int* __restrict__ idx_out,
+                                  float* __restrict__ code_out) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= m) return;
+  float v[DIM], ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < DIM; ++j) { v[j] = e[(long long)row * DIM + j]; ss = fmaf(v[j], v[j], ss); }
+  const float inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);
+  float e2 = 0.f;
+#pragma unroll
+  for (int j = 0; j < DIM; ++j) { v[j] *= inv; e2 = fmaf(v[j], v[j], e2); }
+  float best = INFINITY;
+  int bi = 0x7fffffff;
+  for (int k = lane; k < n; k += 32) {
+    float dot = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < DIM; ++j) {
+      const float c = __ldg(cbn + (long long)k * DIM + j);
+      dot = fmaf(v[j], c, dot);
+      c2 = fmaf(c, c, c2);
+    }
+    const float dist = (e2 - 2.f * dot) + c2;
+    if (dist < best) { best = dist; bi = k; }           // k ascending per lane: first minimum kept
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  if (lane == 0) idx_out[row] = bi;
+  if (code_out && lane < DIM) code_out[(long long)row * DIM + lane] = cb[(long long)bi * DIM + lane];
+}
+
 // find_flattening_point (inference.py:315-330).  Per-row (sum, sum of squares) in fp64, then every
 // window start i checks unbiased std < thr and |mean - target| < 0.1; the smallest hit wins.
 __global__ void flattening_kernel(const float* __restrict__ x, int len, int width, int window, float thr, float target,
@@ -178,6 +260,37 @@ extern "C" int echo_flattening_point(const float* latent, int len, int width, in
   const size_t smem = (size_t)(len + window) * 2 * sizeof(double);
   ECHO_CHECK_ARG(smem <= 48 * 1024, "flattening: latent too long");
   flattening_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(latent, len, width, window, std_threshold, target, index_out);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_conv_in_snake(const float* audio, int batch, int t, int c, const float* w, const float* bias,
+                                  const float* alpha, float* x, void* s, echo_stream_t stream) {
+  ECHO_CHECK_ARG(audio && w && bias && alpha && x && s && batch > 0 && t > 0 && c > 0 && c % 4 == 0, "conv_in: bad argument");
+  const long long n = (long long)t * (c / 4);
+  conv_in_snake_kernel<<<dim3((unsigned)((n + 255) / 256), batch), 256, 0, (cudaStream_t)stream>>>(audio, t, c, w, bias, alpha,
+                                                                                                 x, (bf16*)s);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_snake_bf16(const void* x, int64_t rows, int c, const float* alpha, void* y, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && y && alpha && rows > 0 && c > 0 && c % 4 == 0, "snake_bf16: bad argument");
+  const long long n = rows * c;
+  snake_bf16_kernel<<<(unsigned)((n / 4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, n, c, alpha, (bf16*)y);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_vq_nearest(const float* e, int m, int dim, const float* codebook_normalized, const float* codebook,
+                               int n, int32_t* index_out, float* code_out, echo_stream_t stream) {
+  ECHO_CHECK_ARG(e && codebook_normalized && codebook && index_out && m > 0 && n > 0, "vq_nearest: bad argument");
+  ECHO_CHECK_ARG(dim == 8, "vq_nearest: codebook_dim %d not supported (8)", dim);
+  vq_nearest_kernel<8><<<ceil_div(m, 4), 128, 0, (cudaStream_t)stream>>>(e, m, codebook_normalized, codebook, n, index_out,
+                                                                       code_out);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

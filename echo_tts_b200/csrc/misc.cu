@@ -174,6 +174,28 @@ extern "C" int echo_add_rmsnorm_mod(float* x, int64_t ldx, int m, int d, float e
                         ldy, stream);
 }
 
+// RMSNorm with an fp32 result (autoencoder.py:726-731): the quantizer's input must not be rounded to bf16 (the
+// nearest-code search is precision-sensitive).  One warp per row.
+__global__ void rmsnorm_f32_kernel(const float* __restrict__ x, long long ldx, int m, int d, float eps,
+                                   const float* __restrict__ w, float* __restrict__ y, long long ldy) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= m) return;
+  const float* xr = x + (long long)row * ldx;
+  float ssq = 0.f;
+  for (int c = lane; c < d; c += 32) ssq = fmaf(xr[c], xr[c], ssq);
+  const float rstd = rsqrtf(warp_sum(ssq) / (float)d + eps);
+  float* yr = y + (long long)row * ldy;
+  for (int c = lane; c < d; c += 32) yr[c] = xr[c] * rstd * w[c];
+}
+extern "C" int echo_rmsnorm_f32(const float* x, int64_t ldx, int m, int d, float eps, const float* weight, float* y,
+                                int64_t ldy, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && weight && y && m > 0 && d > 0, "rmsnorm_f32: bad argument");
+  rmsnorm_f32_kernel<<<ceil_div(m, 8), 256, 0, (cudaStream_t)stream>>>(x, (long long)ldx, m, d, eps, weight, y, (long long)ldy);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // fp32 CUDA-core GEMM: 64x64 tile, 16x16 threads, 4x4 micro-tile, K step 16.  Small/accuracy-critical.
 // ---------------------------------------------------------------------------------------------

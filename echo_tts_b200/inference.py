@@ -50,9 +50,12 @@ def load_model_from_hf(repo_id: str = "jordand/echo-tts-base", device: str = "cu
 
 
 def load_fish_ae_from_state_dict(state: dict, device: str = "cuda", dtype=torch.float32, cfg: AEConfig = AE_BASE) -> DAC:
-    if "quantizer.post_module.freqs_cis" not in state:
-        state = dict(state)
-        state["quantizer.post_module.freqs_cis"] = ae_rope_table(cfg)
+    state = dict(state)
+    # RoPE tables are module buffers (autoencoder.py:805-813); rebuild the ones a checkpoint does not carry
+    enc_tr = f"encoder.block.{len(cfg.encoder_rates)}.block.5"
+    for pm, args in (("quantizer.post_module", ()), ("quantizer.pre_module", ()), (enc_tr, (cfg.enc_tr_block_size, 64))):
+        if f"{pm}.norm.weight" in state and f"{pm}.freqs_cis" not in state:
+            state[f"{pm}.freqs_cis"] = ae_rope_table(cfg, *args)
     return DAC(state, cfg=cfg, device=device, dtype=dtype if dtype is not None else torch.float32)
 
 
@@ -126,9 +129,11 @@ def get_text_input_ids_and_mask(text_arr: List[str], max_length: Optional[int], 
 
 @torch.inference_mode()
 def ae_encode(fish_ae, pca_state: PCAState, audio: torch.Tensor) -> torch.Tensor:
-    """inference.py:223-229.  ``fish_ae.encode_zq`` is duck-typed: the B200 DAC does not implement the encode
-    half yet, but any object with the reference's ``encode_zq`` works."""
+    """inference.py:223-229.  The B200 DAC runs encoder + quantizer + PCA projection on its kernels
+    (``DAC.encode_latent``); any other object with the reference's ``encode_zq`` is used duck-typed."""
     assert audio.ndim == 3 and audio.shape[1] == 1
+    if isinstance(fish_ae, DAC):
+        return fish_ae.encode_latent(audio, pca_state.pca_components, pca_state.pca_mean, pca_state.latent_scale)
     z_q = fish_ae.encode_zq(audio).float()
     z_q = (z_q.transpose(1, 2) - pca_state.pca_mean) @ pca_state.pca_components.T
     return z_q * pca_state.latent_scale

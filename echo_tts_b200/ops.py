@@ -380,3 +380,43 @@ def flattening_point(latent: torch.Tensor, window: int = 20, std_threshold: floa
     L.check(L.load().echo_flattening_point(latent.data_ptr(), latent.shape[0], latent.shape[1], window, std_threshold,
                                            target, out.data_ptr(), L.stream()))
     return out
+
+
+def conv_in_snake(audio, w, bias, alpha, x, s) -> None:
+    """audio fp32 [B, T] -> x fp32 [B, T, C] (causal conv k=7, w [C, 7]) and s bf16 [B, T, C] = snake(x, alpha)."""
+    _need(audio, F32, "audio"); _need(x, F32, "x"); _need(s, BF16, "s"); _need(w, F32, "w")
+    B, T = audio.shape
+    Cc = w.shape[0]
+    assert audio.is_contiguous() and x.is_contiguous() and s.is_contiguous() and w.shape == (Cc, 7) and w.is_contiguous()
+    assert x.shape == (B, T, Cc) and s.shape == (B, T, Cc) and bias.numel() == Cc and alpha.numel() == Cc
+    L.check(L.load().echo_conv_in_snake(audio.data_ptr(), B, T, Cc, w.data_ptr(), bias.data_ptr(), alpha.data_ptr(),
+                                        x.data_ptr(), s.data_ptr(), L.stream()))
+
+
+def snake_bf16(x, alpha, y) -> None:
+    _need(x, BF16, "x"); _need(y, BF16, "y"); _need(alpha, F32, "alpha")
+    Cc = x.shape[-1]
+    assert x.is_contiguous() and y.is_contiguous() and y.shape == x.shape and alpha.numel() == Cc
+    L.check(L.load().echo_snake_bf16(x.data_ptr(), x.numel() // Cc, Cc, alpha.data_ptr(), y.data_ptr(), L.stream()))
+
+
+def rmsnorm_f32(x, weight, y, eps: float) -> None:
+    """x fp32 [M, d] -> y fp32 [M, d] = x * rsqrt(mean x^2 + eps) * weight."""
+    _need(x, F32, "x"); _need(y, F32, "y"); _need(weight, F32, "weight")
+    M, d = x.shape
+    assert y.shape == x.shape and x.stride(1) == 1 and y.stride(1) == 1 and weight.numel() == d
+    L.check(L.load().echo_rmsnorm_f32(x.data_ptr(), x.stride(0), M, d, eps, weight.data_ptr(), y.data_ptr(), y.stride(0),
+                                      L.stream()))
+
+
+def vq_nearest(e, codebook_normalized, codebook, index_out, code_out=None) -> None:
+    """e fp32 [M, 8] -> index_out int32 [M] (nearest l2-normalised code), code_out fp32 [M, 8] raw code vectors."""
+    _need(e, F32, "e"); _need(codebook_normalized, F32, "codebook_normalized"); _need(codebook, F32, "codebook")
+    M, dim = e.shape
+    assert e.is_contiguous() and codebook.is_contiguous() and codebook_normalized.is_contiguous()
+    assert codebook.shape == codebook_normalized.shape and codebook.shape[1] == dim
+    assert index_out.is_cuda and index_out.dtype == torch.int32 and index_out.numel() == M and index_out.is_contiguous()
+    if code_out is not None:
+        _need(code_out, F32, "code_out"); assert code_out.shape == e.shape and code_out.is_contiguous()
+    L.check(L.load().echo_vq_nearest(e.data_ptr(), M, dim, codebook_normalized.data_ptr(), codebook.data_ptr(),
+                                     codebook.shape[0], index_out.data_ptr(), L.ptr(code_out), L.stream()))

@@ -304,6 +304,25 @@ int echo_conv_out_tanh(const void* x_bf16, int batch, int t, int c, const float*
 /* element-wise fp32 -> bf16 with optional Snake (autoencoder.py:96-102) over [rows, c] */
 int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * S1-DAC encode helpers (DAC.encode_zq, autoencoder.py:1080-1126; the convolutions, transformers and ConvNeXt blocks
+ * of the encode path run on echo_gemm_bf16 / echo_attention / echo_dwconv_layernorm like the decode path).
+ * ------------------------------------------------------------------------------------------ */
+/* Encoder's first layer (autoencoder.py:917) + the first ResidualUnit's Snake (:884): audio fp32 [B, T] ->
+ * x fp32 [B, T, C] = causal conv k=7 (w [C][7]) + bias, and s bf16 [B, T, C] = snake(x, alpha) */
+int echo_conv_in_snake(const float* audio, int batch, int t, int c, const float* w, const float* bias,
+                       const float* alpha, float* x, void* s_bf16, echo_stream_t stream);
+/* Snake1d on a bf16 operand (autoencoder.py:96-109): x bf16 [rows, c] -> y bf16 [rows, c] */
+int echo_snake_bf16(const void* x_bf16, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
+/* RMSNorm with an fp32 result (autoencoder.py:726-731), y = x * rsqrt(mean x^2 + eps) * weight: the quantizer input */
+int echo_rmsnorm_f32(const float* x, int64_t ldx, int m, int d, float eps, const float* weight, float* y, int64_t ldy,
+                     echo_stream_t stream);
+/* VectorQuantize.decode_latents (autoencoder.py:145-157) in fp32: e [m, dim] (l2-normalised inside), codebook rows
+ * given both l2-normalised (search) and raw (gather); index_out[m] = nearest code (lowest index on ties),
+ * code_out (nullable) fp32 [m, dim] = the raw code vectors (embed_code :138-139).  dim must be 8. */
+int echo_vq_nearest(const float* e, int m, int dim, const float* codebook_normalized, const float* codebook, int n,
+                    int32_t* index_out, float* code_out, echo_stream_t stream);
+
 /* find_flattening_point (inference.py:315-330): latent fp32 [len, width] -> index (device int32) */
 int echo_flattening_point(const float* latent, int len, int width, int window, float std_threshold,
                           float target, int32_t* index_out, echo_stream_t stream);

@@ -1,0 +1,137 @@
+"""S1-DAC encode on the sm_100a path against the reference fixtures and the CPU oracle.
+
+The nearest-code search is a discrete decision: with bf16 tensor-core convolutions upstream a small fraction of
+frames lands on a neighbouring code (the reference run in bf16 does the same), so parity is pinned stage by stage:
+continuous tensors within tolerance, and the quantizer itself bit-exact on identical fp32 input."""
+import os
+
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from echo_tts_b200 import schema as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _dac(cfg):
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    return load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg, encode=True), cfg=cfg)
+
+
+@pytest.fixture(scope="module")
+def tiny():
+    return _dac(S.AE_TINY)
+
+
+def test_conv_in_and_strided_conv_vs_torch():
+    """the two new conv forms: 1 -> C first layer (+ Snake) and the stride-s causal conv as a 2-tap GEMM over [T/s, s*C]"""
+    import torch.nn.functional as F
+    from echo_tts_b200 import ops
+    from echo_tts_b200.autoencoder import _pack_conv_strided
+    g = torch.Generator().manual_seed(0)
+    B, T, C = 2, 1024, 64
+    audio = (torch.rand(B, T, generator=g) * 2 - 1).cuda()
+    w = (torch.randn(C, 7, generator=g) * 0.4).cuda(); b = (torch.randn(C, generator=g) * 0.1).cuda()
+    alpha = (0.5 + torch.rand(C, generator=g)).cuda()
+    x = torch.empty(B, T, C, device="cuda"); s = torch.empty(B, T, C, device="cuda", dtype=torch.bfloat16)
+    ops.conv_in_snake(audio, w, b, alpha, x, s)
+    ref = F.conv1d(F.pad(audio.unsqueeze(1), (6, 0)), w.unsqueeze(1), b).transpose(1, 2)
+    assert rel_l2(x, ref) < 1e-6
+    assert rel_l2(s.float(), ref + torch.sin(alpha * ref) ** 2 / (alpha + 1e-9)) < 3e-3
+    for stride, cin, cout in ((2, 64, 128), (8, 32, 64), (4, 16, 32)):
+        wc = (torch.randn(cout, cin, 2 * stride, generator=g) / (2 * stride * cin) ** 0.5).cuda()
+        bc = (torch.randn(cout, generator=g) * 0.1).cuda()
+        xin = torch.randn(B, T, cin, generator=g).cuda().to(torch.bfloat16)
+        out = torch.empty(B * T // stride, cout, device="cuda")
+        ops.gemm_generic(xin.view(B * T // stride, stride * cin), _pack_conv_strided(wc, stride), taps=(-1, 0), batch=B,
+                         bias=bc, out_f32=out)
+        ref = F.conv1d(F.pad(xin.float().transpose(1, 2), (stride, 0)), wc.to(torch.bfloat16).float(), bc, stride=stride)
+        assert rel_l2(out.view(B, T // stride, cout), ref.transpose(1, 2)) < 2e-5
+
+
+def test_vq_nearest_bit_exact_vs_torch():
+    """VectorQuantize.decode_latents (autoencoder.py:145-157): indices identical to the fp32 torch formula, ties -> lowest"""
+    import torch.nn.functional as F
+    from echo_tts_b200 import ops
+    g = torch.Generator().manual_seed(1)
+    for M, N in ((640, 4096), (37, 1024), (5, 3)):
+        e = torch.randn(M, 8, generator=g).cuda()
+        cb = torch.randn(N, 8, generator=g).cuda()
+        if N > 2:
+            cb[2] = cb[1]                                             # exact tie: the lower index must win
+            e[0] = cb[1] * 3.0
+        cbn = F.normalize(cb)
+        idx = torch.empty(M, device="cuda", dtype=torch.int32); code = torch.empty(M, 8, device="cuda")
+        ops.vq_nearest(e, cbn, cb, idx, code)
+        en = F.normalize(e)
+        dist = en.pow(2).sum(1, keepdim=True) - 2 * en @ cbn.t() + cbn.pow(2).sum(1, keepdim=True).t()
+        want = (-dist).max(1)[1]
+        # fp32 rounding of the two evaluation orders can differ in the last bit: any disagreement must be a near-tie
+        bad = (idx.long() != want).nonzero().flatten()
+        for r in bad.tolist():
+            assert abs(float(dist[r, idx[r]] - dist[r, want[r]])) < 1e-6
+        assert len(bad) <= max(1, M // 200)
+        assert int(idx[0]) == 1 or N <= 2
+        assert torch.equal(code, cb[idx.long()])
+
+
+@pytest.mark.parametrize("name,cfg", [("ae_encode_tiny.pt", S.AE_TINY), ("ae_encode_base.pt", S.AE_BASE)])
+def test_encode_vs_reference_fixture(name, cfg):
+    g = torch.load(os.path.join(GOLDEN, name))
+    dac = _dac(cfg)
+    st = dac.encode_stages(g["audio"].cuda())
+    assert st["z_q"].shape == g["z_q"].shape and st["codes"].shape == g["codes"].shape and st["codes"].dtype == torch.int64
+    # continuous stages: bf16 tensor-core operands vs the reference's fp32 run
+    assert rel_l2(st["z_enc"].cpu(), g["z_enc"].float()) < 2e-2
+    assert rel_l2(st["z_pre"].cpu(), g["z_pre"].float()) < 2e-2
+    # discrete stage: the semantic code (level 0) of a frame flips only on near-ties
+    same0 = (st["codes"][:, 0].cpu() == g["codes"][:, 0]).float().mean().item()
+    assert same0 > 0.8, same0
+    # quantizer alone, teacher-forced with the reference's own fp32 input: bit-exact codes (up to exact fp32 ties)
+    z_pre = g["z_pre"].float().cuda()                                 # fp16-stored fixture: recompute the reference codes
+    from oracle import echo_oracle as O
+    sd = S.synth_ae_state_dict(cfg, encode=True)
+    want = O.rvq_codes(sd, cfg, z_pre.cpu())
+    B, D, Tq = z_pre.shape
+    codes, z_q = dac._rvq(z_pre.transpose(1, 2).reshape(B * Tq, D).contiguous())
+    got = codes.view(-1, B, Tq).permute(1, 0, 2).long().cpu()
+    frames_equal = (got == want).all(dim=1).float().mean().item()
+    assert frames_equal > 0.97, frames_equal
+    assert rel_l2(z_q.view(B, Tq, D).transpose(1, 2).cpu(), O.zq_from_codes(sd, cfg, got)) < 1e-5
+
+
+def test_encode_interface_and_padding(tiny):
+    """reference signature / shapes (autoencoder.py:1080-1126): ragged lengths are right-padded to whole frames;
+    the encoder is causal, so a clip's z_enc is a prefix of a longer clip's"""
+    cfg = S.AE_TINY
+    g = torch.Generator().manual_seed(4)
+    a = (torch.rand(1, 1, cfg.hop * 9 - 11, generator=g) * 2 - 1).cuda()
+    z = tiny.encode_zq(a)
+    assert z.shape == (1, cfg.latent_dim, 9) and z.dtype == tiny.dtype
+    assert tiny.encode_zq(a[:, 0]).shape == z.shape                   # [B, n] accepted like the reference
+    long = tiny.encode_stages(torch.cat([a, torch.zeros(1, 1, 11 + cfg.hop * 3, device="cuda")], -1))
+    short = tiny.encode_stages(a)
+    n = short["z_enc"].shape[-1]
+    assert torch.equal(long["z_enc"][..., :n], short["z_enc"])        # causal + zero right pad: bit-identical prefix
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    dec_only = load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg), cfg=cfg)
+    with pytest.raises(NotImplementedError):
+        dec_only.encode_zq(a)
+
+
+def test_speaker_latent_pipeline_vs_oracle(tiny):
+    """ae_encode + get_speaker_latent_and_mask (inference.py:223-229, 250-309) through the native encode"""
+    from echo_tts_b200.inference import PCAState, ae_encode
+    from oracle import echo_oracle as O
+    cfg = S.AE_TINY
+    comp, mean, scale = O.synth_pca(latent_dim=cfg.latent_dim)
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    g = torch.Generator().manual_seed(6)
+    audio = (torch.rand(1, 1, cfg.hop * 40, generator=g) * 2 - 1) * 0.8
+    lat = ae_encode(tiny, pca, audio.cuda())
+    want = O.ae_encode(S.synth_ae_state_dict(cfg, encode=True), cfg, comp, mean, scale, audio)
+    assert lat.shape == want.shape == (1, 40, 80) and lat.dtype == torch.float32
+    # frames whose codes all agree must agree closely; the rest are near-tie flips (bounded fraction)
+    err = (lat.cpu() - want).norm(dim=-1) / want.norm(dim=-1).clamp_min(1e-6)
+    assert (err < 1e-3).float().mean().item() > 0.7
