@@ -190,7 +190,7 @@ def run_gpu(args):
     pk = peaks()
     t0 = time.time()
     model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=False), init="torch"))
-    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE))
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE, encode=True))
     comp, mean, scale = O.synth_pca()
     pca = PCAState(comp.cuda(), mean.cuda(), scale)
     load_s = time.time() - t0
@@ -266,6 +266,27 @@ def run_gpu(args):
             ts.append(a.elapsed_time(b))
         return sorted(ts)[n // 2]
 
+    # the whole reference-facing pipeline from a 10 s waveform: S1-DAC encode of the speaker clip, text
+    # tokenisation, conditioning, 40 Euler steps, decode, flattening-point crop; host waveform in, host waveform out
+    from functools import partial
+    from echo_tts_b200.inference import sample_pipeline
+    wave = ((torch.rand(1, 441000, generator=torch.Generator().manual_seed(11)) * 2 - 1) * 0.5).pin_memory()
+    sample_fn = partial(sample, **KW)
+    text = "[S1] " + ("the quick brown fox jumps over the lazy dog " * 6)[:250]        # 255 bytes + BOS = 256 valid ids
+
+    def pipeline():
+        audio, _ = sample_pipeline(model, ae, pca, sample_fn, text, wave, 0, pad_to_max_text_length=768)
+        return audio.cpu()
+    pipe_ms = []
+    for i in range(6):                                                 # first calls warm the encoder and capture the graph
+        t_p = time.perf_counter()
+        out_wave = pipeline()
+        torch.cuda.synchronize()
+        pipe_ms.append((time.perf_counter() - t_p) * 1e3)
+    pipeline_rec = dict(ms=sorted(pipe_ms[3:])[1], samples_out=int(out_wave.shape[-1]), speaker_clip_samples=441000,
+                        what="sample_pipeline(): host waveform -> S1-DAC encode -> sampler -> decode -> crop -> host, "
+                             "wall clock, median of 3 after 3 warm-up calls")
+
     # per-step latency: slope between 40- and 20-step schedules, all steps guided / none guided
     all_cfg, no_cfg = dict(KW, cfg_min_t=0.0, cfg_max_t=1.0), dict(KW, cfg_min_t=2.0, cfg_max_t=3.0)
     step_ms = {name: (sampler_ms_median(dict(kw, num_steps=40)) - sampler_ms_median(dict(kw, num_steps=20))) / 20
@@ -285,7 +306,7 @@ def run_gpu(args):
                 generation_roofline=dict(bound="tensor", achieved=step_tflops, peak=pk["bf16_sustained"], unit="TFLOP/s",
                                          frac=step_tflops / pk["bf16_sustained"], flop_per_generation=B * FLOP_GEN,
                                          peak_source=pk["src"] + " sustained"),
-                breakdown_ms=dict(conditioning_plus_sampler=sampler_ms, decode=decode_ms), step_latency_ms=step_ms,
+                breakdown_ms=dict(conditioning_plus_sampler=sampler_ms, decode=decode_ms), step_latency_ms=step_ms, pipeline_from_waveform=pipeline_rec,
                 load_seconds=load_s)
     if not args.no_cpu_baseline:
         del model, ae
