@@ -166,9 +166,9 @@ def gemm_roofline(model, pk):
     flops = 2.0 * M * F2 * D
     ach = flops / sec / 1e12
     # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full` capture
-    # (profiles/r1_ncu_hot_kernels.md: 56.13 MB + 5.90 MB), per launch like `achieved`
+    # (profiles/r1_ncu_hot_kernels.md: 56.17 MB + 5.18 MB), per launch like `achieved`
     return dict(bound="tensor", kernel="gemm_pair_kernel<SWIGLU> (tcgen05 cta_group::2, 256x256 tiles) M=1920 N=11776 K=2048",
-                achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=62.03e6,
+                achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=61.35e6,
                 traffic_unit="bytes/launch (ncu dram read+write)", flop_per_launch=flops,
                 peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6)
 
