@@ -32,7 +32,7 @@ class GemmDesc(C.Structure):
         ("out_bf16", c_p), ("ld_out_bf16", i64), ("out2_bf16", c_p), ("ld_out2_bf16", i64),
         ("snake_alpha", c_p),
         ("n_sections", i32), ("section_width", i32), ("head_dim", i32), ("rope_heads", i32),
-        ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("_pad1", i32),
+        ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("a_ctx", i32),
         ("eps", f32), ("_pad2", f32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
         ("sections", GemmSection * 4), ("split_stride", i64),
         ("workspace", c_p), ("workspace_bytes", i64),
@@ -56,7 +56,7 @@ class AttnSegment(C.Structure):
     _fields_ = [
         ("k", c_p), ("v", c_p), ("row_stride", i64), ("batch_stride", i64),
         ("len", i32), ("kv_batch_mod", i32), ("mask", c_p), ("mask_stride", i64),
-        ("extent", c_p), ("kv_scale", c_p), ("causal", i32), ("window", i32),
+        ("extent", c_p), ("kv_scale", c_p), ("causal", i32), ("window", i32), ("q_offset", i32), ("_pad", i32),
     ]
 
 
@@ -134,6 +134,8 @@ EXPORTS = {
     "echo_embedding": (C.c_int, [c_p, C.c_int, c_p, C.c_int, c_p, c_p]),
     "echo_dwconv_layernorm": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
     "echo_conv_out_tanh": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
+    "echo_dwconv_layernorm_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
+    "echo_conv_out_tanh_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
     "echo_cast_snake": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
     "echo_conv_in_snake": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, c_p, c_p]),
     "echo_snake_bf16": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),

@@ -417,6 +417,19 @@ class DAC:
         a, T2 = self._upsample(a, B, T)
         return self._wave_decoder(a, B, T2).unsqueeze(1).to(self._dtype)
 
+    def pca_operands(self, pca_components: torch.Tensor, pca_mean: torch.Tensor):
+        """(components^T fp32 [1024, 80], mean fp32 [1024]) on the device, cached per PCAState."""
+        dev = self._device
+        key = (pca_components.data_ptr(), pca_mean.data_ptr())
+        if self._pca_cache is None or self._pca_cache[0] != key:
+            self._pca_cache = (key, pca_components.to(dev, F32).t().contiguous(), pca_mean.to(dev, F32).contiguous())
+        return self._pca_cache[1], self._pca_cache[2]
+
+    def decode_stream(self):
+        """Incremental decode_zq for one utterance (echo_tts_b200.streaming.DecodeStream)."""
+        from .streaming import DecodeStream
+        return DecodeStream(self)
+
     @torch.inference_mode()
     def decode_latent(self, z: torch.Tensor, pca_components: torch.Tensor, pca_mean: torch.Tensor,
                       latent_scale: float) -> torch.Tensor:
@@ -424,10 +437,7 @@ class DAC:
         z fp32 [B, T, 80] -> waveform fp32 [B, 1, T*hop]."""
         B, T, lat = z.shape
         dev = self._device
-        key = (pca_components.data_ptr(), pca_mean.data_ptr())
-        if self._pca_cache is None or self._pca_cache[0] != key:
-            self._pca_cache = (key, pca_components.to(dev, F32).t().contiguous(), pca_mean.to(dev, F32).contiguous())
-        _, w, mean = self._pca_cache
+        w, mean = self.pca_operands(pca_components, pca_mean)
         x = torch.empty((B * T, w.shape[0]), device=dev, dtype=F32)
         ops.sgemm(z.to(dev, F32).contiguous().view(B * T, lat), w, addend=mean, out=x, out_scale=1.0 / latent_scale)
         a = self._transformer(x, B, T)

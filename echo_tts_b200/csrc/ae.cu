@@ -7,9 +7,10 @@ namespace {
 
 // ConvNeXt front (autoencoder.py:362-364): causal depthwise conv k=7 then LayerNorm over channels.
 // One CTA per time step, one thread per channel (coalesced across channels), two-pass variance.
+// left_ctx > 0 (streaming decode, batch 1): that many rows of the previous call's input sit in memory before row 0.
 __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_len, const float* __restrict__ w,
                                  const float* __restrict__ b, const float* __restrict__ ln_w,
-                                 const float* __restrict__ ln_b, float eps, bf16* __restrict__ y) {
+                                 const float* __restrict__ ln_b, float eps, bf16* __restrict__ y, int left_ctx) {
   const int t = blockIdx.x, bt = blockIdx.y;
   const float* xb = x + (long long)bt * t_len * c_len;
   __shared__ float red[32];
@@ -25,7 +26,7 @@ __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_l
 #pragma unroll
       for (int k = 0; k < 7; ++k) {
         const int tt = t - 6 + k;
-        if (tt >= 0) acc = fmaf(w[c * 7 + k], xb[(long long)tt * c_len + c], acc);
+        if (tt >= -left_ctx) acc = fmaf(w[c * 7 + k], xb[(long long)tt * c_len + c], acc);
       }
       sum += acc;
     }
@@ -63,7 +64,7 @@ __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_l
 // 256 outputs per CTA; the (256+6) x C input window is staged in shared memory with odd row stride.
 __global__ void __launch_bounds__(256) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
                                                             const float* __restrict__ w, float bias,
-                                                            float* __restrict__ wav) {
+                                                            float* __restrict__ wav, int left_ctx) {
   extern __shared__ float sx[];                 // [(256+6)][c_len+1] fp32
   float* sw = sx + (256 + 6) * (c_len + 1);     // [7][c_len]
   const int bt = blockIdx.y, t0 = blockIdx.x * 256;
@@ -73,7 +74,7 @@ __global__ void __launch_bounds__(256) conv_out_tanh_kernel(const bf16* __restri
   for (int i = threadIdx.x; i < n; i += 256) {
     const int r = i / c_len, c = i % c_len;
     const int tt = t0 - 6 + r;
-    sx[r * (c_len + 1) + c] = (tt >= 0 && tt < t_len) ? bf2f(xb[(long long)tt * c_len + c]) : 0.f;
+    sx[r * (c_len + 1) + c] = (tt >= -left_ctx && tt < t_len) ? bf2f(xb[(long long)tt * c_len + c]) : 0.f;
   }
   __syncthreads();
   const int t = t0 + threadIdx.x;
@@ -219,12 +220,37 @@ __global__ void flattening_kernel(const float* __restrict__ x, int len, int widt
 }
 }  // namespace
 
-extern "C" int echo_dwconv_layernorm(const float* x, int batch, int t, int c, const float* w_dw, const float* b_dw,
-                                     const float* ln_w, const float* ln_b, float eps, void* y, echo_stream_t stream) {
+extern "C" int echo_dwconv_layernorm_ctx(const float* x, int batch, int t, int c, int left_ctx, const float* w_dw,
+                                         const float* b_dw, const float* ln_w, const float* ln_b, float eps, void* y,
+                                         echo_stream_t stream) {
   ECHO_CHECK_ARG(x && w_dw && b_dw && ln_w && ln_b && y && batch > 0 && t > 0, "dwconv_ln: bad argument");
+  ECHO_CHECK_ARG(left_ctx >= 0 && left_ctx <= 6 && (left_ctx == 0 || batch == 1), "dwconv_ln: left_ctx needs batch 1, <= 6 rows");
   ECHO_CHECK_ARG(c > 0 && c <= 1024, "dwconv_ln: c must be <= 1024");
   const int threads = c >= 256 ? 256 : ((c + 31) / 32) * 32;
-  dwconv_ln_kernel<<<dim3(t, batch), threads, 0, (cudaStream_t)stream>>>(x, t, c, w_dw, b_dw, ln_w, ln_b, eps, (bf16*)y);
+  dwconv_ln_kernel<<<dim3(t, batch), threads, 0, (cudaStream_t)stream>>>(x, t, c, w_dw, b_dw, ln_w, ln_b, eps, (bf16*)y,
+                                                                          left_ctx);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_dwconv_layernorm(const float* x, int batch, int t, int c, const float* w_dw, const float* b_dw,
+                                     const float* ln_w, const float* ln_b, float eps, void* y, echo_stream_t stream) {
+  return echo_dwconv_layernorm_ctx(x, batch, t, c, 0, w_dw, b_dw, ln_w, ln_b, eps, y, stream);
+}
+
+extern "C" int echo_conv_out_tanh_ctx(const void* x, int batch, int t, int c, int left_ctx, const float* w, float bias,
+                                      float* wav, echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && w && wav && batch > 0 && t > 0 && c > 0 && c <= 128, "conv_out: bad argument");
+  ECHO_CHECK_ARG(left_ctx >= 0 && left_ctx <= 6 && (left_ctx == 0 || batch == 1), "conv_out: left_ctx needs batch 1, <= 6 rows");
+  const size_t smem = ((size_t)(256 + 6) * (c + 1) + 7 * c) * sizeof(float);
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    ECHO_CUDA(cudaFuncSetAttribute(conv_out_tanh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  conv_out_tanh_kernel<<<dim3(ceil_div(t, 256), batch), 256, smem, (cudaStream_t)stream>>>((const bf16*)x, t, c, w, bias, wav,
+                                                                                               left_ctx);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
@@ -232,17 +258,7 @@ extern "C" int echo_dwconv_layernorm(const float* x, int batch, int t, int c, co
 
 extern "C" int echo_conv_out_tanh(const void* x, int batch, int t, int c, const float* w, float bias, float* wav,
                                   echo_stream_t stream) {
-  ECHO_CHECK_ARG(x && w && wav && batch > 0 && t > 0 && c > 0 && c <= 128, "conv_out: bad argument");
-  const size_t smem = ((size_t)(256 + 6) * (c + 1) + 7 * c) * sizeof(float);
-  static size_t configured = 48 * 1024;
-  if (smem > configured) {
-    ECHO_CUDA(cudaFuncSetAttribute(conv_out_tanh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  conv_out_tanh_kernel<<<dim3(ceil_div(t, 256), batch), 256, smem, (cudaStream_t)stream>>>((const bf16*)x, t, c, w, bias, wav);
-  ECHO_COUNT_LAUNCH();
-  ECHO_LAUNCH_CHECK();
-  return ECHO_OK;
+  return echo_conv_out_tanh_ctx(x, batch, t, c, 0, w, bias, wav, stream);
 }
 
 extern "C" int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y, echo_stream_t stream) {

@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(128) attention_kernel(const __grid_constant__ 
       const echo_attn_segment& sg = D.seg[tid];
       int ext = sg.extent ? min(sg.extent[row], sg.len) : sg.len;
       if (sg.causal) {
-        ext = min(ext, min(q0 + ABM, D.seq));
-        if (sg.window > 0) t0 = max(0, q0 - sg.window + 1) / ABN;
+        ext = min(ext, min(q0 + ABM, D.seq) + sg.q_offset);
+        if (sg.window > 0) t0 = max(0, q0 + sg.q_offset - sg.window + 1) / ABN;
       }
       nt = max(0, (ext + ABN - 1) / ABN - t0);
     }
@@ -152,8 +152,8 @@ __global__ void __launch_bounds__(128) attention_kernel(const __grid_constant__ 
         const int qi = qi0 + (e >> 1) * 8;
         bool ok = s_valid[stage][col] != 0;
         if (sg.causal) {
-          const int j = j0 + col;
-          ok = ok && (j <= qi) && (sg.window <= 0 || j > qi - sg.window);
+          const int j = j0 + col, qk = qi + sg.q_offset;
+          ok = ok && (j <= qk) && (sg.window <= 0 || j > qk - sg.window);
         }
         const float s = ok ? sacc[ni][e] * sl2 : -INFINITY;
         sacc[ni][e] = s;

@@ -141,8 +141,8 @@ static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStre
   using C = TcCfg<BN>;
   CUtensorMap ta, tb;
   {
-    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
-    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)G.rows * G.lda) * 2};
+    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)(G.rows + G.a_ctx), (cuuint64_t)batch};
+    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)(G.rows + G.a_ctx) * G.lda) * 2};
     cuuint32_t box[3] = {BK, BM, 1};
     int rc = echo_make_tmap_bf16(&ta, G.a, 3, dims, str, box);
     if (rc) return rc;
@@ -186,6 +186,14 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   for (int i = 0; i < 8; ++i) G.tap_shift[i] = d->tap_shift[i];
   G.rows = d->rows; G.n = d->n; G.lda = d->lda; G.a_batch_stride = d->a_batch_stride; G.ldb = d->ldb;
   G.a = (const bf16*)d->a; G.b = (const bf16*)d->b;
+  ECHO_CHECK_ARG(d->a_ctx >= 0 && d->a_ctx < (1 << 20), "gemm: bad a_ctx");
+  if (d->a_ctx > 0) {   // left context: the operand view starts a_ctx rows earlier, every tap moves with it
+    G.a_ctx = d->a_ctx;
+    G.a -= (long long)d->a_ctx * d->lda;
+    for (int i = 0; i < 8; ++i) G.tap_shift[i] += d->a_ctx;
+    ECHO_CHECK_ARG(((uintptr_t)G.a % 16) == 0, "gemm: context rows must keep the operand 16-byte aligned");
+    ECHO_CHECK_ARG(d->batch == 1 || d->a_batch_stride >= (long long)(d->rows + d->a_ctx) * d->lda, "gemm: a_batch_stride must span the context rows");
+  }
   ECHO_CHECK_ARG((long long)d->rows * d->batch < (1LL << 31), "gemm: rows * batch must fit 31 bits");
   P.kind = d->epilogue; P.rows = d->rows; P.n = d->n; P.act = d->act;
   P.bias = d->bias; P.gate = d->gate; P.gate_ld = d->gate_ld; P.rows_per_gate = d->rows_per_gate > 0 ? d->rows_per_gate : 1;

@@ -423,8 +423,8 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
   CUtensorMap ta, tb;
   {
-    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, (cuuint64_t)batch};
-    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)G.rows * G.lda) * 2};
+    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)(G.rows + G.a_ctx), (cuuint64_t)batch};
+    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)(G.rows + G.a_ctx) * G.lda) * 2};
     cuuint32_t box[3] = {BK, BM, 1};
     int rc = echo_make_tmap_bf16(&ta, G.a, 3, dims, str, box);
     if (rc) return rc;

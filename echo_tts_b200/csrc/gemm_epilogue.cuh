@@ -9,6 +9,7 @@ struct GemmShape {
   int k_blocks_per_tap, taps, k_tap;
   int tap_shift[8];
   int rows, n;
+  int a_ctx;                 // rows of left context in memory before row 0 (already folded into a and tap_shift)
   long long lda, a_batch_stride, ldb;
   const bf16* a;
   const bf16* b;

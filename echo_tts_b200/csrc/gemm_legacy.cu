@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(256) gemm_legacy_kernel(const __grid_constant_
       const int r = idx >> 2, c = idx & 3;
       const int k = k0 + c * 8;
       const int ar = m0 + r + G.tap_shift[tap];
-      const bool av = (ar >= 0) && (ar < G.rows) && (k < G.k_tap);
+      const bool av = (ar >= 0) && (ar < G.rows + G.a_ctx) && (k < G.k_tap);
       cp_async16(sa + tile_off(r, c), av ? (const void*)(A + (long long)ar * G.lda + k) : (const void*)G.a, av);
       const int br = n0 + r;
       const bool bv = (br < G.n) && (k < G.k_tap);

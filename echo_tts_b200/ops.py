@@ -40,8 +40,9 @@ def gemm_workspace(device: torch.device) -> torch.Tensor:
 
 
 def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), batch: int = 1,
-               impl: Optional[int] = None, block_n: int = 0) -> L.GemmDesc:
-    """a: bf16 [batch*rows, k_tap] (row-major, contiguous rows); w: bf16 [n, taps*k_tap]."""
+               impl: Optional[int] = None, block_n: int = 0, a_ctx: int = 0) -> L.GemmDesc:
+    """a: bf16 [batch*rows, k_tap] (row-major, contiguous rows); w: bf16 [n, taps*k_tap].  ``a_ctx``: rows of left
+    context stored in memory before a[0] (a view into a larger buffer; batch 1): read instead of zero padding."""
     _need(a, BF16, "gemm.a"); _need(w, BF16, "gemm.w")
     assert a.dim() == 2 and w.dim() == 2 and a.stride(1) == 1 and w.stride(1) == 1
     d = L.GemmDesc()
@@ -57,6 +58,8 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
         d.tap_shift[i] = s
     d.impl = GEMM_IMPL if impl is None else impl
     d.block_n = block_n
+    assert a_ctx == 0 or batch == 1
+    d.a_ctx = a_ctx
     d.rows_per_gate = 1
     if d.impl == 2 and STREAM_K:
         ws = gemm_workspace(a.device)
@@ -66,10 +69,10 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
 
 def gemm_generic(a, w, *, taps=(0,), batch=1, bias=None, act=L.ACT_NONE, gate=None, rows_per_gate=0,
                  resid=None, out_f32=None, out_bf16=None, out2_bf16=None, snake_alpha=None,
-                 impl=None, block_n=0, split_out=None) -> None:
+                 impl=None, block_n=0, split_out=None, a_ctx=0) -> None:
     """``split_out``: fp32 [S, M, N] -> split-K over S work units per tile; unit s writes its partial (gated) product to
     split_out[s]; the consumer (rmsnorm_mod / cfg_euler_tail ``delta=``) adds them to the residual stream."""
-    d = _base_gemm(a, w, taps, batch, impl, block_n)
+    d = _base_gemm(a, w, taps, batch, impl, block_n, a_ctx)
     d.epilogue, d.act = L.EPI_GENERIC, act
     M, N = a.shape[0], w.shape[0]
     if split_out is not None:
@@ -217,10 +220,11 @@ class Segment:
     """One KV segment for attention(): k/v bf16 [Bkv, L, H, Dh] (views allowed: strides are passed)."""
 
     def __init__(self, k, v, *, kv_batch_mod=0, mask=None, extent=None, kv_scale=None, causal=False, window=0,
-                 length=None):
+                 length=None, q_offset=0):
         self.k, self.v, self.kv_batch_mod, self.mask, self.extent = k, v, kv_batch_mod, mask, extent
         self.kv_scale, self.causal, self.window = kv_scale, causal, window
         self.length = k.shape[1] if length is None else length
+        self.q_offset = q_offset
 
 
 ATTN_IMPL = int(_os.environ.get("ECHO_ATTN_IMPL", "0"))   # 0 = tcgen05 kernel when eligible; 1 = mma.sync kernel (A/B)
@@ -262,7 +266,7 @@ def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate:
         if s.kv_scale is not None:
             _need(s.kv_scale, F32, "kv_scale")
             sg.kv_scale = s.kv_scale.data_ptr()
-        sg.causal, sg.window = int(s.causal), s.window
+        sg.causal, sg.window, sg.q_offset = int(s.causal), s.window, s.q_offset
     L.check(L.load().echo_attention(C.byref(d), L.stream()))
 
 
@@ -350,21 +354,23 @@ def embedding(ids: torch.Tensor, table: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def dwconv_layernorm(x, w_dw, b_dw, ln_w, ln_b, eps, y) -> None:
-    """x fp32 [B, T, C] -> y bf16 [B, T, C]."""
+def dwconv_layernorm(x, w_dw, b_dw, ln_w, ln_b, eps, y, left_ctx: int = 0) -> None:
+    """x fp32 [B, T, C] -> y bf16 [B, T, C].  ``left_ctx``: rows of the previous call's input that precede x in memory
+    (streaming decode, B == 1)."""
     _need(x, F32, "x"); _need(y, BF16, "y")
     B, T, Cc = x.shape
     assert x.is_contiguous() and y.is_contiguous()
-    L.check(L.load().echo_dwconv_layernorm(x.data_ptr(), B, T, Cc, w_dw.data_ptr(), b_dw.data_ptr(), ln_w.data_ptr(),
-                                           ln_b.data_ptr(), eps, y.data_ptr(), L.stream()))
+    L.check(L.load().echo_dwconv_layernorm_ctx(x.data_ptr(), B, T, Cc, left_ctx, w_dw.data_ptr(), b_dw.data_ptr(),
+                                               ln_w.data_ptr(), ln_b.data_ptr(), eps, y.data_ptr(), L.stream()))
 
 
-def conv_out_tanh(x_bf16, w, bias: float, wav) -> None:
-    """x bf16 [B, T, C] (Snake already applied), w fp32 [7, C] -> wav fp32 [B, T]."""
+def conv_out_tanh(x_bf16, w, bias: float, wav, left_ctx: int = 0) -> None:
+    """x bf16 [B, T, C] (Snake already applied), w fp32 [7, C] -> wav fp32 [B, T].  ``left_ctx`` as in dwconv_layernorm."""
     _need(x_bf16, BF16, "x"); _need(wav, F32, "wav"); _need(w, F32, "w")
     B, T, Cc = x_bf16.shape
     assert x_bf16.is_contiguous() and wav.is_contiguous() and w.shape == (7, Cc) and w.is_contiguous()
-    L.check(L.load().echo_conv_out_tanh(x_bf16.data_ptr(), B, T, Cc, w.data_ptr(), bias, wav.data_ptr(), L.stream()))
+    L.check(L.load().echo_conv_out_tanh_ctx(x_bf16.data_ptr(), B, T, Cc, left_ctx, w.data_ptr(), bias, wav.data_ptr(),
+                                            L.stream()))
 
 
 def cast_snake(x, alpha, y) -> None:

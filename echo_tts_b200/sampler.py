@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Iterator, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -199,17 +199,20 @@ def sample_euler_cfg_independent_guidances(
 
 
 @torch.inference_mode()
-def sample_blockwise_euler_cfg_independent_guidances(
+def blockwise_blocks(
         model: EchoDiT, speaker_latent: torch.Tensor, speaker_mask: torch.Tensor, text_input_ids: torch.Tensor,
         text_mask: torch.Tensor, rng_seed: int, block_sizes: Sequence[int], num_steps: int, cfg_scale_text: float,
         cfg_scale_speaker: float, cfg_min_t: float, cfg_max_t: float, truncation_factor: Optional[float],
         rescale_k: Optional[float], rescale_sigma: Optional[float], speaker_kv_scale: Optional[float],
         speaker_kv_max_layers: Optional[int], speaker_kv_min_t: Optional[float],
         continuation_latent: Optional[torch.Tensor] = None, *, _noises: Optional[Sequence[torch.Tensor]] = None,
-        on_block=None) -> torch.Tensor:
-    """Drop-in for reference ``inference_blockwise.py:14-123``.  Differences in HOW, not WHAT: the latent-prefix KV
-    is encoded for B rows (the reference encodes three identical copies, :72-74) and un-generated patches are
-    skipped by length instead of masked; ``on_block(start, stop, prefix)`` (optional) is the streaming hook."""
+        incremental_prefix: Optional[bool] = None) -> Iterator[Tuple[int, int, torch.Tensor]]:
+    """The block loop of reference ``inference_blockwise.py:14-123`` as a generator: yields ``(start, stop, prefix)``
+    after each block (``prefix[:, :stop]`` is final), which is what a streaming caller decodes.  Differences in HOW,
+    not WHAT: the latent-prefix KV is encoded for B rows (the reference encodes three identical copies, :72-74),
+    un-generated patches are skipped by length instead of masked, and -- when every block boundary falls on a patch
+    boundary -- the prefix KV is grown incrementally (``streaming.PrefixKVStream``: the encoder is causal, so only the
+    new patches are encoded) instead of being recomputed in full at every block."""
     if speaker_kv_scale is not None and speaker_kv_min_t is None:
         raise TypeError("'<' not supported between instances of 'Tensor' and 'NoneType'")
     cfg, dev = model.cfg, model.device
@@ -225,6 +228,16 @@ def sample_blockwise_euler_cfg_independent_guidances(
     if continuation_latent is not None:
         prefix = torch.cat([continuation_latent.to(dev, F32), prefix], 1)
         start = continuation_latent.shape[1]
+    ps = cfg.speaker_patch_size
+    aligned = start % ps == 0 and all(bs % ps == 0 for bs in block_sizes)
+    if incremental_prefix is None:
+        incremental_prefix = os.environ.get("ECHO_PREFIX_INCREMENTAL", "1") != "0"
+    pstream = None
+    if incremental_prefix and aligned and model.has_blockwise and prefix.shape[1] >= ps:
+        from .streaming import PrefixKVStream
+        pstream = PrefixKVStream(model, B, prefix.shape[1])
+        if start > 0:
+            pstream.append(prefix[:, :start])
     mult = None
     mod = None
     for bi, bs in enumerate(block_sizes):
@@ -234,10 +247,13 @@ def sample_blockwise_euler_cfg_independent_guidances(
         mult = plan.final_multiplier
         if mod is None:
             mod = model.build_mod_table(plan.t_dev)
-        kv_lat = model.get_kv_cache_latent(prefix) if prefix.shape[1] >= cfg.speaker_patch_size else None
-        n_prefix = 0
-        if kv_lat is not None:
-            n_prefix = min(kv_lat[0][0].shape[1], -(-start // cfg.speaker_patch_size))     # model.py:243-244
+        if pstream is not None:
+            kv_lat, n_prefix = (pstream.kv, pstream.patches) if pstream.patches > 0 else (None, 0)
+        else:
+            kv_lat = model.get_kv_cache_latent(prefix) if prefix.shape[1] >= ps else None
+            n_prefix = 0
+            if kv_lat is not None:
+                n_prefix = min(kv_lat[0][0].shape[1], -(-start // ps))                         # model.py:243-244
         if _noises is not None:
             x_t = _noises[bi].to(dev, F32).clone()
         else:
@@ -247,7 +263,37 @@ def sample_blockwise_euler_cfg_independent_guidances(
         run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, start_pos=start, kv_latent=kv_lat,
                   n_prefix=n_prefix)
         prefix[:, start:start + bs] = x_t
-        if on_block is not None:
-            on_block(start, start + bs, prefix)
+        if pstream is not None and bi + 1 < len(block_sizes):
+            pstream.append(x_t)
+        yield start, start + bs, prefix
         start += bs
+
+
+@torch.inference_mode()
+def sample_blockwise_euler_cfg_independent_guidances(
+        model: EchoDiT, speaker_latent: torch.Tensor, speaker_mask: torch.Tensor, text_input_ids: torch.Tensor,
+        text_mask: torch.Tensor, rng_seed: int, block_sizes: Sequence[int], num_steps: int, cfg_scale_text: float,
+        cfg_scale_speaker: float, cfg_min_t: float, cfg_max_t: float, truncation_factor: Optional[float],
+        rescale_k: Optional[float], rescale_sigma: Optional[float], speaker_kv_scale: Optional[float],
+        speaker_kv_max_layers: Optional[int], speaker_kv_min_t: Optional[float],
+        continuation_latent: Optional[torch.Tensor] = None, *, _noises: Optional[Sequence[torch.Tensor]] = None,
+        on_block=None, incremental_prefix: Optional[bool] = None) -> torch.Tensor:
+    """Drop-in for reference ``inference_blockwise.py:14-123`` (see ``blockwise_blocks`` for the loop);
+    ``on_block(start, stop, prefix)`` (optional) is the streaming hook."""
+    if speaker_kv_scale is not None and speaker_kv_min_t is None:
+        raise TypeError("'<' not supported between instances of 'Tensor' and 'NoneType'")
+    prefix = None
+    for start, stop, prefix in blockwise_blocks(
+            model, speaker_latent, speaker_mask, text_input_ids, text_mask, rng_seed, block_sizes, num_steps,
+            cfg_scale_text, cfg_scale_speaker, cfg_min_t, cfg_max_t, truncation_factor, rescale_k, rescale_sigma,
+            speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t, continuation_latent, _noises=_noises,
+            incremental_prefix=incremental_prefix):
+        if on_block is not None:
+            on_block(start, stop, prefix)
+    if prefix is None:          # no blocks: the (possibly empty) continuation comes back unchanged
+        cfg, dev = model.cfg, model.device
+        B = text_input_ids.shape[0]
+        prefix = torch.zeros((B, 0, cfg.latent_size), device=dev, dtype=F32)
+        if continuation_latent is not None:
+            prefix = continuation_latent.to(dev, F32).clone()
     return prefix

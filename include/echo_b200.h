@@ -25,7 +25,7 @@ void echo_reset_launch_count(void);
 /* ------------------------------------------------------------------------------------------
  * bf16 tensor-core GEMM with implicit-conv taps and fused epilogues.
  *   acc[b, m, n] = sum_t sum_k A[b, m + tap_shift[t], k] * B[n, t*k_tap + k]     (fp32 accumulate)
- * Rows outside [0, rows) read as zero (causal left padding of CausalConvNet,
+ * Rows outside [-a_ctx, rows) read as zero (causal left padding of CausalConvNet,
  * autoencoder.py:285-289).  impl 2 = persistent CTA-pair tcgen05.mma kernel with TMEM accumulators
  * and TMA loads (the product path); impl 0 = single-CTA tcgen05 kernel, impl 1 = legacy mma.sync
  * kernel, both kept as A/B baselines and debugging aids.
@@ -76,7 +76,10 @@ typedef struct echo_gemm_desc {
    * < rope_heads at position pos_offset + (m % rows_per_seq) * pos_stride) / plain / sigmoid.
    * Replaces model.py:221-232, 199-202, 17-24, 264 (sigmoid of the gate) and 270-293. */
   int32_t n_sections, section_width, head_dim, rope_heads;
-  int32_t pos_offset, pos_stride, rows_per_seq, _pad1;
+  int32_t pos_offset, pos_stride, rows_per_seq;
+  int32_t a_ctx;            /* streaming (S1-DAC decode stream): rows of left context that sit in memory BEFORE row 0 of every
+                             * batch entry of `a`; rows -a_ctx..-1 are read instead of zero-filled (the causal padding of
+                             * the first call is an all-zero context).  a_batch_stride must span them.  0 = none. */
   float eps;
   float _pad2;
   const float* rope_cos;    /* fp32 [max_pos][head_dim/2] */
@@ -158,8 +161,11 @@ typedef struct echo_attn_segment {
   int64_t mask_stride;
   const int32_t* extent;    /* per-row 1 + last valid key (tile skipping), NULL = len */
   const float* kv_scale;    /* device scalar multiplying K and V (speaker_kv_scale), NULL = 1 */
-  int32_t causal;           /* key j visible to query i iff j <= i (+ window: j > i - window) */
+  int32_t causal;           /* key j visible to query i iff j <= i + q_offset (+ window: j > i + q_offset - window) */
   int32_t window;
+  int32_t q_offset;         /* causal segments: key index of query 0 (keys cached from earlier calls precede it:
+                             * incremental encoders, S1-DAC decode stream).  0 = queries and keys aligned. */
+  int32_t _pad;
 } echo_attn_segment;
 
 typedef struct echo_attn_desc {
@@ -301,6 +307,14 @@ int echo_dwconv_layernorm(const float* x, int batch, int t, int c, const float* 
 /* last stage: causal conv k=7, C -> 1, + tanh (autoencoder.py:994): x bf16 [B,T,C] (already Snake'd) */
 int echo_conv_out_tanh(const void* x_bf16, int batch, int t, int c, const float* w /*[7][c]*/, float bias,
                        float* wav, echo_stream_t stream);
+/* Streaming forms of the two causal k=7 kernels above (S1-DAC decode stream, batch 1): `left_ctx` (0..6) rows of the
+ * previous call's input sit in memory immediately BEFORE x and are read where the one-shot kernels pad with zeros
+ * (autoencoder.py:285-289); the first call of a stream passes an all-zero context = the reference's left padding. */
+int echo_dwconv_layernorm_ctx(const float* x, int batch, int t, int c, int left_ctx, const float* w_dw,
+                              const float* b_dw, const float* ln_w, const float* ln_b, float eps, void* y_bf16,
+                              echo_stream_t stream);
+int echo_conv_out_tanh_ctx(const void* x_bf16, int batch, int t, int c, int left_ctx, const float* w, float bias,
+                           float* wav, echo_stream_t stream);
 /* element-wise fp32 -> bf16 with optional Snake (autoencoder.py:96-102) over [rows, c] */
 int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
 

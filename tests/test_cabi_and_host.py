@@ -101,3 +101,23 @@ def test_step_plan_matches_reference_schedule(index_golden):
         class M:
             device = "cpu"; cfg = None
         s(M(), None, None, torch.zeros(1, 1), None, 0, 4, 1., 1., .5, 1., None, None, None, 1.5, None, None)
+
+
+def test_streaming_carry_rows_host_logic():
+    """_Carry (streaming.py): zero context on the first step, and a step shorter than the context keeps the tail of the
+    old context in front of the new rows -- plain tensor logic, checked on CPU tensors."""
+    import torch
+    from echo_tts_b200.streaming import _Carry
+    c = _Carry("cpu")
+    lead, n = 5, 3
+    hist = []
+    for t in (4, 1, 2, 6):
+        buf = torch.full((lead + t, 2), -1.0)
+        c.load("s", buf, lead, n)
+        want = ([0.0] * n + hist)[-n:]
+        assert buf[lead - n:lead, 0].tolist() == want
+        new = [float(len(hist) + i + 1) for i in range(t)]
+        buf[lead:] = torch.tensor(new)[:, None]
+        hist += new
+        c.save("s", buf, lead, t, n)
+        assert c.rows["s"][:, 0].tolist() == ([0.0] * n + hist)[-n:]

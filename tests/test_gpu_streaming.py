@@ -1,0 +1,211 @@
+"""Streaming serving loop (BASELINE config 5) on a B200: the incremental forms must reproduce the
+one-shot paths -- both halves of the S1-DAC decoder and the latent-prefix encoder are causal, so the reference
+satisfies "stream == one-shot" exactly; here the two sides differ by tile-order rounding of bf16 operands only."""
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from echo_tts_b200 import schema as S
+
+pytestmark = pytest.mark.gpu
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+def _rand(shape, seed, scale=1.0, dtype=F32):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, device="cuda", generator=g) * scale).to(dtype)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from echo_tts_b200 import ops as o
+    return o
+
+
+# ---- kernel-level: the two descriptor fields streaming adds ----------------------------------------------------------
+@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("dil,C,N,T,ctx", [(1, 128, 128, 300, 6), (9, 96, 96, 40, 54), (3, 64, 256, 5, 18)])
+def test_gemm_left_context_rows(ops, impl, dil, C, N, T, ctx):
+    """a_ctx: a dilated causal conv over rows [ctx, ctx+T) of a buffer reads the rows in front of it instead of zeros
+    == the tail of the conv over the whole buffer (autoencoder.py:285-289 applied to the concatenated signal)."""
+    buf = _rand((ctx + T, C), 20, dtype=BF16)
+    w = _rand((N, C, 7), 21, (C * 7) ** -0.5, BF16)
+    wp = w.permute(0, 2, 1).reshape(N, 7 * C).contiguous()
+    out = torch.empty((T, N), device="cuda", dtype=F32)
+    ops.gemm_generic(buf[ctx:], wp, taps=tuple(-(6 - k) * dil for k in range(7)), a_ctx=ctx, out_f32=out, impl=impl)
+    xin = torch.nn.functional.pad(buf.float().t()[None], (6 * dil, 0))
+    ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil)[0].t()[ctx:]
+    assert rel_l2(out, ref) < 2e-5
+
+
+@pytest.mark.parametrize("Dh,window,off,S", [(64, 16, 15, 40), (64, 128, 100, 7), (128, 0, 77, 130), (64, 128, 127, 333)])
+def test_attention_query_offset(ops, Dh, window, off, S):
+    """q_offset: queries are the LAST S positions of a causal (windowed) sequence of off + S keys."""
+    import math
+    H = 4
+    q = _rand((1, S, H, Dh), 31, dtype=BF16)
+    k, v = (_rand((1, off + S, H, Dh), i, dtype=BF16) for i in (32, 33))
+    out = torch.empty((S, H * Dh), device="cuda", dtype=BF16)
+    ops.attention(q, [ops.Segment(k, v, causal=True, window=window, q_offset=off)], out)
+    i = torch.arange(S, device="cuda")[:, None] + off
+    j = torch.arange(off + S, device="cuda")[None, :]
+    m = j <= i
+    if window > 0:
+        m &= j > i - window
+    sc = torch.einsum("rshd,rlhd->rhsl", q.float(), k.float()) / math.sqrt(Dh)
+    sc = sc.masked_fill(~m[None, None], float("-inf"))
+    ref = torch.einsum("rhsl,rlhd->rshd", torch.softmax(sc, -1), v.float()).reshape(S, H * Dh)
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
+# ---- DecodeStream: chunked decode == one-shot decode ------------------------------------------------------------------
+def _stream_decode(ae, z, chunks):
+    st = ae.decode_stream()
+    outs, t0 = [], 0
+    for c in chunks:
+        outs.append(st.step(z[:, :, t0:t0 + c]))
+        t0 += c
+    assert t0 == z.shape[2]
+    return torch.cat(outs, -1)
+
+
+def test_decode_stream_tiny_ragged_chunks_vs_oneshot_and_oracle():
+    """Chunks shorter than every carried context (1 frame = 4 rows at the first conv, < 6; < window 16), then longer."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    cfg = S.AE_TINY
+    sd = S.synth_ae_state_dict(cfg)
+    ae = load_fish_ae_from_state_dict(sd, cfg=cfg)
+    z = torch.randn(1, cfg.latent_dim, 56, generator=torch.Generator().manual_seed(5))
+    full = ae.decode_zq(z.cuda())
+    got = _stream_decode(ae, z.cuda(), [1, 1, 3, 2, 9, 24, 16])
+    assert got.shape == full.shape == (1, 1, 56 * cfg.hop)
+    assert rel_l2(got.cpu(), full.cpu()) < 3e-3
+    assert rel_l2(got.cpu(), O.decode_zq(sd, cfg, z)) < 2e-2
+
+
+def test_decode_stream_base_config5_blocks_and_reference_fixture():
+    """BASELINE config 5: four blocks of 160 latents decoded as they arrive == the 640-latent one-shot decode; and the
+    stream over the reference's own fixture input stays within the decode tolerance of the upstream fp32 output."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, ae_decode, PCAState
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE))
+    comp, mean, scale = O.synth_pca()
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    z = _rand((1, 640, 80), 9)
+    full = ae_decode(ae, pca, z)
+    st = ae.decode_stream()
+    got = torch.cat([st.step_latent(z[:, i:i + 160], pca.pca_components, pca.pca_mean, pca.latent_scale)
+                     for i in range(0, 640, 160)], -1)
+    assert got.shape == full.shape == (1, 1, 640 * 2048)
+    # while the attention window is not yet full the key tiles of both paths coincide: bit-identical audio
+    assert torch.equal(got[..., :128 * 2048], full[..., :128 * 2048])
+    # afterwards the stream's key tiles start at (position - 127) instead of a multiple of 64: another bf16 rounding of the
+    # same sums.  Measured 5.7e-3 between the two, and 5.9e-3 from EACH to the fp32 oracle (tools/stream_check.py).
+    assert rel_l2(got, full) < 1e-2
+    a, b = 160 * 2048, 320 * 2048
+    zq = ((z[:, :320].cpu() / scale) @ comp + mean).transpose(1, 2).contiguous()            # inference.py:232-235
+    ref = O.decode_zq(S.synth_ae_state_dict(S.AE_BASE), S.AE_BASE, zq)
+    e_stream, e_full = rel_l2(got[..., a:b].cpu(), ref[..., a:b]), rel_l2(full[..., a:b].cpu(), ref[..., a:b])
+    print(f"frames 160..320 vs fp32 oracle: stream {e_stream:.3e}, one-shot {e_full:.3e}")
+    assert e_stream < 2e-2 and e_stream < 1.5 * e_full
+    g = torch.load(f"{GOLDEN}/ae_base_decode.pt")
+    st = ae.decode_stream()
+    zg = g["z"].cuda()
+    wav = torch.cat([st.step_latent(zg[:, a:b], pca.pca_components, pca.pca_mean, pca.latent_scale)
+                     for a, b in ((0, 5), (5, 6), (6, 12))], -1).cpu()
+    assert rel_l2(wav, g["wav"]) < 2e-2
+
+
+def test_decode_stream_rejects_batches_and_overlong_streams():
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    cfg = S.AE_TINY
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg), cfg=cfg)
+    st = ae.decode_stream()
+    with pytest.raises(ValueError):
+        st.step(torch.zeros(2, cfg.latent_dim, 4, device="cuda"))
+    with pytest.raises(RuntimeError):
+        st.step(torch.zeros(1, cfg.latent_dim, cfg.tr_block_size + 1, device="cuda"))
+
+
+# ---- PrefixKVStream: incremental get_kv_cache_latent --------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def tiny_model():
+    from echo_tts_b200.inference import load_model_from_state_dict
+    return load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_TINY)), cfg=S.ECHO_TINY)
+
+
+@pytest.mark.parametrize("chunks", [[8, 4, 12, 16], [6, 2, 3, 1, 28]])
+def test_prefix_kv_stream_equals_full_encode(tiny_model, chunks):
+    """Appending frames chunk by chunk (also chunks that end inside a patch: those frames wait) gives the (K, V) that
+    get_kv_cache_latent (model.py:623-636) computes from the whole prefix."""
+    from echo_tts_b200.streaming import PrefixKVStream
+    B, T = 2, sum(chunks)
+    lat = _rand((B, T, 80), 41)
+    full = tiny_model.get_kv_cache_latent(lat)
+    ps = PrefixKVStream(tiny_model, B, T)
+    t0 = 0
+    for c in chunks:
+        n = ps.append(lat[:, t0:t0 + c])
+        t0 += c
+        assert n == t0 // tiny_model.cfg.speaker_patch_size
+    assert len(ps.kv) == len(full)
+    for (k, v), (kf, vf) in zip(ps.kv, full):
+        assert k.shape == kf.shape
+        assert rel_l2(k.float(), kf.float()) < 1e-2
+        assert rel_l2(v.float(), vf.float()) < 1e-2
+
+
+def _blockwise_case():
+    g = torch.load(f"{GOLDEN}/dit_tiny_blockwise.pt")
+    args = (g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0)
+    return g, args
+
+
+def test_blockwise_incremental_prefix_equals_recompute_and_reference(tiny_model):
+    from echo_tts_b200.inference_blockwise import sample_blockwise_euler_cfg_independent_guidances as sample
+    g, args = _blockwise_case()
+    kw = dict(continuation_latent=g["continuation"].cuda(), _noises=g["noises"], **g["kwargs"])
+    inc = sample(tiny_model, *args, incremental_prefix=True, **kw).cpu()
+    rec = sample(tiny_model, *args, incremental_prefix=False, **kw).cpu()
+    assert rel_l2(inc, rec) < 5e-3
+    assert rel_l2(inc, g["out"]) < 2e-2                 # the upstream reference's fp32 result
+
+
+def test_blockwise_unaligned_blocks_fall_back_to_full_encode(tiny_model):
+    """Block boundaries inside a patch (the reference encodes the zero-padded partial patch): full re-encode path,
+    checked against the oracle."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference_blockwise import sample_blockwise_euler_cfg_independent_guidances as sample
+    g, args = _blockwise_case()
+    kw = dict(g["kwargs"], block_sizes=[6, 14])
+    noises = [torch.randn(1, b, 80, generator=torch.Generator().manual_seed(3 + b)) for b in (6, 14)]
+    out = sample(tiny_model, *args, continuation_latent=None, _noises=noises, **kw).cpu()
+    sd = S.synth_state_dict(S.dit_schema(S.ECHO_TINY))
+    ref = O.sample_blockwise_euler_cfg_independent_guidances(
+        sd, S.ECHO_TINY, g["speaker_latent"], g["speaker_mask"], g["ids"], g["text_mask"], 0, noises=noises, **kw)
+    assert rel_l2(out, ref) < 2e-2
+
+
+def test_stream_blockwise_audio_equals_final_decode(tiny_model):
+    """The streaming loop: per-block audio chunks concatenate to ae_decode of the final latent, and the latent is the
+    blockwise sampler's."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, ae_decode, PCAState
+    from echo_tts_b200.inference_blockwise import (sample_blockwise_euler_cfg_independent_guidances as sample,
+                                                   stream_blockwise_audio)
+    g, args = _blockwise_case()
+    cfg = S.AE_TINY
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg), cfg=cfg)
+    comp, mean, scale = O.synth_pca(latent_dim=cfg.latent_dim)
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    kw = dict(continuation_latent=g["continuation"].cuda(), _noises=g["noises"], **g["kwargs"])
+    chunks, spans = [], []
+    for wav, a, b in stream_blockwise_audio(tiny_model, ae, pca, *args, decode_continuation=True, **kw):
+        assert wav.shape == (1, 1, (b - a) * cfg.hop)
+        chunks.append(wav)
+        spans.append((a, b))
+    assert spans == [(0, 8), (8, 16), (16, 28)]
+    latent = sample(tiny_model, *args, **kw)
+    full = ae_decode(ae, pca, latent)
+    assert rel_l2(torch.cat(chunks, -1), full) < 3e-3
