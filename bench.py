@@ -173,6 +173,36 @@ def gemm_roofline(model, pk):
                 peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6)
 
 
+def config5_streaming(model, ae, pca, dev, reps=3):
+    """BASELINE.json configs[4]: 4 blocks of 160 latents with prefix conditioning (inference_blockwise.py:14-123, its
+    __main__ settings :161-166: cfg 3.0 / 5.0), each block decoded by the S1-DAC decode stream as soon as it is sampled
+    and its audio copied to the host.  Wall clock per request, median of `reps` after one warm-up request."""
+    from echo_tts_b200.inference_blockwise import stream_blockwise_audio
+    kw = dict({k: v for k, v in KW.items() if k != "sequence_length"}, cfg_scale_speaker=5.0)
+    blocks = [160] * 4
+
+    def request(incremental):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        marks, n = [], 0
+        for wav, a, b in stream_blockwise_audio(model, ae, pca, dev[2], dev[3], dev[0], dev[1], 0, blocks,
+                                                incremental_prefix=incremental, **kw):
+            n += wav.cpu().shape[-1]                      # D2H of the chunk = the moment a client could play it
+            marks.append((time.perf_counter() - t0) * 1e3)
+        return marks, n
+
+    rec = {}
+    for name, inc in (("incremental_prefix", True), ("recomputed_prefix", False)):
+        request(inc)
+        runs = sorted((request(inc) for _ in range(reps)), key=lambda r: r[0][-1])
+        marks, n = runs[reps // 2]
+        rec[name] = dict(total_ms=marks[-1], first_audio_ms=marks[0], block_done_ms=marks, samples_out=n,
+                         audio_sec_per_sec=n / 44100 / (marks[-1] / 1e3))
+    rec["what"] = ("stream_blockwise_audio(): 4 x 160 latents x 40 steps, cfg 3.0/5.0 on t in [0.5,1], per-block streaming "
+                   "S1-DAC decode + D2H, 1 prompt, eager launches; recomputed_prefix = the reference's full prefix re-encode per block")
+    return rec
+
+
 def run_gpu(args):
     from echo_tts_b200 import schema as S, _lib
     from echo_tts_b200.inference import (load_model_from_state_dict, load_fish_ae_from_state_dict, ae_decode, PCAState,
@@ -189,7 +219,7 @@ def run_gpu(args):
     B = args.batch
     pk = peaks()
     t0 = time.time()
-    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=False), init="torch"))
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=True), init="torch"))
     ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE, encode=True))
     comp, mean, scale = O.synth_pca()
     pca = PCAState(comp.cuda(), mean.cuda(), scale)
@@ -287,6 +317,8 @@ def run_gpu(args):
                         what="sample_pipeline(): host waveform -> S1-DAC encode -> sampler -> decode -> crop -> host, "
                              "wall clock, median of 3 after 3 warm-up calls")
 
+    c5 = config5_streaming(model, ae, pca, dev) if (world == 1 and not args.no_config5) else None
+
     # per-step latency: slope between 40- and 20-step schedules, all steps guided / none guided
     all_cfg, no_cfg = dict(KW, cfg_min_t=0.0, cfg_max_t=1.0), dict(KW, cfg_min_t=2.0, cfg_max_t=3.0)
     step_ms = {name: (sampler_ms_median(dict(kw, num_steps=40)) - sampler_ms_median(dict(kw, num_steps=20))) / 20
@@ -308,6 +340,8 @@ def run_gpu(args):
                                          peak_source=pk["src"] + " sustained"),
                 breakdown_ms=dict(conditioning_plus_sampler=sampler_ms, decode=decode_ms), step_latency_ms=step_ms, pipeline_from_waveform=pipeline_rec,
                 load_seconds=load_s)
+    if c5 is not None:
+        line["config5_streaming"] = c5
     if not args.no_cpu_baseline:
         del model, ae
         torch.cuda.empty_cache()
@@ -323,6 +357,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1, help="prompts per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-config5", action="store_true", help="skip the BASELINE configs[4] streaming record")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
