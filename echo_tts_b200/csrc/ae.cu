@@ -218,6 +218,56 @@ __global__ void flattening_kernel(const float* __restrict__ x, int len, int widt
   __syncthreads();
   if (threadIdx.x == 0) out[0] = best;
 }
+// ---- audio front-end (load_audio, inference.py:141-149) ------------------------------------------------------
+// Channel mean + polyphase windowed-sinc resampling (the algorithm of torchaudio.functional.resample, which the reference
+// calls at inference.py:146): output j = f * up + p is sum_k table[k][p] * mono[f * down + k - width], mono = mean over
+// channels, samples outside [0, n) are zero.  The table arrives transposed ([taps][up]) so that the `up` phases of one
+// frame read it coalesced; the input window of a frame is shared by all its phases (L1 broadcast).  HBM-bound on the
+// output stream.  Also folds the peak search of inference.py:147 (max |y|) into the same pass: non-negative floats order
+// like their bit patterns, so one atomicMax per block on the uint32 view is exact.
+__global__ void __launch_bounds__(256) resample_mono_kernel(const float* __restrict__ x, int channels, long long n,
+                                                            long long ldx, int down, int up, int width, int taps,
+                                                            const float* __restrict__ table_t, float* __restrict__ y,
+                                                            long long n_out, unsigned int* __restrict__ absmax_bits) {
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  float acc = 0.f;
+  if (j < n_out) {
+    const long long f = j / up;
+    const int p = (int)(j - f * up);
+    const long long i0 = f * down - width;
+    const float inv_c = 1.f / (float)channels;
+    for (int k = 0; k < taps; ++k) {
+      const long long i = i0 + k;
+      if (i < 0 || i >= n) continue;
+      float m = __ldg(x + i);
+      for (int c = 1; c < channels; ++c) m += __ldg(x + c * ldx + i);
+      if (channels > 1) m *= inv_c;
+      acc = fmaf(__ldg(table_t + (long long)k * up + p), m, acc);
+    }
+    y[j] = acc;
+  }
+  if (absmax_bits) {
+    float a = fabsf(acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, o));
+    __shared__ float red[8];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int w = 1; w < 8; ++w) a = fmaxf(a, red[w]);
+      atomicMax(absmax_bits, __float_as_uint(a));
+    }
+  }
+}
+
+// inference.py:147: audio / max(|audio|.max(), 1)
+__global__ void peak_normalize_kernel(float* __restrict__ y, long long n, const unsigned int* __restrict__ absmax_bits,
+                                      float floor_) {
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const float peak = fmaxf(__uint_as_float(*absmax_bits), floor_);
+  y[j] = y[j] / peak;
+}
 }  // namespace
 
 extern "C" int echo_dwconv_layernorm_ctx(const float* x, int batch, int t, int c, int left_ctx, const float* w_dw,
@@ -307,6 +357,29 @@ extern "C" int echo_vq_nearest(const float* e, int m, int dim, const float* code
   ECHO_CHECK_ARG(dim == 8, "vq_nearest: codebook_dim %d not supported (8)", dim);
   vq_nearest_kernel<8><<<ceil_div(m, 4), 128, 0, (cudaStream_t)stream>>>(e, m, codebook_normalized, codebook, n, index_out,
                                                                        code_out);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_resample_mono(const float* x, int channels, int64_t n, int64_t ldx, int down, int up, int width,
+                                  const float* table_t, float* y, int64_t n_out, uint32_t* absmax_bits,
+                                  echo_stream_t stream) {
+  ECHO_CHECK_ARG(x && table_t && y && channels > 0 && channels <= 64 && n > 0 && n_out > 0, "resample: bad argument");
+  ECHO_CHECK_ARG(down > 0 && up > 0 && width >= 0 && ldx >= n, "resample: bad rates");
+  ECHO_CHECK_ARG(n_out <= ((n + down - 1) / down + 1) * (int64_t)up, "resample: n_out exceeds the frames the input covers");
+  const int taps = 2 * width + down;
+  const unsigned blocks = (unsigned)((n_out + 255) / 256);
+  resample_mono_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, channels, n, ldx, down, up, width, taps, table_t, y, n_out,
+                                                                absmax_bits);
+  ECHO_COUNT_LAUNCH();
+  ECHO_LAUNCH_CHECK();
+  return ECHO_OK;
+}
+
+extern "C" int echo_peak_normalize(float* y, int64_t n, const uint32_t* absmax_bits, float floor_, echo_stream_t stream) {
+  ECHO_CHECK_ARG(y && absmax_bits && n > 0, "peak_normalize: bad argument");
+  peak_normalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(y, n, absmax_bits, floor_);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

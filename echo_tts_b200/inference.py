@@ -9,6 +9,7 @@ from typing import Callable, List, Optional, Tuple
 import torch
 
 from . import ops
+from .audio import load_audio, prepare_audio  # noqa: F401  (inference.py:141-149)
 from .autoencoder import DAC
 from .model import EchoDiT
 from .sampler import sample_euler_cfg_independent_guidances  # noqa: F401  (re-export, inference.py:446)

@@ -337,6 +337,20 @@ int echo_rmsnorm_f32(const float* x, int64_t ldx, int m, int d, float eps, const
 int echo_vq_nearest(const float* e, int m, int dim, const float* codebook_normalized, const float* codebook, int n,
                     int32_t* index_out, float* code_out, echo_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Audio front-end (load_audio, inference.py:141-149), after the file has been decoded to PCM on the host.
+ * ------------------------------------------------------------------------------------------ */
+/* Channel mean (inference.py:145) + polyphase windowed-sinc resampling = torchaudio.functional.resample (inference.py:146;
+ * third party: torchaudio 2.x `_apply_sinc_resample_kernel`, restated in oracle/echo_oracle.py::resample_sinc):
+ *   y[f*up + p] = sum_k table_t[k*up + p] * mono[f*down + k - width],   k in [0, 2*width + down), zeros outside [0, n)
+ * x fp32 [channels][ldx], (down, up) = (orig, new) / gcd, table_t fp32 [2*width + down][up] (host-built filter bank,
+ * transposed), y fp32 [n_out] with n_out = ceil(up * n / down).  absmax_bits (nullable, zeroed by the caller) receives
+ * the bit pattern of max |y| (inference.py:147's peak search fused into the same pass). */
+int echo_resample_mono(const float* x, int channels, int64_t n, int64_t ldx, int down, int up, int width,
+                       const float* table_t, float* y, int64_t n_out, uint32_t* absmax_bits, echo_stream_t stream);
+/* inference.py:147: y /= max(peak, floor) with peak read from absmax_bits (floor = 1: never amplify) */
+int echo_peak_normalize(float* y, int64_t n, const uint32_t* absmax_bits, float floor_, echo_stream_t stream);
+
 /* find_flattening_point (inference.py:315-330): latent fp32 [len, width] -> index (device int32) */
 int echo_flattening_point(const float* latent, int len, int width, int window, float std_threshold,
                           float target, int32_t* index_out, echo_stream_t stream);

@@ -667,3 +667,42 @@ def ae_encode(sd: SD, cfg, pca_components, pca_mean, latent_scale: float, audio:
     """inference.py:223-229: z_q -> PCA projection: ((z_q^T - mean) @ components^T) * latent_scale, [B, T, 80]."""
     z_q = encode_zq(sd, cfg, audio).float()
     return ((z_q.transpose(1, 2) - pca_mean) @ pca_components.T) * latent_scale
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Audio front-end (SURVEY 8 f4): load_audio after the decode, inference.py:145-147.  The resampler is third party:
+# torchaudio (requirements.txt; 2.11.0 installed here) functional.resample, "sinc_interp_hann", lowpass_filter_width 6,
+# rolloff 0.99 -- restated from its published algorithm (_get_sinc_resample_kernel / _apply_sinc_resample_kernel) and
+# pinned against the installed torchaudio in tests/test_audio_frontend.py.
+# ---------------------------------------------------------------------------------------------------------------------
+def resample_sinc(waveform: torch.Tensor, orig_freq: int, new_freq: int, lowpass_filter_width: int = 6,
+                  rolloff: float = 0.99) -> torch.Tensor:
+    """waveform fp32 [..., n] -> [..., ceil(n * new / orig)]: y[f*new + p] = sum_k bank[p, k] * xpad[f*orig + k] with the
+    Hann-windowed sinc bank of width ceil(lpw * orig / (min(orig, new) * rolloff)); frequencies reduced by their gcd."""
+    if orig_freq == new_freq:
+        return waveform
+    g = math.gcd(int(orig_freq), int(new_freq))
+    orig, new = int(orig_freq) // g, int(new_freq) // g
+    base = min(orig, new) * rolloff
+    width = math.ceil(lowpass_filter_width * orig / base)
+    dt = waveform.dtype
+    idx = torch.arange(-width, width + orig, dtype=dt)[None, None] / orig
+    t = torch.arange(0, -new, -1, dtype=dt)[:, None, None] / new + idx
+    t = (t * base).clamp(-lowpass_filter_width, lowpass_filter_width)
+    window = torch.cos(t * math.pi / lowpass_filter_width / 2) ** 2
+    t = t * math.pi
+    bank = torch.where(t == 0, torch.ones((), dtype=dt), t.sin() / t) * (window * (base / orig))    # [new, 1, taps]
+    shape = waveform.shape
+    x = waveform.reshape(-1, shape[-1])
+    n = x.shape[1]
+    x = F.pad(x, (width, width + orig))
+    y = F.conv1d(x[:, None], bank, stride=orig).transpose(1, 2).reshape(x.shape[0], -1)
+    y = y[:, : math.ceil(new * n / orig)]
+    return y.reshape(shape[:-1] + y.shape[-1:])
+
+
+def load_audio_post(samples: torch.Tensor, sample_rate: int) -> torch.Tensor:
+    """inference.py:145-147 on decoded samples [channels, n]: channel mean, resample to 44.1 kHz, / max(peak, 1)."""
+    audio = samples.mean(dim=0).unsqueeze(0)
+    audio = resample_sinc(audio, sample_rate, 44_100)
+    return audio / torch.maximum(audio.abs().max(), torch.tensor(1.0))
