@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--nw", type=int, default=8)
     ap.add_argument("--only", default="")
+    ap.add_argument("--bn", type=int, default=0, help="force block_n of the four projections (0 = library's choice)")
     ap.add_argument("--quick", action="store_true", help="1 rep, 1 weight set (for ncu)")
     args = ap.parse_args()
     from echo_tts_b200 import ops, _lib as L
@@ -58,10 +59,10 @@ def main():
         def f_qkvg(i):
             ops.gemm_sections(xn, W["qkvg"][i % nw], [(L.SEC_NORM_ROPE, qkvg[0], qn), (L.SEC_NORM_ROPE, qkvg[1], kn),
                                                       (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
-                              head_dim=128, rope_heads=H // 2, rope=rope, rows_per_seq=S, eps=1e-5)
+                              head_dim=128, rope_heads=H // 2, rope=rope, rows_per_seq=S, eps=1e-5, block_n=args.bn)
 
         def f_wo(i):
-            ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x)
+            ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x, block_n=args.bn)
 
         ns = max(1, min(4, 74 // (-(-M // 256) * 8)))
         parts = torch.empty((ns, M, D), device="cuda")
@@ -76,10 +77,10 @@ def main():
             ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0), delta=parts)
 
         def f_w13(i):
-            ops.gemm_swiglu(xn, W["w13"][i % nw], hmid)
+            ops.gemm_swiglu(xn, W["w13"][i % nw], hmid, block_n=args.bn)
 
         def f_w2(i):
-            ops.gemm_generic(hm, W["w2"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x)
+            ops.gemm_generic(hm, W["w2"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x, block_n=args.bn)
 
         def f_attn(i):
             segs = [ops.Segment(qkvg[1].view(R, S, H, 128), qkvg[2].view(R, S, H, 128)),
