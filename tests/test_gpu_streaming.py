@@ -209,3 +209,22 @@ def test_stream_blockwise_audio_equals_final_decode(tiny_model):
     latent = sample(tiny_model, *args, **kw)
     full = ae_decode(ae, pca, latent)
     assert rel_l2(torch.cat(chunks, -1), full) < 3e-3
+
+
+@pytest.mark.slow
+def test_full_arch_blockwise_vs_reference_fixture():
+    """BASELINE configs[4] in miniature at the full echo-tts-base architecture (latent encoder included): the upstream
+    blockwise sampler ran it in fp32 on CPU (oracle/gen_golden_blockwise.py: 16-latent continuation + blocks [16, 32],
+    Force-Speaker scale re-applied per block); here bf16 on the B200, prefix KV grown incrementally AND recomputed."""
+    from echo_tts_b200.inference import load_model_from_state_dict
+    from echo_tts_b200.inference_blockwise import sample_blockwise_euler_cfg_independent_guidances as sample
+    g = torch.load(f"{GOLDEN}/dit_base_blockwise.pt")
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE), init=g["init"]))
+    args = (g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 21)
+    kw = dict(continuation_latent=g["continuation"].cuda(), _noises=g["noises"], **g["kwargs"])
+    for inc in (True, False):
+        out = sample(model, *args, incremental_prefix=inc, **kw).cpu()
+        assert torch.equal(out[:, :16], g["continuation"])
+        err = rel_l2(out[:, 16:], g["out"][:, 16:])
+        print(f"full-arch blockwise (incremental_prefix={inc}): generated-latent rel-L2 {err:.3e} (tol 2e-2)")
+        assert err < 2e-2

@@ -69,6 +69,18 @@ def test_blockwise_matches_reference_fixture():
 
 
 @pytest.mark.slow
+def test_full_arch_blockwise_matches_reference_fixture():
+    """Oracle vs the upstream blockwise sampler at the full architecture (oracle/gen_golden_blockwise.py)."""
+    g = torch.load(os.path.join(GOLDEN, "dit_base_blockwise.pt"))
+    sd = S.synth_state_dict(S.dit_schema(S.ECHO_BASE), init=g["init"])
+    out = O.sample_blockwise_euler_cfg_independent_guidances(
+        sd, S.ECHO_BASE, g["speaker_latent"], g["speaker_mask"], g["ids"], g["text_mask"], 21,
+        continuation_latent=g["continuation"], noises=g["noises"], **g["kwargs"])
+    assert torch.equal(out[:, :16], g["continuation"])
+    assert rel_l2(out, g["out"]) < 2e-5
+
+
+@pytest.mark.slow
 def test_ae_decode_matches_reference_fixture():
     g = torch.load(os.path.join(GOLDEN, "ae_base_decode.pt"))
     sd = S.synth_ae_state_dict(S.AE_BASE)
