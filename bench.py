@@ -123,6 +123,52 @@ def cpu_reference_sample(threads=None, repeats=1):
                        f"scaled by FLOPs to the {FLOP_GEN / 1e12:.1f}-TFLOP generation"), sec
 
 
+def eager_gpu_port(reps=3):
+    """The practical bar of SURVEY 8d / BASELINE.md: the reference ALGORITHM as plain PyTorch eager ops on the same B200
+    (the oracle's functional restatement executed under torch.device("cuda"); the upstream repo itself cannot travel to
+    the GPU box), at the reference's default dtypes -- bf16 DiT (inference.py:17), fp32 S1-DAC (inference.py:83).  One
+    three-branch CFG forward, one plain forward and one decode are timed (median of `reps` after a warm-up) and summed
+    20 / 20 / 1 as in config 2; conditioning and the reference's per-step host syncs are left out (in its favour)."""
+    from echo_tts_b200 import schema as S
+    from oracle import echo_oracle as O
+    cfg = S.ECHO_BASE
+    bf = torch.bfloat16
+    sd = {k: (v.cuda().to(bf) if v.is_floating_point() else v.cuda())
+          for k, v in S.synth_state_dict(S.dit_schema(cfg, blockwise=False), init="torch").items()}
+    asd = {k: v.cuda() for k, v in S.synth_ae_state_dict(S.AE_BASE).items()}
+    comp, mean, scale = [t.cuda() if torch.is_tensor(t) else t for t in O.synth_pca()]
+    ids, mask, spk, smask = [t.cuda() for t in synth_inputs(1)]
+
+    def timed(fn):
+        fn()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return sorted(ts)[reps // 2]
+
+    with torch.inference_mode(), torch.device("cuda"):
+        kv_t = O.kv_cache_text(sd, cfg, ids, mask)
+        kv_s = O.kv_cache_speaker(sd, cfg, spk.to(bf))
+        x = torch.randn(1, S_LAT, 80).to(bf)
+        tm3 = torch.cat([mask, torch.zeros_like(mask), mask], 0)
+        sm3 = torch.cat([smask, smask, torch.zeros_like(smask)], 0)
+        rep3 = lambda kv: [(torch.cat([k] * 3, 0), torch.cat([v] * 3, 0)) for k, v in kv]   # inference.py:489-492
+        kv_t3, kv_s3 = rep3(kv_t), rep3(kv_s)
+        cfg_ms = timed(lambda: O.dit_forward(sd, cfg, torch.cat([x] * 3, 0), torch.ones(3).to(bf) * 0.9, tm3, sm3, kv_t3, kv_s3))
+        plain_ms = timed(lambda: O.dit_forward(sd, cfg, x, torch.ones(1).to(bf) * 0.4, mask, smask, kv_t, kv_s))
+        z = torch.randn(1, S_LAT, 80)
+        dec_ms = timed(lambda: O.ae_decode(asd, S.AE_BASE, comp, mean, scale, z))
+    gen_ms = 20 * cfg_ms + 20 * plain_ms + dec_ms
+    return dict(value=AUDIO_SEC_PER_PROMPT / (gen_ms / 1e3), unit="audio-sec/sec", kind="port",
+                what="oracle restatement as torch eager ops on cuda:0, bf16 DiT + fp32 S1-DAC (the reference's default "
+                     "dtypes); 20 x CFG forward + 20 x plain forward + decode, device-timed",
+                cfg_forward_ms=cfg_ms, plain_forward_ms=plain_ms, decode_ms=dec_ms, generation_ms=gen_ms)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -342,6 +388,15 @@ def run_gpu(args):
                 load_seconds=load_s)
     if c5 is not None:
         line["config5_streaming"] = c5
+    if world == 1 and B == 1 and not args.no_eager_gpu:
+        del model, ae
+        torch.cuda.empty_cache()
+        try:
+            line["eager_torch_gpu"] = eager_gpu_port()
+            line["eager_torch_gpu"]["speedup_of_this_engine"] = value / line["eager_torch_gpu"]["value"]
+        except Exception as e:                                         # a baseline must never cost the bench line
+            line["eager_torch_gpu"] = dict(error=f"{type(e).__name__}: {e}"[:300])
+        model = ae = None
     if not args.no_cpu_baseline:
         del model, ae
         torch.cuda.empty_cache()
@@ -357,6 +412,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1, help="prompts per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-eager-gpu", action="store_true", help="skip the torch-eager-on-B200 baseline record")
     ap.add_argument("--no-config5", action="store_true", help="skip the BASELINE configs[4] streaming record")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--nw", type=int, default=8)
     ap.add_argument("--only", default="")
+    ap.add_argument("--seq", type=int, default=640, help="latents per row (160 = a streaming block)")
     ap.add_argument("--bn", type=int, default=0, help="force block_n of the four projections (0 = library's choice)")
     ap.add_argument("--quick", action="store_true", help="1 rep, 1 weight set (for ncu)")
     args = ap.parse_args()
@@ -39,7 +40,7 @@ def main():
     from echo_tts_b200.model import rope_table
     rope = rope_table(128, 4096, "cuda")
     for M in args.m:
-        S = 640
+        S = args.seq
         R = M // S
         xn = rnd(M, D).to(BF16)
         hm = rnd(M, F_).to(BF16)
@@ -108,8 +109,8 @@ def main():
                       ([f_w2_split] if ns > 1 else [f_w2])):
                 f(2 * i); f(2 * i + 1)
 
-        keys = 640 + 256 + 53
-        valid = [keys, 640 + 53, 640 + 256][:R] if R == 3 else [keys] * R
+        keys = S + 256 + 53
+        valid = [keys, S + 53, S + 256][:R] if R == 3 else [keys] * R
         cases = [("qkvg", f_qkvg, 2.0 * M * 4 * D * D), ("wo", f_wo, 2.0 * M * D * D), ("w13", f_w13, 2.0 * M * 2 * F_ * D),
                  ("w2", f_w2, 2.0 * M * D * F_), ("attn", f_attn, sum(4.0 * S * lv * D for lv in valid)),
                  ("norm", f_norm, 0.0)]
