@@ -69,6 +69,36 @@ class AttnDesc(C.Structure):
     ]
 
 
+class AeTrLayer(C.Structure):
+    _fields_ = [("wqkv", c_p), ("wo", c_p), ("w13", c_p), ("w2", c_p), ("attn_norm", c_p), ("ffn_norm", c_p),
+                ("attn_scale", c_p), ("ffn_scale", c_p)]
+
+
+class AeUpsample(C.Structure):
+    _fields_ = [("factor", i32), ("hidden", i32), ("wt", c_p), ("bt", c_p), ("dw", c_p), ("dw_b", c_p), ("ln_w", c_p),
+                ("ln_b", c_p), ("pw1", c_p), ("pb1", c_p), ("pw2", c_p), ("pb2", c_p), ("gamma", c_p)]
+
+
+class AeUnit(C.Structure):
+    _fields_ = [("dilation", i32), ("_pad", i32), ("alpha1", c_p), ("alpha2", c_p), ("w7", c_p), ("b7", c_p),
+                ("w1", c_p), ("b1", c_p)]
+
+
+class AeBlock(C.Structure):
+    _fields_ = [("rate", i32), ("c_in", i32), ("c_out", i32), ("_pad", i32), ("alpha_in", c_p), ("alpha1_rep", c_p),
+                ("wt", c_p), ("bt", c_p), ("units", AeUnit * 3)]
+
+
+class AeDecoderDesc(C.Structure):
+    _fields_ = [
+        ("d", i32), ("tr_layers", i32), ("tr_heads", i32), ("tr_head_dim", i32), ("tr_ffn", i32), ("tr_window", i32),
+        ("tr_eps", f32), ("_pad0", f32), ("tr", C.POINTER(AeTrLayer)), ("tr_norm", c_p), ("rope_cos", c_p),
+        ("rope_sin", c_p), ("rope_len", i32), ("n_up", i32), ("ups", C.POINTER(AeUpsample)), ("conv0_w", c_p),
+        ("conv0_b", c_p), ("c0", i32), ("n_blocks", i32), ("blocks", C.POINTER(AeBlock)), ("alpha_out", c_p),
+        ("w_last", c_p), ("b_last", f32), ("gemm_impl", i32), ("gemm_workspace", c_p), ("gemm_workspace_bytes", i64),
+    ]
+
+
 class TailDesc(C.Structure):
     _fields_ = [
         ("h", c_p), ("ldh", i64), ("norm_w", c_p), ("w_out", c_p), ("b_out", c_p),
@@ -136,6 +166,11 @@ EXPORTS = {
     "echo_conv_out_tanh": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
     "echo_dwconv_layernorm_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
     "echo_conv_out_tanh_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
+    "echo_ae_decode_workspace_bytes": (i64, [C.POINTER(AeDecoderDesc), C.c_int, C.c_int, C.c_int]),
+    "echo_ae_decode": (C.c_int, [C.POINTER(AeDecoderDesc), c_p, C.c_int, C.c_int, c_p, c_p, i64, c_p]),
+    "echo_ae_decode_stream_state_bytes": (i64, [C.POINTER(AeDecoderDesc)]),
+    "echo_ae_decode_stream_init": (C.c_int, [C.POINTER(AeDecoderDesc), c_p, i64, c_p]),
+    "echo_ae_decode_stream_step": (C.c_int, [C.POINTER(AeDecoderDesc), c_p, c_p, C.c_int, C.c_int, c_p, c_p, i64, c_p]),
     "echo_cast_snake": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
     "echo_conv_in_snake": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, c_p, c_p]),
     "echo_snake_bf16": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),

@@ -9,6 +9,8 @@ in-kernel window arithmetic.  bf16 tensor-core operands, fp32 accumulation, fp32
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
 from typing import Dict, Optional
 
 import torch
@@ -412,10 +414,11 @@ class DAC:
     def decode_zq(self, z_q: torch.Tensor) -> torch.Tensor:
         """Reference signature: z_q [B, latent_dim, T] -> waveform [B, 1, T*hop]."""
         B, D, T = z_q.shape
-        x = z_q.to(self._device, F32).transpose(1, 2).contiguous().view(B * T, D)
-        a = self._transformer(x, B, T)
-        a, T2 = self._upsample(a, B, T)
-        return self._wave_decoder(a, B, T2).unsqueeze(1).to(self._dtype)
+        x = z_q.to(self._device, F32).transpose(1, 2).contiguous()
+        if x.data_ptr() == z_q.data_ptr():       # the decode clobbers x (it is post_module's residual stream)
+            x = x.clone()
+        x = x.view(B * T, D)
+        return self._decode_rows(x, B, T).unsqueeze(1).to(self._dtype)
 
     def pca_operands(self, pca_components: torch.Tensor, pca_mean: torch.Tensor):
         """(components^T fp32 [1024, 80], mean fp32 [1024]) on the device, cached per PCAState."""
@@ -424,6 +427,87 @@ class DAC:
         if self._pca_cache is None or self._pca_cache[0] != key:
             self._pca_cache = (key, pca_components.to(dev, F32).t().contiguous(), pca_mean.to(dev, F32).contiguous())
         return self._pca_cache[1], self._pca_cache[2]
+
+    # ------------------------------------------------------------------------------------------
+    # native whole-decode entry points (csrc/ae_decode.cu): the launch sequence of _transformer / _upsample /
+    # _wave_decoder below as ONE C call over caller-lent workspace; ECHO_AE_NATIVE=0 keeps the Python sequence (A/B).
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def use_native() -> bool:
+        return os.environ.get("ECHO_AE_NATIVE", "1") != "0"
+
+    def native_desc(self) -> "L.AeDecoderDesc":
+        """echo_ae_decoder_desc over this object's packed weights (built once; host arrays kept alive on self)."""
+        d = self.__dict__.get("_c_desc")
+        if d is not None:
+            return d
+        cfg = self.cfg
+        p = lambda t: t.data_ptr()
+        tr = (L.AeTrLayer * len(self.post_tr["layers"]))()
+        for i, lw in enumerate(self.post_tr["layers"]):
+            tr[i].wqkv, tr[i].wo, tr[i].w13, tr[i].w2 = p(lw["wqkv"]), p(lw["wo"]), p(lw["w13"]), p(lw["w2"])
+            tr[i].attn_norm, tr[i].ffn_norm, tr[i].attn_scale, tr[i].ffn_scale = p(lw["an"]), p(lw["fn"]), p(lw["ga"]), p(lw["gf"])
+        ups = (L.AeUpsample * len(self.ups))()
+        for i, u in enumerate(self.ups):
+            ups[i].factor, ups[i].hidden = u["factor"], u["pw1"].shape[0]
+            ups[i].wt, ups[i].bt, ups[i].dw, ups[i].dw_b = p(u["wt"]), p(u["bt"]), p(u["dw"]), p(u["dwb"])
+            ups[i].ln_w, ups[i].ln_b, ups[i].pw1, ups[i].pb1 = p(u["lnw"]), p(u["lnb"]), p(u["pw1"]), p(u["pb1"])
+            ups[i].pw2, ups[i].pb2, ups[i].gamma = p(u["pw2"]), p(u["pb2"]), p(u["gamma"])
+        blocks = (L.AeBlock * len(self.blocks))()
+        keep = []
+        c_in = self.conv0_w.shape[0]
+        for i, b in enumerate(self.blocks):
+            r = b["rate"]
+            co = b["wt"].shape[0] // r
+            a1r = b["units"][0]["a1"].repeat(r).contiguous()
+            keep.append(a1r)
+            blocks[i].rate, blocks[i].c_in, blocks[i].c_out = r, c_in, co
+            blocks[i].alpha_in, blocks[i].alpha1_rep, blocks[i].wt, blocks[i].bt = p(b["alpha_in"]), p(a1r), p(b["wt"]), p(b["bt"])
+            assert len(b["units"]) == 3
+            for j, u in enumerate(b["units"]):
+                cu = blocks[i].units[j]
+                cu.dilation, cu.alpha1, cu.alpha2 = u["dil"], p(u["a1"]), p(u["a2"])
+                cu.w7, cu.b7, cu.w1, cu.b1 = p(u["w7"]), p(u["b7"]), p(u["w1"]), p(u["b1"])
+            c_in = co
+        d = L.AeDecoderDesc()
+        d.d, d.tr_layers, d.tr_heads, d.tr_head_dim = cfg.latent_dim, len(tr), cfg.tr_heads, cfg.tr_head_dim
+        d.tr_ffn, d.tr_window, d.tr_eps = cfg.tr_ffn, cfg.tr_window, cfg.tr_eps
+        d.tr, d.tr_norm = tr, p(self.post_tr["norm"])
+        d.rope_cos, d.rope_sin, d.rope_len = p(self.post_tr["rope"][0]), p(self.post_tr["rope"][1]), self.post_tr["rope"][0].shape[0]
+        d.n_up, d.ups = len(ups), ups
+        d.conv0_w, d.conv0_b, d.c0 = p(self.conv0_w), p(self.conv0_b), self.conv0_w.shape[0]
+        d.n_blocks, d.blocks = len(blocks), blocks
+        d.alpha_out, d.w_last, d.b_last = p(self.alpha_out), p(self.w_last), self.b_last
+        gws = ops.gemm_workspace(self._device)
+        d.gemm_impl, d.gemm_workspace, d.gemm_workspace_bytes = ops.GEMM_IMPL, gws.data_ptr(), gws.numel()
+        self._c_desc, self._c_keep = d, (tr, ups, blocks, keep, gws)
+        return d
+
+    def native_workspace(self, B: int, T: int, stream: bool) -> torch.Tensor:
+        """Scratch lent to the native decode, one buffer per (batch, frames, mode), kept for the next call."""
+        cache = self.__dict__.setdefault("_c_ws", {})
+        key = (B, T, stream)
+        ws = cache.get(key)
+        if ws is None:
+            n = int(L.load().echo_ae_decode_workspace_bytes(C.byref(self.native_desc()), B, T, int(stream)))
+            if n < 0:
+                raise RuntimeError(f"echo_b200: {L.load().echo_last_error().decode()}")
+            if len(cache) >= 8:                  # requests of many different lengths: do not hoard scratch
+                cache.clear()
+            ws = cache[key] = torch.empty(n, device=self._device, dtype=torch.uint8)
+        return ws
+
+    def _decode_rows(self, x: torch.Tensor, B: int, T: int) -> torch.Tensor:
+        """x fp32 [B*T, latent_dim] (time-major z_q, clobbered) -> waveform fp32 [B, T*hop]."""
+        if not self.use_native():
+            a = self._transformer(x, B, T)
+            a, T2 = self._upsample(a, B, T)
+            return self._wave_decoder(a, B, T2)
+        ws = self.native_workspace(B, T, False)
+        wav = torch.empty((B, T * self.cfg.hop), device=self._device, dtype=F32)
+        L.check(L.load().echo_ae_decode(C.byref(self.native_desc()), x.data_ptr(), B, T, wav.data_ptr(), ws.data_ptr(),
+                                        ws.numel(), L.stream()))
+        return wav
 
     def decode_stream(self):
         """Incremental decode_zq for one utterance (echo_tts_b200.streaming.DecodeStream)."""
@@ -440,6 +524,4 @@ class DAC:
         w, mean = self.pca_operands(pca_components, pca_mean)
         x = torch.empty((B * T, w.shape[0]), device=dev, dtype=F32)
         ops.sgemm(z.to(dev, F32).contiguous().view(B * T, lat), w, addend=mean, out=x, out_scale=1.0 / latent_scale)
-        a = self._transformer(x, B, T)
-        a, T2 = self._upsample(a, B, T)
-        return self._wave_decoder(a, B, T2).unsqueeze(1)
+        return self._decode_rows(x, B, T).unsqueeze(1)

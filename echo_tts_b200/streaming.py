@@ -19,6 +19,7 @@ halves of the S1-DAC decoder and the latent-prefix encoder are causal, so the ex
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -64,6 +65,14 @@ class DecodeStream:
         self.dac = dac
         self.carry = _Carry(dac.device)
         self.pos = 0                                   # latent frames decoded so far (RoPE position, window fill)
+        self.state = None                              # native path: every carried row in one device buffer
+        if dac.use_native():
+            lib, desc = L.load(), dac.native_desc()
+            n = int(lib.echo_ae_decode_stream_state_bytes(C.byref(desc)))
+            if n < 0:
+                raise RuntimeError(f"echo_b200: {lib.echo_last_error().decode()}")
+            self.state = torch.empty(n, device=dac.device, dtype=torch.uint8)
+            L.check(lib.echo_ae_decode_stream_init(C.byref(desc), self.state.data_ptr(), n, L.stream()))
 
     # -- post_module: 8 causal window-128 layers with a key/value cache ---------------------------------------------
     def _transformer(self, x: torch.Tensor, T: int) -> torch.Tensor:
@@ -170,6 +179,16 @@ class DecodeStream:
         return wav
 
     def _run(self, x: torch.Tensor, T: int) -> torch.Tensor:
+        if self.state is not None:       # one native call (csrc/ae_decode.cu: echo_ae_decode_stream_step)
+            dac = self.dac
+            if self.pos + T > dac.post_tr["rope"][0].shape[0]:
+                raise RuntimeError("stream longer than the post_module RoPE table (block_size, autoencoder.py:805-813)")
+            ws = dac.native_workspace(1, T, True)
+            wav = torch.empty((1, T * dac.cfg.hop), device=dac.device, dtype=F32)
+            L.check(L.load().echo_ae_decode_stream_step(C.byref(dac.native_desc()), self.state.data_ptr(), x.data_ptr(), T,
+                                                        self.pos, wav.data_ptr(), ws.data_ptr(), ws.numel(), L.stream()))
+            self.pos += T
+            return wav.unsqueeze(1)
         a = self._transformer(x, T)
         ab, T2 = self._upsample(a, T)
         wav = self._wave_decoder(ab, T2)
@@ -182,7 +201,10 @@ class DecodeStream:
         B, D, T = z_q.shape
         if B != 1:
             raise ValueError("a DecodeStream carries the state of one utterance: open one stream per batch row")
-        x = z_q.to(self.dac.device, F32).transpose(1, 2).contiguous().view(T, D)
+        x = z_q.to(self.dac.device, F32).transpose(1, 2).contiguous()
+        if x.data_ptr() == z_q.data_ptr():       # the decode clobbers x
+            x = x.clone()
+        x = x.view(T, D)
         return self._run(x, T).to(self.dac.dtype)
 
     @torch.inference_mode()

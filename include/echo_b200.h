@@ -319,6 +319,88 @@ int echo_conv_out_tanh_ctx(const void* x_bf16, int batch, int t, int c, int left
 int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Whole S1-DAC decode (DAC.decode_zq, autoencoder.py:1128-1132) as ONE native call, and its incremental form.
+ * Host code only (csrc/ae_decode.cu): a launch sequence over echo_gemm_bf16 / echo_attention / echo_rmsnorm_mod /
+ * echo_dwconv_layernorm_ctx / echo_conv_out_tanh_ctx.  All pointers are device pointers to the caller's packed weights
+ * (layouts: echo_tts_b200/autoencoder.py, the packing functions cite the reference modules); the descriptor arrays
+ * themselves are HOST memory.  No allocation inside: the caller lends a workspace (echo_ae_decode_workspace_bytes).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct echo_ae_tr_layer {      /* one TransformerBlock of post_module (autoencoder.py:682-724) */
+  const void* wqkv;         /* bf16 [3*heads*head_dim, d] */
+  const void* wo;           /* bf16 [d, heads*head_dim] */
+  const void* w13;          /* bf16 [2*ffn, d], rows interleaved in groups of 64 (w1 | w3) */
+  const void* w2;           /* bf16 [d, ffn] */
+  const float *attn_norm, *ffn_norm;     /* RMSNorm weights [d] */
+  const float *attn_scale, *ffn_scale;   /* LayerScale gamma [d] */
+} echo_ae_tr_layer;
+
+typedef struct echo_ae_upsample {      /* CausalTransConvNet (k == stride) + ConvNeXtBlock (autoencoder.py:427-435, 340-373) */
+  int32_t factor, hidden;   /* upsampling factor; ConvNeXt hidden width */
+  const void* wt;           /* bf16 [factor*d, d] (pixel-shuffle view of the transposed conv) */
+  const float* bt;          /* [factor*d] */
+  const float *dw, *dw_b;   /* depthwise k=7 [d, 7], [d] */
+  const float *ln_w, *ln_b; /* LayerNorm [d] */
+  const void* pw1;          /* bf16 [hidden, d] */
+  const float* pb1;
+  const void* pw2;          /* bf16 [d, hidden] */
+  const float* pb2;
+  const float* gamma;       /* [d] */
+} echo_ae_upsample;
+
+typedef struct echo_ae_unit {          /* ResidualUnit (autoencoder.py:879-900) */
+  int32_t dilation, _pad;
+  const float *alpha1, *alpha2;   /* Snake alphas [c] */
+  const void* w7;           /* bf16 [c, 7*c] tap-major */
+  const float* b7;
+  const void* w1;           /* bf16 [c, c] */
+  const float* b1;
+} echo_ae_unit;
+
+typedef struct echo_ae_block {         /* DecoderBlock (autoencoder.py:932-968) */
+  int32_t rate, c_in, c_out, _pad;
+  const float* alpha_in;    /* Snake before the transposed conv [c_in]: applied by the PRODUCER of this block's input */
+  const float* alpha1_rep;  /* units[0].alpha1 repeated `rate` times [rate*c_out] */
+  const void* wt;           /* bf16 [rate*c_out, 2*c_in] (taps 0, -1) */
+  const float* bt;          /* [rate*c_out] */
+  echo_ae_unit units[3];
+} echo_ae_block;
+
+typedef struct echo_ae_decoder_desc {
+  int32_t d, tr_layers, tr_heads, tr_head_dim, tr_ffn, tr_window;
+  float tr_eps, _pad0;
+  const echo_ae_tr_layer* tr;             /* HOST array [tr_layers] */
+  const float* tr_norm;                   /* final RMSNorm [d] */
+  const float *rope_cos, *rope_sin;       /* fp32 [rope_len][tr_head_dim/2] (the module's own bf16-rounded table) */
+  int32_t rope_len, n_up;
+  const echo_ae_upsample* ups;            /* HOST array [n_up] */
+  const void* conv0_w;                    /* bf16 [c0, 7*d] */
+  const float* conv0_b;
+  int32_t c0, n_blocks;
+  const echo_ae_block* blocks;            /* HOST array [n_blocks] */
+  const float* alpha_out;                 /* Snake before the last conv [c_last] */
+  const float* w_last;                    /* fp32 [7][c_last] */
+  float b_last;
+  int32_t gemm_impl;
+  void* gemm_workspace;                   /* optional stream-K scratch (echo_gemm_desc.workspace) */
+  int64_t gemm_workspace_bytes;
+} echo_ae_decoder_desc;
+
+/* bytes of scratch echo_ae_decode (stream == 0) / echo_ae_decode_stream_step (stream != 0, batch 1) need for `frames` */
+int64_t echo_ae_decode_workspace_bytes(const echo_ae_decoder_desc* d, int batch, int frames, int stream);
+/* x: fp32 [batch*frames, d] = z_q time-major (after the PCA inverse, inference.py:234), CLOBBERED (it is the residual
+ * stream of post_module); wav: fp32 [batch, frames*hop]. */
+int echo_ae_decode(const echo_ae_decoder_desc* d, float* x, int batch, int frames, float* wav, void* workspace,
+                   int64_t workspace_bytes, echo_stream_t stream);
+/* Incremental decode of ONE utterance (no reference counterpart; README.md:124 leaves streaming out).  `state` carries,
+ * per layer, what the next call needs: the last window-1 keys/values of every post_module layer and the last
+ * (k-1)*dilation input rows of every causal conv (zeros = the reference's left padding, autoencoder.py:283-289).
+ * `position` = frames decoded so far (RoPE position; caller-owned).  Results equal echo_ae_decode of the concatenation. */
+int64_t echo_ae_decode_stream_state_bytes(const echo_ae_decoder_desc* d);
+int echo_ae_decode_stream_init(const echo_ae_decoder_desc* d, void* state, int64_t state_bytes, echo_stream_t stream);
+int echo_ae_decode_stream_step(const echo_ae_decoder_desc* d, void* state, float* x, int frames, int position,
+                               float* wav, void* workspace, int64_t workspace_bytes, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * S1-DAC encode helpers (DAC.encode_zq, autoencoder.py:1080-1126; the convolutions, transformers and ConvNeXt blocks
  * of the encode path run on echo_gemm_bf16 / echo_attention / echo_dwconv_layernorm like the decode path).
  * ------------------------------------------------------------------------------------------ */

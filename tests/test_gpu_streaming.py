@@ -228,3 +228,50 @@ def test_full_arch_blockwise_vs_reference_fixture():
         err = rel_l2(out[:, 16:], g["out"][:, 16:])
         print(f"full-arch blockwise (incremental_prefix={inc}): generated-latent rel-L2 {err:.3e} (tol 2e-2)")
         assert err < 2e-2
+
+
+# ---- native whole-decode entry points (echo_ae_decode, echo_ae_decode_stream_*) ------------------------------------------
+@pytest.mark.parametrize("cfg_name", ["AE_TINY", "AE_BASE"])
+def test_native_decode_equals_python_launch_sequence(cfg_name, monkeypatch):
+    """csrc/ae_decode.cu issues the launches of autoencoder.py's Python sequence: same kernels, same order, same
+    operands -> bit-identical audio, one-shot (batch 2) and streamed; the input tensor is left untouched."""
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    cfg = getattr(S, cfg_name)
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg), cfg=cfg)
+    z = _rand((2, cfg.latent_dim, 24), 77)
+    z0 = z.clone()
+    chunks = [(0, 1), (1, 6), (6, 24)]
+
+    def both():
+        full = ae.decode_zq(z)
+        st = ae.decode_stream()
+        return full, torch.cat([st.step(z[:1, :, a:b]) for a, b in chunks], -1)
+
+    monkeypatch.setenv("ECHO_AE_NATIVE", "1")
+    n_full, n_stream = both()
+    assert ae.decode_stream().state is not None
+    monkeypatch.setenv("ECHO_AE_NATIVE", "0")
+    p_full, p_stream = both()
+    assert ae.decode_stream().state is None
+    assert torch.equal(z, z0)
+    assert torch.equal(n_full, p_full)
+    assert torch.equal(n_stream, p_stream)
+
+
+def test_native_decode_argument_errors():
+    import ctypes as C
+    from echo_tts_b200 import _lib as L
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict
+    cfg = S.AE_TINY
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(cfg), cfg=cfg)
+    lib, desc = L.load(), ae.native_desc()
+    need = lib.echo_ae_decode_workspace_bytes(C.byref(desc), 1, 8, 0)
+    assert need > 0 and lib.echo_ae_decode_workspace_bytes(C.byref(desc), 2, 8, 0) > need
+    assert lib.echo_ae_decode_workspace_bytes(C.byref(desc), 2, 8, 1) == -1          # a stream is one utterance
+    x = torch.zeros(8, cfg.latent_dim, device="cuda")
+    wav = torch.zeros(1, 8 * cfg.hop, device="cuda")
+    small = torch.empty(1024, device="cuda", dtype=torch.uint8)
+    rc = lib.echo_ae_decode(C.byref(desc), x.data_ptr(), 1, 8, wav.data_ptr(), small.data_ptr(), small.numel(), None)
+    assert rc != 0 and b"workspace too small" in lib.echo_last_error()
+    rc = lib.echo_ae_decode_stream_init(C.byref(desc), small.data_ptr(), 16, None)
+    assert rc != 0 and b"state too small" in lib.echo_last_error()
