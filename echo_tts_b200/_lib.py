@@ -69,6 +69,22 @@ class AttnDesc(C.Structure):
     ]
 
 
+class EncLayer(C.Structure):
+    _fields_ = [("w_qkvg", c_p), ("w_o", c_p), ("w13", c_p), ("w2", c_p), ("q_norm", c_p), ("k_norm", c_p),
+                ("attn_norm", c_p), ("mlp_norm", c_p)]
+
+
+class EncodeKVDesc(C.Structure):
+    _fields_ = [
+        ("n_layers", i32), ("d", i32), ("heads", i32), ("ffn", i32), ("eps", f32), ("causal", i32),
+        ("layers", C.POINTER(EncLayer)), ("out_norm", c_p), ("rope_cos", c_p), ("rope_sin", c_p), ("rope_len", i32),
+        ("rows", i32), ("seq", i32), ("past", i32), ("x", c_p), ("mask", c_p), ("mask_stride", i64), ("extent", c_p),
+        ("enc_cache", c_p), ("enc_cap", i32), ("dec_layers", i32), ("dec_d", i32), ("dec_heads", i32),
+        ("w_kv", C.POINTER(c_p)), ("k_norm", C.POINTER(c_p)), ("rope_heads", i32), ("pos_stride", i32),
+        ("kv_out", c_p), ("out_cap", i32), ("gemm_impl", i32), ("gemm_workspace", c_p), ("gemm_workspace_bytes", i64),
+    ]
+
+
 class AeTrLayer(C.Structure):
     _fields_ = [("wqkv", c_p), ("wo", c_p), ("w13", c_p), ("w2", c_p), ("attn_norm", c_p), ("ffn_norm", c_p),
                 ("attn_scale", c_p), ("ffn_scale", c_p)]
@@ -166,6 +182,8 @@ EXPORTS = {
     "echo_conv_out_tanh": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
     "echo_dwconv_layernorm_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
     "echo_conv_out_tanh_ctx": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, C.c_int, c_p, f32, c_p, c_p]),
+    "echo_encode_kv_workspace_bytes": (i64, [C.POINTER(EncodeKVDesc)]),
+    "echo_encode_kv": (C.c_int, [C.POINTER(EncodeKVDesc), c_p, i64, c_p]),
     "echo_ae_decode_workspace_bytes": (i64, [C.POINTER(AeDecoderDesc), C.c_int, C.c_int, C.c_int]),
     "echo_ae_decode": (C.c_int, [C.POINTER(AeDecoderDesc), c_p, C.c_int, C.c_int, c_p, c_p, i64, c_p]),
     "echo_ae_decode_stream_state_bytes": (i64, [C.POINTER(AeDecoderDesc)]),

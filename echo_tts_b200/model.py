@@ -12,6 +12,7 @@ bf16 tensor-core operands with fp32 accumulation, fp32 softmax statistics.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -224,6 +225,73 @@ class EchoDiT:
                               eps=cfg.norm_eps)
         return KVList.from_buffer(buf, B, Ls, H)
 
+    # ------------------------------------------------------------------------------------------
+    # native form of _run_encoder + _project_kv: ONE call (csrc/encode_kv.cu: echo_encode_kv); ECHO_ENC_NATIVE=0 keeps
+    # the Python launch sequence above (A/B, bit-identical)
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def use_native_encoders() -> bool:
+        return os.environ.get("ECHO_ENC_NATIVE", "1") != "0"
+
+    def _enc_arrays(self, enc: _EncoderWeights, key: str):
+        """HOST arrays of weight pointers for echo_encode_kv (built once per encoder / projection family)."""
+        cache = self.__dict__.setdefault("_c_enc", {})
+        ent = cache.get((id(enc), key))
+        if ent is None:
+            la = (L.EncLayer * len(enc.layers))()
+            for i, lw in enumerate(enc.layers):
+                la[i].w_qkvg, la[i].w_o, la[i].w13, la[i].w2 = (lw[k].data_ptr() for k in ("qkvg", "wo", "w13", "w2"))
+                la[i].q_norm, la[i].k_norm = lw["qn"].data_ptr(), lw["kn"].data_ptr()
+                la[i].attn_norm, la[i].mlp_norm = lw["an"].data_ptr(), lw["mn"].data_ptr()
+            wkv = (C.c_void_p * len(self.layers))(*[lw[key].data_ptr() for lw in self.layers])
+            kn = (C.c_void_p * len(self.layers))(*[lw["kn"].data_ptr() for lw in self.layers])
+            ent = cache[(id(enc), key)] = (la, wkv, kn)
+        return ent
+
+    def encode_kv_native(self, enc: _EncoderWeights, x: torch.Tensor, B: int, Ls: int, *, causal: bool,
+                         mask: Optional[torch.Tensor], norm_w: torch.Tensor, key: str, rope_patch: bool = False,
+                         past: int = 0, enc_cache: Optional[torch.Tensor] = None, kv_out: Optional[torch.Tensor] = None
+                         ) -> torch.Tensor:
+        """x fp32 [B*Ls, d_enc] (clobbered) -> kv_out bf16 [layers, 2, B, cap, D] with positions [past, past+Ls) written.
+        ``enc_cache`` bf16 [enc_layers, 2, B, cap_e, d_enc] holds the encoder's own K/V across incremental calls."""
+        cfg, dev = self.cfg, self._device
+        la, wkv, kn = self._enc_arrays(enc, key)
+        if kv_out is None:
+            kv_out = torch.empty((cfg.num_layers, 2, B, Ls, cfg.model_size), device=dev, dtype=BF16)
+        ext = ops.mask_extent(mask) if mask is not None else None
+        d = L.EncodeKVDesc()
+        d.n_layers, d.d, d.heads, d.ffn = len(enc.layers), x.shape[1], enc.heads, enc.layers[0]["w2"].shape[1]
+        d.eps, d.causal, d.layers, d.out_norm = cfg.norm_eps, int(causal), la, norm_w.data_ptr()
+        d.rope_cos, d.rope_sin, d.rope_len = self.rope[0].data_ptr(), self.rope[1].data_ptr(), self.rope[0].shape[0]
+        d.rows, d.seq, d.past, d.x = B, Ls, past, x.data_ptr()
+        if mask is not None:
+            assert mask.dtype in (torch.bool, torch.uint8) and mask.stride(1) == 1 and mask.shape[0] == B
+            d.mask, d.mask_stride, d.extent = mask.data_ptr(), mask.stride(0), ext.data_ptr()
+        if enc_cache is not None:
+            assert enc_cache.is_contiguous() and enc_cache.dtype == BF16 and enc_cache.shape[:3] == (len(enc.layers), 2, B)
+            d.enc_cache, d.enc_cap = enc_cache.data_ptr(), enc_cache.shape[3]
+        assert kv_out.is_contiguous() and kv_out.dtype == BF16 and kv_out.shape[:3] == (cfg.num_layers, 2, B)
+        d.dec_layers, d.dec_d, d.dec_heads = cfg.num_layers, cfg.model_size, cfg.num_heads
+        d.w_kv, d.k_norm = C.cast(wkv, C.POINTER(C.c_void_p)), C.cast(kn, C.POINTER(C.c_void_p))
+        d.rope_heads, d.pos_stride = (cfg.num_heads // 2, cfg.speaker_patch_size) if rope_patch else (0, 1)
+        d.kv_out, d.out_cap = kv_out.data_ptr(), kv_out.shape[3]
+        gws = ops.gemm_workspace(dev)
+        d.gemm_impl, d.gemm_workspace, d.gemm_workspace_bytes = ops.GEMM_IMPL, gws.data_ptr(), gws.numel()
+        lib = L.load()
+        n = int(lib.echo_encode_kv_workspace_bytes(C.byref(d)))
+        if n < 0:
+            raise RuntimeError(f"echo_b200: {lib.echo_last_error().decode()}")
+        ws = torch.empty(n, device=dev, dtype=torch.uint8)
+        L.check(lib.echo_encode_kv(C.byref(d), ws.data_ptr(), n, L.stream()))
+        return kv_out
+
+    def _encode(self, enc, x, B, Ls, *, causal, mask, norm_w, key, rope_patch=False) -> KVCache:
+        if self.use_native_encoders():
+            buf = self.encode_kv_native(enc, x, B, Ls, causal=causal, mask=mask, norm_w=norm_w, key=key, rope_patch=rope_patch)
+            return KVList.from_buffer(buf.view(self.cfg.num_layers, 2, B * Ls, self.cfg.model_size), B, Ls, self.cfg.num_heads)
+        self._run_encoder(enc, x, B, Ls, causal=causal, mask=mask)
+        return self._project_kv(x, norm_w, key, B, Ls, rope_patch=rope_patch)
+
     @torch.inference_mode()
     def get_kv_cache_text(self, text_input_ids: torch.Tensor, text_mask: Optional[torch.Tensor]) -> KVCache:
         """model.py:606-613."""
@@ -231,8 +299,7 @@ class EchoDiT:
         ids = text_input_ids.to(self._device, torch.int32).contiguous().view(-1)
         x = ops.embedding(ids, self.text_emb)
         mask = text_mask.to(self._device).contiguous() if text_mask is not None else None
-        self._run_encoder(self.text_enc, x, B, Lt, causal=False, mask=mask)
-        return self._project_kv(x, self.text_norm, "kv_text", B, Lt)
+        return self._encode(self.text_enc, x, B, Lt, causal=False, mask=mask, norm_w=self.text_norm, key="kv_text")
 
     def _patch_encode(self, enc, in_w, in_b, latent: torch.Tensor):
         cfg = self.cfg
@@ -243,14 +310,13 @@ class EchoDiT:
         xin = latent.to(self._device, F32).contiguous().view(B * Ls, Cc * p)
         x = torch.empty((B * Ls, in_w.shape[0]), device=self._device, dtype=F32)
         ops.sgemm(xin, in_w, bias=in_b, out=x, out_scale=1.0 / 6.0)          # model.py:461-462
-        self._run_encoder(enc, x, B, Ls, causal=True, mask=None)
         return x, B, Ls
 
     @torch.inference_mode()
     def get_kv_cache_speaker(self, speaker_latent: torch.Tensor) -> KVCache:
         """model.py:615-621."""
         x, B, Ls = self._patch_encode(self.spk_enc, self.spk_in_w, self.spk_in_b, speaker_latent)
-        return self._project_kv(x, self.spk_norm, "kv_speaker", B, Ls)
+        return self._encode(self.spk_enc, x, B, Ls, causal=True, mask=None, norm_w=self.spk_norm, key="kv_speaker")
 
     @torch.inference_mode()
     def get_kv_cache_latent(self, prefix_latent: torch.Tensor) -> KVCache:
@@ -261,7 +327,8 @@ class EchoDiT:
             z = torch.empty((prefix_latent.shape[0], 0, self.cfg.num_heads, 128), device=self._device, dtype=BF16)
             return [(z, z) for _ in range(self.cfg.num_layers)]
         x, B, Ls = self._patch_encode(self.lat_enc, self.lat_in_w, self.lat_in_b, prefix_latent)
-        return self._project_kv(x, self.lat_norm, "kv_latent", B, Ls, rope_patch=True)
+        return self._encode(self.lat_enc, x, B, Ls, causal=True, mask=None, norm_w=self.lat_norm, key="kv_latent",
+                            rope_patch=True)
 
     # ------------------------------------------------------------------------------------------
     # one velocity evaluation (EchoDiT.forward, model.py:563-604) -- ends at the final residual stream;

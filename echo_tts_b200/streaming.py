@@ -263,6 +263,14 @@ class PrefixKVStream:
         H = enc.heads
         d = model.lat_in_w.shape[0]
         Dm, Hm = cfg.model_size, cfg.num_heads
+        if model.use_native_encoders():          # one native call; it walks the prompt rows itself (csrc/encode_kv.cu)
+            xin = lat[:, :n_new * p].contiguous().view(B * n_new, p * cfg.latent_size)
+            x = torch.empty((B * n_new, d), device=dev, dtype=F32)
+            ops.sgemm(xin, model.lat_in_w, bias=model.lat_in_b, out=x, out_scale=1.0 / 6.0)          # model.py:461-462
+            model.encode_kv_native(enc, x, B, n_new, causal=True, mask=None, norm_w=model.lat_norm, key="kv_latent",
+                                   rope_patch=True, past=P0, enc_cache=self.enc_kv, kv_out=self.buf)
+            self.patches = P0 + n_new
+            return self.patches
         # one pass per prompt row: rows of a batch are independent, and a single-row view keeps [cached | new] keys
         # contiguous in the preallocated buffers
         for b in range(B):

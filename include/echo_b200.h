@@ -319,6 +319,51 @@ int echo_conv_out_tanh_ctx(const void* x_bf16, int batch, int t, int c, int left
 int echo_cast_snake(const float* x, int64_t rows, int c, const float* alpha, void* y_bf16, echo_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Conditioning encoders as ONE native call each (host code, csrc/encode_kv.cu): a TextEncoder / SpeakerEncoder stack
+ * (EncoderTransformerBlock, model.py:311-339; SelfAttention :106-161) followed by the per-decoder-layer key/value
+ * projections (JointAttention.get_kv_cache_text/speaker/latent, model.py:270-293).  Replaces
+ * EchoDiT.get_kv_cache_text / _speaker / _latent (model.py:606-636) after the embedding / patch projection.
+ * Incremental form (`past` > 0): the encoder is causal, so positions already encoded never change -- only the new
+ * positions are run, against the cached per-layer encoder K/V, and their projections are appended (blockwise
+ * generation re-encodes the whole prefix three times per block in the reference, inference_blockwise.py:72-74).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct echo_enc_layer {
+  const void* w_qkvg;       /* bf16 [4*d, d]  (wq | wk | wv | gate) */
+  const void* w_o;          /* bf16 [d, d] */
+  const void* w13;          /* bf16 [2*ffn, d], 64-row groups w1 | w3 */
+  const void* w2;           /* bf16 [d, ffn] */
+  const float *q_norm, *k_norm;        /* per-head RMSNorm weights [d] */
+  const float *attn_norm, *mlp_norm;   /* RMSNorm [d] */
+} echo_enc_layer;
+
+typedef struct echo_encode_kv_desc {
+  int32_t n_layers, d, heads, ffn;     /* encoder; head_dim is 128 */
+  float eps;
+  int32_t causal;                      /* 1: SpeakerEncoder / latent encoder, 0: TextEncoder */
+  const echo_enc_layer* layers;        /* HOST array [n_layers] */
+  const float* out_norm;               /* text_norm / speaker_norm / latent_norm [d] (model.py:608, 617, 628) */
+  const float *rope_cos, *rope_sin;    /* fp32 [rope_len][64] */
+  int32_t rope_len;
+  int32_t rows, seq, past;             /* prompts, NEW positions per prompt, positions encoded by earlier calls */
+  float* x;                            /* fp32 [rows*seq, d]: embedding / patch projection; clobbered (residual stream) */
+  const uint8_t* mask;                 /* key-valid bytes [rows][mask_stride] or NULL (text padding mask, model.py:410-418) */
+  int64_t mask_stride;
+  const int32_t* extent;               /* per-row 1 + last valid key, or NULL */
+  void* enc_cache;                     /* bf16 [n_layers][2][rows][enc_cap][d] encoder K / V, or NULL (then past must be 0) */
+  int32_t enc_cap;
+  int32_t dec_layers, dec_d, dec_heads;
+  const void* const* w_kv;             /* HOST array [dec_layers]: bf16 [2*dec_d, d]  (wk_* | wv_*) */
+  const float* const* k_norm;          /* HOST array [dec_layers]: fp32 [dec_d] */
+  int32_t rope_heads, pos_stride;      /* latent prefix: dec_heads/2 heads rotated at position pos_stride * index (model.py:284-293); else 0, 1 */
+  void* kv_out;                        /* bf16 [dec_layers][2][rows][out_cap][dec_d]; this call writes positions [past, past+seq) */
+  int32_t out_cap, gemm_impl;
+  void* gemm_workspace;
+  int64_t gemm_workspace_bytes;
+} echo_encode_kv_desc;
+int64_t echo_encode_kv_workspace_bytes(const echo_encode_kv_desc* d);
+int echo_encode_kv(const echo_encode_kv_desc* d, void* workspace, int64_t workspace_bytes, echo_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Whole S1-DAC decode (DAC.decode_zq, autoencoder.py:1128-1132) as ONE native call, and its incremental form.
  * Host code only (csrc/ae_decode.cu): a launch sequence over echo_gemm_bf16 / echo_attention / echo_rmsnorm_mod /
  * echo_dwconv_layernorm_ctx / echo_conv_out_tanh_ctx.  All pointers are device pointers to the caller's packed weights

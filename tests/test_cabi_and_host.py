@@ -28,17 +28,17 @@ def test_ctypes_struct_sizes_match_c(tmp_path):
     import ctypes
     from echo_tts_b200 import _lib
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "echo_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
+    src.write_text('#include <stdio.h>\n#include "echo_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                    'sizeof(echo_gemm_desc),sizeof(echo_sgemm_desc),sizeof(echo_attn_desc),sizeof(echo_attn_segment),'
                    'sizeof(echo_tail_desc),sizeof(echo_gemm_section),sizeof(echo_dit_layer),sizeof(echo_dit_kv),'
                    'sizeof(echo_dit_step_desc),sizeof(echo_ae_tr_layer),sizeof(echo_ae_upsample),sizeof(echo_ae_unit),'
-                   'sizeof(echo_ae_block),sizeof(echo_ae_decoder_desc));return 0;}')
+                   'sizeof(echo_ae_block),sizeof(echo_ae_decoder_desc),sizeof(echo_enc_layer),sizeof(echo_encode_kv_desc));return 0;}')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     sizes = list(map(int, subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()))
     mine = [ctypes.sizeof(c) for c in (_lib.GemmDesc, _lib.SgemmDesc, _lib.AttnDesc, _lib.AttnSegment, _lib.TailDesc,
                                        _lib.GemmSection, _lib.DitLayer, _lib.DitKV, _lib.DitStepDesc, _lib.AeTrLayer,
-                                       _lib.AeUpsample, _lib.AeUnit, _lib.AeBlock, _lib.AeDecoderDesc)]
+                                       _lib.AeUpsample, _lib.AeUnit, _lib.AeBlock, _lib.AeDecoderDesc, _lib.EncLayer, _lib.EncodeKVDesc)]
     assert sizes == mine
 
 

@@ -275,3 +275,31 @@ def test_native_decode_argument_errors():
     assert rc != 0 and b"workspace too small" in lib.echo_last_error()
     rc = lib.echo_ae_decode_stream_init(C.byref(desc), small.data_ptr(), 16, None)
     assert rc != 0 and b"state too small" in lib.echo_last_error()
+
+
+def test_native_encoders_equal_python_launch_sequence(tiny_model, monkeypatch):
+    """echo_encode_kv issues the launches of model.py's _run_encoder + _project_kv: bit-identical caches for the text
+    (padding mask), speaker (causal) and latent-prefix (causal, rotated keys) encoders, from scratch and incremental."""
+    from echo_tts_b200.streaming import PrefixKVStream
+    B = 2
+    ids = torch.randint(1, 200, (B, 24), dtype=torch.int32, device="cuda")
+    mask = torch.ones(B, 24, dtype=torch.bool, device="cuda")
+    mask[1, 13:] = False
+    spk = _rand((B, 20, 80), 51)
+    lat = _rand((B, 28, 80), 52)
+
+    def all_caches():
+        kt = tiny_model.get_kv_cache_text(ids, mask)
+        ks = tiny_model.get_kv_cache_speaker(spk)
+        kl = tiny_model.get_kv_cache_latent(lat)
+        ps = PrefixKVStream(tiny_model, B, 28)
+        for a, b in ((0, 8), (8, 14), (14, 28)):
+            ps.append(lat[:, a:b])
+        return [torch.stack([torch.stack([k, v]) for k, v in c]) for c in (kt, ks, kl, ps.kv)]
+
+    monkeypatch.setenv("ECHO_ENC_NATIVE", "1")
+    native = all_caches()
+    monkeypatch.setenv("ECHO_ENC_NATIVE", "0")
+    python = all_caches()
+    for a, b in zip(native, python):
+        assert a.shape == b.shape and torch.equal(a, b)
