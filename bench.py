@@ -233,7 +233,7 @@ def config5_streaming(model, ae, pca, dev, reps=3):
         marks, n = [], 0
         for wav, a, b in stream_blockwise_audio(model, ae, pca, dev[2], dev[3], dev[0], dev[1], 0, blocks,
                                                 incremental_prefix=incremental, **kw):
-            n += wav.cpu().shape[-1]                      # D2H of the chunk = the moment a client could play it
+            n += wav.cpu().numel()                        # D2H of the chunk = the moment a client could play it
             marks.append((time.perf_counter() - t0) * 1e3)
         return marks, n
 
@@ -245,7 +245,7 @@ def config5_streaming(model, ae, pca, dev, reps=3):
         rec[name] = dict(total_ms=marks[-1], first_audio_ms=marks[0], block_done_ms=marks, samples_out=n,
                          audio_sec_per_sec=n / 44100 / (marks[-1] / 1e3))
     rec["what"] = ("stream_blockwise_audio(): 4 x 160 latents x 40 steps, cfg 3.0/5.0 on t in [0.5,1], per-block streaming "
-                   "S1-DAC decode + D2H, 1 prompt, eager launches; recomputed_prefix = the reference's full prefix re-encode per block")
+                   "S1-DAC decode + D2H, " + str(dev[0].shape[0]) + " prompt(s), eager launches; recomputed_prefix = the reference's full prefix re-encode per block")
     return rec
 
 

@@ -49,99 +49,113 @@ int check(const echo_encode_kv_desc* D) {
   return ECHO_OK;
 }
 
-// dry: workspace == nullptr, only sizes.  A "group" is the set of prompt rows one launch covers: all of them when the
-// new positions of consecutive rows are adjacent in the caches (cap == seq), else one row at a time.
+int scatter_rows(bf16* dst, int64_t dst_pitch_elems, const bf16* src, int64_t row_elems, int rows, cudaStream_t st) {
+  ECHO_CUDA(cudaMemcpy2DAsync(dst, (size_t)dst_pitch_elems * 2, src, (size_t)row_elems * 2, (size_t)row_elems * 2, (size_t)rows,
+                              cudaMemcpyDeviceToDevice, st));
+  return ECHO_OK;
+}
+
+// dry: workspace == nullptr, only sizes.  All prompt rows go through every launch together.  When the new positions of
+// consecutive rows are not adjacent in a cache (incremental calls: row b's new keys live at [b][past .. past+seq) of a
+// [rows][cap] buffer) the GEMM writes them densely to scratch and one strided copy per tensor scatters them.
 int walk(const echo_encode_kv_desc* D, void* workspace, cudaStream_t st, int64_t* need) {
   const bool dry = workspace == nullptr;
-  const int d = D->d, H = D->heads, L = D->seq, P0 = D->past;
-  const bool enc_adjacent = !D->enc_cache || (D->enc_cap == L && P0 == 0);
-  const bool out_adjacent = D->out_cap == L && P0 == 0;
-  const bool batched = enc_adjacent && out_adjacent;
-  const int gr = batched ? D->rows : 1, ngroups = batched ? 1 : D->rows;
-  const int M = gr * L;
+  const int d = D->d, H = D->heads, L = D->seq, P0 = D->past, R = D->rows;
+  const int64_t cap = D->enc_cap, ocap = D->out_cap;
+  const bool enc_direct = D->enc_cache && cap == L && P0 == 0;
+  const bool out_direct = ocap == L && P0 == 0;
+  const int M = R * L;
   Bump ws{static_cast<uint8_t*>(workspace)};
   bf16* xn = ws.take<bf16>((int64_t)M * d);
   bf16* q = ws.take<bf16>((int64_t)M * d);
   bf16* gate = ws.take<bf16>((int64_t)M * d);
   bf16* ao = ws.take<bf16>((int64_t)M * d);
   bf16* hmid = ws.take<bf16>((int64_t)M * D->ffn);
-  bf16* kscr = D->enc_cache ? nullptr : ws.take<bf16>((int64_t)M * d);
-  bf16* vscr = D->enc_cache ? nullptr : ws.take<bf16>((int64_t)M * d);
+  bf16* kscr = enc_direct ? nullptr : ws.take<bf16>((int64_t)M * d);
+  bf16* vscr = enc_direct ? nullptr : ws.take<bf16>((int64_t)M * d);
+  bf16* koscr = out_direct ? nullptr : ws.take<bf16>((int64_t)M * D->dec_d);
+  bf16* voscr = out_direct ? nullptr : ws.take<bf16>((int64_t)M * D->dec_d);
   if (need) *need = ws.off + 256;
   if (dry) return ECHO_OK;
   bf16* cache = static_cast<bf16*>(D->enc_cache);
   bf16* out = static_cast<bf16*>(D->kv_out);
-  const int64_t cap = D->enc_cap, ocap = D->out_cap;
-  for (int gi = 0; gi < ngroups; ++gi) {
-    const int b0 = batched ? 0 : gi;
-    float* x = D->x + (int64_t)b0 * L * d;
-    for (int l = 0; l < D->n_layers; ++l) {
-      const echo_enc_layer& lw = D->layers[l];
-      // encoder K / V of this layer for prompt row b0: [cap][d] inside the cache, or scratch [M][d]
-      bf16* kc = cache ? cache + (((int64_t)l * 2 + 0) * D->rows + b0) * cap * d : kscr;
-      bf16* vc = cache ? cache + (((int64_t)l * 2 + 1) * D->rows + b0) * cap * d : vscr;
-      const int64_t kcap = cache ? cap : L;
-      if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, lw.attn_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
-      {
-        echo_gemm_desc g;
-        gemm_init(D, &g, xn, d, M, d, lw.w_qkvg, 4 * d, ECHO_EPI_SECTIONS);
-        g.n_sections = 4; g.section_width = d; g.head_dim = 128; g.rope_heads = H;
-        g.pos_offset = P0; g.pos_stride = 1; g.rows_per_seq = L; g.eps = D->eps;
-        g.rope_cos = D->rope_cos; g.rope_sin = D->rope_sin; g.ld_sec_out = d;
-        g.sections[0].type = ECHO_SEC_NORM_ROPE; g.sections[0].out = q; g.sections[0].norm_weight = lw.q_norm;
-        g.sections[1].type = ECHO_SEC_NORM_ROPE; g.sections[1].out = kc + (int64_t)P0 * d; g.sections[1].norm_weight = lw.k_norm;
-        g.sections[2].type = ECHO_SEC_PLAIN; g.sections[2].out = vc + (int64_t)P0 * d;
-        g.sections[3].type = ECHO_SEC_SIGMOID; g.sections[3].out = gate;
-        if (int rc = echo_gemm_bf16(&g, st)) return rc;
-      }
-      {
-        echo_attn_desc a;
-        memset(&a, 0, sizeof(a));
-        a.q = q; a.q_row_stride = d; a.q_batch_stride = (int64_t)L * d;
-        a.gate = gate; a.out = ao;
-        a.rows = gr; a.seq = L; a.heads = H; a.head_dim = 128;
-        a.n_seg = 1; a.impl = 0;
-        a.softmax_scale = 1.0f / sqrtf(128.0f);
-        echo_attn_segment& s = a.seg[0];
-        s.k = kc; s.v = vc; s.row_stride = d; s.batch_stride = kcap * d;
-        s.len = P0 + L; s.causal = D->causal; s.q_offset = P0;
-        if (D->mask) { s.mask = D->mask + (int64_t)b0 * D->mask_stride; s.mask_stride = D->mask_stride; }
-        if (D->extent) s.extent = D->extent + b0;
-        if (int rc = echo_attention(&a, st)) return rc;
-      }
-      {
-        echo_gemm_desc g;
-        gemm_init(D, &g, ao, d, M, d, lw.w_o, d, ECHO_EPI_GENERIC);
-        g.resid = x; g.ld_resid = d; g.out_f32 = x; g.ld_out_f32 = d;
-        if (int rc = echo_gemm_bf16(&g, st)) return rc;
-      }
-      if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, lw.mlp_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
-      {
-        echo_gemm_desc g;
-        gemm_init(D, &g, xn, d, M, d, lw.w13, 2 * D->ffn, ECHO_EPI_SWIGLU);
-        g.out_bf16 = hmid; g.ld_out_bf16 = D->ffn;
-        if (int rc = echo_gemm_bf16(&g, st)) return rc;
-      }
-      {
-        echo_gemm_desc g;
-        gemm_init(D, &g, hmid, D->ffn, M, D->ffn, lw.w2, d, ECHO_EPI_GENERIC);
-        g.resid = x; g.ld_resid = d; g.out_f32 = x; g.ld_out_f32 = d;
-        if (int rc = echo_gemm_bf16(&g, st)) return rc;
-      }
-    }
-    // text_norm / speaker_norm / latent_norm, then the 2 * dec_layers projections (K normalised per head, prefix K rotated)
-    if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, D->out_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
-    for (int l = 0; l < D->dec_layers; ++l) {
-      bf16* ko = out + ((((int64_t)l * 2 + 0) * D->rows + b0) * ocap + P0) * D->dec_d;
-      bf16* vo = out + ((((int64_t)l * 2 + 1) * D->rows + b0) * ocap + P0) * D->dec_d;
+  float* x = D->x;
+  for (int l = 0; l < D->n_layers; ++l) {
+    const echo_enc_layer& lw = D->layers[l];
+    // this layer's encoder K / V: [rows][cap][d] inside the cache, or dense scratch [rows][seq][d]
+    bf16* kc = cache ? cache + ((int64_t)l * 2 + 0) * R * cap * d : kscr;
+    bf16* vc = cache ? cache + ((int64_t)l * 2 + 1) * R * cap * d : vscr;
+    const int64_t kcap = cache ? cap : L;
+    bf16* ksec = enc_direct ? kc : kscr;
+    bf16* vsec = enc_direct ? vc : vscr;
+    if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, lw.attn_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
+    {
       echo_gemm_desc g;
-      gemm_init(D, &g, xn, d, M, d, D->w_kv[l], 2 * D->dec_d, ECHO_EPI_SECTIONS);
-      g.n_sections = 2; g.section_width = D->dec_d; g.head_dim = 128; g.rope_heads = D->rope_heads;
-      g.pos_offset = P0 * D->pos_stride; g.pos_stride = D->pos_stride; g.rows_per_seq = L; g.eps = D->eps;
-      g.rope_cos = D->rope_cos; g.rope_sin = D->rope_sin; g.ld_sec_out = D->dec_d;
-      g.sections[0].type = ECHO_SEC_NORM_ROPE; g.sections[0].out = ko; g.sections[0].norm_weight = D->k_norm[l];
-      g.sections[1].type = ECHO_SEC_PLAIN; g.sections[1].out = vo;
+      gemm_init(D, &g, xn, d, M, d, lw.w_qkvg, 4 * d, ECHO_EPI_SECTIONS);
+      g.n_sections = 4; g.section_width = d; g.head_dim = 128; g.rope_heads = H;
+      g.pos_offset = P0; g.pos_stride = 1; g.rows_per_seq = L; g.eps = D->eps;
+      g.rope_cos = D->rope_cos; g.rope_sin = D->rope_sin; g.ld_sec_out = d;
+      g.sections[0].type = ECHO_SEC_NORM_ROPE; g.sections[0].out = q; g.sections[0].norm_weight = lw.q_norm;
+      g.sections[1].type = ECHO_SEC_NORM_ROPE; g.sections[1].out = ksec; g.sections[1].norm_weight = lw.k_norm;
+      g.sections[2].type = ECHO_SEC_PLAIN; g.sections[2].out = vsec;
+      g.sections[3].type = ECHO_SEC_SIGMOID; g.sections[3].out = gate;
       if (int rc = echo_gemm_bf16(&g, st)) return rc;
+    }
+    if (cache && !enc_direct) {
+      if (int rc = scatter_rows(kc + (int64_t)P0 * d, cap * d, kscr, (int64_t)L * d, R, st)) return rc;
+      if (int rc = scatter_rows(vc + (int64_t)P0 * d, cap * d, vscr, (int64_t)L * d, R, st)) return rc;
+    }
+    {
+      echo_attn_desc a;
+      memset(&a, 0, sizeof(a));
+      a.q = q; a.q_row_stride = d; a.q_batch_stride = (int64_t)L * d;
+      a.gate = gate; a.out = ao;
+      a.rows = R; a.seq = L; a.heads = H; a.head_dim = 128;
+      a.n_seg = 1; a.impl = 0;
+      a.softmax_scale = 1.0f / sqrtf(128.0f);
+      echo_attn_segment& s = a.seg[0];
+      s.k = kc; s.v = vc; s.row_stride = d; s.batch_stride = kcap * d;
+      s.len = P0 + L; s.causal = D->causal; s.q_offset = P0;
+      s.mask = D->mask; s.mask_stride = D->mask_stride; s.extent = D->extent;
+      if (int rc = echo_attention(&a, st)) return rc;
+    }
+    {
+      echo_gemm_desc g;
+      gemm_init(D, &g, ao, d, M, d, lw.w_o, d, ECHO_EPI_GENERIC);
+      g.resid = x; g.ld_resid = d; g.out_f32 = x; g.ld_out_f32 = d;
+      if (int rc = echo_gemm_bf16(&g, st)) return rc;
+    }
+    if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, lw.mlp_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
+    {
+      echo_gemm_desc g;
+      gemm_init(D, &g, xn, d, M, d, lw.w13, 2 * D->ffn, ECHO_EPI_SWIGLU);
+      g.out_bf16 = hmid; g.ld_out_bf16 = D->ffn;
+      if (int rc = echo_gemm_bf16(&g, st)) return rc;
+    }
+    {
+      echo_gemm_desc g;
+      gemm_init(D, &g, hmid, D->ffn, M, D->ffn, lw.w2, d, ECHO_EPI_GENERIC);
+      g.resid = x; g.ld_resid = d; g.out_f32 = x; g.ld_out_f32 = d;
+      if (int rc = echo_gemm_bf16(&g, st)) return rc;
+    }
+  }
+  // text_norm / speaker_norm / latent_norm, then the 2 * dec_layers projections (K normalised per head, prefix K rotated)
+  if (int rc = echo_rmsnorm_mod(x, d, M, d, D->eps, D->out_norm, nullptr, 0, 0, nullptr, 0, xn, d, st)) return rc;
+  const int dd = D->dec_d;
+  for (int l = 0; l < D->dec_layers; ++l) {
+    bf16* ko = out + ((int64_t)l * 2 + 0) * R * ocap * dd;
+    bf16* vo = out + ((int64_t)l * 2 + 1) * R * ocap * dd;
+    echo_gemm_desc g;
+    gemm_init(D, &g, xn, d, M, d, D->w_kv[l], 2 * dd, ECHO_EPI_SECTIONS);
+    g.n_sections = 2; g.section_width = dd; g.head_dim = 128; g.rope_heads = D->rope_heads;
+    g.pos_offset = P0 * D->pos_stride; g.pos_stride = D->pos_stride; g.rows_per_seq = L; g.eps = D->eps;
+    g.rope_cos = D->rope_cos; g.rope_sin = D->rope_sin; g.ld_sec_out = dd;
+    g.sections[0].type = ECHO_SEC_NORM_ROPE; g.sections[0].out = out_direct ? ko : koscr; g.sections[0].norm_weight = D->k_norm[l];
+    g.sections[1].type = ECHO_SEC_PLAIN; g.sections[1].out = out_direct ? vo : voscr;
+    if (int rc = echo_gemm_bf16(&g, st)) return rc;
+    if (!out_direct) {
+      if (int rc = scatter_rows(ko + (int64_t)P0 * dd, ocap * dd, koscr, (int64_t)L * dd, R, st)) return rc;
+      if (int rc = scatter_rows(vo + (int64_t)P0 * dd, ocap * dd, voscr, (int64_t)L * dd, R, st)) return rc;
     }
   }
   return ECHO_OK;
