@@ -49,6 +49,8 @@ struct Tiling {
   int num_tiles;          // work units: tiles_m * tiles_n * batch * splits
   int splits;             // split-K: units per tile (unit index = tile * splits + split)
   long long split_stride; // elements between the partial outputs
+  int tail_start;         // >= 0: units from this index on are HALF-width tiles, two per wide tile (the ragged last round
+                          // of a launch runs as one round of narrow tiles: shorter main loop and exposed epilogue); -1 off
   int stream_k;           // 1: contiguous k-block ranges per pair (num_tiles = plain tile count, splits = 1)
   int* sk_flags;          // [pairs][2 CTAs][EPI_WARPS] 0/1, self-resetting
   float* sk_partials;     // [pairs][2 CTAs][128 x 256] fp32 in the exchange layout of sk_cell()
@@ -58,12 +60,13 @@ constexpr int SK_FLAG_BYTES = 16384;
 constexpr long long SK_SLOT_FLOATS = 2LL * BM * ACC_COLS;      // one pair's partial accumulator (256 KB)
 
 // One work unit: k-blocks [kb0, kb1) of `tile`.  All three warp roles walk the same sequence.
-struct Unit { int tile, split, kb0, kb1; };
+// sub: -1 = full-width tile, 0 / 1 = left / right half-width tile of `tile`
+struct Unit { int tile, split, kb0, kb1, sub; };
 struct Sched {
-  int sk, total_kb, splits, unit, step, end;
+  int sk, total_kb, splits, unit, step, end, tail;
   long long u, e;
   __device__ Sched(const Tiling& T, int pair, int npairs, int total_kb_) {
-    sk = T.stream_k; total_kb = total_kb_; splits = T.splits;
+    sk = T.stream_k; total_kb = total_kb_; splits = T.splits; tail = T.tail_start;
     unit = pair; step = npairs; end = T.num_tiles;
     const long long U = (long long)T.num_tiles * total_kb;
     u = U * pair / npairs; e = U * (pair + 1) / npairs;
@@ -71,7 +74,7 @@ struct Sched {
   __device__ bool next(Unit& w) {
     if (sk) {
       if (u >= e) return false;
-      w.tile = (int)(u / total_kb); w.split = 0;
+      w.tile = (int)(u / total_kb); w.split = 0; w.sub = -1;
       w.kb0 = (int)(u - (long long)w.tile * total_kb);
       const long long rem = e - u;
       w.kb1 = rem < (long long)(total_kb - w.kb0) ? w.kb0 + (int)rem : total_kb;
@@ -79,8 +82,13 @@ struct Sched {
       return true;
     }
     if (unit >= end) return false;
-    w.tile = unit / splits; w.split = unit - w.tile * splits;
-    w.kb0 = total_kb * w.split / splits; w.kb1 = total_kb * (w.split + 1) / splits;      // 32-bit: k-blocks x splits is tiny
+    if (tail >= 0 && unit >= tail) {       // narrow tail (splits == 1): two half-width units per remaining wide tile
+      const int j = unit - tail;
+      w.tile = tail + (j >> 1); w.sub = j & 1; w.split = 0; w.kb0 = 0; w.kb1 = total_kb;
+    } else {
+      w.tile = unit / splits; w.split = unit - w.tile * splits; w.sub = -1;
+      w.kb0 = total_kb * w.split / splits; w.kb1 = total_kb * (w.split + 1) / splits;    // 32-bit: k-blocks x splits is tiny
+    }
     unit += step;
     return true;
   }
@@ -192,7 +200,7 @@ __device__ __forceinline__ void sk_merge(int bn, uint32_t tacc, uint32_t tside, 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P,
+                 const __grid_constant__ CUtensorMap tmap_bn, const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P,
                  const __grid_constant__ Tiling T) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -209,13 +217,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
   const int total_kb = G.k_blocks_per_tap * G.taps;
   const int half_n = T.bn >> 1;
-  const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_n * BK * 2);
   long long* const trace = T.trace ? T.trace + (long long)blockIdx.x * 32 : nullptr;
   if (trace && threadIdx.x == 0) trace[0] = clock64();
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
+    if (T.tail_start >= 0) ptx::prefetch_tensormap(&tmap_bn);
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full_bar[s], 1);        // leader's producer: arrive.expect_tx (both CTAs' bytes)
       ptx::mbar_init(&empty_bar[s], 1);       // tcgen05.commit multicast to both CTAs
@@ -251,7 +259,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int rest = tile / T.tiles_m;
         const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
         const int m0 = mt * (2 * BM) + (int)rank * BM;
-        const int n0 = nt * T.bn + (int)rank * half_n;
+        const int half_u = w.sub < 0 ? half_n : half_n >> 1;            // rows of B this CTA stages for the unit
+        const int n0 = nt * T.bn + (w.sub > 0 ? half_n : 0) + (int)rank * half_u;
+        const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_u * BK * 2);
         const int kb0 = w.kb0, kb1 = w.kb1;
         const bool first_u = first_unit;
         first_unit = false;
@@ -264,7 +274,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], stage_tx);
           const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
           ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
-          ptx::tma_load_2d_cg2(sb, &tmap_b, lbar, tap * G.k_tap + kk * BK, n0);
+          ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
@@ -272,7 +282,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {   // whole warp converged; one elected lane issues (keeps UTCHMMA free of election loops)
-      const uint32_t idesc = ptx::umma_idesc_bf16(2 * BM, T.bn);
+      const uint32_t idesc_wide = ptx::umma_idesc_bf16(2 * BM, T.bn), idesc_narrow = ptx::umma_idesc_bf16(2 * BM, T.bn >> 1);
       uint32_t tc = 0, ph = 0;
       int s = 0;
       bool first = true, first_unit = true;
@@ -280,6 +290,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       Unit w;
       for (; sch.next(w); ++tc) {
         const int kb0 = w.kb0, kb1 = w.kb1;
+        const uint32_t idesc = w.sub < 0 ? idesc_wide : idesc_narrow;
         const bool first_u = first_unit;
         first_unit = false;
         const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
@@ -345,13 +356,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
       const int m0 = mt * (2 * BM) + (int)rank * BM;
       const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
+      const int bn_u = w.sub < 0 ? T.bn : T.bn >> 1;
+      const int nc0 = nt * T.bn + (w.sub > 0 ? (T.bn >> 1) : 0);
       EpiPre<EPI> pre;
-      epilogue_prefetch_t<EPI>(T.bn, P, lane, half, batch, m0 + q * 32, nt * T.bn, pre);
+      epilogue_prefetch_t<EPI>(bn_u, P, lane, half, batch, m0 + q * 32, nc0, pre);
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
       TmemLoader2 L{tmem_base + as * ACC_COLS + lane_base};
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre, split,
+      run_epilogue_t<EPI>(bn_u, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nc0, pre, split,
                           split * T.split_stride);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
@@ -421,7 +434,20 @@ extern "C" long long echo_gemm_workspace_bytes(void) {
 template <int EPI>
 static int launch_pair_t(int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tbn;
+  // Narrow tail: when the last round of whole-tile scheduling is ragged and its tiles, cut in two along N, still fit ONE
+  // round, those tiles run half-width -- a shorter main loop and half the exposed epilogue at the end of the launch
+  // (q/k/v/gate projection: 256 tiles = 3 rounds of 74 + 34 -> 68 half tiles; 96 tiles at 640 tokens = 74 + 22 -> 44).
+  int tail_start = -1;
+  {
+    const int P2 = num_sms() / 2;
+    const int wide = ceil_div(G.rows, 2 * BM) * ceil_div(G.n, bn) * batch;
+    const int rem = wide % P2;
+    if (splits == 1 && bn == 256 && G.n % 256 == 0 && !g_debug_noload && getenv_int("ECHO_GEMM_TAIL", 1)) {
+      if (wide > P2 && rem > 0 && 2 * rem <= P2) tail_start = wide - rem;
+      else if (2 * wide <= P2) tail_start = 0;      // a single sparse round: every tile half-width, twice the pairs busy
+    }
+  }
   {
     cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)(G.rows + G.a_ctx), (cuuint64_t)batch};
     cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)(G.rows + G.a_ctx) * G.lda) * 2};
@@ -435,6 +461,12 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     cuuint32_t box[2] = {BK, (cuuint32_t)(bn / 2)};
     int rc = echo_make_tmap_bf16(&tb, G.b, 2, dims, str, box);
     if (rc) return rc;
+    tbn = tb;                                   // half-width tiles of the narrow tail: a box of bn/4 rows
+    if (tail_start >= 0) {
+      box[1] = (cuuint32_t)(bn / 4);
+      rc = echo_make_tmap_bf16(&tbn, G.b, 2, dims, str, box);
+      if (rc) return rc;
+    }
   }
   static bool attr_set = false;
   if (!attr_set) {
@@ -452,9 +484,11 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   T.splits = splits;
   T.split_stride = split_stride;
   T.num_tiles = T.tiles_m * T.tiles_n * batch * splits;
+  T.tail_start = tail_start;
+  if (tail_start >= 0) T.num_tiles = tail_start + 2 * (T.num_tiles - tail_start);
   int pairs = T.num_tiles < num_sms() / 2 ? T.num_tiles : num_sms() / 2;
   T.stream_k = 0; T.sk_flags = nullptr; T.sk_partials = nullptr;
-  if (splits == 1 && workspace && workspace_bytes >= echo_gemm_workspace_bytes() && !g_debug_noload) {
+  if (splits == 1 && tail_start < 0 && workspace && workspace_bytes >= echo_gemm_workspace_bytes() && !g_debug_noload) {
     // stream-K when whole-tile scheduling would idle more than ~8 % of the machine in its last round and every pair
     // still gets a few k-blocks of work
     const int P2 = num_sms() / 2, total_kb = G.k_blocks_per_tap * G.taps;
@@ -467,7 +501,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
       pairs = P2;
     }
   }
-  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, G, P, T));
+  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, tbn, G, P, T));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

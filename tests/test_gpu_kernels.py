@@ -219,3 +219,35 @@ def test_rmsnorm_mod(ops):
     ref = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5) * tab[:, 1].repeat_interleave(S, 0) + \
         tab[:, 0].repeat_interleave(S, 0)
     assert rel_l2(y.float(), ref) < 3e-3
+
+
+# ---- narrow tail: the ragged last round of a launch runs as half-width tiles (gemm2.cu launch_pair_t) ------------------
+@pytest.mark.parametrize("M,N,K", [(1920, 8192, 320), (640, 8192, 256), (2000, 5120, 192), (700, 8192, 64)])
+def test_gemm_narrow_tail_matches_plain_schedule(ops, M, N, K, monkeypatch):
+    """Shapes whose 256-wide tiles leave a ragged last round that fits one round of 128-wide tiles (e.g. 8 x 32 = 256
+    tiles on 74 CTA pairs: 3 rounds + 34).  Same per-element sums as the plain schedule -> bit-identical results, for
+    the generic, sections (per-head RMSNorm + RoPE + sigmoid) and SwiGLU epilogues; and both match the fp32 reference."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200 import _lib as L
+    a = _rand((M, K), 61, dtype=BF16)
+    w = _rand((N, K), 62, K ** -0.5, BF16)
+    bias = _rand((N,), 63)
+    D = N // 4
+    qn, kn = _rand((D,), 64).abs() + 0.5, _rand((D,), 65).abs() + 0.5
+    cos, sin = O.rope_table(128, 4096)
+    rope = (cos.cuda().contiguous(), sin.cuda().contiguous())
+    res = {}
+    for tail in ("1", "0"):
+        monkeypatch.setenv("ECHO_GEMM_TAIL", tail)
+        out = torch.full((M, N), float("nan"), device="cuda", dtype=F32)
+        ops.gemm_generic(a, w, bias=bias, out_f32=out, impl=2)
+        sec = torch.full((4, M, D), float("nan"), device="cuda", dtype=BF16)
+        ops.gemm_sections(a, w, [(L.SEC_NORM_ROPE, sec[0], qn), (L.SEC_NORM_ROPE, sec[1], kn), (L.SEC_PLAIN, sec[2], None),
+                                 (L.SEC_SIGMOID, sec[3], None)], head_dim=128, rope_heads=D // 256, rope=rope,
+                          rows_per_seq=M, eps=1e-5, impl=2)
+        sw = torch.full((M, N // 2), float("nan"), device="cuda", dtype=BF16)
+        ops.gemm_swiglu(a, w, sw, impl=2)
+        res[tail] = (out, sec, sw)
+    for x, y in zip(res["1"], res["0"]):
+        assert torch.equal(x, y)
+    assert rel_l2(res["1"][0], a.float() @ w.float().t() + bias) < 2e-5

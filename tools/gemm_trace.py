@@ -20,11 +20,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--m", type=int, default=1920)
     ap.add_argument("--case", default="wo,w2,qkvg,w13")
+    ap.add_argument("--seq", type=int, default=640)
     args = ap.parse_args()
     from echo_tts_b200 import ops, _lib as L
     from echo_tts_b200.model import rope_table
     lib = L.load()
-    D, F_, H, S = 2048, 5888, 16, 640
+    D, F_, H, S = 2048, 5888, 16, args.seq
     M = args.m
     g = torch.Generator(device="cuda").manual_seed(0)
     rnd = lambda *s, sc=1.0: (torch.randn(s, device="cuda", generator=g) * sc)
