@@ -60,32 +60,60 @@ __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_l
   }
 }
 
-// Last stage (autoencoder.py:994): causal conv k=7, C -> 1, + tanh on Snake'd bf16 input.
-// 256 outputs per CTA; the (256+6) x C input window is staged in shared memory with odd row stride.
+// Last stage (autoencoder.py:994): causal conv k=7, C -> 1, + tanh on Snake'd bf16 input.  HBM-bound (C*2 bytes in, 4 out
+// per sample).  One warp per run of 32*RUNS outputs, channels across lanes (lane l owns channels l, l+32, ...): every
+// input row is read ONCE from global (64-byte warp loads, no shared memory) and scattered into the <= 7 outputs it feeds;
+// 32 per-lane partial outputs live in registers and one 31-shuffle transpose-reduction per 32 outputs leaves output
+// t0 + l in lane l for a coalesced store.  left_ctx as in dwconv_ln_kernel.
+template <int NC>
 __global__ void __launch_bounds__(256) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
                                                             const float* __restrict__ w, float bias,
-                                                            float* __restrict__ wav, int left_ctx) {
-  extern __shared__ float sx[];                 // [(256+6)][c_len+1] fp32
-  float* sw = sx + (256 + 6) * (c_len + 1);     // [7][c_len]
-  const int bt = blockIdx.y, t0 = blockIdx.x * 256;
+                                                            float* __restrict__ wav, int left_ctx, int runs) {
+  const int lane = threadIdx.x & 31, bt = blockIdx.y;
+  const long long warp_id = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const bf16* xb = x + (long long)bt * t_len * c_len;
-  for (int i = threadIdx.x; i < 7 * c_len; i += 256) sw[i] = w[i];
-  const int n = (256 + 6) * c_len;
-  for (int i = threadIdx.x; i < n; i += 256) {
-    const int r = i / c_len, c = i % c_len;
-    const int tt = t0 - 6 + r;
-    sx[r * (c_len + 1) + c] = (tt >= -left_ctx && tt < t_len) ? bf2f(xb[(long long)tt * c_len + c]) : 0.f;
+  float wk[7][NC];
+#pragma unroll
+  for (int k = 0; k < 7; ++k)
+#pragma unroll
+    for (int j = 0; j < NC; ++j) wk[k][j] = (lane + 32 * j < c_len) ? __ldg(w + k * c_len + lane + 32 * j) : 0.f;
+  for (int run = 0; run < runs; ++run) {
+    const long long t0 = (warp_id * runs + run) * 32;
+    if (t0 >= t_len) return;
+    float acc[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int rl = 0; rl < 38; ++rl) {
+      const long long r = t0 - 6 + rl;
+      float xv[NC];
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        const int c = lane + 32 * j;
+        xv[j] = (r >= -left_ctx && r < t_len && c < c_len) ? bf2f(xb[r * c_len + c]) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 7; ++k) {
+        const int tl = rl - k;                 // row r = t - 6 + k of output t = t0 + tl
+        if (tl >= 0 && tl < 32) {
+#pragma unroll
+          for (int j = 0; j < NC; ++j) acc[tl] = fmaf(wk[k][j], xv[j], acc[tl]);
+        }
+      }
+    }
+    // transpose-reduce: afterwards acc[0] of lane l = sum over lanes of acc[l]
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+      const bool up = (lane & s) != 0;
+#pragma unroll
+      for (int i = 0; i < s; ++i) {
+        const float send = up ? acc[i] : acc[i + s];
+        const float keep = up ? acc[i + s] : acc[i];
+        acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+      }
+    }
+    if (t0 + lane < t_len) wav[(long long)bt * t_len + t0 + lane] = tanhf(acc[0] + bias);
   }
-  __syncthreads();
-  const int t = t0 + threadIdx.x;
-  if (t >= t_len) return;
-  float acc = bias;
-  for (int k = 0; k < 7; ++k) {
-    const float* row = sx + (threadIdx.x + k) * (c_len + 1);
-    const float* wk = sw + k * c_len;
-    for (int c = 0; c < c_len; ++c) acc = fmaf(row[c], wk[c], acc);
-  }
-  wav[(long long)bt * t_len + t] = tanhf(acc);
 }
 
 __global__ void cast_snake_kernel(const float* __restrict__ x, long long n, int c_len, const float* __restrict__ alpha,
@@ -293,14 +321,17 @@ extern "C" int echo_conv_out_tanh_ctx(const void* x, int batch, int t, int c, in
                                       float* wav, echo_stream_t stream) {
   ECHO_CHECK_ARG(x && w && wav && batch > 0 && t > 0 && c > 0 && c <= 128, "conv_out: bad argument");
   ECHO_CHECK_ARG(left_ctx >= 0 && left_ctx <= 6 && (left_ctx == 0 || batch == 1), "conv_out: left_ctx needs batch 1, <= 6 rows");
-  const size_t smem = ((size_t)(256 + 6) * (c + 1) + 7 * c) * sizeof(float);
-  static size_t configured = 48 * 1024;
-  if (smem > configured) {
-    ECHO_CUDA(cudaFuncSetAttribute(conv_out_tanh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+  const int runs = t >= (1 << 16) ? 4 : 1;                       // 32 * runs outputs per warp
+  const int per_cta = 8 * 32 * runs;
+  const dim3 grid(ceil_div(t, per_cta), batch);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bf16* xp = (const bf16*)x;
+  switch ((c + 31) / 32) {
+    case 1: conv_out_tanh_kernel<1><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
+    case 2: conv_out_tanh_kernel<2><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
+    case 3: conv_out_tanh_kernel<3><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
+    default: conv_out_tanh_kernel<4><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
   }
-  conv_out_tanh_kernel<<<dim3(ceil_div(t, 256), batch), 256, smem, (cudaStream_t)stream>>>((const bf16*)x, t, c, w, bias, wav,
-                                                                                               left_ctx);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
