@@ -241,7 +241,8 @@ class DAC:
             ops.gemm_generic(s1, u["w7"], taps=tuple(-(6 - k) * d for k in range(7)), batch=B, bias=u["b7"],
                              out2_bf16=s2, snake_alpha=u["a2"])
             nxt = units[j + 1]["a1"] if j + 1 < len(units) else next_alpha
-            ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out_f32=x, out2_bf16=s1, snake_alpha=nxt)
+            ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out2_bf16=s1, snake_alpha=nxt,
+                             out_f32=(x if j + 1 < len(units) else None))   # after the last unit only snake(x) is read
 
     def _encoder(self, audio: torch.Tensor):
         """Encoder.forward (autoencoder.py:903-929): audio fp32 [B, T] (T a multiple of the hop) ->
@@ -404,7 +405,8 @@ class DAC:
                     nxt = self.blocks[bi + 1]["alpha_in"]
                 else:
                     nxt = self.alpha_out
-                ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out_f32=x, out2_bf16=s1, snake_alpha=nxt)
+                ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out2_bf16=s1, snake_alpha=nxt,
+                             out_f32=(x if j + 1 < len(units) else None))   # after the last unit only snake(x) is read
             s = s1
         wav = torch.empty((B, T), device=dev, dtype=F32)
         ops.conv_out_tanh(s.view(B, T, -1), self.w_last, self.b_last, wav)

@@ -269,7 +269,8 @@ void wave_decoder(Ctx& c, bf16* ab, int B, int T, float* wav) {
       if (c.live()) {
         echo_gemm_desc g;
         gemm_init(c, &g, s2, co, B * T, 1, co, u.w1, co, 1, nullptr, 0, ECHO_EPI_GENERIC);
-        g.bias = u.b1; g.resid = x; g.ld_resid = co; g.out_f32 = x; g.ld_out_f32 = co;
+        g.bias = u.b1; g.resid = x; g.ld_resid = co;
+        if (j + 1 < 3) { g.out_f32 = x; g.ld_out_f32 = co; }     // after the last unit only snake(x) is read again
         g.out2_bf16 = s1; g.ld_out2_bf16 = co; g.snake_alpha = nxt;
         c.run(echo_gemm_bf16(&g, c.st));
       }

@@ -170,7 +170,8 @@ class DecodeStream:
                     nxt = dac.blocks[bi + 1]["alpha_in"]
                 else:
                     nxt = dac.alpha_out
-                ops.gemm_generic(s2, u["w1"], bias=u["b1"], resid=x, out_f32=x, out2_bf16=s1, snake_alpha=nxt)
+                ops.gemm_generic(s2, u["w1"], bias=u["b1"], resid=x, out2_bf16=s1, snake_alpha=nxt,
+                             out_f32=(x if j + 1 < len(units) else None))   # after the last unit only snake(x) is read
             sb, lead = s1b, LEAD
         wav = torch.empty((1, T), device=dev, dtype=F32)
         self.carry.load("out", sb, lead, 6)
