@@ -324,6 +324,10 @@ def run_gpu(args):
     ev[0].record(); lat = sample(model, dev[2], dev[3], dev[0], dev[1], 5, **KW); ev[1].record()
     ae_decode(ae, pca, lat); ev[2].record(); torch.cuda.synchronize()
     sampler_ms, decode_ms = ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     audio = world * B * AUDIO_SEC_PER_PROMPT * args.steps
