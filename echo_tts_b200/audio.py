@@ -21,7 +21,7 @@ from . import _lib as L
 F32 = torch.float32
 TARGET_SR = 44_100
 
-_FILTER_BANKS: Dict[Tuple[int, int, str], Tuple[torch.Tensor, int, int, int]] = {}
+_FILTER_BANKS: Dict[Tuple[int, int, str], tuple] = {}
 
 
 def sinc_filter_bank(orig_freq: int, new_freq: int, lowpass_filter_width: int = 6, rolloff: float = 0.99):
@@ -43,7 +43,7 @@ def sinc_filter_bank(orig_freq: int, new_freq: int, lowpass_filter_width: int = 
     return bank, width, down, up
 
 
-def _device_bank(orig_freq: int, new_freq: int, device) -> Tuple[torch.Tensor, int, int, int]:
+def _device_bank(orig_freq: int, new_freq: int, device) -> tuple:
     key = (int(orig_freq), int(new_freq), str(device))
     ent = _FILTER_BANKS.get(key)
     if ent is None:
@@ -51,7 +51,13 @@ def _device_bank(orig_freq: int, new_freq: int, device) -> Tuple[torch.Tensor, i
             bank, width, down, up = torch.ones(1, 1), 0, 1, 1          # functional.resample returns the input unchanged
         else:
             bank, width, down, up = sinc_filter_bank(orig_freq, new_freq)
-        ent = (bank.t().contiguous().to(device), width, down, up)      # [taps][up]: phases of one frame read coalesced
+        # per-phase tap range that matters: beyond +-lowpass_filter_width zero crossings the Hann window is zero up to
+        # rounding (|weight| < 1e-9 of the peak there; torchaudio multiplies through all 2*width + down taps regardless)
+        live = bank.abs() > 1e-9 * float(bank.abs().max())
+        idx = torch.arange(bank.shape[1])
+        lo = torch.where(live, idx, bank.shape[1]).min(dim=1).values.to(torch.int32)
+        hi = (torch.where(live, idx, -1).max(dim=1).values + 1).to(torch.int32)
+        ent = (bank.t().contiguous().to(device), width, down, up, lo.to(device), hi.to(device))   # table [taps][up]
         _FILTER_BANKS[key] = ent
     return ent
 
@@ -67,13 +73,13 @@ def prepare_audio(samples: torch.Tensor, sample_rate: int, device="cuda", target
         raise ValueError("prepare_audio: samples must be [channels, n] with n > 0")
     x = samples.to(device, F32).contiguous()
     C_, n = x.shape
-    table_t, width, down, up = _device_bank(sample_rate, target_rate, x.device)
+    table_t, width, down, up, tap_lo, tap_hi = _device_bank(sample_rate, target_rate, x.device)
     n_out = -(-up * n // down)
     y = torch.empty((1, n_out), device=x.device, dtype=F32)
     peak = torch.zeros(1, device=x.device, dtype=torch.int32)
     lib = L.load()
-    L.check(lib.echo_resample_mono(x.data_ptr(), C_, n, x.stride(0), down, up, width, table_t.data_ptr(), y.data_ptr(),
-                                   n_out, peak.data_ptr() if normalize else None, L.stream()))
+    L.check(lib.echo_resample_mono(x.data_ptr(), C_, n, x.stride(0), down, up, width, table_t.data_ptr(), tap_lo.data_ptr(),
+                                   tap_hi.data_ptr(), y.data_ptr(), n_out, peak.data_ptr() if normalize else None, L.stream()))
     if normalize:
         L.check(lib.echo_peak_normalize(y.data_ptr(), n_out, peak.data_ptr(), 1.0, L.stream()))
     return y

@@ -66,7 +66,7 @@ __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_l
 // 32 per-lane partial outputs live in registers and one 31-shuffle transpose-reduction per 32 outputs leaves output
 // t0 + l in lane l for a coalesced store.  left_ctx as in dwconv_ln_kernel.
 template <int NC>
-__global__ void __launch_bounds__(256) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
+__global__ void __launch_bounds__(256, 2) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
                                                             const float* __restrict__ w, float bias,
                                                             float* __restrict__ wav, int left_ctx, int runs) {
   const int lane = threadIdx.x & 31, bt = blockIdx.y;
@@ -255,8 +255,10 @@ __global__ void flattening_kernel(const float* __restrict__ x, int len, int widt
 // like their bit patterns, so one atomicMax per block on the uint32 view is exact.
 __global__ void __launch_bounds__(256) resample_mono_kernel(const float* __restrict__ x, int channels, long long n,
                                                             long long ldx, int down, int up, int width, int taps,
-                                                            const float* __restrict__ table_t, float* __restrict__ y,
-                                                            long long n_out, unsigned int* __restrict__ absmax_bits) {
+                                                            const float* __restrict__ table_t,
+                                                            const int* __restrict__ tap_lo, const int* __restrict__ tap_hi,
+                                                            float* __restrict__ y, long long n_out,
+                                                            unsigned int* __restrict__ absmax_bits) {
   const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   float acc = 0.f;
   if (j < n_out) {
@@ -264,7 +266,8 @@ __global__ void __launch_bounds__(256) resample_mono_kernel(const float* __restr
     const int p = (int)(j - f * up);
     const long long i0 = f * down - width;
     const float inv_c = 1.f / (float)channels;
-    for (int k = 0; k < taps; ++k) {
+    const int k0 = tap_lo ? __ldg(tap_lo + p) : 0, k1 = tap_hi ? __ldg(tap_hi + p) : taps;
+    for (int k = k0; k < k1; ++k) {
       const long long i = i0 + k;
       if (i < 0 || i >= n) continue;
       float m = __ldg(x + i);
@@ -394,15 +397,16 @@ extern "C" int echo_vq_nearest(const float* e, int m, int dim, const float* code
 }
 
 extern "C" int echo_resample_mono(const float* x, int channels, int64_t n, int64_t ldx, int down, int up, int width,
-                                  const float* table_t, float* y, int64_t n_out, uint32_t* absmax_bits,
-                                  echo_stream_t stream) {
+                                  const float* table_t, const int32_t* tap_lo, const int32_t* tap_hi, float* y,
+                                  int64_t n_out, uint32_t* absmax_bits, echo_stream_t stream) {
   ECHO_CHECK_ARG(x && table_t && y && channels > 0 && channels <= 64 && n > 0 && n_out > 0, "resample: bad argument");
   ECHO_CHECK_ARG(down > 0 && up > 0 && width >= 0 && ldx >= n, "resample: bad rates");
+  ECHO_CHECK_ARG((tap_lo == nullptr) == (tap_hi == nullptr), "resample: tap_lo and tap_hi go together");
   ECHO_CHECK_ARG(n_out <= ((n + down - 1) / down + 1) * (int64_t)up, "resample: n_out exceeds the frames the input covers");
   const int taps = 2 * width + down;
   const unsigned blocks = (unsigned)((n_out + 255) / 256);
-  resample_mono_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, channels, n, ldx, down, up, width, taps, table_t, y, n_out,
-                                                                absmax_bits);
+  resample_mono_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, channels, n, ldx, down, up, width, taps, table_t, tap_lo,
+                                                                tap_hi, y, n_out, absmax_bits);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

@@ -472,9 +472,13 @@ int echo_vq_nearest(const float* e, int m, int dim, const float* codebook_normal
  *   y[f*up + p] = sum_k table_t[k*up + p] * mono[f*down + k - width],   k in [0, 2*width + down), zeros outside [0, n)
  * x fp32 [channels][ldx], (down, up) = (orig, new) / gcd, table_t fp32 [2*width + down][up] (host-built filter bank,
  * transposed), y fp32 [n_out] with n_out = ceil(up * n / down).  absmax_bits (nullable, zeroed by the caller) receives
- * the bit pattern of max |y| (inference.py:147's peak search fused into the same pass). */
+ * the bit pattern of max |y| (inference.py:147's peak search fused into the same pass).
+ * tap_lo / tap_hi (nullable, int32 [up]): per-phase range [lo, hi) of taps whose weight is not negligible -- the Hann
+ * window is zero beyond +-lowpass_filter_width zero crossings, so ~2*width of the 2*width + down taps matter; the caller
+ * derives the ranges from the table (torchaudio multiplies through all of them). */
 int echo_resample_mono(const float* x, int channels, int64_t n, int64_t ldx, int down, int up, int width,
-                       const float* table_t, float* y, int64_t n_out, uint32_t* absmax_bits, echo_stream_t stream);
+                       const float* table_t, const int32_t* tap_lo, const int32_t* tap_hi, float* y, int64_t n_out,
+                       uint32_t* absmax_bits, echo_stream_t stream);
 /* inference.py:147: y /= max(peak, floor) with peak read from absmax_bits (floor = 1: never amplify) */
 int echo_peak_normalize(float* y, int64_t n, const uint32_t* absmax_bits, float floor_, echo_stream_t stream);
 
