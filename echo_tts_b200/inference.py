@@ -200,7 +200,7 @@ def sample_pipeline(model: EchoDiT, fish_ae, pca_state: PCAState, sample_fn: Sam
                     pad_to_max_speaker_latent_length: Optional[int] = None,
                     pad_to_max_text_length: Optional[int] = None, normalize_text: bool = False) -> Tuple[torch.Tensor, str]:
     """inference.py:346-400.  ``speaker_audio`` may also be a ``(speaker_latent, speaker_mask)`` tuple of already
-    encoded latents (extension: lets callers skip the not-yet-accelerated AE encode)."""
+    encoded latents (extension: lets callers reuse a speaker they have already encoded)."""
     MAX_SPK, MAX_TEXT = 6400, 768
     device, dtype = model.device, model.dtype
     ids, mask, norm_text = get_text_input_ids_and_mask(

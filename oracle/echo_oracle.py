@@ -706,3 +706,62 @@ def load_audio_post(samples: torch.Tensor, sample_rate: int) -> torch.Tensor:
     audio = samples.mean(dim=0).unsqueeze(0)
     audio = resample_sinc(audio, sample_rate, 44_100)
     return audio / torch.maximum(audio.abs().max(), torch.tensor(1.0))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# sample_pipeline (inference.py:346-400) and get_speaker_latent_and_mask (inference.py:250-309) composed from the
+# restatements above.  Pinned live against the upstream functions in tests/test_oracle_vs_reference.py.
+# ---------------------------------------------------------------------------------------------------------------------
+def speaker_latent_and_mask(asd: SD, acfg, pca, audio: torch.Tensor, max_speaker_latent_length: int = 6400,
+                            audio_chunk_size: int = 640 * 2048, pad_to_max: bool = False,
+                            divis_by_patch_size: Optional[int] = 4):
+    """inference.py:250-309: audio [1, n] -> (latent fp32 [1, T, 80], mask bool [1, T]); the S1-DAC hop of 2048 is
+    hard-coded upstream (:262), so this holds for the full-size autoencoder only."""
+    comp, mean, scale = pca
+    hop = 2048
+    assert audio.ndim == 2 and audio.shape[0] == 1
+    audio = audio[:, : max_speaker_latent_length * hop]
+    chunks = []
+    for i in range(0, audio.shape[1], audio_chunk_size):
+        c = audio[:, i:i + audio_chunk_size]
+        if c.shape[1] < audio_chunk_size:
+            c = F.pad(c, (0, audio_chunk_size - c.shape[1]))
+        chunks.append(ae_encode(asd, acfg, comp, mean, scale, c.unsqueeze(0)))
+    lat = torch.cat(chunks, dim=1)
+    actual = audio.shape[1] // hop
+    mask = (torch.arange(lat.shape[1]) < actual).unsqueeze(0)
+    if pad_to_max and lat.shape[1] < max_speaker_latent_length:
+        lat = F.pad(lat, (0, 0, 0, max_speaker_latent_length - lat.shape[1]))
+        mask = F.pad(mask, (0, max_speaker_latent_length - mask.shape[1]))
+    elif not pad_to_max:
+        lat, mask = lat[:, :actual], mask[:, :actual]
+    if divis_by_patch_size is not None:
+        n = lat.shape[1] // divis_by_patch_size * divis_by_patch_size
+        lat, mask = lat[:, :n], mask[:, :n]
+    return lat, mask
+
+
+def sample_pipeline(sd: SD, cfg, asd: SD, acfg, pca, sampler_kwargs: dict, text_prompt: str, speaker_audio, rng_seed: int,
+                    pad_to_max_speaker_latent_length: Optional[int] = None, pad_to_max_text_length: Optional[int] = None,
+                    normalize_text: bool = False, noise: Optional[torch.Tensor] = None, hop: int = 2048):
+    """inference.py:346-400 -> (audio fp32 [1, 1, crop * hop], normalised text, latent).  ``speaker_audio``: None (the
+    zero speaker of :377-383), a waveform [1, n], or an already encoded (latent, mask) pair.  The text is ALWAYS padded to
+    max_length = min(pad_to_max_text_length or 768, 768): get_text_input_ids_and_mask allocates max_length columns and its
+    ``pad_to_max=False`` slice ``[:, :max_length]`` is a no-op (:209-210).  ``hop`` = samples per latent (2048 upstream,
+    hard-coded in the crop :337)."""
+    max_len = min(pad_to_max_text_length or 768, 768)
+    ids, mask, texts = text_ids_and_mask([text_prompt], max_len, normalize=normalize_text)
+    if speaker_audio is None:
+        n = pad_to_max_speaker_latent_length or 4
+        spk, smask = torch.zeros((1, n, 80)), torch.zeros((1, n), dtype=torch.bool)
+    elif isinstance(speaker_audio, tuple):
+        spk, smask = speaker_audio
+    else:
+        spk, smask = speaker_latent_and_mask(asd, acfg, pca, speaker_audio,
+                                             max_speaker_latent_length=pad_to_max_speaker_latent_length or 6400,
+                                             pad_to_max=(pad_to_max_speaker_latent_length is not None))
+    latent = sample_euler_cfg_independent_guidances(sd, cfg, spk, smask, ids, mask, rng_seed, noise=noise, **sampler_kwargs)
+    comp, mean, scale = pca
+    audio = ae_decode(asd, acfg, comp, mean, scale, latent)
+    crop = find_flattening_point(latent[0])
+    return audio[..., : crop * hop], texts[0], latent

@@ -304,3 +304,39 @@ def test_full_size_decode_is_causal():
     head = ae_decode(ae, pca, z[:, :320].cuda())
     assert rel_l2(head.cpu(), wav[..., : 320 * 2048].cpu()) < 1e-3
     assert int(find_flattening_point(z[0].cuda())) == O.find_flattening_point(z[0]) == 400
+
+
+@pytest.mark.parametrize("speaker,pad_text,pad_spk,normalize", [(None, None, None, True), (None, 64, 8, False),
+                                                                ("latent", 96, None, True)])
+def test_sample_pipeline_vs_oracle(tiny_model, speaker, pad_text, pad_spk, normalize):
+    """sample_pipeline (inference.py:346-400) through the public API -- tokenise, zero speaker / given speaker latent,
+    sampler, ae_decode, flattening-point crop -- against the oracle's composition (itself pinned live against the upstream
+    function, tests/test_oracle_vs_reference.py::test_sample_pipeline_live) with the same injected x_T."""
+    from functools import partial
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, sample_pipeline, PCAState
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    cfg, acfg = S.ECHO_TINY, S.AE_TINY
+    sd, asd = S.synth_state_dict(S.dit_schema(cfg)), S.synth_ae_state_dict(acfg)
+    ae = load_fish_ae_from_state_dict(asd, cfg=acfg)
+    comp, mean, scale = O.synth_pca(latent_dim=acfg.latent_dim)
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    kw = dict(num_steps=4, cfg_scale_text=3.0, cfg_scale_speaker=8.0, cfg_min_t=0.5, cfg_max_t=1.0, truncation_factor=0.9,
+              rescale_k=None, rescale_sigma=None, speaker_kv_scale=None, speaker_kv_max_layers=None,
+              speaker_kv_min_t=None, sequence_length=24)
+    g = torch.Generator().manual_seed(5)
+    noise = torch.randn(1, 24, 80, generator=g)
+    spk = None
+    if speaker == "latent":
+        spk = (torch.randn(1, 16, 80, generator=g), torch.ones(1, 16, dtype=torch.bool))
+    text = "Pipeline: parity — check…"
+    audio, ntext = sample_pipeline(tiny_model, ae, pca, partial(sample, _noise=noise, **kw), text,
+                                   None if spk is None else (spk[0].cuda(), spk[1].cuda()), 3,
+                                   pad_to_max_speaker_latent_length=pad_spk, pad_to_max_text_length=pad_text,
+                                   normalize_text=normalize)
+    ref, rtext, _ = O.sample_pipeline(sd, cfg, asd, acfg, (comp, mean, scale), kw, text, spk, 3,
+                                      pad_to_max_speaker_latent_length=pad_spk, pad_to_max_text_length=pad_text,
+                                      normalize_text=normalize, noise=noise)
+    assert ntext == rtext                                  # text handling bit-exact
+    assert audio.shape == ref.shape                        # same crop index
+    assert rel_l2(audio.cpu(), ref) < 3e-2                 # decode of a latent that is itself within 2e-2

@@ -97,3 +97,34 @@ def test_ae_encode_live(ns):
         assert torch.equal(o["codes"], r["codes"])
         for k in ("z_enc", "z_pre", "z_q"):
             assert o[k].shape == r[k].shape and rel_l2(o[k], r[k].float()) < 1e-5
+
+
+def test_sample_pipeline_live(ns, tiny):
+    """inference.py:346-400 end to end (tokenise -> zero speaker -> sampler -> ae_decode -> flattening-point crop) on the
+    tiny DiT + tiny S1-DAC: upstream function vs the oracle's composition, same injected x_T."""
+    from functools import partial
+    cfg, sd, ref = tiny
+    acfg = S.AE_TINY
+    asd = S.synth_ae_state_dict(acfg, encode=True)
+    ae = ref_import.build_ae_cfg(ns, acfg, asd)
+    comp, mean, scale = O.synth_pca(latent_dim=acfg.latent_dim)
+    pca = ns.inference.PCAState(pca_components=comp, pca_mean=mean, latent_scale=scale)
+    kw = dict(num_steps=4, cfg_scale_text=3.0, cfg_scale_speaker=8.0, cfg_min_t=0.5, cfg_max_t=1.0, truncation_factor=0.9,
+              rescale_k=None, rescale_sigma=None, speaker_kv_scale=None, speaker_kv_max_layers=None,
+              speaker_kv_min_t=None, sequence_length=24)
+    noise = torch.randn(1, 24, 80, generator=torch.Generator().manual_seed(5))
+    for text, pad_text, pad_spk, normalize in (("Pipeline live pin.", None, None, True), ("[S1] padded: yes", 64, 8, False)):
+        real_randn = torch.randn
+        torch.randn = lambda *a, **k: noise.clone()
+        try:
+            audio_r, text_r = ns.inference.sample_pipeline(
+                ref, ae, pca, partial(ns.inference.sample_euler_cfg_independent_guidances, **kw), text, None, 3,
+                pad_to_max_speaker_latent_length=pad_spk, pad_to_max_text_length=pad_text, normalize_text=normalize)
+        finally:
+            torch.randn = real_randn
+        audio_o, text_o, _ = O.sample_pipeline(sd, cfg, asd, acfg, (comp, mean, scale), kw, text, None, 3,
+                                               pad_to_max_speaker_latent_length=pad_spk, pad_to_max_text_length=pad_text,
+                                               normalize_text=normalize, noise=noise)
+        assert text_o == text_r
+        assert audio_o.shape == audio_r.shape
+        assert rel_l2(audio_o, audio_r.float()) < 1e-4
