@@ -155,8 +155,15 @@ def ae_reconstruct(fish_ae, pca_state: PCAState, audio: torch.Tensor) -> torch.T
 @torch.inference_mode()
 def get_speaker_latent_and_mask(fish_ae, pca_state: PCAState, audio: torch.Tensor, max_speaker_latent_length: int = 6400,
                                 audio_chunk_size: int = 640 * 2048, pad_to_max: bool = False,
-                                divis_by_patch_size: Optional[int] = 4) -> Tuple[torch.Tensor, torch.Tensor]:
-    """inference.py:250-309 (chunked encode, mask, pad/trim, multiple-of-patch trim) -- length logic bit-exact."""
+                                divis_by_patch_size: Optional[int] = 4, *, _encode_padding: bool = False
+                                ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """inference.py:250-309 (chunked encode, mask, pad/trim, multiple-of-patch trim) -- length logic bit-exact.
+
+    The reference pads the last chunk to 30 s of audio before encoding it (:268-271) and, unless ``pad_to_max``, throws the
+    frames of the padding away again (:289-291).  The S1-DAC encoder is causal end to end (convolutions, window-limited
+    transformers, downsampling), so the kept frames do not depend on the padding: without ``pad_to_max`` only the real
+    samples (rounded up to a whole frame) are encoded -- a 10 s clip costs a third of the 30 s the reference encodes,
+    with identical latents (``tests/test_gpu_encode.py::test_speaker_clip_trimmed_encode_equals_padded``)."""
     hop = 2048
     assert audio.ndim == 2 and audio.shape[0] == 1
     audio = audio[:, : max_speaker_latent_length * hop]
@@ -164,7 +171,8 @@ def get_speaker_latent_and_mask(fish_ae, pca_state: PCAState, audio: torch.Tenso
     for i in range(0, audio.shape[1], audio_chunk_size):
         c = audio[:, i:i + audio_chunk_size]
         if c.shape[1] < audio_chunk_size:
-            c = torch.nn.functional.pad(c, (0, audio_chunk_size - c.shape[1]))
+            keep = audio_chunk_size if (pad_to_max or _encode_padding) else -(-c.shape[1] // hop) * hop
+            c = torch.nn.functional.pad(c, (0, keep - c.shape[1]))
         chunks.append(ae_encode(fish_ae, pca_state, c.unsqueeze(0)))
     lat = torch.cat(chunks, dim=1)
     actual = audio.shape[1] // hop

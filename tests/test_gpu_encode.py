@@ -135,3 +135,20 @@ def test_speaker_latent_pipeline_vs_oracle(tiny):
     # frames whose codes all agree must agree closely; the rest are near-tie flips (bounded fraction)
     err = (lat.cpu() - want).norm(dim=-1) / want.norm(dim=-1).clamp_min(1e-6)
     assert (err < 1e-3).float().mean().item() > 0.7
+
+
+def test_speaker_clip_trimmed_encode_equals_padded():
+    """get_speaker_latent_and_mask (inference.py:250-309) at the full-size S1-DAC: encoding only the real samples of a
+    short clip gives the latents the reference's pad-to-30-s-then-trim procedure gives (the encoder is causal)."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, get_speaker_latent_and_mask, PCAState
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE, encode=True))
+    comp, mean, scale = O.synth_pca()
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    g = torch.Generator().manual_seed(12)
+    for n in (2048 * 37 + 500, 2048 * 8, 640 * 2048 + 2048 * 5 + 17):        # ragged, exact frames, two chunks
+        audio = ((torch.rand(1, n, generator=g) * 2 - 1) * 0.7).cuda()
+        lat, mask = get_speaker_latent_and_mask(ae, pca, audio)
+        lat_ref, mask_ref = get_speaker_latent_and_mask(ae, pca, audio, _encode_padding=True)
+        assert lat.shape == lat_ref.shape == (1, n // 2048 // 4 * 4, 80) and torch.equal(mask, mask_ref)
+        assert torch.equal(lat, lat_ref)
