@@ -225,6 +225,10 @@ def sample_pipeline(model: EchoDiT, fish_ae, pca_state: PCAState, sample_fn: Sam
             max_speaker_latent_length=pad_to_max_speaker_latent_length or MAX_SPK,
             pad_to_max=(pad_to_max_speaker_latent_length is not None))
     latent = sample_fn(model, spk, smask, ids, mask, rng_seed)
-    audio = ae_decode(fish_ae, pca_state, latent)
-    audio = crop_audio_to_flattening_point(audio, latent[0])
-    return audio, norm_text[0]
+    # inference.py:395-397 decodes every latent and then cuts the waveform at the flattening point; the decoder is causal,
+    # so the kept samples depend on the kept latents only: find the point first (it is a function of the latent) and
+    # decode just that prefix
+    crop = find_flattening_point(latent[0])
+    if crop == 0:
+        return torch.zeros((latent.shape[0], 1, 0), device=latent.device, dtype=torch.float32), norm_text[0]
+    return ae_decode(fish_ae, pca_state, latent[:, :crop]), norm_text[0]

@@ -340,3 +340,22 @@ def test_sample_pipeline_vs_oracle(tiny_model, speaker, pad_text, pad_spk, norma
     assert ntext == rtext                                  # text handling bit-exact
     assert audio.shape == ref.shape                        # same crop index
     assert rel_l2(audio.cpu(), ref) < 3e-2                 # decode of a latent that is itself within 2e-2
+
+
+def test_sample_pipeline_decodes_only_the_kept_prefix(tiny_model):
+    """A latent that flattens out early: the pipeline's audio (prefix decode) equals decode-everything-then-crop
+    (inference.py:395-397) -- S1-DAC decode is causal."""
+    from oracle import echo_oracle as O
+    from echo_tts_b200.inference import load_fish_ae_from_state_dict, sample_pipeline, ae_decode, PCAState
+    acfg = S.AE_TINY
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(acfg), cfg=acfg)
+    comp, mean, scale = O.synth_pca(latent_dim=acfg.latent_dim)
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    g = torch.Generator().manual_seed(2)
+    for flat_from in (13, 0):
+        lat = torch.cat([torch.randn(1, flat_from, 80, generator=g), 0.01 * torch.randn(1, 40 - flat_from, 80, generator=g)], 1).cuda()
+        audio, _ = sample_pipeline(tiny_model, ae, pca, lambda *a: lat, "x", None, 0)
+        full = ae_decode(ae, pca, lat)
+        assert audio.shape == (1, 1, flat_from * acfg.hop)
+        if flat_from:
+            assert rel_l2(audio, full[..., : audio.shape[-1]]) < 2e-3
