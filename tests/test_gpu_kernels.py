@@ -251,3 +251,23 @@ def test_gemm_narrow_tail_matches_plain_schedule(ops, M, N, K, monkeypatch):
     for x, y in zip(res["1"], res["0"]):
         assert torch.equal(x, y)
     assert rel_l2(res["1"][0], a.float() @ w.float().t() + bias) < 2e-5
+
+
+def test_gemm_narrow_tail_with_batches_and_taps(ops, monkeypatch):
+    """Narrow tail on a batched implicit-GEMM conv (6 row tiles x 4 column tiles x 4 batch entries = 96 tiles -> 74 + 22
+    -> 44 half-width tiles): tile -> (row tile, column tile, batch) decoding of the half tiles, bit-identical to the plain
+    schedule and equal to the fp32 conv."""
+    B, T, C, N, dil = 4, 1500, 128, 1024, 3
+    x = _rand((B, T, C), 71, dtype=BF16)
+    w = _rand((N, C, 7), 72, (C * 7) ** -0.5, BF16)
+    wp = w.permute(0, 2, 1).reshape(N, 7 * C).contiguous()
+    outs = {}
+    for tail in ("1", "0"):
+        monkeypatch.setenv("ECHO_GEMM_TAIL", tail)
+        out = torch.full((B * T, N), float("nan"), device="cuda", dtype=F32)
+        ops.gemm_generic(x.view(B * T, C), wp, taps=tuple(-(6 - k) * dil for k in range(7)), batch=B, out_f32=out, impl=2)
+        outs[tail] = out
+    assert torch.equal(outs["1"], outs["0"])
+    xin = torch.nn.functional.pad(x.float().transpose(1, 2), (6 * dil, 0))
+    ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil).transpose(1, 2).reshape(B * T, N)
+    assert rel_l2(outs["1"], ref) < 2e-5
