@@ -39,10 +39,12 @@ constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCR
 // optional in-kernel timeline (32 clock64 slots per CTA), enabled with echo_debug_gemm_trace(ptr)
 static long long* g_trace_ptr = nullptr;
 static int g_debug_noload = 0;   // debug: MMAs re-use whatever is in the ring (no TMA after the first fill): isolates MMA issue rate
+static int g_debug_skip = 0;     // debug (timing only, results garbage): 1 = never load A, 2 = never load B
 
 struct Tiling {
   long long* trace;       // nullptr unless tracing: [cta][32] SM-clock stamps
   int noload;             // debug only
+  int skip;               // debug only: operand whose loads are left out (1 = A, 2 = B)
   int stages, stage_bytes; // operand ring: stage = A (16 KB) + this CTA's half of B (bn/2 rows x 128 B)
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
@@ -271,10 +273,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
           uint8_t* sa = smem + s * STAGE_SZ;
           uint8_t* sb = sa + A_BYTES;
-          if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], stage_tx);
+          const uint32_t tx = T.skip == 1 ? 2u * (uint32_t)(half_u * BK * 2) : T.skip == 2 ? 2u * (uint32_t)A_BYTES : stage_tx;
+          if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], tx);
           const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
-          ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
-          ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
+          if (T.skip != 1) ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
+          if (T.skip != 2) ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
           if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
@@ -476,6 +479,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   Tiling T;
   T.trace = g_trace_ptr;
   T.noload = g_debug_noload;
+  T.skip = g_debug_skip;
   T.bn = bn;
   T.stage_bytes = A_BYTES + (bn / 2) * BK * 2;
   T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
@@ -515,6 +519,8 @@ extern "C" void echo_debug_gemm_trace(long long* device_buf) {
   g_trace_ptr = device_buf;
   const char* e = getenv("ECHO_GEMM_NOLOAD");    // results are garbage in this mode; timing experiments only
   g_debug_noload = (device_buf && e && e[0] == '1') ? 1 : 0;
+  const char* k = getenv("ECHO_GEMM_SKIP");      // "A" / "B": leave that operand's loads out (timing experiments only)
+  g_debug_skip = (device_buf && k) ? (k[0] == 'A' ? 1 : k[0] == 'B' ? 2 : 0) : 0;
 }
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)

@@ -101,7 +101,9 @@ long long echo_gemm_workspace_bytes(void);
 /* Debug aid (no reference counterpart): while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every
  * impl-2 GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles
  * done, [7] exit, and for its first six tiles t: [8+4t] accumulator stage free, [9+4t] MMAs issued, [10+4t]
- * accumulator ready, [11+4t] epilogue done.  Pass NULL to switch it off. */
+ * accumulator ready, [11+4t] epilogue done.  Pass NULL to switch it off.  While tracing, the environment variables
+ * ECHO_GEMM_NOLOAD=1 (no TMA after the first ring fill) and ECHO_GEMM_SKIP=A|B (that operand is never loaded) turn the
+ * launch into a timing experiment (results are garbage): they separate the MMA rate from each operand's feed. */
 void echo_debug_gemm_trace(long long* device_buf);
 
 /* ------------------------------------------------------------------------------------------
