@@ -216,7 +216,9 @@ def gemm_roofline(model, pk):
     return dict(bound="tensor", kernel="gemm_pair_kernel<SWIGLU> (tcgen05 cta_group::2, 256x256 tiles) M=1920 N=11776 K=2048",
                 achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=61.35e6,
                 traffic_unit="bytes/launch (ncu dram read+write)", flop_per_launch=flops,
-                peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6)
+                peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6,
+                note="main loop is shared-memory-bandwidth bound: 669 clk per 64-wide k-block = 80 KB of operand reads + TMA "
+                     "writes per SM at 120 of 128 B/clk; MMAs alone 491 clk (DESIGN.md section 4, tools/gemm_trace.py)")
 
 
 def config5_streaming(model, ae, pca, dev, reps=3):
