@@ -21,7 +21,12 @@ constexpr int EPI_GENERIC_LEAN = 3;               // per-warp scratch: 32 rows x
 
 // The scratch is addressed in the shared state space explicitly: through a generic pointer the compiler emits
 // generic LD/ST (address translation, long-scoreboard latency) instead of LDS/STS.
+// -DECHO_DEBUG_EPI_NOSMEM (timing experiments only, results garbage): the transpose leaves shared memory alone, which
+// shows how much of the main loop's shared-memory bandwidth the overlapped epilogues take.
 __device__ __forceinline__ void sc_store_row(float* sc, int lane, const float* v) {
+#ifdef ECHO_DEBUG_EPI_NOSMEM
+  return;
+#endif
   const uint32_t row = smem_u32(sc) + (uint32_t)lane * 128u;
 #pragma unroll
   for (int k = 0; k < 8; ++k)
@@ -32,6 +37,10 @@ __device__ __forceinline__ void sc_store_row(float* sc, int lane, const float* v
 }
 __device__ __forceinline__ float4 sc_load4(const float* sc, int row, int cg) {
   float4 x;
+#ifdef ECHO_DEBUG_EPI_NOSMEM
+  x = make_float4((float)row, (float)cg, 0.f, 0.f);
+  return x;
+#endif
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w)
                : "r"(smem_u32(sc) + (uint32_t)(row * 128 + ((cg ^ (row & 7)) << 4)))
