@@ -359,3 +359,28 @@ def test_sample_pipeline_decodes_only_the_kept_prefix(tiny_model):
         assert audio.shape == (1, 1, flat_from * acfg.hop)
         if flat_from:
             assert rel_l2(audio, full[..., : audio.shape[-1]]) < 2e-3
+
+
+@pytest.mark.slow
+def test_config4_full_size_long_reference_properties(base_model):
+    """BASELINE configs[3] shape (5-minute speaker reference = 6400 latents = 1600 cached speaker keys, Force Speaker
+    speaker_kv_scale 1.5 over 24 layers until t < 0.9), two prompts, 10 steps.  (1) The speaker encoder is causal and
+    masked keys cannot matter: a 3000-latent reference padded to 6400 (mask False) == the same reference unpadded.
+    (2) Prompts are independent: row 0 of the batch == the single-prompt run.  (3) Replay determinism."""
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    kw = dict(FULL_KW, num_steps=10, speaker_kv_scale=1.5, speaker_kv_max_layers=24, speaker_kv_min_t=0.9)
+    ids, mask, _, _ = [t.cuda() for t in _full_inputs(B=2)]
+    g = torch.Generator().manual_seed(23)
+    spk = torch.randn(2, 6400, 80, generator=g)
+    smask = torch.ones(2, 6400, dtype=torch.bool)
+    smask[1, 3000:] = False
+    spk[1, 3000:] = 0.0                                   # what get_speaker_latent_and_mask pads with (inference.py:287)
+    noise = torch.randn(2, 640, 80, generator=g)
+    both = sample(base_model, spk.cuda(), smask.cuda(), ids, mask, 0, _noise=noise, **kw).cpu()
+    assert both.shape == (2, 640, 80) and bool(torch.isfinite(both).all())
+    short = sample(base_model, spk[1:, :3000].cuda(), smask[1:, :3000].cuda(), ids[1:], mask[1:], 0, _noise=noise[1:], **kw).cpu()
+    assert rel_l2(short, both[1:]) < X_TOL
+    single = sample(base_model, spk[:1].cuda(), smask[:1].cuda(), ids[:1], mask[:1], 0, _noise=noise[:1], **kw).cpu()
+    assert rel_l2(single, both[:1]) < X_TOL
+    again = sample(base_model, spk.cuda(), smask.cuda(), ids, mask, 0, _noise=noise, **kw).cpu()
+    assert torch.equal(again, both)
