@@ -54,14 +54,9 @@ def peaks():
 
 
 def synth_inputs(B, seed=7):
-    g = torch.Generator().manual_seed(seed)
-    ids = torch.zeros((B, L_TEXT), dtype=torch.int32)
-    mask = torch.zeros((B, L_TEXT), dtype=torch.bool)
-    ids[:, 1:N_TEXT_VALID] = torch.randint(32, 127, (B, N_TEXT_VALID - 1), generator=g, dtype=torch.int32)
-    mask[:, :N_TEXT_VALID] = True
-    spk = torch.randn((B, T_SPK, 80), generator=g)
-    smask = torch.ones((B, T_SPK), dtype=torch.bool)
-    return ids, mask, spk, smask
+    """Synthetic request of the configs[1] shapes (shared with the parity tests and the fixture generators)."""
+    from echo_tts_b200 import schema as S
+    return S.synth_request(B, n_valid=N_TEXT_VALID, pad_to=L_TEXT, t_spk=T_SPK, seed=seed)
 
 
 class ClockSampler(threading.Thread):
@@ -94,33 +89,46 @@ class ClockSampler(threading.Thread):
 
 def cpu_reference_sample(threads=None, repeats=1):
     """Time the reference algorithm's CPU path (oracle port, fp32, all host threads) on a bounded sample of the
-    workload: ONE CFG forward of config 2 (3 rows x 640 latents, 768-padded text with 256 valid, 53 speaker
-    patches), then scale by algorithmic FLOPs to the whole generation."""
+    workload, as BASELINE.md section 5 lays out: the conditioning KV build, ONE three-branch CFG forward, ONE single
+    forward and the whole S1-DAC decode of 640 latents are each timed at the configs[1] shapes; a generation is
+    conditioning + 20 CFG forwards + 20 single forwards + decode (scaled by STEP COUNT only, never by FLOPs)."""
     from echo_tts_b200 import schema as S
     from oracle import echo_oracle as O
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
     cfg = S.ECHO_BASE
     sd = S.synth_state_dict(S.dit_schema(cfg, blockwise=False), init="torch")
+    asd = S.synth_ae_state_dict(S.AE_BASE)
+    comp, mean, scale = S.synth_pca()
     ids, mask, spk, smask = synth_inputs(1)
+    med = lambda ts: sorted(ts)[len(ts) // 2]
+
+    def clock(fn, n):
+        ts, out = [], None
+        for _ in range(n):
+            t0 = time.perf_counter()
+            out = fn()
+            ts.append(time.perf_counter() - t0)
+        return med(ts), out
     with torch.inference_mode():
-        kv_t = O.kv_cache_text(sd, cfg, ids, mask)
-        kv_s = O.kv_cache_speaker(sd, cfg, spk)
+        cond_s, (kv_t, kv_s) = clock(lambda: (O.kv_cache_text(sd, cfg, ids, mask), O.kv_cache_speaker(sd, cfg, spk)), 1)
         x = torch.randn(1, S_LAT, 80, generator=torch.Generator().manual_seed(1))
         tm3 = torch.cat([mask, torch.zeros_like(mask), mask], 0)
         sm3 = torch.cat([smask, smask, torch.zeros_like(smask)], 0)
         rep3 = lambda kv: [(torch.cat([k] * 3, 0), torch.cat([v] * 3, 0)) for k, v in kv]
         kv_t3, kv_s3 = rep3(kv_t), rep3(kv_s)
-        times = []
-        for _ in range(repeats):
-            t0 = time.perf_counter()
-            O.dit_forward(sd, cfg, torch.cat([x] * 3, 0), torch.ones(3) * 0.9, tm3, sm3, kv_t3, kv_s3)
-            times.append(time.perf_counter() - t0)
-    sec = sorted(times)[len(times) // 2]
-    gen_sec = sec * FLOP_GEN / FLOP_CFG
+        cfg_s, _ = clock(lambda: O.dit_forward(sd, cfg, torch.cat([x] * 3, 0), torch.ones(3) * 0.9, tm3, sm3, kv_t3, kv_s3), repeats)
+        plain_s, _ = clock(lambda: O.dit_forward(sd, cfg, x, torch.ones(1) * 0.4, mask, smask, kv_t, kv_s), repeats)
+        del sd, kv_t3, kv_s3
+        dec_s, _ = clock(lambda: O.ae_decode(asd, S.AE_BASE, comp, mean, scale, x), 1)
+    gen_sec = cond_s + 20 * cfg_s + 20 * plain_s + dec_s
     return dict(value=AUDIO_SEC_PER_PROMPT / gen_sec, unit="audio-sec/CPU-sec", cores=threads, kind="port",
-                sample=f"1 CFG forward (3x640 tokens, {FLOP_CFG / 1e12:.2f} TFLOP) in {sec:.2f} s, median of {repeats}; "
-                       f"scaled by FLOPs to the {FLOP_GEN / 1e12:.1f}-TFLOP generation"), sec
+                sample=f"configs[1] shapes, fp32, {threads} threads: conditioning {cond_s:.2f} s, one 3-branch CFG forward "
+                       f"{cfg_s:.2f} s, one single forward {plain_s:.2f} s (median of {repeats}), S1-DAC decode of 640 latents "
+                       f"{dec_s:.2f} s; generation = conditioning + 20 x CFG + 20 x single + decode = {gen_sec:.1f} s "
+                       f"(step-count scaling only)",
+                conditioning_s=cond_s, cfg_forward_s=cfg_s, plain_forward_s=plain_s, decode_s=dec_s,
+                generation_s=gen_sec), gen_sec
 
 
 def eager_gpu_port(reps=3):
@@ -136,7 +144,7 @@ def eager_gpu_port(reps=3):
     sd = {k: (v.cuda().to(bf) if v.is_floating_point() else v.cuda())
           for k, v in S.synth_state_dict(S.dit_schema(cfg, blockwise=False), init="torch").items()}
     asd = {k: v.cuda() for k, v in S.synth_ae_state_dict(S.AE_BASE).items()}
-    comp, mean, scale = [t.cuda() if torch.is_tensor(t) else t for t in O.synth_pca()]
+    comp, mean, scale = [t.cuda() if torch.is_tensor(t) else t for t in S.synth_pca()]
     ids, mask, spk, smask = [t.cuda() for t in synth_inputs(1)]
 
     def timed(fn):
@@ -176,7 +184,7 @@ def run_reference(args):
     cb, sec = cpu_reference_sample(repeats=max(1, min(args.steps, 3)))
     line = dict(metric="audio-sec generated per GPU-sec, 640-latent 40-step CFG", impl="reference", value=cb["value"],
                 unit="audio-sec/sec", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
-                ms_per_step=sec * FLOP_GEN / FLOP_CFG * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None,
+                ms_per_step=sec * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic", config=workload_config(1), cpu_baseline=cb,
                 e2e=dict(value=cb["value"], unit="audio-sec/sec", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
@@ -189,36 +197,95 @@ def workload_config(B):
                 prompts_per_gpu=B, l2="weights (5.6 GB bf16) exceed the 126 MB L2; no explicit flush")
 
 
-def gemm_roofline(model, pk):
-    """Dominant kernel: the CTA-pair tcgen05 GEMM (csrc/gemm2.cu).  Timed live with CUDA events on the launch stream over all 24 layers'
-    w1|w3 operands (24 x 48 MB > L2) at the CFG-step shape M=1920, N=11776, K=2048 (43 % of step FLOPs)."""
-    from echo_tts_b200 import ops
-    M, D, F2 = 3 * S_LAT, 2048, 2 * 5888
-    a = torch.randn((M, D), device="cuda").to(torch.bfloat16)
-    out = torch.empty((M, F2 // 2), device="cuda", dtype=torch.bfloat16)
-    for lw in model.layers[:3]:
-        ops.gemm_swiglu(a, lw["w13"], out)
+def _event_us(fn, n, warm=2):
+    """Mean microseconds of fn(i) over n back-to-back launches replayed from a CUDA graph (no Python / ctypes launch
+    overhead between kernels), CUDA events on the launch stream, after `warm` eager calls and one untimed replay."""
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        for i in range(n):
+            fn(i)
+    gr.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 3
     e0.record()
-    for _ in range(reps):
-        for lw in model.layers:
-            ops.gemm_swiglu(a, lw["w13"], out)
+    gr.replay()
     e1.record()
     torch.cuda.synchronize()
-    n = reps * len(model.layers)
-    sec = e0.elapsed_time(e1) / 1e3 / n
+    return e0.elapsed_time(e1) * 1e3 / n
+
+
+def roofline_traffic():
+    """`roofline.traffic`: dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, taken from the
+    committed `ncu --set full` capture named in profiles/roofline_traffic.json (written by tools/ncu_summary.py); null
+    when no capture of the current kernel is committed -- never a literal in this file."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if not os.path.isfile(p):
+        return None, None
+    d = json.load(open(p))
+    return d.get("bytes_per_launch"), d.get("source")
+
+
+def gemm_roofline(model, pk):
+    """Dominant kernel: the CTA-pair tcgen05 GEMM (csrc/gemm2.cu).  Timed live with CUDA events on the launch stream over all 24 layers'
+    w1|w3 operands (24 x 48 MB > L2) at the CFG-step shape M=1920, N=11776, K=2048 (43 % of step FLOPs).
+    `cublas_same_shape`: every projection of a decoder layer at both step shapes (M = 1920 guided, 640 un-guided) through
+    this library's kernel WITH its fused epilogue and through torch.matmul (cuBLAS, plain bf16 GEMM, no epilogue), same
+    event timing, each cycling the 24 layers' weights so operands stream from HBM."""
+    from echo_tts_b200 import ops, _lib as L
+    D, F, H = 2048, 5888, 16
+    layers = model.layers
+    nl = len(layers)
+    table = {}
+    for M in (3 * S_LAT, S_LAT):
+        R = M // S_LAT
+        xn = torch.randn((M, D), device="cuda").to(torch.bfloat16)
+        hm = torch.randn((M, F), device="cuda").to(torch.bfloat16)
+        x = torch.randn((M, D), device="cuda")
+        gate = torch.randn((R, D), device="cuda")
+        qkvg = torch.empty((4, M, D), device="cuda", dtype=torch.bfloat16)
+        hmid = torch.empty((M, F), device="cuda", dtype=torch.bfloat16)
+        ns = model.k_splits(M)
+        parts = torch.empty((ns, M, D), device="cuda") if ns > 1 else None
+
+        def resid(a, key):
+            if ns > 1:
+                return lambda i: ops.gemm_generic(a, layers[i % nl][key], gate=gate, rows_per_gate=S_LAT, split_out=parts)
+            return lambda i: ops.gemm_generic(a, layers[i % nl][key], gate=gate, rows_per_gate=S_LAT, resid=x, out_f32=x)
+        mine = dict(
+            qkvg=lambda i: ops.gemm_sections(xn, layers[i % nl]["qkvg"],
+                                             [(L.SEC_NORM_ROPE, qkvg[0], layers[i % nl]["qn"]), (L.SEC_NORM_ROPE, qkvg[1], layers[i % nl]["kn"]),
+                                              (L.SEC_PLAIN, qkvg[2], None), (L.SEC_SIGMOID, qkvg[3], None)],
+                                             head_dim=128, rope_heads=H // 2, rope=model.rope, rows_per_seq=S_LAT, eps=1e-5),
+            wo=resid(xn, "wo"), w13=lambda i: ops.gemm_swiglu(xn, layers[i % nl]["w13"], hmid), w2=resid(hm, "w2"))
+        shapes = dict(qkvg=(4 * D, D), wo=(D, D), w13=(2 * F, D), w2=(D, F))
+        for name, (N, K) in shapes.items():
+            a = hm if K == F else xn
+            out = torch.empty((M, N), device="cuda", dtype=torch.bfloat16)
+            us_mine = _event_us(mine[name], 2 * nl)
+            us_cublas = _event_us(lambda i: torch.matmul(a, layers[i % nl][name].t(), out=out), 2 * nl)
+            fl = 2.0 * M * N * K
+            table[f"{name}_m{M}"] = dict(m=M, n=N, k=K, us=us_mine, tflops=fl / us_mine / 1e6, cublas_us=us_cublas,
+                                         cublas_tflops=fl / us_cublas / 1e6, speed_vs_cublas=us_cublas / us_mine,
+                                         split_k=(ns if name in ("wo", "w2") else 1))
+    M, F2 = 3 * S_LAT, 2 * F
+    a = torch.randn((M, D), device="cuda").to(torch.bfloat16)
+    out = torch.empty((M, F), device="cuda", dtype=torch.bfloat16)
+    n = 3 * nl
+    sec = _event_us(lambda i: ops.gemm_swiglu(a, layers[i % nl]["w13"], out), n, warm=3) / 1e6
     flops = 2.0 * M * F2 * D
     ach = flops / sec / 1e12
-    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full` capture
-    # (profiles/r1_ncu_hot_kernels.md: 56.17 MB + 5.18 MB), per launch like `achieved`
+    traffic, src = roofline_traffic()
     return dict(bound="tensor", kernel="gemm_pair_kernel<SWIGLU> (tcgen05 cta_group::2, 256x256 tiles) M=1920 N=11776 K=2048",
-                achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=61.35e6,
-                traffic_unit="bytes/launch (ncu dram read+write)", flop_per_launch=flops,
-                peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6,
-                note="main loop is shared-memory-bandwidth bound: 669 clk per 64-wide k-block = 80 KB of operand reads + TMA "
-                     "writes per SM at 120 of 128 B/clk; MMAs alone 491 clk (DESIGN.md section 4, tools/gemm_trace.py)")
+                achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"], traffic=traffic,
+                traffic_unit="bytes/launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)", traffic_source=src,
+                flop_per_launch=flops, peak_source=pk["src"] + " burst", launches_timed=n, us_per_launch=sec * 1e6,
+                cublas_same_shape=table,
+                cublas_note="torch.matmul(a, w.t()) bf16 = cuBLAS plain GEMM writing bf16 [M, N]; this library's figure "
+                            "includes the fused epilogue (head RMSNorm + RoPE + sigmoid / SwiGLU / gated residual, split-K "
+                            "partials where split_k > 1)")
 
 
 def config5_streaming(model, ae, pca, dev, reps=3):
@@ -251,12 +318,112 @@ def config5_streaming(model, ae, pca, dev, reps=3):
     return rec
 
 
+def config3_batched(model, ae, pca, world, rank, local, total_prompts=64, per_forward=8):
+    """BASELINE.json configs[2]: 64 independent prompts x 640 latents x 40 steps (distinct texts with valid lengths in
+    [64, 512], distinct speaker references and seeds), dealt to the ranks in batches of 8 prompts per forward
+    by serving.run_sharded -- data-parallel, no data-path collective.  Device-timed (CUDA events around this rank's
+    batches, waveforms copied to the host inside the region), max over ranks."""
+    from echo_tts_b200 import schema as S, serving
+    from echo_tts_b200.inference import ae_decode, find_flattening_point
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    n_batches = total_prompts // per_forward
+    lens = torch.randint(64, 513, (total_prompts,), generator=torch.Generator().manual_seed(64)).tolist()
+
+    def make(bi):
+        ids, mask, spk, smask = S.synth_request(per_forward, n_valid=N_TEXT_VALID, pad_to=L_TEXT, t_spk=T_SPK, seed=1000 + bi)
+        for j in range(per_forward):
+            n = lens[bi * per_forward + j]
+            if n < N_TEXT_VALID:
+                ids[j, n:] = 0; mask[j, n:] = False
+            elif n > N_TEXT_VALID:
+                extra = torch.randint(32, 127, (n - N_TEXT_VALID,), generator=torch.Generator().manual_seed(7000 + bi * 8 + j),
+                                      dtype=torch.int32)
+                ids[j, N_TEXT_VALID:n] = extra; mask[j, :n] = True
+        return [t.pin_memory() for t in (ids, mask, spk, smask)]
+    batches = [make(bi) for bi in range(n_batches)]
+
+    def generate(item, bi):
+        ids, mask, spk, smask = [t.cuda(non_blocking=True) for t in item]
+        lat = sample(model, spk, smask, ids, mask, 500 + bi, **KW)
+        wav = ae_decode(ae, pca, lat).cpu()
+        return dict(batch=bi, samples=int(wav.shape[-1]) * per_forward,
+                    crop=[int(find_flattening_point(lat[j])) for j in range(per_forward)])
+    for i in range(3):                                                 # eager, capture, replay at the batch-8 shape
+        generate(batches[0], 0)
+    torch.cuda.synchronize()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res = serving.run_sharded(batches, generate)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = serving.max_over_ranks_ms(e0.elapsed_time(e1), torch.device("cuda", local))
+    if rank != 0:
+        return None
+    audio = total_prompts * AUDIO_SEC_PER_PROMPT
+    return dict(value=audio / (ms / 1e3), unit="audio-sec/sec", ms=ms, prompts=total_prompts, prompts_per_forward=per_forward,
+                batches_per_rank=[len(serving.shard_indices(n_batches, r, world)) for r in range(world)],
+                samples_out=sum(r["samples"] for r in res), flop=total_prompts * FLOP_GEN,
+                tflops=total_prompts * FLOP_GEN / (ms / 1e3) / 1e12,
+                what="BASELINE.json configs[2]: 64 prompts x 640 latents x 40 steps dealt round-robin in batches of 8 "
+                     "(serving.run_sharded), no data-path collective; CUDA events around each rank's batches incl. the "
+                     "waveform D2H, max over ranks")
+
+
+def cfg_split_record(model, world, rank, local, reps=3):
+    """Optional CFG-branch split (BASELINE configs[2] note): ranks 0..2 evaluate one guidance branch each and
+    exchange the branch velocities once per guided step -- NCCL all-gather, or the fused NVLink peer-store exchange.  ms per
+    clip (sampler only, configs[1] request) for both exchanges and for the single-GPU graph, max over the three ranks."""
+    import torch.distributed as dist
+    from echo_tts_b200 import serving
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    group = dist.new_group([0, 1, 2])
+    if rank >= 3:
+        return None
+    ids, mask, spk, smask = [t.cuda() for t in synth_inputs(1)]
+    noise = torch.randn(1, S_LAT, 80, generator=torch.Generator().manual_seed(3))
+    dev = torch.device("cuda", local)
+
+    def timed(fn):
+        for _ in range(3):                                             # eager, capture, replay
+            out = fn()
+        torch.cuda.synchronize(); dist.barrier(group)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            out = fn()
+        e1.record()
+        torch.cuda.synchronize(); dist.barrier(group)
+        return out, serving.max_over_ranks_ms(e0.elapsed_time(e1) / reps, dev, group)
+    rec = {}
+    outs = {}
+    for ex in ("nccl", "p2p"):
+        try:
+            outs[ex], rec[f"ms_{ex}"] = timed(lambda: serving.sample_euler_cfg_split(model, spk, smask, ids, mask, 0, group=group,
+                                                                                     exchange=ex, _noise=noise, **KW))
+        except Exception as e:                                         # a latency option must never cost the bench line
+            rec[f"error_{ex}"] = f"{type(e).__name__}: {e}"[:300]
+    single, rec["ms_single_gpu_graph"] = timed(lambda: sample(model, spk, smask, ids, mask, 0, _noise=noise, **KW))
+    if "nccl" in outs:
+        gathered = [torch.empty_like(single) for _ in range(3)]
+        dist.all_gather(gathered, outs["nccl"].contiguous(), group=group)
+        rec["ranks_bit_identical"] = all(torch.equal(gathered[0], g) for g in gathered[1:])
+        rec["rel_l2_vs_single_gpu"] = float((outs["nccl"] - single).norm() / single.norm())
+        if "p2p" in outs:
+            rec["p2p_equals_nccl"] = bool(torch.equal(outs["p2p"], outs["nccl"]))
+    rec["what"] = ("serving.sample_euler_cfg_split on ranks 0-2: one branch per GPU on guided steps, one exchange of [1,640,80] "
+                   "fp32 velocities per guided step (nccl = all-gather; p2p = tail kernel stores into peers' symmetric buffers), "
+                   "combine + Euler redundantly on every rank; sampler only, ms per clip, max over the three ranks")
+    return rec if rank == 0 else None
+
+
 def run_gpu(args):
     from echo_tts_b200 import schema as S, _lib
     from echo_tts_b200.inference import (load_model_from_state_dict, load_fish_ae_from_state_dict, ae_decode, PCAState,
                                          find_flattening_point)
     from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
-    from oracle import echo_oracle as O   # only synth_pca() (synthetic PCA constants) and the cpu_baseline leg
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -269,7 +436,7 @@ def run_gpu(args):
     t0 = time.time()
     model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=True), init="torch"))
     ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE, encode=True))
-    comp, mean, scale = O.synth_pca()
+    comp, mean, scale = S.synth_pca()
     pca = PCAState(comp.cuda(), mean.cuda(), scale)
     load_s = time.time() - t0
     ids, mask, spk, smask = synth_inputs(B, seed=7 + rank)
@@ -326,6 +493,13 @@ def run_gpu(args):
     ev[0].record(); lat = sample(model, dev[2], dev[3], dev[0], dev[1], 5, **KW); ev[1].record()
     ae_decode(ae, pca, lat); ev[2].record(); torch.cuda.synchronize()
     sampler_ms, decode_ms = ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])
+    c3 = config3_batched(model, ae, pca, world, rank, local) if (B == 1 and not args.no_config3) else None
+    split = None
+    if world >= 3 and B == 1 and not args.no_cfg_split:
+        try:
+            split = cfg_split_record(model, world, rank, local)
+        except Exception as e:
+            split = dict(error=f"{type(e).__name__}: {e}"[:300]) if rank == 0 else None
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
@@ -394,6 +568,10 @@ def run_gpu(args):
                 load_seconds=load_s)
     if c5 is not None:
         line["config5_streaming"] = c5
+    if c3 is not None:
+        line["config3"] = c3
+    if split is not None:
+        line["cfg_split"] = split
     if world == 1 and B == 1 and not args.no_eager_gpu:
         del model, ae
         torch.cuda.empty_cache()
@@ -403,7 +581,7 @@ def run_gpu(args):
         except Exception as e:                                         # a baseline must never cost the bench line
             line["eager_torch_gpu"] = dict(error=f"{type(e).__name__}: {e}"[:300])
         model = ae = None
-    if not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline:      # rank 0 at N = 1 only (the contract)
         del model, ae
         torch.cuda.empty_cache()
         line["cpu_baseline"], _ = cpu_reference_sample()
@@ -420,6 +598,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-eager-gpu", action="store_true", help="skip the torch-eager-on-B200 baseline record")
     ap.add_argument("--no-config5", action="store_true", help="skip the BASELINE configs[4] streaming record")
+    ap.add_argument("--no-config3", action="store_true", help="skip the BASELINE configs[2] record (64 prompts, 8 per forward)")
+    ap.add_argument("--no-cfg-split", action="store_true", help="skip the CFG-branch split record (needs >= 3 GPUs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

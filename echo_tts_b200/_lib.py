@@ -123,6 +123,7 @@ class TailDesc(C.Structure):
         ("eps", f32), ("cfg_text", f32), ("cfg_speaker", f32), ("rescale_k", f32), ("rescale_sigma", f32),
         ("use_rescale", i32), ("update_x", i32), ("n_delta", i32), ("delta", c_p), ("delta_stride", i64),
         ("v_peer", c_p * 2), ("flag_peer", c_p * 2), ("wait_flag", c_p * 2), ("wait_value", i32), ("_pad_tail", i32),
+        ("guidance", c_p),
     ]
 
 
@@ -163,8 +164,8 @@ EXPORTS = {
     "echo_reset_launch_count": (None, []),
     "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
     "echo_gemm_workspace_bytes": (C.c_longlong, []),
-    "echo_debug_gemm_trace": (None, [c_p]),
-    "echo_debug_attn_trace": (None, [c_p]),
+    "echo_debug_gemm_trace": (C.c_int, [c_p]),
+    "echo_debug_attn_trace": (C.c_int, [c_p]),
     "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),
     "echo_timestep_embedding": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p]),
     "echo_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, C.c_int, c_p, i64, c_p, i64, c_p]),

@@ -35,7 +35,11 @@ struct AttnSeg {
   const float* kv_scale;
 };
 struct AttnParams {
-  long long* trace;      // nullptr unless tracing: [cta][64] clock64 stamps
+#ifdef ECHO_DEBUG
+  long long* trace;      // nullptr unless tracing: [cta][64] clock64 stamps (debug builds only)
+#else
+  static constexpr long long* trace = nullptr;
+#endif
   int rows, seq, heads, n_seg;
   int static_first;      // segment 0 has no mask / extent and len > 0: tile 0 is known before the tile list is built
   float softmax_scale;
@@ -113,7 +117,9 @@ __device__ __forceinline__ void tma_store_commit_wait() {
 }
 
 struct Maps { CUtensorMap q, k[4], v[4], gate, out; };
+#ifdef ECHO_DEBUG
 static long long* g_attn_trace = nullptr;   // debug timeline, see echo_debug_attn_trace
+#endif
 
 __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_constant__ Maps M,
                                                               const __grid_constant__ AttnParams A) {
@@ -138,7 +144,11 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * QT, head = blockIdx.y, row = blockIdx.z;
+#ifdef ECHO_DEBUG
   long long* const trace = A.trace ? A.trace + ((long long)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 64 : nullptr;
+#else
+  constexpr long long* trace = nullptr;
+#endif
   if (trace && tid == 0) trace[0] = clock64();
   pdl_launch_dependents();
 
@@ -490,7 +500,16 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
 // Debug aid: >= 64 int64 per CTA; [0] start, [1] setup done, per tile j < 12: [4+4j] S(j) ready, [5+4j] PV(j-1) done,
 // [6+4j] P(j) published, [7+4j] PV(j) issued (MMA lane); [2] warp 0 past the PDL wait, [3] tile list built,
 // [60] last PV done (+ gate tile landed), [61] epilogue done, [62] exit, [63] #tiles.
-extern "C" void echo_debug_attn_trace(long long* device_buf) { g_attn_trace = device_buf; }
+extern "C" int echo_debug_attn_trace(long long* device_buf) {
+#ifdef ECHO_DEBUG
+  g_attn_trace = device_buf;
+  return ECHO_OK;
+#else
+  if (!device_buf) return ECHO_OK;
+  echo_set_error("echo_debug_attn_trace: this library was built without -DECHO_DEBUG (make -C echo_tts_b200/csrc DEBUG=1)");
+  return ECHO_ERR_UNSUPPORTED;
+#endif
+}
 
 // Returns ECHO_ERR_UNSUPPORTED (without setting an error) when the descriptor is outside this kernel's domain so
 // that echo_attention() can fall back to the generic mma.sync kernel (causal / windowed / head_dim 64 encoders).
@@ -529,7 +548,9 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
       M.gate = M.out;
     }
   }
+#ifdef ECHO_DEBUG
   A.trace = g_attn_trace;
+#endif
   A.static_first = (d->n_seg > 0 && d->seg[0].len > 0 && !d->seg[0].mask && !d->seg[0].extent) ? 1 : 0;
   A.rows = d->rows; A.seq = d->seq; A.heads = d->heads; A.n_seg = d->n_seg;
   A.softmax_scale = d->softmax_scale;

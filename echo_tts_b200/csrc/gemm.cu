@@ -1,110 +1,11 @@
-// bf16 GEMM / implicit causal conv for sm_100a.
-//   impl 0: TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> shared memory ring -> tcgen05.mma (one issuing
-//           thread, fp32 accumulator in TMEM) -> tcgen05.ld epilogue.  Warp roles: 0 = TMA producer,
-//           1 = TMEM owner + MMA issuer, 2..5 = epilogue (one TMEM lane quarter each).
-//   impl 1: legacy mma.sync.m16n8k16 kernel (same epilogues) kept as A/B baseline.
+// bf16 GEMM / implicit causal conv for sm_100a -- host side of the one GEMM kernel of this library, the CTA-pair
+// tcgen05 kernel of gemm2.cu: argument checking, descriptor -> kernel parameters, tile-width choice, tensor maps.
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 #include "gemm_epilogue.cuh"
 
-
 constexpr int BM = 128;
 constexpr int BK = 64;
-
-template <int BN>
-struct TcCfg {
-  static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
-  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-};
-
-struct TmemLoader {
-  uint32_t taddr;
-  __device__ __forceinline__ void load32(int col, float* v) { ptx::tmem_ld32(taddr + (uint32_t)col, v); }
-};
-
-template <int BN, int EPI>
-__global__ void __launch_bounds__(192, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                    const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P) {
-  using C = TcCfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + C::STAGES;
-  uint64_t* tmem_full_bar = empty_bar + C::STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, batch = blockIdx.z;
-  const int total_kb = G.k_blocks_per_tap * G.taps;
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tensormap(&tmap_a);
-    ptx::prefetch_tensormap(&tmap_b);
-    for (int s = 0; s < C::STAGES; ++s) {
-      ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
-    }
-    ptx::mbar_init(tmem_full_bar, 1);
-    ptx::fence_barrier_init();
-  }
-  if (warp == 1) {
-    ptx::tmem_alloc(tmem_slot, BN);
-    ptx::tmem_relinquish();
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      for (int kb = 0; kb < total_kb; ++kb) {
-        const int s = kb % C::STAGES;
-        const uint32_t ph = (kb / C::STAGES) & 1;
-        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
-        const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
-        uint8_t* sa = smem + s * C::STAGE_BYTES;
-        uint8_t* sb = sa + C::A_BYTES;
-        ptx::mbar_arrive_expect_tx(&full_bar[s], C::STAGE_BYTES);
-        ptx::tma_load_3d(sa, &tmap_a, &full_bar[s], kk * BK, m0 + G.tap_shift[tap], batch);
-        ptx::tma_load_2d(sb, &tmap_b, &full_bar[s], tap * G.k_tap + kk * BK, n0);
-      }
-    }
-    __syncwarp();
-  } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN);
-      for (int kb = 0; kb < total_kb; ++kb) {
-        const int s = kb % C::STAGES;
-        const uint32_t ph = (kb / C::STAGES) & 1;
-        ptx::mbar_wait(&full_bar[s], ph);
-        ptx::tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * C::STAGE_BYTES);
-        const uint64_t da = ptx::umma_desc_sw128(sa);
-        const uint64_t db = ptx::umma_desc_sw128(sa + C::A_BYTES);
-#pragma unroll
-        for (int k = 0; k < BK / 16; ++k)   // 16 bf16 = 32 B = 2 descriptor units per UMMA_K step
-          ptx::umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-        ptx::umma_commit(&empty_bar[s]);     // frees the smem slot once these MMAs retire
-      }
-      ptx::umma_commit(tmem_full_bar);       // accumulator complete
-    }
-    __syncwarp();
-  } else {
-    const int q = warp & 3;                  // TMEM lane quarter this warp may read
-    ptx::mbar_wait(tmem_full_bar, 0);
-    ptx::tc_fence_after();
-    TmemLoader L{tmem_base + ((uint32_t)(q * 32) << 16)};
-    run_epilogue<EPI>(BN, P, L, batch, m0 + q * 32 + lane, n0);
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem_base, BN);
-}
 
 // -------------------------------------------------------------------------------------------
 // host side: tensor maps through the driver entry point (no link-time libcuda dependency)
@@ -136,38 +37,6 @@ int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint
   return ECHO_OK;
 }
 
-template <int BN, int EPI>
-static int launch_tc(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
-  using C = TcCfg<BN>;
-  CUtensorMap ta, tb;
-  {
-    cuuint64_t dims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)(G.rows + G.a_ctx), (cuuint64_t)batch};
-    cuuint64_t str[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)(batch > 1 ? G.a_batch_stride : (long long)(G.rows + G.a_ctx) * G.lda) * 2};
-    cuuint32_t box[3] = {BK, BM, 1};
-    int rc = echo_make_tmap_bf16(&ta, G.a, 3, dims, str, box);
-    if (rc) return rc;
-  }
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)G.taps * G.k_tap, (cuuint64_t)G.n};
-    cuuint64_t str[1] = {(cuuint64_t)G.ldb * 2};
-    cuuint32_t box[2] = {BK, BN};
-    int rc = echo_make_tmap_bf16(&tb, G.b, 2, dims, str, box);
-    if (rc) return rc;
-  }
-  static bool attr_set = false;
-  if (!attr_set) {
-    ECHO_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
-    attr_set = true;
-  }
-  dim3 grid(ceil_div(G.n, BN), ceil_div(G.rows, BM), batch);
-  gemm_tcgen05_kernel<BN, EPI><<<grid, 192, C::SMEM, st>>>(ta, tb, G, P);
-  ECHO_COUNT_LAUNCH();
-  ECHO_LAUNCH_CHECK();
-  return ECHO_OK;
-}
-
-template <int EPI>
-int launch_legacy(const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm_legacy.cu
 int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
                           const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm2.cu
 
@@ -198,7 +67,7 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   P.kind = d->epilogue; P.rows = d->rows; P.n = d->n; P.act = d->act;
   P.bias = d->bias; P.gate = d->gate; P.gate_ld = d->gate_ld; P.rows_per_gate = d->rows_per_gate > 0 ? d->rows_per_gate : 1;
   P.resid = d->resid; P.ld_resid = d->ld_resid; P.out_f32 = d->out_f32; P.ld_out_f32 = d->ld_out_f32;
-  P.red_resid = (d->impl == 2 && d->resid && d->resid == d->out_f32 && d->ld_resid == d->ld_out_f32 && !d->out_bf16 &&
+  P.red_resid = (d->resid && d->resid == d->out_f32 && d->ld_resid == d->ld_out_f32 && !d->out_bf16 &&
                  !d->out2_bf16 && d->k_splits <= 1) ? 1 : 0;
   P.out_bf16 = (bf16*)d->out_bf16; P.ld_out_bf16 = d->ld_out_bf16;
   P.out2_bf16 = (bf16*)d->out2_bf16; P.ld_out2_bf16 = d->ld_out2_bf16; P.snake_alpha = d->snake_alpha;
@@ -210,7 +79,7 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
     P.sec[i].type = d->sections[i].type; P.sec[i].out = (bf16*)d->sections[i].out;
     P.sec[i].norm_w = d->sections[i].norm_weight;
   }
-  if (d->impl == 2) {   // vectorised epilogue: 16-byte loads of the per-column vectors
+  {   // vectorised epilogue: 16-byte loads of the per-column vectors
     auto al16 = [](const void* p) { return ((uintptr_t)p % 16) == 0; };
     ECHO_CHECK_ARG(al16(d->bias) && al16(d->gate) && al16(d->snake_alpha) && al16(d->resid) && al16(d->out_f32) &&
                    d->gate_ld % 4 == 0, "gemm: bias/gate/alpha/resid/out_f32 must be 16-byte aligned (gate_ld %% 4)");
@@ -242,36 +111,6 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
     ECHO_CHECK_ARG(false, "gemm: unknown epilogue %d", d->epilogue);
   }
   return ECHO_OK;
-}
-
-static int pick_block_n(const echo_gemm_desc* d) {
-  int bn = d->block_n;
-  if (bn == 0) {
-    // fewest wasted columns first, then enough CTAs to cover 148 SMs
-    const long long mt = (long long)ceil_div(d->rows, BM) * d->batch;
-    bn = 256;
-    if (d->n % 256 != 0 || mt * (d->n / 256) < 148) bn = 128;
-    if (bn == 128 && d->n <= 64) bn = 64;
-  }
-  if (d->epilogue == ECHO_EPI_SECTIONS) {
-    if (bn < d->head_dim) bn = d->head_dim;
-    while (d->section_width % bn != 0 && bn > d->head_dim) bn >>= 1;
-  }
-  if (d->epilogue == ECHO_EPI_SWIGLU && bn < 128) bn = 128;
-  return bn;
-}
-
-template <int EPI>
-static int dispatch_bn(int bn, const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
-  switch (bn) {
-    case 256: return launch_tc<256, EPI>(G, P, batch, st);
-    case 128: return launch_tc<128, EPI>(G, P, batch, st);
-    case 64:
-      if (EPI == ECHO_EPI_GENERIC) return launch_tc<64, ECHO_EPI_GENERIC>(G, P, batch, st);
-      if (EPI == ECHO_EPI_SECTIONS) return launch_tc<64, ECHO_EPI_SECTIONS>(G, P, batch, st);
-  }
-  echo_set_error("gemm: unsupported block_n %d for epilogue %d", bn, EPI);
-  return ECHO_ERR_UNSUPPORTED;
 }
 
 // Tile width for the CTA-pair kernel: fewest (rounds x tile cost) over the 74 pairs; ties go to the wider tile.
@@ -313,34 +152,15 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
   int rc = fill_params(d, G, P);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (d->impl == 1) {
-    if (d->epilogue == ECHO_EPI_SECTIONS) ECHO_CHECK_ARG(d->section_width % 128 == 0, "legacy gemm: section_width %% 128");
-    switch (d->epilogue) {
-      case ECHO_EPI_GENERIC: return launch_legacy<ECHO_EPI_GENERIC>(G, P, d->batch, st);
-      case ECHO_EPI_SECTIONS: return launch_legacy<ECHO_EPI_SECTIONS>(G, P, d->batch, st);
-      default: return launch_legacy<ECHO_EPI_SWIGLU>(G, P, d->batch, st);
-    }
-  }
-  if (d->impl == 2) {
-    const int bn = pick_block_n_pair(d);
-    ECHO_CHECK_ARG(bn > 0, "pair gemm: no tile width fits epilogue %d (n=%d)", d->epilogue, d->n);
-    if (d->epilogue == ECHO_EPI_SECTIONS)
-      ECHO_CHECK_ARG(d->section_width % bn == 0 && bn % d->head_dim == 0, "gemm: block_n %d does not tile sections", bn);
-    if (d->epilogue == ECHO_EPI_SWIGLU) ECHO_CHECK_ARG(bn % 128 == 0, "gemm: swiglu needs block_n %% 128 == 0");
-    if (d->k_splits > 1)
-      ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
-                     !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
-    return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
-                                 d->batch, st);
-  }
-  ECHO_CHECK_ARG(d->k_splits <= 1, "gemm: k_splits is an impl-2 feature");
-  ECHO_CHECK_ARG(d->impl == 0, "gemm: unknown impl %d", d->impl);
-  const int bn = pick_block_n(d);
+  ECHO_CHECK_ARG(d->impl == 0 || d->impl == 2, "gemm: impl %d: only the CTA-pair tcgen05 kernel (0 / 2) exists", d->impl);
+  const int bn = pick_block_n_pair(d);
+  ECHO_CHECK_ARG(bn > 0, "pair gemm: no tile width fits epilogue %d (n=%d)", d->epilogue, d->n);
   if (d->epilogue == ECHO_EPI_SECTIONS)
     ECHO_CHECK_ARG(d->section_width % bn == 0 && bn % d->head_dim == 0, "gemm: block_n %d does not tile sections", bn);
-  switch (d->epilogue) {
-    case ECHO_EPI_GENERIC: return dispatch_bn<ECHO_EPI_GENERIC>(bn, G, P, d->batch, st);
-    case ECHO_EPI_SECTIONS: return dispatch_bn<ECHO_EPI_SECTIONS>(bn, G, P, d->batch, st);
-    default: return dispatch_bn<ECHO_EPI_SWIGLU>(bn, G, P, d->batch, st);
-  }
+  if (d->epilogue == ECHO_EPI_SWIGLU) ECHO_CHECK_ARG(bn % 128 == 0, "gemm: swiglu needs block_n %% 128 == 0");
+  if (d->k_splits > 1)
+    ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
+                   !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
+  return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
+                               d->batch, st);
 }

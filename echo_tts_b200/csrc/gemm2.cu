@@ -36,15 +36,26 @@ constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
 constexpr int SCRATCH_BYTES = EPI_WARPS * EPI_SC_FLOATS * 4;   // per-epilogue-warp 32x32 fp32 transpose scratch
 constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
 
-// optional in-kernel timeline (32 clock64 slots per CTA), enabled with echo_debug_gemm_trace(ptr)
+// Debug builds only (make DEBUG=1 -> -DECHO_DEBUG): an in-kernel timeline (32 clock64 slots per CTA, enabled with
+// echo_debug_gemm_trace(ptr)) and two timing experiments whose RESULTS ARE GARBAGE (operand loads left out).  None of it
+// exists in the product library: the fields below are compile-time zeros there and every use folds away.
+#ifdef ECHO_DEBUG
 static long long* g_trace_ptr = nullptr;
-static int g_debug_noload = 0;   // debug: MMAs re-use whatever is in the ring (no TMA after the first fill): isolates MMA issue rate
-static int g_debug_skip = 0;     // debug (timing only, results garbage): 1 = never load A, 2 = never load B
+static int g_debug_noload = 0;   // MMAs re-use whatever is in the ring (no TMA after the first fill): isolates MMA issue rate
+static int g_debug_skip = 0;     // 1 = never load A, 2 = never load B
+#else
+constexpr int g_debug_noload = 0;
+#endif
 
 struct Tiling {
+#ifdef ECHO_DEBUG
   long long* trace;       // nullptr unless tracing: [cta][32] SM-clock stamps
-  int noload;             // debug only
-  int skip;               // debug only: operand whose loads are left out (1 = A, 2 = B)
+  int noload;
+  int skip;               // operand whose loads are left out (1 = A, 2 = B)
+#else
+  static constexpr long long* trace = nullptr;
+  static constexpr int noload = 0, skip = 0;
+#endif
   int stages, stage_bytes; // operand ring: stage = A (16 KB) + this CTA's half of B (bn/2 rows x 128 B)
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
@@ -219,7 +230,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
   const int total_kb = G.k_blocks_per_tap * G.taps;
   const int half_n = T.bn >> 1;
+#ifdef ECHO_DEBUG
   long long* const trace = T.trace ? T.trace + (long long)blockIdx.x * 32 : nullptr;
+#else
+  constexpr long long* trace = nullptr;
+#endif
   if (trace && threadIdx.x == 0) trace[0] = clock64();
 
   if (warp == 0 && lane == 0) {
@@ -413,6 +428,9 @@ int getenv_int(const char* name, int dflt) {
   const char* e = getenv(name);
   return e && e[0] ? atoi(e) : dflt;
 }
+// scheduler switches (A/B measurements), read ONCE per process -- not per launch
+int use_narrow_tail() { static const int v = getenv_int("ECHO_GEMM_TAIL", 1); return v; }
+int use_stream_k() { static const int v = getenv_int("ECHO_STREAM_K", 0); return v; }
 int num_sms() {
   static int n = 0;
   if (!n) {
@@ -446,7 +464,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     const int P2 = num_sms() / 2;
     const int wide = ceil_div(G.rows, 2 * BM) * ceil_div(G.n, bn) * batch;
     const int rem = wide % P2;
-    if (splits == 1 && bn == 256 && G.n % 256 == 0 && !g_debug_noload && getenv_int("ECHO_GEMM_TAIL", 1)) {
+    if (splits == 1 && bn == 256 && G.n % 256 == 0 && !g_debug_noload && use_narrow_tail()) {
       if (wide > P2 && rem > 0 && 2 * rem <= P2) tail_start = wide - rem;
       else if (2 * wide <= P2) tail_start = 0;      // a single sparse round: every tile half-width, twice the pairs busy
     }
@@ -477,9 +495,11 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     attr_set = true;
   }
   Tiling T;
+#ifdef ECHO_DEBUG
   T.trace = g_trace_ptr;
   T.noload = g_debug_noload;
   T.skip = g_debug_skip;
+#endif
   T.bn = bn;
   T.stage_bytes = A_BYTES + (bn / 2) * BK * 2;
   T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
@@ -498,7 +518,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     const int P2 = num_sms() / 2, total_kb = G.k_blocks_per_tap * G.taps;
     const long long tiles = T.num_tiles, rounds = (tiles + P2 - 1) / P2;
     const bool ragged = tiles * 100 < rounds * P2 * 92;
-    if (ragged && total_kb >= 8 && tiles * total_kb >= 4LL * P2 && getenv_int("ECHO_STREAM_K", 0)) {
+    if (ragged && total_kb >= 8 && tiles * total_kb >= 4LL * P2 && use_stream_k()) {
       T.stream_k = 1;
       T.sk_flags = reinterpret_cast<int*>(workspace);
       T.sk_partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_FLAG_BYTES);
@@ -515,12 +535,19 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
 // [0] start, [1] setup done, [2] first operands landed, [6] all roles done, [7] exit, and for the CTA's first six
 // tiles t: [8+4t] accumulator stage free (MMA thread), [9+4t] MMAs issued, [10+4t] accumulator ready (epilogue
 // warp 2), [11+4t] epilogue done.  Pass NULL to switch tracing off.
-extern "C" void echo_debug_gemm_trace(long long* device_buf) {
+extern "C" int echo_debug_gemm_trace(long long* device_buf) {
+#ifdef ECHO_DEBUG
   g_trace_ptr = device_buf;
   const char* e = getenv("ECHO_GEMM_NOLOAD");    // results are garbage in this mode; timing experiments only
   g_debug_noload = (device_buf && e && e[0] == '1') ? 1 : 0;
   const char* k = getenv("ECHO_GEMM_SKIP");      // "A" / "B": leave that operand's loads out (timing experiments only)
   g_debug_skip = (device_buf && k) ? (k[0] == 'A' ? 1 : k[0] == 'B' ? 2 : 0) : 0;
+  return ECHO_OK;
+#else
+  if (!device_buf) return ECHO_OK;
+  echo_set_error("echo_debug_gemm_trace: this library was built without -DECHO_DEBUG (make -C echo_tts_b200/csrc DEBUG=1)");
+  return ECHO_ERR_UNSUPPORTED;
+#endif
 }
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)

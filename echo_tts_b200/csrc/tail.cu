@@ -11,17 +11,24 @@ constexpr int PP = 5, CW = 5;
 
 // v = v_c + a (v_c - v_ut) + b (v_c - v_us)  (inference.py:526-530), optional temporal score rescale (inference.py:431-443),
 // x += v dt (inference.py:558)
-__device__ __forceinline__ float combine3(const echo_tail_desc& D, float vc, float vt, float vs) {
-  return vc + D.cfg_text * (vc - vt) + D.cfg_speaker * (vc - vs);
+// guidance constants: immediates of the descriptor, or (graph replay with per-request values) a device vector
+struct Guidance { float cfg_text, cfg_speaker, rescale_k, rescale_sigma; };
+__device__ __forceinline__ Guidance load_guidance(const echo_tail_desc& D) {
+  if (D.guidance) return Guidance{D.guidance[0], D.guidance[1], D.guidance[2], D.guidance[3]};
+  return Guidance{D.cfg_text, D.cfg_speaker, D.rescale_k, D.rescale_sigma};
 }
-__device__ __forceinline__ float rescale_and_step(const echo_tail_desc& D, float v, float t, float dt, long long xi) {
+__device__ __forceinline__ float combine3(const Guidance& G, float vc, float vt, float vs) {
+  return vc + G.cfg_text * (vc - vt) + G.cfg_speaker * (vc - vs);
+}
+__device__ __forceinline__ float rescale_and_step(const echo_tail_desc& D, const Guidance& G, float v, float t, float dt,
+                                                  long long xi) {
   if (D.update_x) {
     const float x = D.x_t[xi];
     if (D.use_rescale && t < 1.f) {
       const float omt = 1.f - t;
       const float snr = (omt * omt) / (t * t);
-      const float sg2 = D.rescale_sigma * D.rescale_sigma;
-      const float ratio = (snr * sg2 + 1.f) / (snr * sg2 / D.rescale_k + 1.f);
+      const float sg2 = G.rescale_sigma * G.rescale_sigma;
+      const float ratio = (snr * sg2 + 1.f) / (snr * sg2 / G.rescale_k + 1.f);
       v = 1.f / omt * (ratio * (omt * v + x) - x);
     }
     D.x_t[xi] = x + v * dt;
@@ -37,14 +44,15 @@ __global__ void __launch_bounds__(256) cfg_combine_euler_kernel(const __grid_con
   pdl_wait();
   if (D.wait_flag[0]) {
     // fused exchange: the other two ranks' tail kernels pushed their branch velocities into our v_out over NVLink and
-    // then bumped these counters (release, system scope).  Bounded wait: a lost peer traps instead of hanging the GPU.
+    // then bumped these counters (release, system scope).  Bounded wait (~1 minute: a peer that is merely late -- first-call
+    // warm-up, a paused rank -- is waited for; a lost one traps instead of hanging the GPU for good).
     if (threadIdx.x < 2) {
       const int32_t* f = D.wait_flag[threadIdx.x];
       int v = 0;
       const long long t0 = clock64();
       do {
         asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-        if (v < D.wait_value && clock64() - t0 > 6000000000LL) { printf("echo: CFG-split peer never arrived\n"); __trap(); }
+        if (v < D.wait_value && clock64() - t0 > 120000000000LL) { printf("echo: CFG-split peer never arrived\n"); __trap(); }
       } while (v < D.wait_value);
     }
     __syncthreads();
@@ -52,8 +60,9 @@ __global__ void __launch_bounds__(256) cfg_combine_euler_kernel(const __grid_con
   const int s = D.step ? D.step[0] : 0;
   const float t = D.sched[s * 4 + 0], dt = D.sched[s * 4 + 1];
   const long long n = (long long)D.positions * D.latent;
+  const Guidance G = load_guidance(D);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    rescale_and_step(D, combine3(D, D.v_out[i], D.v_out[n + i], D.v_out[2 * n + i]), t, dt, i);
+    rescale_and_step(D, G, combine3(G, D.v_out[i], D.v_out[n + i], D.v_out[2 * n + i]), t, dt, i);
 }
 
 template <int BR>
@@ -130,6 +139,7 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
 
   const int s = D.step ? D.step[0] : 0;
   const float t = D.sched ? D.sched[s * 4 + 0] : 0.f, dt = D.sched ? D.sched[s * 4 + 1] : 0.f;
+  const Guidance G = load_guidance(D);
   for (int i = threadIdx.x; i < PP * D.latent; i += blockDim.x) {
     const int pl = i / D.latent, c = i % D.latent;
     const int p = pos0 + pl;
@@ -148,9 +158,9 @@ __global__ void __launch_bounds__(256) cfg_euler_tail_kernel(const __grid_consta
         D.v_out[((long long)1 * D.positions + p) * D.latent + c] = vt;
         D.v_out[((long long)2 * D.positions + p) * D.latent + c] = vs;
       }
-      v = combine3(D, vc, vt, vs);
+      v = combine3(G, vc, vt, vs);
     }
-    rescale_and_step(D, v, t, dt, (long long)p * D.latent + c);
+    rescale_and_step(D, G, v, t, dt, (long long)p * D.latent + c);
   }
   if (D.flag_peer[0]) {
     __threadfence_system();
@@ -172,12 +182,9 @@ extern "C" int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream
                  "tail: the fused exchange needs branches == 1, two peer buffers and two peer counters");
   const size_t smem = ((size_t)d->branches * PP * (d->d + d->latent)) * sizeof(float);
   ECHO_CHECK_ARG(smem <= 220 * 1024, "tail: d = %d too wide for the shared-memory row cache", d->d);
-  static size_t configured = 0;
-  if (smem > configured) {
-    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  // the attribute is per device: set it on every launch (a host-side table write, no device work)
+  ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ECHO_CUDA(cudaFuncSetAttribute(cfg_euler_tail_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (d->branches == 3)
     ECHO_CUDA(echo_launch(cfg_euler_tail_kernel<3>, dim3(ceil_div(d->positions, PP)), dim3(256), smem, (cudaStream_t)stream, *d));
   else

@@ -334,10 +334,16 @@ class EchoDiT:
     # one velocity evaluation (EchoDiT.forward, model.py:563-604) -- ends at the final residual stream;
     # out_norm/out_proj live in the fused sampler tail.
     # ------------------------------------------------------------------------------------------
+    WS_CAPACITY = 8      # activation workspaces kept per model (LRU); captured graphs hold their own references
+
     def workspace(self, rows: int, S: int) -> dict:
         key = (rows, S)
         ws = self._ws.get(key)
+        if ws is not None:
+            self._ws[key] = self._ws.pop(key)        # most recently used last (dicts keep insertion order)
         if ws is None:
+            while len(self._ws) >= self.WS_CAPACITY:
+                self._ws.pop(next(iter(self._ws)))
             cfg, dev = self.cfg, self._device
             M, D = rows * S, cfg.model_size
             ns = self.k_splits(M)

@@ -11,11 +11,8 @@ import torch
 from . import _lib as L
 
 BF16, F32 = torch.bfloat16, torch.float32
-import os as _os
-# 2 = CTA-pair persistent tcgen05 kernel (product path); 0 = single-CTA tcgen05 kernel; 1 = legacy mma.sync
-# (A/B baselines, tests only).  ECHO_GEMM_IMPL overrides for A/B measurements.
 STREAM_K = True   # lend the stream-K workspace; the library decides (ECHO_STREAM_K=1 enables it, default off)
-GEMM_IMPL = int(_os.environ.get("ECHO_GEMM_IMPL", "2"))
+GEMM_IMPL = 2     # echo_gemm_desc.impl: the CTA-pair persistent tcgen05 kernel -- the only GEMM kernel of the library
 
 
 def _need(t: torch.Tensor, dtype, name: str):
@@ -227,7 +224,8 @@ class Segment:
         self.q_offset = q_offset
 
 
-ATTN_IMPL = int(_os.environ.get("ECHO_ATTN_IMPL", "0"))   # 0 = tcgen05 kernel when eligible; 1 = mma.sync kernel (A/B)
+ATTN_IMPL = 0     # echo_attn_desc.impl: 0 = tcgen05 kernel where eligible (head_dim 128, non-causal), else the general
+                  # (causal / window / head_dim 64) kernel; tests pass impl=1 to run the general kernel at the DiT shapes
 
 
 def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate: Optional[torch.Tensor] = None,
@@ -280,7 +278,7 @@ def mask_extent(mask: torch.Tensor) -> torch.Tensor:
 
 def tail_desc(norm_w, w_out, b_out, *, positions, branches, eps, h=None, x_t=None, sched=None, step=None,
               cfg_text=0.0, cfg_speaker=0.0, rescale_k=None, rescale_sigma=None, v_out=None, v_comb_out=None,
-              update_x=True, delta=None, push_to=None) -> L.TailDesc:
+              update_x=True, delta=None, push_to=None, guidance=None) -> L.TailDesc:
     """Descriptor of the fused sampler tail.  ``h`` (final residual stream) may be left out when the descriptor rides
     on ``echo_dit_step``, which fills it in.  ``push_to``: ((v_peer0, flag_peer0), (v_peer1, flag_peer1)) P2P-mapped
     tensors on the two other ranks of a CFG-branch split (branches == 1): the kernel stores its velocities there too
@@ -312,6 +310,9 @@ def tail_desc(norm_w, w_out, b_out, *, positions, branches, eps, h=None, x_t=Non
     d.use_rescale = int(rescale_k is not None and rescale_sigma is not None)
     d.rescale_k, d.rescale_sigma = (rescale_k or 1.0), (rescale_sigma or 0.0)
     d.update_x = int(update_x)
+    if guidance is not None:      # device fp32 [4] (cfg_text, cfg_speaker, rescale_k, rescale_sigma): overrides the immediates
+        _need(guidance, F32, "guidance"); assert guidance.numel() == 4 and guidance.is_contiguous()
+        d.guidance = guidance.data_ptr()
     return d
 
 

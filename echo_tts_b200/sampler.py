@@ -71,10 +71,15 @@ def _prep_masks(model: EchoDiT, text_mask: torch.Tensor, speaker_mask: torch.Ten
 
 def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tensor, B: int, masks, kv_text: KVCache,
               kv_spk: KVCache, p: dict, *, start_pos: int = 0, kv_latent: Optional[KVCache] = None, n_prefix: int = 0,
-              trace: Optional[list] = None) -> None:
+              trace: Optional[list] = None, teacher: Optional[Dict[int, torch.Tensor]] = None,
+              guidance: Optional[torch.Tensor] = None) -> list:
     """The hot loop (inference.py:508-558): x_t fp32 [B, S, latent] updated in place; launches only.  Without a trace
     the whole loop is ONE native call (``echo_dit_sample``: per step the DiT forward over 3B or B rows + the fused
-    out-projection / CFG combine / rescale / Euler tail); with a trace, one ``echo_dit_step`` per step."""
+    out-projection / CFG combine / rescale / Euler tail); with a trace, one ``echo_dit_step`` per step, and
+    ``teacher[i]`` (parity tests) replaces x_t before step i -- velocities at the reference's own x_t.
+    ``guidance``: device fp32 [4] (cfg scales, rescale k / sigma) read by the tail kernel instead of the immediates, so
+    a captured graph serves every guidance setting.  Returns the objects the launches point into (workspaces, pointer
+    arrays): a CUDA graph captured around this call must keep them alive."""
     cfg = model.cfg
     tm3, te3, sm3, se3 = masks
     S = x_t.shape[1]
@@ -86,7 +91,7 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
         tail = ops.tail_desc(model.out_norm, model.out_w, model.out_b, positions=B * S, branches=R // B,
                              eps=cfg.norm_eps, x_t=x_t, sched=plan.sched[i:], cfg_text=p["cfg_scale_text"],
                              cfg_speaker=p["cfg_scale_speaker"], rescale_k=p["rescale_k"] if use_rescale else None,
-                             rescale_sigma=p["rescale_sigma"] if use_rescale else None, **tail_kw)
+                             rescale_sigma=p["rescale_sigma"] if use_rescale else None, guidance=guidance, **tail_kw)
         return model.step_desc(x_t, mod[i:i + 1], B, R, text_mask=tm3, text_extent=te3, spk_mask=sm3, spk_extent=se3,
                                kv_text=kv_text, kv_speaker=kv_spk, kv_latent=kv_latent, start_pos=start_pos,
                                n_prefix=n_prefix, spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None),
@@ -101,15 +106,18 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
                                     n, C.cast(flags, C.c_void_p), mod.stride(0),
                                     plan.kv_mult.stride(0) if plan.uses_kv_scale else 0, plan.sched.stride(0),
                                     L.stream()))
-        return
+        return [keep3, keep1]
     for i, has_cfg in enumerate(plan.has_cfg):
         R = 3 * B if has_cfg else B
         v_out = torch.empty((R * S, cfg.latent_size), device=x_t.device, dtype=F32)
         v_comb = torch.empty((B * S, cfg.latent_size), device=x_t.device, dtype=F32)
+        if teacher is not None and i in teacher:
+            x_t.copy_(teacher[i].to(x_t.device, F32).view_as(x_t))
         x_in = x_t.clone()
         d, keep = step(R, i, v_out=v_out, v_comb_out=v_comb)
         L.check(lib.echo_dit_step(C.byref(d), L.stream()))
         trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
+    return []
 
 
 class _GraphEntry:
@@ -117,6 +125,31 @@ class _GraphEntry:
         self.calls = 0
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.static: Dict[str, torch.Tensor] = {}
+
+
+def graph_cache_capacity() -> int:
+    """Captured sampler graphs kept per model (least recently used evicted).  An entry's private pool pins the 24-layer
+    text + speaker KV caches and the encoder scratch of its shape (~160 MB at 53 speaker patches, > 450 MB at 1600)."""
+    return max(1, int(os.environ.get("ECHO_GRAPH_CACHE", "8")))
+
+
+def _graph_entry(model: EchoDiT, key) -> _GraphEntry:
+    """LRU lookup in the per-model graph cache.  Keys hold SHAPES and the schedule only (text / speaker lengths as the
+    caller bucketed them -- audio.request_buckets -- steps, the CFG window's step set, rescale on/off, kv-scale on/off);
+    guidance scales, rescale constants, speaker-KV multipliers and the t schedule are device data refreshed per call."""
+    from collections import OrderedDict
+    cache = model.__dict__.get("_graphs")
+    if not isinstance(cache, OrderedDict):
+        cache = model.__dict__["_graphs"] = OrderedDict(cache or {})
+    ent = cache.get(key)
+    if ent is None:
+        ent = cache[key] = _GraphEntry()
+    cache.move_to_end(key)
+    while len(cache) > graph_cache_capacity():
+        _, old = cache.popitem(last=False)
+        old.graph = None            # drops the graph, its private memory pool and the static input buffers
+        old.static.clear()
+    return ent
 
 
 def _use_graphs() -> bool:
@@ -130,9 +163,11 @@ def sample_euler_cfg_independent_guidances(
         cfg_min_t: float, cfg_max_t: float, truncation_factor: Optional[float], rescale_k: Optional[float],
         rescale_sigma: Optional[float], speaker_kv_scale: Optional[float], speaker_kv_max_layers: Optional[int],
         speaker_kv_min_t: Optional[float], sequence_length: Optional[int] = None, *,
-        _noise: Optional[torch.Tensor] = None, _trace: Optional[list] = None) -> torch.Tensor:
+        _noise: Optional[torch.Tensor] = None, _trace: Optional[list] = None,
+        _teacher: Optional[Dict[int, torch.Tensor]] = None) -> torch.Tensor:
     """Drop-in for reference ``inference.py:446-560`` (same positional/keyword arguments, fp32 [B, S, 80] out).
-    ``_noise`` injects x_T and ``_trace`` collects per-step velocities (parity tests only)."""
+    ``_noise`` injects x_T, ``_trace`` collects per-step velocities and ``_teacher`` (with a trace) forces x_t at the
+    given steps (parity tests only)."""
     if sequence_length is None:
         sequence_length = 640
     if speaker_kv_scale is not None and speaker_kv_min_t is None:
@@ -156,10 +191,10 @@ def sample_euler_cfg_independent_guidances(
         kv_s = model.get_kv_cache_speaker(spk)                                             # inference.py:483
         return kv_t, kv_s, _prep_masks(model, tmask, smask)
 
-    key = ("euler", B, S, text_input_ids.shape[1], speaker_latent.shape[1], num_steps, tuple(plan.has_cfg),
-           p["cfg_scale_text"], p["cfg_scale_speaker"], rescale_k, rescale_sigma, plan.uses_kv_scale)
-    cache = model.__dict__.setdefault("_graphs", {})
-    ent: _GraphEntry = cache.setdefault(key, _GraphEntry())
+    use_rescale = rescale_k is not None and rescale_sigma is not None
+    key = ("euler", B, S, text_input_ids.shape[1], speaker_latent.shape[1], num_steps, tuple(plan.has_cfg), use_rescale,
+           plan.uses_kv_scale)
+    ent = _graph_entry(model, key)
     ent.calls += 1
     if _trace is not None or not _use_graphs() or ent.calls == 1:
         # plain launches: parity traces, ECHO_CUDA_GRAPH=0, and the first request with a new shape (warms kernels up)
@@ -167,7 +202,7 @@ def sample_euler_cfg_independent_guidances(
             ent.calls -= 1
         kv_text, kv_spk, masks = conditioning(text_input_ids, text_mask, speaker_latent, speaker_mask)
         mod = model.build_mod_table(plan.t_dev)
-        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, trace=_trace)
+        run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, trace=_trace, teacher=_teacher)
         return x_t.view(B, S, cfg.latent_size)
 
     # ---- CUDA-graph path: conditioning encoders + all Euler steps are ONE captured graph over static input buffers,
@@ -181,16 +216,20 @@ def sample_euler_cfg_independent_guidances(
         st["x_t"] = x_t.clone()
         st["mod"] = model.build_mod_table(plan.t_dev)     # depends on the schedule only (part of the key)
         st["plan"] = plan
+        st["guidance"] = torch.zeros(4, device=dev, dtype=F32)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             kv_text, kv_spk, masks = conditioning(st["ids"], st["tmask"], st["spk"], st["smask"])
-            run_steps(model, st["x_t"], plan, st["mod"], B, masks, kv_text, kv_spk, p)
+            st["keep"] = run_steps(model, st["x_t"], plan, st["mod"], B, masks, kv_text, kv_spk, p,
+                                   guidance=st["guidance"])
         ent.graph = g
     st["ids"].copy_(text_input_ids)
     st["tmask"].copy_(text_mask)
     st["spk"].copy_(speaker_latent)
     st["smask"].copy_(speaker_mask)
     st["x_t"].copy_(x_t)
+    st["guidance"].copy_(torch.tensor([p["cfg_scale_text"], p["cfg_scale_speaker"], rescale_k if use_rescale else 1.0,
+                                       rescale_sigma if use_rescale else 0.0], dtype=F32), non_blocking=True)
     if plan.uses_kv_scale:
         st["plan"].kv_mult.copy_(plan.kv_mult)
     st["plan"].sched.copy_(plan.sched)
@@ -206,7 +245,7 @@ def blockwise_blocks(
         rescale_k: Optional[float], rescale_sigma: Optional[float], speaker_kv_scale: Optional[float],
         speaker_kv_max_layers: Optional[int], speaker_kv_min_t: Optional[float],
         continuation_latent: Optional[torch.Tensor] = None, *, _noises: Optional[Sequence[torch.Tensor]] = None,
-        incremental_prefix: Optional[bool] = None) -> Iterator[Tuple[int, int, torch.Tensor]]:
+        incremental_prefix: Optional[bool] = None, _trace: Optional[list] = None) -> Iterator[Tuple[int, int, torch.Tensor]]:
     """The block loop of reference ``inference_blockwise.py:14-123`` as a generator: yields ``(start, stop, prefix)``
     after each block (``prefix[:, :stop]`` is final), which is what a streaming caller decodes.  Differences in HOW,
     not WHAT: the latent-prefix KV is encoded for B rows (the reference encodes three identical copies, :72-74),
@@ -261,7 +300,7 @@ def blockwise_blocks(
         if truncation_factor is not None:
             x_t = x_t * truncation_factor
         run_steps(model, x_t, plan, mod, B, masks, kv_text, kv_spk, p, start_pos=start, kv_latent=kv_lat,
-                  n_prefix=n_prefix)
+                  n_prefix=n_prefix, trace=_trace)
         prefix[:, start:start + bs] = x_t
         if pstream is not None and bi + 1 < len(block_sizes):
             pstream.append(x_t)
@@ -277,7 +316,7 @@ def sample_blockwise_euler_cfg_independent_guidances(
         rescale_k: Optional[float], rescale_sigma: Optional[float], speaker_kv_scale: Optional[float],
         speaker_kv_max_layers: Optional[int], speaker_kv_min_t: Optional[float],
         continuation_latent: Optional[torch.Tensor] = None, *, _noises: Optional[Sequence[torch.Tensor]] = None,
-        on_block=None, incremental_prefix: Optional[bool] = None) -> torch.Tensor:
+        on_block=None, incremental_prefix: Optional[bool] = None, _trace: Optional[list] = None) -> torch.Tensor:
     """Drop-in for reference ``inference_blockwise.py:14-123`` (see ``blockwise_blocks`` for the loop);
     ``on_block(start, stop, prefix)`` (optional) is the streaming hook."""
     if speaker_kv_scale is not None and speaker_kv_min_t is None:
@@ -287,7 +326,7 @@ def sample_blockwise_euler_cfg_independent_guidances(
             model, speaker_latent, speaker_mask, text_input_ids, text_mask, rng_seed, block_sizes, num_steps,
             cfg_scale_text, cfg_scale_speaker, cfg_min_t, cfg_max_t, truncation_factor, rescale_k, rescale_sigma,
             speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t, continuation_latent, _noises=_noises,
-            incremental_prefix=incremental_prefix):
+            incremental_prefix=incremental_prefix, _trace=_trace):
         if on_block is not None:
             on_block(start, stop, prefix)
     if prefix is None:          # no blocks: the (possibly empty) continuation comes back unchanged

@@ -396,3 +396,26 @@ def synth_ae_state_dict(cfg: AEConfig = AE_BASE, seed: int = 4321, encode: bool 
         if cfg.enc_tr_layers > 0:
             sd[f"encoder.block.{len(cfg.encoder_rates)}.block.5.freqs_cis"] = ae_rope_table(cfg, cfg.enc_tr_block_size, 64)
     return sd
+
+
+def synth_pca(latent_size: int = 80, latent_dim: int = 1024, seed: int = 99):
+    """Synthetic ``PCAState`` constants (``inference.py:116-135``; no network for the real file): orthonormal component
+    rows, small mean, scale 0.5.  -> (components [latent_size, latent_dim], mean [latent_dim], latent_scale)."""
+    g = torch.Generator().manual_seed(seed)
+    q, _ = torch.linalg.qr(torch.randn(latent_dim, latent_size, generator=g))
+    return q.t().contiguous(), 0.05 * torch.randn(latent_dim, generator=g), 0.5
+
+
+def synth_request(B: int = 1, n_valid: int = 256, pad_to: int = 768, t_spk: int = 212, seed: int = 7):
+    """Synthetic request tensors of the BASELINE.json shapes: BOS + ``n_valid - 1`` printable ASCII bytes
+    padded to ``pad_to`` (``inference.py:185-217``), an N(0,1) speaker latent of ``t_spk`` frames with an all-true
+    mask.  CPU generator => identical on every machine; bench.py, the parity tests and the fixture generators
+    (``oracle/gen_golden_full.py``) all draw their inputs here.  -> (ids int32, text_mask bool, speaker_latent, speaker_mask)"""
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.zeros((B, pad_to), dtype=torch.int32)
+    mask = torch.zeros((B, pad_to), dtype=torch.bool)
+    ids[:, 1:n_valid] = torch.randint(32, 127, (B, n_valid - 1), generator=g, dtype=torch.int32)
+    mask[:, :n_valid] = True
+    spk = torch.randn((B, t_spk, 80), generator=g)
+    smask = torch.ones((B, t_spk), dtype=torch.bool)
+    return ids, mask, spk, smask

@@ -26,9 +26,8 @@ void echo_reset_launch_count(void);
  * bf16 tensor-core GEMM with implicit-conv taps and fused epilogues.
  *   acc[b, m, n] = sum_t sum_k A[b, m + tap_shift[t], k] * B[n, t*k_tap + k]     (fp32 accumulate)
  * Rows outside [-a_ctx, rows) read as zero (causal left padding of CausalConvNet,
- * autoencoder.py:285-289).  impl 2 = persistent CTA-pair tcgen05.mma kernel with TMEM accumulators
- * and TMA loads (the product path); impl 0 = single-CTA tcgen05 kernel, impl 1 = legacy mma.sync
- * kernel, both kept as A/B baselines and debugging aids.
+ * autoencoder.py:285-289).  ONE kernel: the persistent CTA-pair tcgen05.mma kernel with TMEM accumulators
+ * and TMA loads (csrc/gemm2.cu); `impl` is kept in the descriptor for ABI stability (0 or 2: that kernel).
  * Replaces every nn.Linear / Conv1d / ConvTranspose1d on the path: model.py:217-224, 266, 308;
  * autoencoder.py:285-316, 365-367, 667, 704, 717.
  * ------------------------------------------------------------------------------------------ */
@@ -50,7 +49,7 @@ typedef struct echo_gemm_desc {
   int32_t rows, batch, n, k_tap, taps;
   int32_t tap_shift[8];
   int32_t epilogue;         /* ECHO_EPI_* */
-  int32_t impl;             /* 2 = CTA-pair tcgen05 kernel (product path); 0 = single-CTA tcgen05; 1 = legacy mma.sync */
+  int32_t impl;             /* 0 or 2: the CTA-pair tcgen05 kernel (the only GEMM kernel); anything else is refused */
   int32_t block_n;          /* 0 = auto; 64 / 128 / 256 */
   int32_t act;              /* GENERIC: activation applied after bias */
   /* GENERIC: v = act(acc + bias[n]) * gate[(m / rows_per_gate) * gate_ld + n] + resid[m, n]
@@ -98,13 +97,14 @@ typedef struct echo_gemm_desc {
 int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
 long long echo_gemm_workspace_bytes(void);
 
-/* Debug aid (no reference counterpart): while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every
- * impl-2 GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles
+/* Debug aid (no reference counterpart; DEBUG BUILDS ONLY: `make -C echo_tts_b200/csrc DEBUG=1` compiles it in with
+ * -DECHO_DEBUG, the product library returns ECHO_ERR_UNSUPPORTED for a non-NULL buffer and contains none of it):
+ * while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles
  * done, [7] exit, and for its first six tiles t: [8+4t] accumulator stage free, [9+4t] MMAs issued, [10+4t]
  * accumulator ready, [11+4t] epilogue done.  Pass NULL to switch it off.  While tracing, the environment variables
  * ECHO_GEMM_NOLOAD=1 (no TMA after the first ring fill) and ECHO_GEMM_SKIP=A|B (that operand is never loaded) turn the
  * launch into a timing experiment (results are garbage): they separate the MMA rate from each operand's feed. */
-void echo_debug_gemm_trace(long long* device_buf);
+int echo_debug_gemm_trace(long long* device_buf);
 
 /* ------------------------------------------------------------------------------------------
  * fp32 CUDA-core GEMM for the accuracy-critical small projections:
@@ -182,9 +182,9 @@ typedef struct echo_attn_desc {
   echo_attn_segment seg[4];
 } echo_attn_desc;
 int echo_attention(const echo_attn_desc* d, echo_stream_t stream);
-/* Debug aid (no reference counterpart): while non-NULL, every tcgen05 attention launch records 64 clock64() stamps per
- * CTA (layout documented at the definition in csrc/attention2.cu).  Pass NULL to switch it off. */
-void echo_debug_attn_trace(long long* device_buf);
+/* Debug aid (no reference counterpart; debug builds only, as echo_debug_gemm_trace): while non-NULL, every tcgen05
+ * attention launch records 64 clock64() stamps per CTA (layout documented at the definition in csrc/attention2.cu). */
+int echo_debug_attn_trace(long long* device_buf);
 
 /* extent[r] = 1 + index of last non-zero byte of mask[r, :len] (0 if none) */
 int echo_mask_extent(const uint8_t* mask, int rows, int len, int64_t stride, int32_t* extent,
@@ -222,6 +222,9 @@ typedef struct echo_tail_desc {
   int32_t* flag_peer[2];
   const int32_t* wait_flag[2];
   int32_t wait_value, _pad_tail;
+  /* nullable device fp32 [4] = {cfg_text, cfg_speaker, rescale_k, rescale_sigma}: when given it overrides the four
+   * immediates above, so one captured CUDA graph serves every guidance setting (use_rescale stays a launch-time flag) */
+  const float* guidance;
 } echo_tail_desc;
 int echo_cfg_euler_tail(const echo_tail_desc* d, echo_stream_t stream);
 /* Combine-only variant for the multi-GPU CFG-branch split: d->v_out is INPUT, the three branch

@@ -321,7 +321,8 @@ def sample_blockwise_euler_cfg_independent_guidances(
         block_sizes: Sequence[int], num_steps: int, cfg_scale_text: float, cfg_scale_speaker: float,
         cfg_min_t: float, cfg_max_t: float, truncation_factor=None, rescale_k=None, rescale_sigma=None,
         speaker_kv_scale=None, speaker_kv_max_layers=None, speaker_kv_min_t=None,
-        continuation_latent=None, noises: Optional[Sequence[torch.Tensor]] = None) -> torch.Tensor:
+        continuation_latent=None, noises: Optional[Sequence[torch.Tensor]] = None,
+        trace: Optional[list] = None) -> torch.Tensor:
     """inference_blockwise.py:14-123."""
     B = text_input_ids.shape[0]
     p = dict(num_steps=num_steps, cfg_scale_text=cfg_scale_text, cfg_scale_speaker=cfg_scale_speaker,
@@ -345,7 +346,7 @@ def sample_blockwise_euler_cfg_independent_guidances(
             torch.randn((B, bs, cfg.latent_size), generator=gen)
         if truncation_factor is not None:
             x_t = x_t * truncation_factor
-        x_t = _euler_block(sd, cfg, x_t, t_schedule(num_steps), kv_text, kv_spk, text_mask, speaker_mask, p, None,
+        x_t = _euler_block(sd, cfg, x_t, t_schedule(num_steps), kv_text, kv_spk, text_mask, speaker_mask, p, trace,
                            start_pos=start, kv_lat3=kv_lat3, kv_lat1=kv_lat1)
         prefix[:, start:start + bs] = x_t
         start += bs
@@ -534,10 +535,9 @@ def ae_decode(sd: SD, cfg, pca_components, pca_mean, latent_scale: float, z: tor
 
 
 def synth_pca(latent_size: int = 80, latent_dim: int = 1024, seed: int = 99):
-    """Synthetic PCAState (no network for the real one): orthonormal rows, small mean, scale 0.5."""
-    g = torch.Generator().manual_seed(seed)
-    q, _ = torch.linalg.qr(torch.randn(latent_dim, latent_size, generator=g))
-    return q.t().contiguous(), 0.05 * torch.randn(latent_dim, generator=g), 0.5
+    """Synthetic PCAState constants: lives in ``echo_tts_b200.schema`` (shared with the product-side bench arm)."""
+    from echo_tts_b200.schema import synth_pca as _sp
+    return _sp(latent_size, latent_dim, seed)
 
 
 # ---------------------------------------------------------------------------------------------------------------------

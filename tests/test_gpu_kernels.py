@@ -30,7 +30,7 @@ def _rand(shape, seed, scale=1.0, dtype=F32):
     return (torch.randn(shape, device="cuda", generator=g) * scale).to(dtype)
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 @pytest.mark.parametrize("M,N,K,bn", [(128, 256, 64, 0), (256, 512, 512, 256), (200, 384, 320, 128), (1920, 2048, 2048, 0),
                                       (64, 96, 96, 0), (640, 2048, 5888, 128), (130, 64, 128, 64), (700, 192, 192, 0),
                                       (5000, 8192, 256, 0), (1920, 11776, 2048, 256)])
@@ -47,7 +47,7 @@ def test_gemm_plain(ops, impl, M, N, K, bn):
     assert rel_l2(outb.float(), ref) < 4e-3
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 def test_gemm_generic_epilogue_full(ops, L, impl):
     M, N, K, S = 384, 256, 192, 128
     a, w = _rand((M, K), 4, dtype=BF16), _rand((N, K), 5, K ** -0.5, BF16)
@@ -61,7 +61,7 @@ def test_gemm_generic_epilogue_full(ops, L, impl):
     assert rel_l2(sn.float(), ref + torch.sin(alpha * ref) ** 2 / (alpha + 1e-9)) < 4e-3
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 @pytest.mark.parametrize("dil,taps_n,C,N,B,T", [(1, 7, 128, 128, 2, 300), (9, 7, 96, 96, 1, 700), (3, 7, 64, 256, 3, 130)])
 def test_gemm_causal_conv_taps(ops, impl, dil, taps_n, C, N, B, T):
     """implicit-GEMM causal dilated conv1d == F.conv1d on left-padded input (autoencoder.py:285-289)."""
@@ -76,7 +76,7 @@ def test_gemm_causal_conv_taps(ops, impl, dil, taps_n, C, N, B, T):
     assert rel_l2(out, ref) < 2e-5
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 def test_gemm_conv_transpose(ops, impl):
     """2-tap GEMM == causal ConvTranspose1d(k=2s, stride s) with right trim (autoencoder.py:310-316)."""
     from echo_tts_b200.autoencoder import _pack_convT
@@ -89,7 +89,7 @@ def test_gemm_conv_transpose(ops, impl):
     assert rel_l2(out.view(B, T * s, Cout), ref.transpose(1, 2)) < 2e-5
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 def test_gemm_swiglu(ops, impl):
     M, K, F_ = 256, 256, 384
     a = _rand((M, K), 14, dtype=BF16)
@@ -100,7 +100,7 @@ def test_gemm_swiglu(ops, impl):
     assert rel_l2(out.float(), ref) < 4e-3
 
 
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 @pytest.mark.parametrize("hd,H,rope_heads", [(128, 4, 2), (64, 4, 4)])
 def test_gemm_sections_norm_rope(ops, L, impl, hd, H, rope_heads):
     from oracle import echo_oracle as O

@@ -41,18 +41,34 @@ def test_tiny_sampler_vs_reference_fixture(tiny_model, name):
     assert rel_l2(out, g["x_final"]) < X_TOL
 
 
-def test_tiny_sampler_teacher_forced_vs_oracle(tiny_model):
-    """Each step's velocities at the ORACLE's x_t (no error accumulation): isolates the forward pass."""
+@pytest.mark.parametrize("init,c_tol", [
+    ("torch", V_TOL),   # the contract: nn.Linear-default-init weights (what random-init of the reference gives), 1e-2 on
+                        # the COMBINED velocity too (12 v_c - 3 v_ut - 8 v_us amplifies branch error ~10x)
+    ("unit", 5e-2),     # stress: unit-gain weights, every sub-layer O(1) of the residual stream (documented looser bound)
+])
+def test_tiny_sampler_teacher_forced_vs_oracle(init, c_tol):
+    """Each step's velocities at the ORACLE's x_t (teacher forcing: no error accumulation): isolates the forward pass."""
     from oracle import echo_oracle as O
-    g, out, trace = _run_fixture(tiny_model, "dit_tiny_sampler_opts.pt")
-    sd = S.synth_state_dict(S.dit_schema(S.ECHO_TINY))
-    otrace = []
+    from echo_tts_b200.inference import load_model_from_state_dict
+    from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
+    g = torch.load(os.path.join(GOLDEN, "dit_tiny_sampler_opts.pt"))
+    sd = S.synth_state_dict(S.dit_schema(S.ECHO_TINY), init=init)
+    model = load_model_from_state_dict(sd, cfg=S.ECHO_TINY)
+    otrace, trace = [], []
     O.sample_euler_cfg_independent_guidances(sd, S.ECHO_TINY, g["speaker_latent"], g["speaker_mask"], g["ids"],
                                              g["text_mask"], 0, noise=g["noise"], trace=otrace, **g["kwargs"])
+    sample(model, g["speaker_latent"].cuda(), g["speaker_mask"].cuda(), g["ids"].cuda(), g["text_mask"].cuda(), 0,
+           _noise=g["noise"], _trace=trace, _teacher={b["i"]: b["x_in"] for b in otrace}, **g["kwargs"])
+    worst = 0.0
     for a, b in zip(trace, otrace):
         assert a["has_cfg"] == b["has_cfg"]
-        assert rel_l2(a["x_in"].cpu(), b["x_in"]) < X_TOL
-        assert rel_l2(a["v"].cpu(), b["v"]) < 5e-2          # combined velocity: CFG amplifies branch error ~10x
+        assert torch.equal(a["x_in"].cpu(), b["x_in"].view_as(a["x_in"]))
+        n = 3 if a["has_cfg"] else 1
+        for va, vb in zip(a["v_branches"].cpu().chunk(n, 0), b["v_branches"].chunk(n, 0)):
+            assert rel_l2(va, vb) < V_TOL
+        worst = max(worst, rel_l2(a["v"].cpu(), b["v"]))
+    print(f"tiny teacher-forced ({init} init): worst combined velocity rel-L2 {worst:.3e} (tol {c_tol})")
+    assert worst < c_tol
 
 
 def test_graph_replay_equals_eager(tiny_model):

@@ -23,7 +23,7 @@ def ops():
 
 
 # ---- kernel-level: the two descriptor fields streaming adds ----------------------------------------------------------
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [2])
 @pytest.mark.parametrize("dil,C,N,T,ctx", [(1, 128, 128, 300, 6), (9, 96, 96, 40, 54), (3, 64, 256, 5, 18)])
 def test_gemm_left_context_rows(ops, impl, dil, C, N, T, ctx):
     """a_ctx: a dilated causal conv over rows [ctx, ctx+T) of a buffer reads the rows in front of it instead of zeros

@@ -81,6 +81,27 @@ def test_full_arch_blockwise_matches_reference_fixture():
 
 
 @pytest.mark.slow
+def test_full_size_block_behind_prefix_matches_reference_fixture():
+    """Oracle vs the upstream blockwise sampler at BASELINE configs[4]'s size: a 160-latent block behind a 480-latent
+    prefix (oracle/gen_golden_full.py c5) -- per-branch and combined velocities of both steps and the block's latent."""
+    from oracle.gen_golden_full import c5_inputs
+    g = torch.load(os.path.join(GOLDEN, "dit_base_c5.pt"))
+    ids, mask, spk, smask, cont, noise = c5_inputs()
+    assert abs(float(cont.double().sum() + noise.double().sum() + spk.double().sum()) - g["input_checksum"]) < 1e-6
+    sd = S.synth_state_dict(S.dit_schema(S.ECHO_BASE), init=g["init"])
+    trace = []
+    out = O.sample_blockwise_euler_cfg_independent_guidances(sd, S.ECHO_BASE, spk, smask, ids, mask, 0,
+                                                             continuation_latent=cont, noises=[noise], trace=trace,
+                                                             **g["kwargs"])
+    assert rel_l2(out[:, 480:], g["out_block"]) < 2e-5
+    assert len(trace) == len(g["steps"]) == 2
+    for mine, ref in zip(trace, g["steps"]):
+        assert mine["has_cfg"] == ref["has_cfg"]
+        assert rel_l2(mine["v_branches"], ref["v_branches"].float()) < 1e-3     # branches are stored in fp16
+        assert rel_l2(mine["v"], ref["v"]) < 1e-4
+
+
+@pytest.mark.slow
 def test_ae_decode_matches_reference_fixture():
     g = torch.load(os.path.join(GOLDEN, "ae_base_decode.pt"))
     sd = S.synth_ae_state_dict(S.AE_BASE)

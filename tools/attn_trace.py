@@ -40,7 +40,7 @@ def main():
     torch.cuda.synchronize()
     n = 5 * H * R
     buf = torch.zeros((n, 64), device="cuda", dtype=torch.int64)
-    lib.echo_debug_attn_trace(buf.data_ptr())
+    L.check(lib.echo_debug_attn_trace(buf.data_ptr()))   # needs the debug build: make -C echo_tts_b200/csrc DEBUG=1
     torch.cuda.synchronize()
     fn()
     torch.cuda.synchronize()

@@ -53,7 +53,7 @@ def main():
             fn()
         torch.cuda.synchronize()
         buf.zero_()
-        lib.echo_debug_gemm_trace(buf.data_ptr())
+        L.check(lib.echo_debug_gemm_trace(buf.data_ptr()))   # needs the debug build: make -C echo_tts_b200/csrc DEBUG=1
         fn()
         torch.cuda.synchronize()
         lib.echo_debug_gemm_trace(None)
