@@ -25,10 +25,9 @@ def main():
     from echo_tts_b200 import schema as S
     from echo_tts_b200.inference import load_model_from_state_dict, load_fish_ae_from_state_dict, ae_decode, PCAState
     from echo_tts_b200.sampler import sample_euler_cfg_independent_guidances as sample
-    from oracle import echo_oracle as O   # synthetic PCA constants only
     model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(S.ECHO_BASE, blockwise=False), init="torch"))
     ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(S.AE_BASE))
-    comp, mean, scale = O.synth_pca()
+    comp, mean, scale = S.synth_pca()
     pca = PCAState(comp.cuda(), mean.cuda(), scale)
     ids, mask, spk, smask = [t.cuda() for t in bench.synth_inputs(args.batch)]
     kw = dict(bench.KW, num_steps=2)          # t = 0.999 (CFG on), 0.4995 (CFG off)
