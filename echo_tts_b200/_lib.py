@@ -197,6 +197,10 @@ EXPORTS = {
     "echo_snake_bf16": (C.c_int, [c_p, i64, C.c_int, c_p, c_p, c_p]),
     "echo_rmsnorm_f32": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, c_p]),
     "echo_vq_nearest": (C.c_int, [c_p, C.c_int, C.c_int, c_p, c_p, C.c_int, c_p, c_p, c_p]),
+    "echo_split_bf16x3": (C.c_int, [c_p, i64, i64, C.c_int, C.c_int, c_p, c_p, i64, c_p]),
+    "echo_rope_f32": (C.c_int, [c_p, i64, i64, C.c_int, C.c_int, c_p, c_p, C.c_int, C.c_int, C.c_int, c_p]),
+    "echo_attention_window_f32": (C.c_int, [c_p, c_p, c_p, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, f32, c_p, i64, c_p]),
+    "echo_dwconv_layernorm_f32": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, f32, c_p, c_p]),
     "echo_resample_mono": (C.c_int, [c_p, C.c_int, i64, i64, C.c_int, C.c_int, C.c_int, c_p, c_p, c_p, c_p, i64, c_p, c_p]),
     "echo_peak_normalize": (C.c_int, [c_p, i64, c_p, f32, c_p]),
     "echo_flattening_point": (C.c_int, [c_p, C.c_int, C.c_int, C.c_int, f32, f32, c_p, c_p]),

@@ -28,9 +28,9 @@ def _fold_wn(sd, prefix: str, dev) -> torch.Tensor:
     return g * v / v.flatten(1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
 
 
-def _pack_conv(w: torch.Tensor) -> torch.Tensor:
+def _pack_conv(w: torch.Tensor, dtype=BF16) -> torch.Tensor:
     """Conv1d weight [Cout, Cin, K] -> GEMM B operand [Cout, K*Cin] (tap-major K axis), bf16."""
-    return w.permute(0, 2, 1).reshape(w.shape[0], -1).to(BF16).contiguous()
+    return w.permute(0, 2, 1).reshape(w.shape[0], -1).to(dtype).contiguous()
 
 
 def _fold_wn_plain(sd, prefix: str, dev) -> torch.Tensor:
@@ -40,14 +40,14 @@ def _fold_wn_plain(sd, prefix: str, dev) -> torch.Tensor:
     return g * v / v.flatten(1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
 
 
-def _pack_conv_strided(w: torch.Tensor, stride: int) -> torch.Tensor:
+def _pack_conv_strided(w: torch.Tensor, stride: int, dtype=BF16) -> torch.Tensor:
     """Strided causal Conv1d weight [Cout, Cin, K], K = taps*stride (left pad K - stride, autoencoder.py:283-289) ->
     GEMM B operand [Cout, taps * stride*Cin] over the input viewed as [T/stride, stride*Cin] rows:
     out[t] = sum_tap sum_j sum_ci x[(t - (taps-1) + tap)*stride + j, ci] * w[co, ci, tap*stride + j]."""
     cout, cin, k = w.shape
     taps = k // stride
     assert taps * stride == k
-    return w.reshape(cout, cin, taps, stride).permute(0, 2, 3, 1).reshape(cout, k * cin).to(BF16).contiguous()
+    return w.reshape(cout, cin, taps, stride).permute(0, 2, 3, 1).reshape(cout, k * cin).to(dtype).contiguous()
 
 
 def _pack_convT(w: torch.Tensor, stride: int) -> torch.Tensor:
@@ -147,22 +147,21 @@ class DAC:
         n = len(cfg.encoder_rates)
         for i, r in enumerate(cfg.encoder_rates):
             b = f"{eb}.{i + 1}.block"
-            blk = dict(rate=r, units=[], alpha_out=f(f"{b}.3.alpha").reshape(-1),
-                       wd=_pack_conv_strided(_fold_wn(sd, f"{b}.4", dev), r), bd=f(f"{b}.4.conv.bias"))
+            blk = dict(rate=r, units=[], alpha_out=f(f"{b}.3.alpha").reshape(-1), bd=f(f"{b}.4.conv.bias"))
             for j, dil in enumerate((1, 3, 9)):
                 ru = f"{b}.{j}.block"
                 blk["units"].append(dict(dil=dil, a1=f(f"{ru}.0.alpha").reshape(-1), a2=f(f"{ru}.2.alpha").reshape(-1),
-                                         w7=_pack_conv(_fold_wn(sd, f"{ru}.1", dev)), b7=f(f"{ru}.1.conv.bias"),
-                                         w1=_pack_conv(_fold_wn(sd, f"{ru}.3", dev)), b1=f(f"{ru}.3.conv.bias")))
+                                         b7=f(f"{ru}.1.conv.bias"), b1=f(f"{ru}.3.conv.bias")))
             self.enc_blocks.append(blk)
         self.enc_tr = (self._load_transformer(sd, f"{eb}.{n}.block.5", cfg.enc_tr_layers) if cfg.enc_tr_layers > 0 else None)
         self.enc_alpha_out = f(f"{eb}.{n + 1}.alpha").reshape(-1)
-        self.enc_out_w, self.enc_out_b = _pack_conv(_fold_wn(sd, f"{eb}.{n + 2}", dev)), f(f"{eb}.{n + 2}.conv.bias")
+        self.enc_out_b = f(f"{eb}.{n + 2}.conv.bias")
         self.downs = []
         for u, fac in enumerate(cfg.up_factors):
             p = f"quantizer.downsample.{u}"
             d = self._load_convnext(sd, f"{p}.1")
-            d.update(factor=fac, wd=_pack_conv_strided(sd[f"{p}.0.conv.weight"].to(dev).float(), fac), bd=f(f"{p}.0.conv.bias"))
+            d.update(factor=fac, bd=f(f"{p}.0.conv.bias"))
+            del d["pw1"], d["pw2"]
             self.downs.append(d)
         self.pre_tr = self._load_transformer(sd, "quantizer.pre_module", cfg.tr_layers)
         self.quantizers = []
@@ -174,6 +173,48 @@ class DAC:
             self.quantizers.append(dict(w_in=w_in, b_in=f(f"{p}.in_proj.bias"), w_out=w_out, b_out=f(f"{p}.out_proj.bias"),
                                         w_out_neg=(-w_out).contiguous(), b_out_neg=(-f(f"{p}.out_proj.bias")).contiguous(),
                                         cb=cb, cbn=torch.nn.functional.normalize(cb).contiguous()))   # autoencoder.py:149
+        self._load_encoder_split(sd)
+
+    def _load_encoder_split(self, sd) -> None:
+        """The encode half's GEMM weights once more as two-term bf16 splits ([w_hi | w_hi | w_lo] per group of input
+        channels, ``ops.pack_split_weight``): operands of the three-product fp32-class GEMMs in front of the RVQ's
+        integer decision (csrc/precise.cu)."""
+        cfg, dev = self.cfg, self._device
+        eb = "encoder.block"
+        n = len(cfg.encoder_rates)
+        C = cfg.encoder_dim
+        for i, blk in enumerate(self.enc_blocks):
+            b = f"{eb}.{i + 1}.block"
+            for j, u in enumerate(blk["units"]):
+                ru = f"{b}.{j}.block"
+                u["w7s"] = ops.pack_split_weight(_pack_conv(_fold_wn(sd, f"{ru}.1", dev), F32), C)
+                u["w1s"] = ops.pack_split_weight(_pack_conv(_fold_wn(sd, f"{ru}.3", dev), F32), C)
+            blk["wds"] = ops.pack_split_weight(_pack_conv_strided(_fold_wn(sd, f"{b}.4", dev), blk["rate"], F32), C)
+            C *= 2
+        self.enc_out_ws = ops.pack_split_weight(_pack_conv(_fold_wn(sd, f"{eb}.{n + 2}", dev), F32), C)
+        D = cfg.latent_dim
+        for u, dw in enumerate(self.downs):
+            p = f"quantizer.downsample.{u}"
+            dw["wds"] = ops.pack_split_weight(_pack_conv_strided(sd[f"{p}.0.conv.weight"].to(dev).float(), dw["factor"], F32), D)
+            w1, w2 = sd[f"{p}.1.pwconv1.weight"].to(dev).float(), sd[f"{p}.1.pwconv2.weight"].to(dev).float()
+            dw["pw1s"], dw["pw2s"] = ops.pack_split_weight(w1, w1.shape[1]), ops.pack_split_weight(w2, w2.shape[1])
+
+        def tr_split(tw, pm, n_layers):
+            for i in range(n_layers):
+                p, lw = f"{pm}.layers.{i}", tw["layers"][i]
+                g = lambda k: sd[f"{p}.{k}.weight"].to(dev).float()
+                lw["wqkvs"] = ops.pack_split_weight(g("attention.wqkv"), g("attention.wqkv").shape[1])
+                lw["wos"] = ops.pack_split_weight(g("attention.wo"), g("attention.wo").shape[1])
+                w13 = torch.cat([g("feed_forward.w1"), g("feed_forward.w3")], 0)              # un-interleaved [w1; w3]
+                lw["w13s"] = ops.pack_split_weight(w13, w13.shape[1])
+                lw["w2s"] = ops.pack_split_weight(g("feed_forward.w2"), g("feed_forward.w2").shape[1])
+        if self.enc_tr is not None:
+            tr_split(self.enc_tr, f"{eb}.{n}.block.5", cfg.enc_tr_layers)
+        tr_split(self.pre_tr, "quantizer.pre_module", cfg.tr_layers)
+        for tw in (self.enc_tr, self.pre_tr):        # the plain bf16 operands serve the decode half's post_module only
+            for lw in (tw["layers"] if tw is not None else []):
+                for k in ("wqkv", "wo", "w13", "w2"):
+                    del lw[k]
 
     @property
     def device(self):
@@ -233,68 +274,90 @@ class DAC:
     # ------------------------------------------------------------------------------------------
     # encode half
     # ------------------------------------------------------------------------------------------
-    def _residual_units(self, units, x, s1, s2, B: int, next_alpha) -> None:
-        """Three ResidualUnits (autoencoder.py:879-900): x fp32 residual stream in place; s1 = snake(x) bf16 on entry,
-        = snake(x_out, next_alpha) on exit."""
-        for j, u in enumerate(units):
-            d = u["dil"]
-            ops.gemm_generic(s1, u["w7"], taps=tuple(-(6 - k) * d for k in range(7)), batch=B, bias=u["b7"],
-                             out2_bf16=s2, snake_alpha=u["a2"])
-            nxt = units[j + 1]["a1"] if j + 1 < len(units) else next_alpha
-            ops.gemm_generic(s2, u["w1"], batch=B, bias=u["b1"], resid=x, out2_bf16=s1, snake_alpha=nxt,
-                             out_f32=(x if j + 1 < len(units) else None))   # after the last unit only snake(x) is read
+    # ------------------------------------------------------------------------------------------
+    # fp32-class encode (the path encode_zq runs): every contraction as a three-product split-bf16 GEMM over fp32
+    # activations (csrc/precise.cu) so that the RVQ codes -- an integer decision -- equal the reference's fp32 run
+    # ------------------------------------------------------------------------------------------
+    def _transformer_split(self, x: torch.Tensor, B: int, T: int, tw: dict, *, heads: int, ffn: int, window: int) -> torch.Tensor:
+        """WindowLimitedTransformer (autoencoder.py:744-802) on an fp32 residual stream [B*T, D] (in place) -> final
+        RMSNorm fp32 [B*T, D]."""
+        cfg, dev = self.cfg, self._device
+        M, D = x.shape
+        Dh = cfg.tr_head_dim
+        assert heads * Dh == D and T <= tw["rope"][0].shape[0]
+        xn = torch.empty((M, D), device=dev, dtype=F32)
+        a = torch.empty((M, 3 * D), device=dev, dtype=BF16)
+        qkv = torch.empty((M, 3 * D), device=dev, dtype=F32)
+        ao = torch.empty((M, D), device=dev, dtype=F32)
+        h13 = torch.empty((M, 2 * ffn), device=dev, dtype=F32)
+        ah = torch.empty((M, 3 * ffn), device=dev, dtype=BF16)
+        for lw in tw["layers"]:
+            ops.rmsnorm_f32(x, lw["an"], xn, cfg.tr_eps)
+            ops.split_bf16x3(xn, a)
+            ops.gemm_generic(a, lw["wqkvs"], out_f32=qkv)
+            ops.rope_f32(qkv[:, :D], heads, Dh, tw["rope"], T)
+            ops.rope_f32(qkv[:, D:2 * D], heads, Dh, tw["rope"], T)
+            ops.attention_window_f32(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], ao, batch=B, heads=heads, head_dim=Dh,
+                                     window=window)
+            ops.split_bf16x3(ao, a)
+            ops.gemm_generic(a, lw["wos"], gate=lw["ga"], resid=x, out_f32=x)
+            ops.rmsnorm_f32(x, lw["fn"], xn, cfg.tr_eps)
+            ops.split_bf16x3(xn, a)
+            ops.gemm_generic(a, lw["w13s"], out_f32=h13)
+            ops.split_bf16x3(h13, ah, mode=ops.SPLIT_SWIGLU)
+            ops.gemm_generic(ah, lw["w2s"], gate=lw["gf"], resid=x, out_f32=x)
+        ops.rmsnorm_f32(x, tw["norm"], xn, cfg.tr_eps)
+        return xn
 
-    def _encoder(self, audio: torch.Tensor):
-        """Encoder.forward (autoencoder.py:903-929): audio fp32 [B, T] (T a multiple of the hop) ->
-        (z fp32 [B*T', latent], z bf16 [B*T', latent], T' = T / prod(encoder_rates))."""
+    def _encoder_split(self, audio: torch.Tensor):
+        """Encoder.forward (autoencoder.py:903-929): audio fp32 [B, T] -> (z fp32 [B*T', latent], T')."""
         cfg, dev = self.cfg, self._device
         B, T = audio.shape
         C = self.enc_in_w.shape[0]
         x = torch.empty((B, T, C), device=dev, dtype=F32)
-        s1 = torch.empty((B, T, C), device=dev, dtype=BF16)
-        ops.conv_in_snake(audio, self.enc_in_w, self.enc_in_b, self.enc_blocks[0]["units"][0]["a1"], x, s1)
-        x, s1 = x.view(B * T, C), s1.view(B * T, C)
-        n = len(self.enc_blocks)
-        for i, blk in enumerate(self.enc_blocks):
+        scratch = torch.empty((B, T, C), device=dev, dtype=BF16)
+        ops.conv_in_snake(audio, self.enc_in_w, self.enc_in_b, self.enc_blocks[0]["units"][0]["a1"], x, scratch)
+        del scratch
+        x = x.view(B * T, C)
+        for blk in self.enc_blocks:
             r = blk["rate"]
-            s2 = torch.empty_like(s1)
-            self._residual_units(blk["units"], x, s1, s2, B, blk["alpha_out"])
-            del s2, x
+            t = torch.empty_like(x)
+            a = torch.empty((B * T, 3 * C), device=dev, dtype=BF16)
+            for u in blk["units"]:                               # ResidualUnit (autoencoder.py:879-900)
+                d = u["dil"]
+                ops.split_bf16x3(x, a, mode=ops.SPLIT_SNAKE, alpha=u["a1"])
+                ops.gemm_generic(a, u["w7s"], taps=tuple(-(6 - k) * d for k in range(7)), batch=B, bias=u["b7"], out_f32=t)
+                ops.split_bf16x3(t, a, mode=ops.SPLIT_SNAKE, alpha=u["a2"])
+                ops.gemm_generic(a, u["w1s"], batch=B, bias=u["b1"], resid=x, out_f32=x)
+            ops.split_bf16x3(x, a, mode=ops.SPLIT_SNAKE, alpha=blk["alpha_out"])
+            del t, x
             T, C = T // r, 2 * C
-            a = s1.view(B * T, r * C // 2)                   # strided conv = 2-tap conv over [T/r, r*C] rows
             x = torch.empty((B * T, C), device=dev, dtype=F32)
-            if i + 1 < n:
-                s1 = torch.empty((B * T, C), device=dev, dtype=BF16)
-                ops.gemm_generic(a, blk["wd"], taps=(-1, 0), batch=B, bias=blk["bd"], out_f32=x, out2_bf16=s1,
-                                 snake_alpha=self.enc_blocks[i + 1]["units"][0]["a1"])
-            else:
-                ops.gemm_generic(a, blk["wd"], taps=(-1, 0), batch=B, bias=blk["bd"], out_f32=x)
-        s = torch.empty((B * T, C), device=dev, dtype=BF16)
+            ops.gemm_generic(a.view(B * T, r * 3 * (C // 2)), blk["wds"], taps=(-1, 0), batch=B, bias=blk["bd"], out_f32=x)
+            del a
         if self.enc_tr is not None:
-            xn = self._transformer(x, B, T, self.enc_tr, heads=cfg.enc_tr_heads, ffn=3 * C, window=cfg.enc_tr_window)
-            ops.snake_bf16(xn, self.enc_alpha_out, s)
-        else:
-            ops.cast_snake(x, self.enc_alpha_out, s)
+            x = self._transformer_split(x, B, T, self.enc_tr, heads=cfg.enc_tr_heads, ffn=3 * C, window=cfg.enc_tr_window)
+        a = ops.split_bf16x3(x, mode=ops.SPLIT_SNAKE, alpha=self.enc_alpha_out)
         z = torch.empty((B * T, cfg.latent_dim), device=dev, dtype=F32)
-        zb = torch.empty((B * T, cfg.latent_dim), device=dev, dtype=BF16)
-        ops.gemm_generic(s, self.enc_out_w, taps=(-2, -1, 0), batch=B, bias=self.enc_out_b, out_f32=z, out_bf16=zb)
-        return z, zb, T
+        ops.gemm_generic(a, self.enc_out_ws, taps=(-2, -1, 0), batch=B, bias=self.enc_out_b, out_f32=z)
+        return z, T
 
-    def _downsample(self, zb: torch.Tensor, B: int, T: int):
-        """quantizer.downsample (autoencoder.py:416-425): zb bf16 [B*T, D] -> fp32 [B*T/prod(factors), D]."""
+    def _downsample_split(self, z: torch.Tensor, B: int, T: int):
+        """quantizer.downsample (autoencoder.py:416-425): z fp32 [B*T, D] -> fp32 [B*T/prod(factors), D]."""
         dev = self._device
-        D = zb.shape[1]
-        x = None
-        for i, dw in enumerate(self.downs):
+        D = z.shape[1]
+        x = z
+        for dw in self.downs:
             fac = dw["factor"]
+            a = ops.split_bf16x3(x)
             T //= fac
             x = torch.empty((B * T, D), device=dev, dtype=F32)
-            ops.gemm_generic(zb.view(B * T, fac * D), dw["wd"], batch=B, bias=dw["bd"], out_f32=x)   # k == stride: one tap
-            if i + 1 < len(self.downs):
-                zb = torch.empty((B * T, D), device=dev, dtype=BF16)
-                self._convnext(x, dw, B, T, out_bf16=zb)
-            else:
-                self._convnext(x, dw, B, T, out_f32=x)
+            ops.gemm_generic(a.view(B * T, fac * 3 * D), dw["wds"], batch=B, bias=dw["bd"], out_f32=x)   # k == stride: one tap
+            y = torch.empty((B * T, D), device=dev, dtype=F32)                                      # ConvNeXtBlock :340-373
+            ops.dwconv_layernorm_f32(x.view(B, T, D), dw["dw"], dw["dwb"], dw["lnw"], dw["lnb"], 1e-6, y.view(B, T, D))
+            hmid = torch.empty((B * T, dw["pw1s"].shape[0]), device=dev, dtype=F32)
+            ops.gemm_generic(ops.split_bf16x3(y), dw["pw1s"], bias=dw["pb1"], act=L.ACT_GELU, out_f32=hmid)
+            ops.gemm_generic(ops.split_bf16x3(hmid), dw["pw2s"], bias=dw["pb2"], gate=dw["gamma"], resid=x, out_f32=x)
         return x, T
 
     def _rvq(self, z: torch.Tensor):
@@ -333,9 +396,9 @@ class DAC:
         T = -(-n // hop) * hop                                     # right pad to whole frames (autoencoder.py:1091-1092)
         audio = torch.zeros((B, T), device=dev, dtype=F32)
         audio[:, :n] = a[:, 0].to(dev, F32)
-        z_enc, zb, Te = self._encoder(audio)
-        x, Tq = self._downsample(zb, B, Te)
-        z_pre = self._transformer(x, B, Tq, self.pre_tr, out_f32=True)
+        z_enc, Te = self._encoder_split(audio)
+        x, Tq = self._downsample_split(z_enc, B, Te)
+        z_pre = self._transformer_split(x, B, Tq, self.pre_tr, heads=cfg.tr_heads, ffn=cfg.tr_ffn, window=cfg.tr_window)
         codes, z_q = self._rvq(z_pre)
         cf = lambda t, Tn: t.view(B, Tn, -1).transpose(1, 2)
         return dict(z_enc=cf(z_enc, Te), z_pre=cf(z_pre, Tq), z_q=cf(z_q, Tq), z_q_rows=z_q,

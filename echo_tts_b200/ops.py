@@ -416,6 +416,70 @@ def rmsnorm_f32(x, weight, y, eps: float) -> None:
                                       L.stream()))
 
 
+SPLIT_PLAIN, SPLIT_SNAKE, SPLIT_SWIGLU = 0, 1, 2
+
+
+def split_bf16x3(x: torch.Tensor, out: Optional[torch.Tensor] = None, *, mode: int = SPLIT_PLAIN,
+                 alpha: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 [M, C] (2C columns in SWIGLU mode) -> bf16 [M, 3C] = [hi | lo | hi]: the activation operand of a
+    three-product split GEMM (csrc/precise.cu), with Snake / SwiGLU applied in fp32 first."""
+    _need(x, F32, "x")
+    assert x.dim() == 2 and x.stride(1) == 1
+    M, Cc = x.shape
+    if mode == SPLIT_SWIGLU:
+        assert Cc % 2 == 0
+        Cc //= 2
+    if out is None:
+        out = torch.empty((M, 3 * Cc), device=x.device, dtype=BF16)
+    _need(out, BF16, "out")
+    assert out.shape == (M, 3 * Cc) and out.stride(1) == 1
+    if alpha is not None:
+        _need(alpha, F32, "alpha"); assert alpha.numel() == Cc and alpha.is_contiguous()
+    L.check(L.load().echo_split_bf16x3(x.data_ptr(), x.stride(0), M, Cc, mode, L.ptr(alpha), out.data_ptr(), out.stride(0),
+                                       L.stream()))
+    return out
+
+
+def pack_split_weight(w2d: torch.Tensor, group: int) -> torch.Tensor:
+    """fp32 [N, G * group] (G taps / sub-steps of `group` input channels each) -> bf16 [N, G * 3 * group] with every
+    group laid out [w_hi | w_hi | w_lo]: the weight operand matching split_bf16x3's [hi | lo | hi] rows.  Load time."""
+    N, K = w2d.shape
+    assert K % group == 0
+    w = w2d.float().reshape(N, K // group, group)
+    hi = w.to(BF16)
+    lo = (w - hi.float()).to(BF16)
+    return torch.stack([hi, hi, lo], dim=2).reshape(N, 3 * K).contiguous()
+
+
+def rope_f32(x: torch.Tensor, heads: int, head_dim: int, rope: Tuple[torch.Tensor, torch.Tensor], rows_per_seq: int,
+             pos_offset: int = 0) -> None:
+    """Rotary embedding in place on fp32 rows x[:, :heads * head_dim] (interleaved pairs, all heads)."""
+    _need(x, F32, "x"); _need(rope[0], F32, "rope_cos"); _need(rope[1], F32, "rope_sin")
+    assert x.dim() == 2 and x.stride(1) == 1 and x.shape[1] >= heads * head_dim
+    assert rope[0].is_contiguous() and rope[1].is_contiguous() and rope[0].shape[1] == head_dim // 2
+    L.check(L.load().echo_rope_f32(x.data_ptr(), x.stride(0), x.shape[0], heads, head_dim, rope[0].data_ptr(),
+                                   rope[1].data_ptr(), rope[0].shape[0], rows_per_seq, pos_offset, L.stream()))
+
+
+def attention_window_f32(q, k, v, out, *, batch: int, heads: int, head_dim: int, window: int) -> None:
+    """fp32 causal sliding-window attention: q / k / v fp32 [B*T, >= H*Dh] views sharing one row stride, out fp32."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (out, "out")):
+        _need(t, F32, n); assert t.dim() == 2 and t.stride(1) == 1
+    assert q.stride(0) == k.stride(0) == v.stride(0) and q.shape[0] % batch == 0 and out.shape[0] == q.shape[0]
+    L.check(L.load().echo_attention_window_f32(q.data_ptr(), k.data_ptr(), v.data_ptr(), q.stride(0), batch,
+                                               q.shape[0] // batch, heads, head_dim, window, head_dim ** -0.5,
+                                               out.data_ptr(), out.stride(0), L.stream()))
+
+
+def dwconv_layernorm_f32(x, w_dw, b_dw, ln_w, ln_b, eps, y) -> None:
+    """x fp32 [B, T, C] -> y fp32 [B, T, C] (ConvNeXt depthwise conv k = 7 + LayerNorm, fp32 result)."""
+    _need(x, F32, "x"); _need(y, F32, "y")
+    B, T, Cc = x.shape
+    assert x.is_contiguous() and y.is_contiguous()
+    L.check(L.load().echo_dwconv_layernorm_f32(x.data_ptr(), B, T, Cc, w_dw.data_ptr(), b_dw.data_ptr(), ln_w.data_ptr(),
+                                               ln_b.data_ptr(), eps, y.data_ptr(), L.stream()))
+
+
 def vq_nearest(e, codebook_normalized, codebook, index_out, code_out=None) -> None:
     """e fp32 [M, 8] -> index_out int32 [M] (nearest l2-normalised code), code_out fp32 [M, 8] raw code vectors."""
     _need(e, F32, "e"); _need(codebook_normalized, F32, "codebook_normalized"); _need(codebook, F32, "codebook")

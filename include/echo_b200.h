@@ -469,6 +469,29 @@ int echo_rmsnorm_f32(const float* x, int64_t ldx, int m, int d, float eps, const
 int echo_vq_nearest(const float* e, int m, int dim, const float* codebook_normalized, const float* codebook, int n,
                     int32_t* index_out, float* code_out, echo_stream_t stream);
 
+/* fp32-class arithmetic of the encode path (csrc/precise.cu): the RVQ nearest-code search is an integer decision, so
+ * every contraction in front of it (Encoder autoencoder.py:903-929, downsample :416-425, pre_module :744-802) runs on
+ * echo_gemm_bf16 with both operands split in two bf16 terms and three products accumulated in fp32
+ * (x w ~= hi w_hi + lo w_hi + hi w_lo): the activation operand is laid out [hi | lo | hi] along K by echo_split_bf16x3,
+ * the weights are packed [w_hi | w_hi | w_lo] per tap at load.
+ * echo_split_bf16x3: x fp32 [rows, c] (row stride ldx) -> out bf16 [rows, 3c] (row stride ldo).
+ *   mode 0: y = x;  1: y = snake(x, alpha[c]) (Snake1d :96-109, precise sinf);
+ *   mode 2: y = silu(x[:, :c]) * x[:, c:2c] (FeedForward :717; x has 2c columns). */
+int echo_split_bf16x3(const float* x, int64_t ldx, int64_t rows, int c, int mode, const float* alpha, void* out_bf16,
+                      int64_t ldo, echo_stream_t stream);
+/* apply_rotary_emb (autoencoder.py:816-826) in place on fp32 rows [rows, ldx]: heads x head_dim columns, interleaved
+ * pairs, position = pos_offset + row % rows_per_seq; cos / sin fp32 [rope_len, head_dim / 2]. */
+int echo_rope_f32(float* x, int64_t ldx, int64_t rows, int heads, int head_dim, const float* cos_t, const float* sin_t,
+                  int rope_len, int rows_per_seq, int pos_offset, echo_stream_t stream);
+/* fp32 causal sliding-window attention (WindowLimitedTransformer mask, autoencoder.py:762-773: key j visible to query
+ * i iff i - window < j <= i): q / k / v fp32 rows [batch * t, ld] with head h at columns h * 64 (head_dim must be 64),
+ * out fp32 [batch * t, ldo]. */
+int echo_attention_window_f32(const float* q, const float* k, const float* v, int64_t ld, int batch, int t, int heads,
+                              int head_dim, int window, float softmax_scale, float* out, int64_t ldo, echo_stream_t stream);
+/* echo_dwconv_layernorm with an fp32 result (ConvNeXtBlock front, autoencoder.py:362-364). */
+int echo_dwconv_layernorm_f32(const float* x, int batch, int t, int c, const float* w_dw, const float* b_dw,
+                              const float* ln_w, const float* ln_b, float eps, float* y, echo_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Audio front-end (load_audio, inference.py:141-149), after the file has been decoded to PCM on the host.
  * ------------------------------------------------------------------------------------------ */

@@ -1,8 +1,8 @@
 """S1-DAC encode on the sm_100a path against the reference fixtures and the CPU oracle.
 
-The nearest-code search is a discrete decision: with bf16 tensor-core convolutions upstream a small fraction of
-frames lands on a neighbouring code (the reference run in bf16 does the same), so parity is pinned stage by stage:
-continuous tensors within tolerance, and the quantizer itself bit-exact on identical fp32 input."""
+The nearest-code search is a discrete decision, so the contractions in front of it run at fp32-class accuracy
+(three-product split-bf16 GEMMs on the tcgen05 kernel, fp32 activations, csrc/precise.cu) and the codes must be
+IDENTICAL to the reference's fp32 run; continuous tensors are held to the fixtures' storage precision."""
 import os
 
 import pytest
@@ -78,27 +78,95 @@ def test_vq_nearest_bit_exact_vs_torch():
 
 @pytest.mark.parametrize("name,cfg", [("ae_encode_tiny.pt", S.AE_TINY), ("ae_encode_base.pt", S.AE_BASE)])
 def test_encode_vs_reference_fixture(name, cfg):
+    """DAC.encode / encode_zq (autoencoder.py:1080-1126) against the upstream fp32 run: the RVQ codes are integers and
+    must be IDENTICAL; the continuous stages sit at the fixture's own storage precision (fp16: 5e-4)."""
     g = torch.load(os.path.join(GOLDEN, name))
     dac = _dac(cfg)
     st = dac.encode_stages(g["audio"].cuda())
     assert st["z_q"].shape == g["z_q"].shape and st["codes"].shape == g["codes"].shape and st["codes"].dtype == torch.int64
-    # continuous stages: bf16 tensor-core operands vs the reference's fp32 run
-    assert rel_l2(st["z_enc"].cpu(), g["z_enc"].float()) < 2e-2
-    assert rel_l2(st["z_pre"].cpu(), g["z_pre"].float()) < 2e-2
-    # discrete stage: the semantic code (level 0) of a frame flips only on near-ties
-    same0 = (st["codes"][:, 0].cpu() == g["codes"][:, 0]).float().mean().item()
-    assert same0 > 0.8, same0
-    # quantizer alone, teacher-forced with the reference's own fp32 input: bit-exact codes (up to exact fp32 ties)
-    z_pre = g["z_pre"].float().cuda()                                 # fp16-stored fixture: recompute the reference codes
+    e_enc, e_pre = rel_l2(st["z_enc"].cpu(), g["z_enc"].float()), rel_l2(st["z_pre"].cpu(), g["z_pre"].float())
+    n_diff = int((st["codes"].cpu() != g["codes"]).sum())
+    print(f"{name}: z_enc rel-L2 {e_enc:.2e}, z_pre rel-L2 {e_pre:.2e} (fixture stored in fp16), "
+          f"codes differing {n_diff} of {g['codes'].numel()}")
+    assert e_enc < 1e-3 and e_pre < 1e-3
+    assert torch.equal(st["codes"].cpu(), g["codes"])                 # index handling: bit-exact
+    assert rel_l2(st["z_q"].cpu(), g["z_q"].float()) < 1e-3
+    if "latent" in g:                                                 # ae_encode (inference.py:223-229) incl. the PCA projection
+        from echo_tts_b200.inference import PCAState, ae_encode
+        comp, mean, scale = S.synth_pca()
+        lat = ae_encode(dac, PCAState(comp.cuda(), mean.cuda(), scale), g["audio"].cuda()).cpu()
+        err = (lat - g["latent"]).norm(dim=-1) / g["latent"].norm(dim=-1).clamp_min(1e-6)
+        assert lat.shape == g["latent"].shape and float(err.max()) < 1e-3, err
+    # the quantizer alone on the reference's own input reproduces the reference's codes as well
     from oracle import echo_oracle as O
     sd = S.synth_ae_state_dict(cfg, encode=True)
+    z_pre = g["z_pre"].float().cuda()
     want = O.rvq_codes(sd, cfg, z_pre.cpu())
     B, D, Tq = z_pre.shape
     codes, z_q = dac._rvq(z_pre.transpose(1, 2).reshape(B * Tq, D).contiguous())
     got = codes.view(-1, B, Tq).permute(1, 0, 2).long().cpu()
-    frames_equal = (got == want).all(dim=1).float().mean().item()
-    assert frames_equal > 0.97, frames_equal
+    assert torch.equal(got, want)
     assert rel_l2(z_q.view(B, Tq, D).transpose(1, 2).cpu(), O.zq_from_codes(sd, cfg, got)) < 1e-5
+
+
+def test_split_gemm_is_fp32_class():
+    """x w through split_bf16x3 / pack_split_weight on the tcgen05 GEMM (three bf16 products, fp32 accumulate) against
+    the fp64 product: ~1e-5 relative, against 4e-3 for plain bf16 operands; Snake and SwiGLU front-ends in fp32."""
+    from echo_tts_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    M, K, N = 300, 192, 96
+    x = torch.randn(M, K, generator=g).cuda()
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
+    out = torch.empty(M, N, device="cuda")
+    ops.gemm_generic(ops.split_bf16x3(x), ops.pack_split_weight(w, K), out_f32=out)
+    ref = (x.double() @ w.double().t()).float()
+    assert rel_l2(out, ref) < 3e-5
+    alpha = (0.5 + torch.rand(K, generator=g)).cuda()
+    ops.gemm_generic(ops.split_bf16x3(x, mode=ops.SPLIT_SNAKE, alpha=alpha), ops.pack_split_weight(w, K), out_f32=out)
+    xs = x.double() + torch.sin(alpha.double() * x.double()) ** 2 / (alpha.double() + 1e-9)
+    assert rel_l2(out, (xs @ w.double().t()).float()) < 3e-5
+    x2 = torch.randn(M, 2 * K, generator=g).cuda()
+    ops.gemm_generic(ops.split_bf16x3(x2, mode=ops.SPLIT_SWIGLU), ops.pack_split_weight(w, K), out_f32=out)
+    sw = torch.nn.functional.silu(x2[:, :K].double()) * x2[:, K:].double()
+    assert rel_l2(out, (sw @ w.double().t()).float()) < 3e-5
+    # taps: the packed groups follow the (tap, channel) K order of the implicit-GEMM convolution
+    import torch.nn.functional as F
+    B, T, C, Co = 2, 160, 32, 48
+    xc = torch.randn(B, T, C, generator=g).cuda()
+    wc = (torch.randn(Co, C, 7, generator=g) / (7 * C) ** 0.5).cuda()
+    oc = torch.empty(B * T, Co, device="cuda")
+    wp = ops.pack_split_weight(wc.permute(0, 2, 1).reshape(Co, -1), C)
+    ops.gemm_generic(ops.split_bf16x3(xc.view(B * T, C)), wp, taps=tuple(-(6 - k) * 3 for k in range(7)), batch=B, out_f32=oc)
+    refc = F.conv1d(F.pad(xc.double().transpose(1, 2), (18, 0)), wc.double(), dilation=3).transpose(1, 2).float()
+    assert rel_l2(oc.view(B, T, Co), refc) < 3e-5
+
+
+def test_window_attention_f32_and_rope_vs_torch():
+    from echo_tts_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    for B, T, H, W in ((2, 100, 2, 16), (1, 300, 3, 128), (1, 40, 1, 512)):
+        D = H * 64
+        qkv = torch.randn(B * T, 3 * D, generator=g).cuda()
+        ang = torch.rand(T + 5, 32, generator=g) * 6.28
+        rope = (torch.cos(ang).cuda().contiguous(), torch.sin(ang).cuda().contiguous())
+        ref_in = qkv.clone().double().view(B, T, 3, H, 64)
+
+        def rot(x):
+            xe, xo = x[..., 0::2], x[..., 1::2]
+            c, s_ = rope[0][:T].double()[None, :, None, :], rope[1][:T].double()[None, :, None, :]
+            return torch.stack([xe * c - xo * s_, xo * c + xe * s_], -1).flatten(-2)
+        qd, kd, vd = rot(ref_in[:, :, 0]), rot(ref_in[:, :, 1]), ref_in[:, :, 2]
+        ops.rope_f32(qkv[:, :D], H, 64, rope, T)
+        ops.rope_f32(qkv[:, D:2 * D], H, 64, rope, T)
+        assert rel_l2(qkv[:, :D].view(B, T, H, 64), qd.float()) < 1e-6
+        out = torch.empty(B * T, D, device="cuda")
+        ops.attention_window_f32(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], out, batch=B, heads=H, head_dim=64, window=W)
+        i = torch.arange(T, device="cuda")
+        win = (i[None, :] <= i[:, None]) & (i[None, :] > i[:, None] - W)
+        sc = torch.einsum("bthd,bshd->bhts", qd, kd) / 8.0
+        sc = sc.masked_fill(~win[None, None], float("-inf"))
+        ref = torch.einsum("bhts,bshd->bthd", torch.softmax(sc, -1), vd).reshape(B * T, D).float()
+        assert rel_l2(out, ref) < 2e-6
 
 
 def test_encode_interface_and_padding(tiny):
@@ -132,9 +200,8 @@ def test_speaker_latent_pipeline_vs_oracle(tiny):
     lat = ae_encode(tiny, pca, audio.cuda())
     want = O.ae_encode(S.synth_ae_state_dict(cfg, encode=True), cfg, comp, mean, scale, audio)
     assert lat.shape == want.shape == (1, 40, 80) and lat.dtype == torch.float32
-    # frames whose codes all agree must agree closely; the rest are near-tie flips (bounded fraction)
     err = (lat.cpu() - want).norm(dim=-1) / want.norm(dim=-1).clamp_min(1e-6)
-    assert (err < 1e-3).float().mean().item() > 0.7
+    assert float(err.max()) < 1e-3, err                          # every frame: the codes are the oracle's
 
 
 def test_speaker_clip_trimmed_encode_equals_padded():
