@@ -143,7 +143,10 @@ def ae_encode(fish_ae, pca_state: PCAState, audio: torch.Tensor) -> torch.Tensor
 @torch.inference_mode()
 def ae_decode(fish_ae: DAC, pca_state: PCAState, z_q: torch.Tensor) -> torch.Tensor:
     """inference.py:232-235 -> waveform fp32 [B, 1, T*2048]."""
-    return fish_ae.decode_latent(z_q, pca_state.pca_components, pca_state.pca_mean, pca_state.latent_scale).float()
+    torch.cuda.nvtx.range_push("echo.ae_decode")
+    wav = fish_ae.decode_latent(z_q, pca_state.pca_components, pca_state.pca_mean, pca_state.latent_scale).float()
+    torch.cuda.nvtx.range_pop()
+    return wav
 
 
 @torch.inference_mode()

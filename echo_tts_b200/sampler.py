@@ -86,6 +86,7 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
     use_rescale = p["rescale_k"] is not None and p["rescale_sigma"] is not None
     n = len(plan.has_cfg)
     lib = L.load()
+    torch.cuda.nvtx.range_push(f"echo.euler_steps[{n}]")
 
     def step(R: int, i: int, **tail_kw):
         tail = ops.tail_desc(model.out_norm, model.out_w, model.out_b, positions=B * S, branches=R // B,
@@ -106,6 +107,7 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
                                     n, C.cast(flags, C.c_void_p), mod.stride(0),
                                     plan.kv_mult.stride(0) if plan.uses_kv_scale else 0, plan.sched.stride(0),
                                     L.stream()))
+        torch.cuda.nvtx.range_pop()
         return [keep3, keep1]
     for i, has_cfg in enumerate(plan.has_cfg):
         R = 3 * B if has_cfg else B
@@ -117,6 +119,7 @@ def run_steps(model: EchoDiT, x_t: torch.Tensor, plan: StepPlan, mod: torch.Tens
         d, keep = step(R, i, v_out=v_out, v_comb_out=v_comb)
         L.check(lib.echo_dit_step(C.byref(d), L.stream()))
         trace.append(dict(i=i, has_cfg=has_cfg, x_in=x_in, v_branches=v_out.view(R, S, -1), v=v_comb.view(B, S, -1)))
+    torch.cuda.nvtx.range_pop()
     return []
 
 
@@ -187,9 +190,12 @@ def sample_euler_cfg_independent_guidances(
         x_t = x_t * truncation_factor
 
     def conditioning(ids, tmask, spk, smask):
+        torch.cuda.nvtx.range_push("echo.conditioning")
         kv_t = model.get_kv_cache_text(ids, tmask)                                         # inference.py:482
         kv_s = model.get_kv_cache_speaker(spk)                                             # inference.py:483
-        return kv_t, kv_s, _prep_masks(model, tmask, smask)
+        out = kv_t, kv_s, _prep_masks(model, tmask, smask)
+        torch.cuda.nvtx.range_pop()
+        return out
 
     use_rescale = rescale_k is not None and rescale_sigma is not None
     key = ("euler", B, S, text_input_ids.shape[1], speaker_latent.shape[1], num_steps, tuple(plan.has_cfg), use_rescale,
@@ -233,7 +239,9 @@ def sample_euler_cfg_independent_guidances(
     if plan.uses_kv_scale:
         st["plan"].kv_mult.copy_(plan.kv_mult)
     st["plan"].sched.copy_(plan.sched)
+    torch.cuda.nvtx.range_push("echo.sampler_graph_replay")
     ent.graph.replay()
+    torch.cuda.nvtx.range_pop()
     return st["x_t"].clone().view(B, S, cfg.latent_size)
 
 

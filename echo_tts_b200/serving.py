@@ -90,7 +90,8 @@ def sample_euler_cfg_split(model, speaker_latent, speaker_mask, text_input_ids, 
                            cfg_scale_text: float, cfg_scale_speaker: float, cfg_min_t: float, cfg_max_t: float,
                            truncation_factor, rescale_k, rescale_sigma, speaker_kv_scale, speaker_kv_max_layers,
                            speaker_kv_min_t, sequence_length: Optional[int] = None, *, group=None,
-                           exchange: str = "nccl", _noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+                           exchange: str = "nccl", use_graph: bool = True,
+                           _noise: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``sample_euler_cfg_independent_guidances`` with the three guidance branches of every CFG step evaluated on
     three GPUs (ranks 0/1/2 of ``group`` = cond / text-dropped / speaker-dropped; every rank holds the full model and
     receives the same inputs and seed).  Per CFG step: one forward over B rows instead of 3B, ONE all-gather of the
@@ -119,10 +120,6 @@ def sample_euler_cfg_split(model, speaker_latent, speaker_mask, text_input_ids, 
         x_t = torch.randn((B, S, cfg.latent_size), device=dev, dtype=F32, generator=rng)
     if truncation_factor is not None:
         x_t = x_t * truncation_factor
-    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)
-    kv_spk = model.get_kv_cache_speaker(speaker_latent)
-    tm3, te3, sm3, se3 = _prep_masks(model, text_mask, speaker_mask)
-    mod = model.build_mod_table(plan.t_dev)
     use_rescale = rescale_k is not None and rescale_sigma is not None
     mine = branch_rows(rank, B)
     P = B * S
@@ -130,39 +127,92 @@ def sample_euler_cfg_split(model, speaker_latent, speaker_mask, text_input_ids, 
         lib = __import__("echo_tts_b200._lib", fromlist=["load"]).load()
         v3_all, flags, hf, peer_v, peer_f = _p2p_buffers(group, rank, P, cfg.latent_size, dev)
         others = [r for r in range(3) if r != rank]
-        flags.zero_()
-        torch.cuda.synchronize()
-        hf.barrier()                                                             # nobody pushes before everyone zeroed
-        ctas, n_guided = int(lib.echo_cfg_tail_ctas(P)), 0
+        ctas = int(lib.echo_cfg_tail_ctas(P))
     elif exchange == "nccl":
         v3 = torch.empty((3, P, cfg.latent_size), device=dev, dtype=F32)
     else:
         raise ValueError(f"exchange must be 'nccl' or 'p2p', got {exchange!r}")
-    for i, has_cfg in enumerate(plan.has_cfg):
-        rows = mine if has_cfg else slice(0, B)
-        h, pending = model.forward_hidden(x_t, mod[i:i + 1], B, text_mask=tm3[rows], text_extent=te3[rows],
-                                          spk_mask=sm3[rows], spk_extent=se3[rows], kv_text=kv_text, kv_speaker=kv_spk,
-                                          spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
-        if has_cfg and exchange == "p2p":
-            par, n_guided = n_guided & 1, n_guided + 1
-            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
-                               v_out=v3_all[par, rank], update_x=False, delta=pending,
-                               push_to=[(pv[par, rank], pf[rank:rank + 1]) for pv, pf in zip(peer_v, peer_f)])
-            ops.cfg_combine_euler(v3_all[par], x_t.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
-                                  cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
-                                  rescale_sigma=rescale_sigma if use_rescale else None,
-                                  wait=(flags[others[0]:others[0] + 1], flags[others[1]:others[1] + 1], ctas * n_guided))
-        elif has_cfg:
-            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
-                               v_out=v3[rank], update_x=False, delta=pending)
-            dist.all_gather_into_tensor(v3.view(-1), v3[rank].view(-1), group=group)
-            ops.cfg_combine_euler(v3, x_t.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
-                                  cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
-                                  rescale_sigma=rescale_sigma if use_rescale else None)
+
+    def body(ids, tmask, spk, smask, x):
+        """conditioning + the whole Euler loop on x (in place): launches only (CUDA-graph capturable with p2p)"""
+        kv_text = model.get_kv_cache_text(ids, tmask)
+        kv_spk = model.get_kv_cache_speaker(spk)
+        tm3, te3, sm3, se3 = _prep_masks(model, tmask, smask)
+        n_guided = 0
+        for i, has_cfg in enumerate(plan.has_cfg):
+            rows = mine if has_cfg else slice(0, B)
+            h, pending = model.forward_hidden(x, mod[i:i + 1], B, text_mask=tm3[rows], text_extent=te3[rows],
+                                              spk_mask=sm3[rows], spk_extent=se3[rows], kv_text=kv_text, kv_speaker=kv_spk,
+                                              spk_scale=(plan.kv_mult[i] if plan.uses_kv_scale else None))
+            if has_cfg and exchange == "p2p":
+                par, n_guided = n_guided & 1, n_guided + 1
+                ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
+                                   v_out=v3_all[par, rank], update_x=False, delta=pending,
+                                   push_to=[(pv[par, rank], pf[rank:rank + 1]) for pv, pf in zip(peer_v, peer_f)])
+                ops.cfg_combine_euler(v3_all[par], x.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
+                                      cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
+                                      rescale_sigma=rescale_sigma if use_rescale else None,
+                                      wait=(flags[others[0]:others[0] + 1], flags[others[1]:others[1] + 1], ctas * n_guided))
+            elif has_cfg:
+                ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=P, branches=1, eps=cfg.norm_eps,
+                                   v_out=v3[rank], update_x=False, delta=pending)
+                dist.all_gather_into_tensor(v3.view(-1), v3[rank].view(-1), group=group)
+                ops.cfg_combine_euler(v3, x.view(P, -1), plan.sched[i], cfg_text=float(cfg_scale_text),
+                                      cfg_speaker=float(cfg_scale_speaker), rescale_k=rescale_k if use_rescale else None,
+                                      rescale_sigma=rescale_sigma if use_rescale else None)
+            else:
+                ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=1, eps=cfg.norm_eps,
+                                   x_t=x, sched=plan.sched[i], rescale_k=rescale_k if use_rescale else None,
+                                   rescale_sigma=rescale_sigma if use_rescale else None, delta=pending)
+
+    if exchange != "p2p" or not use_graph:
+        mod = model.build_mod_table(plan.t_dev)
+        if exchange == "p2p":
+            flags.zero_()
+            torch.cuda.synchronize()
+            hf.barrier()                                                         # nobody pushes before everyone zeroed
+        body(text_input_ids, text_mask, speaker_latent, speaker_mask, x_t)
+    else:
+        # fused exchange: no collective call inside the loop, so conditioning + all 40 steps replay as ONE CUDA graph per
+        # rank (keyed like the single-GPU sampler's; the counters are zeroed and the ranks meet before every replay)
+        from .sampler import _graph_entry
+        key = ("cfg_split", id(group), B, S, text_input_ids.shape[1], speaker_latent.shape[1], num_steps,
+               tuple(plan.has_cfg), float(cfg_scale_text), float(cfg_scale_speaker), rescale_k, rescale_sigma,
+               plan.uses_kv_scale)
+        ent = _graph_entry(model, key)
+        ent.calls += 1
+        st = ent.static
+        if ent.calls == 1:                                                       # first request of a shape: plain launches
+            mod = model.build_mod_table(plan.t_dev)
+            flags.zero_()
+            torch.cuda.synchronize()
+            hf.barrier()
+            body(text_input_ids, text_mask, speaker_latent, speaker_mask, x_t)
         else:
-            ops.cfg_euler_tail(h, model.out_norm, model.out_w, model.out_b, positions=B * S, branches=1, eps=cfg.norm_eps,
-                               x_t=x_t, sched=plan.sched[i], rescale_k=rescale_k if use_rescale else None,
-                               rescale_sigma=rescale_sigma if use_rescale else None, delta=pending)
+            if ent.graph is None:
+                st["ids"] = text_input_ids.to(dev, torch.int32).contiguous().clone()
+                st["tmask"] = text_mask.to(dev).contiguous().clone()
+                st["spk"] = speaker_latent.to(dev, F32).contiguous().clone()
+                st["smask"] = speaker_mask.to(dev).contiguous().clone()
+                st["x_t"] = x_t.clone()
+                st["plan"] = plan
+                mod = st["mod"] = model.build_mod_table(plan.t_dev)
+                st["ws"] = model.workspace(B, S)                                   # the captured launches point into it
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    body(st["ids"], st["tmask"], st["spk"], st["smask"], st["x_t"])
+                ent.graph = g
+            st["ids"].copy_(text_input_ids); st["tmask"].copy_(text_mask)
+            st["spk"].copy_(speaker_latent); st["smask"].copy_(speaker_mask)
+            st["x_t"].copy_(x_t)
+            if plan.uses_kv_scale:
+                st["plan"].kv_mult.copy_(plan.kv_mult)
+            st["plan"].sched.copy_(plan.sched)
+            flags.zero_()
+            torch.cuda.synchronize()
+            hf.barrier()
+            ent.graph.replay()
+            x_t = st["x_t"].clone()
     if exchange == "p2p":
         torch.cuda.synchronize()
         hf.barrier()               # peers may still be reading / writing our symmetric buffers: free them together
