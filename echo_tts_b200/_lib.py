@@ -166,6 +166,8 @@ EXPORTS = {
     "echo_reset_launch_count": (None, []),
     "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
     "echo_gemm_workspace_bytes": (C.c_longlong, []),
+    "echo_gemm_bf16_splitk_noalloc": (C.c_int, [C.POINTER(GemmDesc), c_p]),
+    "echo_noalloc_scratch_bytes": (C.c_longlong, []),
     "echo_debug_gemm_trace": (C.c_int, [c_p]),
     "echo_debug_attn_trace": (C.c_int, [c_p]),
     "echo_sgemm_f32": (C.c_int, [C.POINTER(SgemmDesc), c_p]),

@@ -97,6 +97,22 @@ typedef struct echo_gemm_desc {
 int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
 long long echo_gemm_workspace_bytes(void);
 
+/* NO COUNTERPART IN THE REFERENCE.  Allocation-free split-K GEMM for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it):
+ * echo_gemm_bf16 in its split-K form (d->k_splits >= 2, GENERIC epilogue, no activation, fp32 output) with the partial
+ * products [k_splits][rows * batch][n] fp32 held in a file-scope `static __device__` array of
+ * ECHO_NOALLOC_SCRATCH_BYTES instead of a caller-lent buffer, followed by a fixed-order reduction:
+ *     out_f32[m, n] = (resid ? resid[m, n] : 0) + sum_s gate * (A_s W_s^T + bias [s == 0])
+ * i.e. the result echo_gemm_bf16 gives without k_splits (up to fp32 summation order).  d->split_stride / d->workspace
+ * are ignored; resid may alias out_f32.  Calls no cudaMalloc / cudaFree / allocating library routine; every GPU that
+ * loads the library holds the array until exit.  Requests with k_splits * rows * batch * n * 4 > ECHO_NOALLOC_SCRATCH_BYTES
+ * are refused (ECHO_ERR_INVALID, message in echo_last_error()).  All calls on a device share the one array, which keeps
+ * the previous call's contents (nothing needs clearing: a call overwrites every element it reads); calls that overlap on
+ * the GPU race -- serialise them (one stream, or graph edges between them). */
+#define ECHO_NOALLOC_SCRATCH_BYTES (32LL << 20)
+int echo_gemm_bf16_splitk_noalloc(const echo_gemm_desc* d, echo_stream_t stream);
+long long echo_noalloc_scratch_bytes(void);
+
 /* Debug aid (no reference counterpart; DEBUG BUILDS ONLY: `make -C echo_tts_b200/csrc DEBUG=1` compiles it in with
  * -DECHO_DEBUG, the product library returns ECHO_ERR_UNSUPPORTED for a non-NULL buffer and contains none of it):
  * while `device_buf` (>= 32 int64 per CTA of the launch) is non-NULL, every GEMM launch records clock64() per CTA: [0] start, [1] setup done, [2] first operands landed, [6] roles
