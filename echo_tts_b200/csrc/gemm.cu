@@ -25,12 +25,23 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
+static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
+                     const cuuint64_t* strides_b, const cuuint32_t* box);
 int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                         const cuuint32_t* box) {
+  return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, dims, strides_b, box);
+}
+// fp32 output tiles of the TMA epilogue (box rows of 32 floats = 128 B, SWIZZLE_128B)
+int echo_make_tmap_f32(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                       const cuuint32_t* box) {
+  return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_b, box);
+}
+static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
+                     const cuuint64_t* strides_b, const cuuint32_t* box) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { echo_set_error("cuTensorMapEncodeTiled entry point unavailable"); return ECHO_ERR_CUDA; }
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_b, box, estr,
+  CUresult r = enc(m, dt, rank, const_cast<void*>(base), dims, strides_b, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { echo_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return ECHO_ERR_CUDA; }

@@ -32,7 +32,8 @@ constexpr int MAX_STAGES = 10;
 constexpr int ACC_STAGES = 2;
 constexpr int ACC_COLS = 256;
 constexpr int EPI_WARPS = 8;       // two per TMEM lane quarter
-constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
+constexpr int B_PRODUCER_WARP = 2 + EPI_WARPS;   // optional second TMA producer (the B operand), Tiling::split_b
+constexpr int NTHREADS = 64 + 32 * EPI_WARPS + 32;   // 352: register allocation rounds the CTA to 384 threads either way
 constexpr int SCRATCH_BYTES = EPI_WARPS * EPI_SC_FLOATS * 4;   // per-epilogue-warp 32x32 fp32 transpose scratch
 constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
 
@@ -64,6 +65,7 @@ struct Tiling {
   long long split_stride; // elements between the partial outputs
   int tail_start;         // >= 0: units from this index on are HALF-width tiles, two per wide tile (the ragged last round
                           // of a launch runs as one round of narrow tiles: shorter main loop and exposed epilogue); -1 off
+  int split_b;            // 1: warp B_PRODUCER_WARP issues the B-operand loads, warp 0 the A-operand loads (two issue streams)
   int stream_k;           // 1: contiguous k-block ranges per pair (num_tiles = plain tile count, splits = 1)
   int* sk_flags;          // [pairs][2 CTAs][EPI_WARPS] 0/1, self-resetting
   float* sk_partials;     // [pairs][2 CTAs][128 x 256] fp32 in the exchange layout of sk_cell()
@@ -213,16 +215,17 @@ __device__ __forceinline__ void sk_merge(int bn, uint32_t tacc, uint32_t tside, 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const __grid_constant__ CUtensorMap tmap_bn, const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P,
-                 const __grid_constant__ Tiling T) {
+                 const __grid_constant__ CUtensorMap tmap_bn, const __grid_constant__ CUtensorMap tmap_out,
+                 const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P, const __grid_constant__ Tiling T) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + RING_BYTES);
+  // operand ring | per-warp epilogue scratch (1024-byte aligned: the TMA epilogue reads it as SWIZZLE_128B tiles) | barriers
+  float* scratch = reinterpret_cast<float*>(smem + RING_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + RING_BYTES + SCRATCH_BYTES);
   uint64_t* empty_bar = full_bar + MAX_STAGES;
   uint64_t* tmem_full_bar = empty_bar + MAX_STAGES;
   uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
-  float* scratch = reinterpret_cast<float*>(smem + RING_BYTES + 256);
   const int STAGES = T.stages, STAGE_SZ = T.stage_bytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -241,6 +244,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
     if (T.tail_start >= 0) ptx::prefetch_tensormap(&tmap_bn);
+    if (EPI == EPI_GENERIC_LEAN) ptx::prefetch_tensormap(&tmap_out);
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full_bar[s], 1);        // leader's producer: arrive.expect_tx (both CTAs' bytes)
       ptx::mbar_init(&empty_bar[s], 1);       // tcgen05.commit multicast to both CTAs
@@ -263,40 +267,48 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   pdl_launch_dependents();    // the next kernel may begin its own setup
   pdl_wait();                 // everything below reads / writes memory the previous kernel may still be producing
 
-  if (warp == 0) {
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      Sched sch(T, pair, npairs, total_kb);
-      Unit w;
-      bool first_unit = true;
-      while (sch.next(w)) {
-        const int tile = w.tile;
-        const int mt = tile % T.tiles_m;
-        const int rest = tile / T.tiles_m;
-        const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
-        const int m0 = mt * (2 * BM) + (int)rank * BM;
-        const int half_u = w.sub < 0 ? half_n : half_n >> 1;            // rows of B this CTA stages for the unit
-        const int n0 = nt * T.bn + (w.sub > 0 ? half_n : 0) + (int)rank * half_u;
-        const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_u * BK * 2);
-        const int kb0 = w.kb0, kb1 = w.kb1;
-        const bool first_u = first_unit;
-        first_unit = false;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          if (T.noload && (kb - kb0 >= STAGES || !first_u)) break;
-          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
-          const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
-          uint8_t* sa = smem + s * STAGE_SZ;
-          uint8_t* sb = sa + A_BYTES;
-          const uint32_t tx = T.skip == 1 ? 2u * (uint32_t)(half_u * BK * 2) : T.skip == 2 ? 2u * (uint32_t)A_BYTES : stage_tx;
-          if (rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], tx);
-          const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
-          if (T.skip != 1) ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
-          if (T.skip != 2) ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
-          if (++s == STAGES) { s = 0; ph ^= 1; }
-        }
+  // TMA producer loop.  do_a / do_b: which operand this thread loads; the leader CTA's A producer also posts the
+  // transaction count of the whole stage (both CTAs, both operands) on the leader's full barrier.
+  auto produce = [&](const bool do_a, const bool do_b) {
+    int s = 0;
+    uint32_t ph = 0;
+    Sched sch(T, pair, npairs, total_kb);
+    Unit w;
+    bool first_unit = true;
+    while (sch.next(w)) {
+      const int tile = w.tile;
+      const int mt = tile % T.tiles_m;
+      const int rest = tile / T.tiles_m;
+      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
+      const int m0 = mt * (2 * BM) + (int)rank * BM;
+      const int half_u = w.sub < 0 ? half_n : half_n >> 1;            // rows of B this CTA stages for the unit
+      const int n0 = nt * T.bn + (w.sub > 0 ? half_n : 0) + (int)rank * half_u;
+      const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_u * BK * 2);
+      const int kb0 = w.kb0, kb1 = w.kb1;
+      const bool first_u = first_unit;
+      first_unit = false;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (T.noload && (kb - kb0 >= STAGES || !first_u)) break;
+        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+        const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
+        uint8_t* sa = smem + s * STAGE_SZ;
+        uint8_t* sb = sa + A_BYTES;
+        const uint32_t tx = T.skip == 1 ? 2u * (uint32_t)(half_u * BK * 2) : T.skip == 2 ? 2u * (uint32_t)A_BYTES : stage_tx;
+        if (do_a && rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], tx);
+        const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
+        if (do_a && T.skip != 1) ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
+        if (do_b && T.skip != 2) ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
+        if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
+  };
+  if (warp == 0) {
+    if (lane == 0) produce(true, T.split_b == 0);
+    __syncwarp();
+  } else if (warp == B_PRODUCER_WARP) {
+    // B bytes may land on the leader's full barrier before the A producer has posted the stage's transaction count: the
+    // phase cannot complete until that arrive, and a transiently negative tx-count is legal
+    if (T.split_b && lane == 0) produce(false, true);
     __syncwarp();
   } else if (warp == 1) {
     if (rank == 0) {   // whole warp converged; one elected lane issues (keeps UTCHMMA free of election loops)
@@ -382,8 +394,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
       TmemLoader2 L{tmem_base + as * ACC_COLS + lane_base};
-      run_epilogue_t<EPI>(bn_u, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nc0, pre, split,
-                          split * T.split_stride);
+      // LEAN, last unit of this CTA: every MMA of the launch that reads this CTA's ring has retired (the accumulator is
+      // complete and no load follows), so the ring stages each chunk in its own 4 KB slot -- no waiting between chunks
+      float* stage = scratch + ew * EPI_SC_FLOATS;
+      int stage_stride = 0;
+      if (EPI == EPI_GENERIC_LEAN && !T.stream_k) {
+        Sched peek = sch;
+        Unit wn;
+        if (!peek.next(wn)) {
+          stage = reinterpret_cast<float*>(smem) + ew * (ACC_COLS / 64) * EPI_SC_FLOATS;
+          stage_stride = EPI_SC_FLOATS;
+        }
+      }
+      run_epilogue_t<EPI>(bn_u, P, L, stage, lane, half, batch, m0 + q * 32, nc0, pre, &tmap_out, split,
+                          split * T.split_stride, stage_stride);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
@@ -412,7 +436,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       TmemLoader2 L{tacc};
       EpiPre<EPI> pre;
       epilogue_prefetch_t<EPI>(T.bn, P, lane, half, batch, m0 + q * 32, nt * T.bn, pre);
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre, 0, 0);
+      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre,
+                          &tmap_out, 0, 0);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
@@ -431,6 +456,8 @@ int getenv_int(const char* name, int dflt) {
 // scheduler switches (A/B measurements), read ONCE per process -- not per launch
 int use_narrow_tail() { static const int v = getenv_int("ECHO_GEMM_TAIL", 1); return v; }
 int use_stream_k() { static const int v = getenv_int("ECHO_STREAM_K", 0); return v; }
+int use_split_b() { static const int v = getenv_int("ECHO_GEMM_SPLITB", 1); return v; }
+int max_stages() { static const int v = getenv_int("ECHO_GEMM_STAGES", MAX_STAGES); return v < 2 ? 2 : v; }
 int num_sms() {
   static int n = 0;
   if (!n) {
@@ -445,6 +472,8 @@ int num_sms() {
 
 int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                         const cuuint32_t* box);   // gemm.cu
+int echo_make_tmap_f32(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                       const cuuint32_t* box);    // gemm.cu
 
 // Bytes of the optional stream-K workspace (echo_gemm_desc.workspace): flags + one partial accumulator per CTA pair.
 // The caller zeroes it once after allocation and must not share it between streams that run GEMMs concurrently.
@@ -489,12 +518,25 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
       if (rc) return rc;
     }
   }
+  CUtensorMap tout = ta;                        // unused unless the epilogue leaves through TMA
+  if (EPI == EPI_GENERIC_LEAN) {
+    // fp32 output [splits][batch][rows][n]: 32 x 32 boxes; rows past a batch entry / columns past n are clipped
+    const long long ld = P.ld_out_f32;
+    const long long bstride = (long long)G.rows * ld;
+    const long long sstride = splits > 1 ? split_stride : bstride * batch;
+    cuuint64_t dims[4] = {(cuuint64_t)G.n, (cuuint64_t)G.rows, (cuuint64_t)batch, (cuuint64_t)splits};
+    cuuint64_t str[3] = {(cuuint64_t)ld * 4, (cuuint64_t)bstride * 4, (cuuint64_t)sstride * 4};
+    cuuint32_t box[4] = {32, 32, 1, 1};
+    int rc = echo_make_tmap_f32(&tout, P.out_f32, 4, dims, str, box);
+    if (rc) return rc;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     ECHO_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
     attr_set = true;
   }
   Tiling T;
+  T.split_b = use_split_b();
 #ifdef ECHO_DEBUG
   T.trace = g_trace_ptr;
   T.noload = g_debug_noload;
@@ -503,6 +545,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   T.bn = bn;
   T.stage_bytes = A_BYTES + (bn / 2) * BK * 2;
   T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
+  if (T.stages > max_stages()) T.stages = max_stages();
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
   T.splits = splits;
@@ -525,7 +568,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
       pairs = P2;
     }
   }
-  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, tbn, G, P, T));
+  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, tbn, tout, G, P, T));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
@@ -564,7 +607,8 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, v
   }
   switch (epi) {
     case ECHO_EPI_GENERIC:
-      if (P.act == ECHO_ACT_NONE && !P.out_bf16 && !P.out2_bf16)
+      // LEAN (TMA epilogue): fp32 output only, residual absent or updated in place
+      if (P.act == ECHO_ACT_NONE && !P.out_bf16 && !P.out2_bf16 && P.out_f32 && (P.red_resid || !P.resid))
         return launch_pair_t<EPI_GENERIC_LEAN>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
       return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
     case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);

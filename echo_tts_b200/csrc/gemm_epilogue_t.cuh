@@ -15,8 +15,8 @@
 #include "gemm_epilogue.cuh"
 
 constexpr int EPI_SC_FLOATS = 32 * 32;
-// Kernel-internal epilogue id: GENERIC without activation / bf16 / Snake outputs (the DiT's two residual projections
-// and their split-K form).  Same arithmetic as GENERIC; the point is a small, contiguous instruction footprint.
+// Kernel-internal epilogue id: GENERIC without activation / bf16 / Snake outputs and with the residual either absent or
+// updated in place (the DiT's two residual projections and their split-K form): leaves through TMA (epi_t_lean_tma).
 constexpr int EPI_GENERIC_LEAN = 3;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
 
 // The scratch is addressed in the shared state space explicitly: through a generic pointer the compiler emits
@@ -361,10 +361,126 @@ __device__ __forceinline__ void epi_t_swiglu(const int BN, const EpiParams& P, L
   }
 }
 
+// ---- LEAN via TMA (the DiT's gated-residual projections and their split-K partials) ---------------------------------
+// The LEAN cases -- x += gate * (acc + bias) in place, or out = gate * (acc + bias) (split-K partial products) -- need no
+// per-lane global access at all: the chunk is scaled in the row-per-thread TMEM layout, written once to the warp's
+// scratch in the SWIZZLE_128B pattern (the XOR swizzle sc_store_row already uses), and leaves as ONE bulk tensor
+// operation issued by lane 0: a TMA reduce-add (x += ..., executed in the L2, one add per element: deterministic) or a TMA
+// store.  Rows past the batch entry and columns past n are clipped by the tensor map.  Versus the register path (8 LDS +
+// 8 STG / RED per lane and chunk plus their address arithmetic) the exposed last epilogue of a launch is ~3x shorter.
+__device__ __forceinline__ void tma_out_4d(const void* tmap, const void* src, bool reduce_add, int c0, int c1, int c2, int c3) {
+  if (reduce_add)
+    asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+  else
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_out_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+// Per-column vectors of the warp's (up to four) chunks, one column per lane, fetched BEFORE the warp waits for the tile's
+// MMAs (their L2 latency, ~1 k clocks under load, would otherwise sit on every chunk of the exposed epilogue); broadcast
+// with shuffles when the chunk is processed.  ga / gb: the gate rows of the block's first / last row (rows_per_gate >= 32:
+// a 32-row block touches at most two gate rows).
+struct LeanPre {
+  float ga[4], gb[4], bs[4];
+};
+__device__ __forceinline__ void epi_t_lean_prefetch(const int BN, const EpiParams& P, int lane, const EpiRows& R, LeanPre& A) {
+  if (R.nrows <= 0) return;
+  const int cend = min(BN, P.n - R.n0);
+  const unsigned rpg = (unsigned)P.rows_per_gate;
+  const unsigned g0 = (unsigned)R.mg0 / rpg;
+  const bool two = ((unsigned)R.mg0 - g0 * rpg) + (unsigned)(R.nrows - 1) >= rpg;
+  const bool fast = P.gate && rpg >= 32u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = R.half * 32 + 64 * i;
+    const int n = R.n0 + c + lane;
+    const bool ok = c < cend && n < P.n;
+    A.ga[i] = (fast && ok) ? __ldg(P.gate + (long long)g0 * P.gate_ld + n) : 1.f;
+    A.gb[i] = (fast && ok && two) ? __ldg(P.gate + (long long)(g0 + 1u) * P.gate_ld + n) : A.ga[i];
+    A.bs[i] = (P.bias && ok && R.split == 0) ? __ldg(P.bias + n) : 0.f;
+  }
+}
+
+// `sc_stride` (floats): 0 = every chunk is staged in the same scratch (the bulk operation of chunk i must have read it
+// before chunk i + 1 is written); > 0 = chunk i is staged at sc + i * sc_stride (the CTA's LAST tile: the operand ring is
+// idle by then and serves as staging, so no chunk waits for the one before -- this is the exposed epilogue of a launch).
+template <class Loader>
+__device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
+                                               const EpiRows& R, const void* tmap_out, const LeanPre& A, int sc_stride = 0) {
+  if (R.nrows <= 0) return;                                // warp-uniform
+  const int cend = min(BN, P.n - R.n0);                    // columns of this tile that exist (multiple of 8)
+  const unsigned rpg = (unsigned)P.rows_per_gate;
+  const unsigned g0 = (unsigned)R.mg0 / rpg, rem0 = (unsigned)R.mg0 - g0 * rpg;
+  const bool two = rem0 + (unsigned)(R.nrows - 1) >= rpg;  // warp-uniform: the block straddles a gate-row boundary
+  const bool hi = rem0 + (unsigned)lane >= rpg;            // this lane's row takes the second gate row
+  const bool slow_gate = P.gate && rpg < 32u;              // more than two gate rows per block: per-lane loads (not the DiT)
+  const bool has_bias = P.bias && R.split == 0;
+  const float* grow = (slow_gate && lane < R.nrows)
+                          ? P.gate + (long long)(((unsigned)R.mg0 + (unsigned)lane) / rpg) * P.gate_ld : nullptr;
+  uint32_t row_addr = smem_u32(sc) + (uint32_t)lane * 128u;
+  bool pending = false;
+  int i = 0;
+#pragma unroll 1
+  for (int c = R.half * 32; c < cend; c += 64, ++i) {
+    const int n = R.n0 + c;
+    float v[32];
+    L.load32(c, v);
+    const float ga = i == 0 ? A.ga[0] : (i == 1 ? A.ga[1] : (i == 2 ? A.ga[2] : A.ga[3]));
+    const float gb = i == 0 ? A.gb[0] : (i == 1 ? A.gb[1] : (i == 2 ? A.gb[2] : A.gb[3]));
+    const float bs = i == 0 ? A.bs[0] : (i == 1 ? A.bs[1] : (i == 2 ? A.bs[2] : A.bs[3]));
+    if (has_bias) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, bs, j);
+    }
+    if (P.gate && !slow_gate) {
+      if (two) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float a = __shfl_sync(0xffffffffu, ga, j), b = __shfl_sync(0xffffffffu, gb, j);
+          v[j] *= hi ? b : a;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] *= __shfl_sync(0xffffffffu, ga, j);
+      }
+    } else if (grow) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (n + 4 * k < P.n) {
+          const float4 g = __ldg(reinterpret_cast<const float4*>(grow + n) + k);
+          v[4 * k] *= g.x; v[4 * k + 1] *= g.y; v[4 * k + 2] *= g.z; v[4 * k + 3] *= g.w;
+        }
+      }
+    }
+    if (pending && sc_stride == 0) {                       // the previous chunk's bulk operation has read the scratch
+      if (lane == 0) tma_out_wait_read();
+      __syncwarp();
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + (uint32_t)((k ^ (lane & 7)) << 4)),
+                   "f"(v[4 * k]), "f"(v[4 * k + 1]), "f"(v[4 * k + 2]), "f"(v[4 * k + 3])
+                   : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the bulk copy
+    __syncwarp();
+    if (lane == 0) tma_out_4d(tmap_out, sc, P.red_resid != 0, n, R.mb0, R.batch_idx, R.split);
+    pending = true;
+    sc += sc_stride;
+    row_addr += (uint32_t)sc_stride * 4u;
+  }
+  if (pending) {                                           // the staging memory (and, at exit, the CTA's shared memory) is free again
+    if (lane == 0) tma_out_wait_read();
+    __syncwarp();
+  }
+}
+
 // What an epilogue can fetch before its accumulator exists (kept in registers across the wait for the MMAs).
 template <int EPI> struct EpiPre {};
 template <> struct EpiPre<ECHO_EPI_GENERIC> { GenAux a; };
-template <> struct EpiPre<EPI_GENERIC_LEAN> { GenAux a; };
+template <> struct EpiPre<EPI_GENERIC_LEAN> { LeanPre a; };
 // (SECTIONS: holding the RoPE rows of the first chunk across the wait costs 36 registers and spills; measured slower)
 
 __device__ __forceinline__ EpiRows epi_rows(const EpiParams& P, int half, int batch_idx, int mb0, int n0, int split,
@@ -379,15 +495,16 @@ template <int EPI>
 __device__ __forceinline__ void epilogue_prefetch_t(const int BN, const EpiParams& P, int lane, int half, int batch_idx,
                                                     int mb0, int n0, EpiPre<EPI>& pre) {
   const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, 0, 0);
-  if constexpr (EPI == ECHO_EPI_GENERIC || EPI == EPI_GENERIC_LEAN) epi_t_generic_prefetch(BN, P, lane, R, pre.a);
+  if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic_prefetch(BN, P, lane, R, pre.a);
+  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_lean_prefetch(BN, P, lane, R, pre.a);
 }
 template <int EPI, class Loader>
 __device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
-                                               int batch_idx, int mb0, int n0, EpiPre<EPI>& pre, int split = 0,
-                                               long long out_off = 0) {
+                                               int batch_idx, int mb0, int n0, EpiPre<EPI>& pre, const void* tmap_out,
+                                               int split = 0, long long out_off = 0, int sc_stride = 0) {
   const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, split, out_off);
   if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic<false>(BN, P, L, sc, lane, R, pre.a);
-  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_generic<true>(BN, P, L, sc, lane, R, pre.a);
+  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_lean_tma(BN, P, L, sc, lane, R, tmap_out, pre.a, sc_stride);
   else if constexpr (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
   else epi_t_swiglu(BN, P, L, sc, lane, R);
 }
