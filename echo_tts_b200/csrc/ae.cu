@@ -358,7 +358,10 @@ extern "C" int echo_flattening_point(const float* latent, int len, int width, in
                                      float target, int32_t* index_out, echo_stream_t stream) {
   ECHO_CHECK_ARG(latent && index_out && len > 0 && width > 0 && window > 0, "flattening: bad argument");
   const size_t smem = (size_t)(len + window) * 2 * sizeof(double);
-  ECHO_CHECK_ARG(smem <= 48 * 1024, "flattening: latent too long");
+  ECHO_CHECK_ARG(smem <= 227 * 1024, "flattening: latent of %d frames too long (prefix sums of %zu bytes exceed 227 KB of shared memory)",
+                 len, smem);
+  if (smem > 48 * 1024)   // the reference accepts any length (inference.py:315-330); per device, so set on every long call
+    ECHO_CUDA(cudaFuncSetAttribute(flattening_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   flattening_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(latent, len, width, window, std_threshold, target, index_out);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();

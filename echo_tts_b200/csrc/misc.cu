@@ -203,7 +203,10 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo
   __shared__ float sA[16][64 + 4];
   __shared__ float sW[16][64 + 4];
   const int z = blockIdx.z;
-  pdl_launch_dependents();
+  // NO early trigger here (the implicit one at grid exit applies): this kernel writes the AdaLN modulation table, which
+  // rmsnorm_mod_kernel requests BEFORE its own griddepcontrol.wait.  With an early trigger, a kernel two launches behind
+  // (table sgemm -> in_proj sgemm -> norm, the model.__call__ path) could be resident while the table is still being
+  // written; without it every kernel launched after an sgemm starts only once that sgemm has completed.
   pdl_wait();
   const float* A = D.a + z * D.a_zstride;
   const float* W = D.w + z * D.w_zstride;

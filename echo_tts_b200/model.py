@@ -161,6 +161,10 @@ class EchoDiT:
         T = t.numel()
         dev = self._device
         t = t.to(dev, F32).contiguous()
+        if getattr(self, "round_t_to_model_dtype", False) and self._dtype != F32:
+            # the reference's default bf16 path rounds t to the model dtype before the sinusoidal embedding
+            # (inference.py:517 `.to(dtype)`, model.py:39); off by default: the parity oracle is the fp32 path
+            t = t.to(self._dtype).to(F32)
         emb = ops.timestep_embedding(t, cfg.timestep_embed_size)
         h1 = torch.empty((T, D), device=dev, dtype=F32)
         h2 = torch.empty((T, D), device=dev, dtype=F32)

@@ -198,3 +198,13 @@ def test_flattening_point_matches_golden(ops):
     cases = torch.load(os.path.join(GOLDEN, "flatten_cases.pt"))
     for name, data in cases.items():
         assert int(ops.flattening_point(data.cuda().contiguous()).item()) == idx[name], name
+
+
+def test_flattening_point_long_latent_vs_oracle(ops):
+    """A 6400-frame latent (a long continuation; more than the 48 KB default of shared memory holds): the reference accepts
+    any length (inference.py:315-330) and the index must still be the reference loop's."""
+    from oracle import echo_oracle as O
+    g = torch.Generator().manual_seed(31)
+    for flat_from in (5000, 6399, 17):
+        data = torch.cat([torch.randn(flat_from, 80, generator=g), 0.01 * torch.randn(6400 - flat_from, 80, generator=g)])
+        assert int(ops.flattening_point(data.cuda().contiguous()).item()) == O.find_flattening_point(data)

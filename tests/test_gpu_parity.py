@@ -400,3 +400,40 @@ def test_config4_full_size_long_reference_properties(base_model):
     assert rel_l2(single, both[:1]) < X_TOL
     again = sample(base_model, spk.cuda(), smask.cuda(), ids, mask, 0, _noise=noise, **kw).cpu()
     assert torch.equal(again, both)
+
+
+def test_round_t_to_model_dtype_switch(tiny_model):
+    """The reference's default bf16 path rounds t to bf16 before the timestep embedding (inference.py:517, model.py:39);
+    the engine keeps t in fp32 (the parity oracle is the fp32 path) unless ``model.round_t_to_model_dtype`` is set."""
+    t = torch.tensor([0.999, 0.7243, 0.4995, 0.0249]).cuda()
+    base = tiny_model.build_mod_table(t)
+    tiny_model.round_t_to_model_dtype = True
+    try:
+        rounded = tiny_model.build_mod_table(t)
+    finally:
+        tiny_model.round_t_to_model_dtype = False
+    want = tiny_model.build_mod_table(t.to(torch.bfloat16).float())
+    assert torch.equal(rounded, want) and not torch.equal(rounded, base)
+    assert torch.equal(tiny_model.build_mod_table(t), base)
+
+
+def test_model_call_right_after_table_build_is_race_free(tiny_model):
+    """model.__call__ launches table sgemms -> in_proj sgemm -> norm back to back (programmatic dependent launches): the
+    norm requests its table rows before its own grid-dependency wait, so the table writers must have completed by then.
+    Ten fresh calls with different t must each equal a call made after a full synchronize."""
+    gen = torch.Generator().manual_seed(9)
+    ids = torch.randint(1, 255, (1, 20), generator=gen, dtype=torch.int32).cuda()
+    tmask = torch.ones(1, 20, dtype=torch.bool).cuda()
+    spk = torch.randn(1, 16, 80, generator=gen).cuda()
+    smask = torch.ones(1, 16, dtype=torch.bool).cuda()
+    kt, ks = tiny_model.get_kv_cache_text(ids, tmask), tiny_model.get_kv_cache_speaker(spk)
+    x = torch.randn(1, 40, 80, generator=gen).cuda()
+    for i in range(10):
+        t = torch.tensor([0.05 + 0.09 * i]).cuda()
+        torch.cuda.synchronize()
+        got = tiny_model(x, t, tmask, smask, kt, ks).clone()
+        torch.cuda.synchronize()
+        mod = tiny_model.build_mod_table(t)
+        torch.cuda.synchronize()
+        want = tiny_model(x, t, tmask, smask, kt, ks)
+        assert torch.equal(got, want), i
