@@ -314,7 +314,9 @@ def config5_streaming(model, ae, pca, dev, reps=3):
         rec[name] = dict(total_ms=marks[-1], first_audio_ms=marks[0], block_done_ms=marks, samples_out=n,
                          audio_sec_per_sec=n / 44100 / (marks[-1] / 1e3))
     rec["what"] = ("stream_blockwise_audio(): 4 x 160 latents x 40 steps, cfg 3.0/5.0 on t in [0.5,1], per-block streaming "
-                   "S1-DAC decode + D2H, " + str(dev[0].shape[0]) + " prompt(s), eager launches; recomputed_prefix = the reference's full prefix re-encode per block")
+                   "S1-DAC decode + D2H, " + str(dev[0].shape[0]) + " prompt(s); incremental_prefix: one CUDA graph per block (conditioning / prefix-KV "
+                   "append + 40 steps) and per decode-stream step; recomputed_prefix = the reference's full prefix re-encode per "
+                   "block, plain launches")
     return rec
 
 

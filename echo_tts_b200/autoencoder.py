@@ -579,6 +579,16 @@ class DAC:
         from .streaming import DecodeStream
         return DecodeStream(self)
 
+    def stream_pool(self, n: int):
+        """``n`` decode streams kept on this object across requests and reset for a new utterance each: their state buffers
+        and captured step graphs are reused (a graph is keyed by frames per step and stream position)."""
+        pool = self.__dict__.setdefault("_stream_pool", [])
+        while len(pool) < n:
+            pool.append(self.decode_stream())
+        for st in pool[:n]:
+            st.reset()
+        return pool[:n]
+
     @torch.inference_mode()
     def decode_latent(self, z: torch.Tensor, pca_components: torch.Tensor, pca_mean: torch.Tensor,
                       latent_scale: float) -> torch.Tensor:

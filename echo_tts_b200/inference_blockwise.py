@@ -23,7 +23,7 @@ def stream_blockwise_audio(model, fish_ae, pca_state, speaker_latent: torch.Tens
     it; its audio is yielded too when ``decode_continuation`` is set.  ``sampler_kwargs`` are the reference sampler's
     keyword arguments (num_steps, cfg_scale_text, ... speaker_kv_min_t)."""
     B = text_input_ids.shape[0]
-    streams = [fish_ae.decode_stream() for _ in range(B)]
+    streams = fish_ae.stream_pool(B)            # kept across requests (state reset): their step graphs are reused
 
     def decode(lat: torch.Tensor) -> torch.Tensor:
         return torch.cat([st.step_latent(lat[b:b + 1], pca_state.pca_components, pca_state.pca_mean,

@@ -245,6 +245,70 @@ def sample_euler_cfg_independent_guidances(
     return st["x_t"].clone().view(B, S, cfg.latent_size)
 
 
+def _blockwise_graphed(model: EchoDiT, ent: "_GraphEntry", speaker_latent, speaker_mask, text_input_ids, text_mask, rng,
+                       block_sizes, num_steps, cfg_min_t, cfg_max_t, truncation_factor, speaker_kv_scale,
+                       speaker_kv_max_layers, speaker_kv_min_t, p) -> Iterator[Tuple[int, int, torch.Tensor]]:
+    """The block loop of ``blockwise_blocks`` as one CUDA graph per block (captured at the second request of a key, replayed
+    afterwards).  Yields the STATIC prefix buffer: consume ``prefix[:, start:stop]`` before asking for the next request."""
+    from .streaming import PrefixKVStream
+    cfg, dev = model.cfg, model.device
+    B = text_input_ids.shape[0]
+    use_rescale = p["rescale_k"] is not None and p["rescale_sigma"] is not None
+    st = ent.static
+    if "blocks" not in st:
+        st["ids"] = text_input_ids.to(dev, torch.int32).contiguous().clone()
+        st["tmask"] = text_mask.to(dev).contiguous().clone()
+        st["spk"] = speaker_latent.to(dev, F32).contiguous().clone()
+        st["smask"] = speaker_mask.to(dev).contiguous().clone()
+        st["guidance"] = torch.zeros(4, device=dev, dtype=F32)
+        st["prefix"] = torch.zeros((B, sum(block_sizes), cfg.latent_size), device=dev, dtype=F32)
+        st["pstream"] = PrefixKVStream(model, B, sum(block_sizes))
+        st["mod"] = None
+        st["blocks"] = []
+    st["ids"].copy_(text_input_ids); st["tmask"].copy_(text_mask)
+    st["spk"].copy_(speaker_latent); st["smask"].copy_(speaker_mask)
+    st["guidance"].copy_(torch.tensor([p["cfg_scale_text"], p["cfg_scale_speaker"], p["rescale_k"] if use_rescale else 1.0,
+                                       p["rescale_sigma"] if use_rescale else 0.0], dtype=F32), non_blocking=True)
+    mult, start = None, 0
+    for bi, bs in enumerate(block_sizes):
+        plan = StepPlan(dev, num_steps, cfg_min_t, cfg_max_t, speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t,
+                        cfg.num_layers, initial_multiplier=mult)                     # inference_blockwise.py:68-70
+        mult = plan.final_multiplier
+        x_t = torch.randn((B, bs, cfg.latent_size), device=dev, dtype=F32, generator=rng)     # inference_blockwise.py:76
+        if truncation_factor is not None:
+            x_t = x_t * truncation_factor
+        if bi >= len(st["blocks"]):
+            if st["mod"] is None:
+                st["mod"] = model.build_mod_table(plan.t_dev)
+            blk = dict(x_t=x_t.clone(), plan=plan)
+            pstream = st["pstream"]
+            if bi == 0:
+                pstream.patches = 0
+                pstream.pending = torch.empty((B, 0, cfg.latent_size), device=dev, dtype=F32)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                if bi == 0:
+                    st["cond"] = (model.get_kv_cache_text(st["ids"], st["tmask"]), model.get_kv_cache_speaker(st["spk"]),
+                                  _prep_masks(model, st["tmask"], st["smask"]))
+                else:
+                    pstream.append(st["blocks"][bi - 1]["x_t"])
+                kv_text, kv_spk, masks = st["cond"]
+                kv_lat, n_prefix = (pstream.kv, pstream.patches) if pstream.patches > 0 else (None, 0)
+                blk["keep"] = run_steps(model, blk["x_t"], plan, st["mod"], B, masks, kv_text, kv_spk, p, start_pos=start,
+                                        kv_latent=kv_lat, n_prefix=n_prefix, guidance=st["guidance"])
+                st["prefix"][:, start:start + bs].copy_(blk["x_t"])
+            blk["graph"] = g
+            st["blocks"].append(blk)
+        blk = st["blocks"][bi]
+        blk["x_t"].copy_(x_t)
+        blk["plan"].sched.copy_(plan.sched)
+        if plan.uses_kv_scale:
+            blk["plan"].kv_mult.copy_(plan.kv_mult)
+        blk["graph"].replay()
+        yield start, start + bs, st["prefix"]
+        start += bs
+
+
 @torch.inference_mode()
 def blockwise_blocks(
         model: EchoDiT, speaker_latent: torch.Tensor, speaker_mask: torch.Tensor, text_input_ids: torch.Tensor,
@@ -267,9 +331,6 @@ def blockwise_blocks(
     p = dict(cfg_scale_text=float(cfg_scale_text), cfg_scale_speaker=float(cfg_scale_speaker), rescale_k=rescale_k,
              rescale_sigma=rescale_sigma)
     rng = torch.Generator(device=dev).manual_seed(rng_seed)
-    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)
-    kv_spk = model.get_kv_cache_speaker(speaker_latent)
-    masks = _prep_masks(model, text_mask, speaker_mask)
     prefix = torch.zeros((B, sum(block_sizes), cfg.latent_size), device=dev, dtype=F32)
     start = 0
     if continuation_latent is not None:
@@ -279,6 +340,26 @@ def blockwise_blocks(
     aligned = start % ps == 0 and all(bs % ps == 0 for bs in block_sizes)
     if incremental_prefix is None:
         incremental_prefix = os.environ.get("ECHO_PREFIX_INCREMENTAL", "1") != "0"
+    # ---- CUDA-graph path (the serving case: no continuation, patch-aligned blocks, incremental prefix): one captured graph
+    #      per block -- block 0 = conditioning encoders + its Euler steps, block i = append block i-1 to the prefix KV + its
+    #      Euler steps -- over static buffers, keyed by shapes and schedule only.  First request of a key: plain launches.
+    if (_use_graphs() and _noises is None and _trace is None and start == 0 and aligned and incremental_prefix
+            and model.has_blockwise and len(block_sizes) > 0 and min(block_sizes) >= ps):
+        use_rescale = rescale_k is not None and rescale_sigma is not None
+        plan0 = StepPlan(dev, num_steps, cfg_min_t, cfg_max_t, speaker_kv_scale, speaker_kv_max_layers, speaker_kv_min_t,
+                         cfg.num_layers)
+        key = ("blockwise", B, tuple(int(b) for b in block_sizes), text_input_ids.shape[1], speaker_latent.shape[1],
+               num_steps, tuple(plan0.has_cfg), use_rescale, plan0.uses_kv_scale)
+        ent = _graph_entry(model, key)
+        ent.calls += 1
+        if ent.calls >= 2:
+            yield from _blockwise_graphed(model, ent, speaker_latent, speaker_mask, text_input_ids, text_mask, rng, block_sizes,
+                                          num_steps, cfg_min_t, cfg_max_t, truncation_factor, speaker_kv_scale,
+                                          speaker_kv_max_layers, speaker_kv_min_t, p)
+            return
+    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)
+    kv_spk = model.get_kv_cache_speaker(speaker_latent)
+    masks = _prep_masks(model, text_mask, speaker_mask)
     pstream = None
     if incremental_prefix and aligned and model.has_blockwise and prefix.shape[1] >= ps:
         from .streaming import PrefixKVStream
@@ -337,6 +418,8 @@ def sample_blockwise_euler_cfg_independent_guidances(
             incremental_prefix=incremental_prefix, _trace=_trace):
         if on_block is not None:
             on_block(start, stop, prefix)
+    if prefix is not None:
+        prefix = prefix.clone()      # the graph path yields its static prefix buffer
     if prefix is None:          # no blocks: the (possibly empty) continuation comes back unchanged
         cfg, dev = model.cfg, model.device
         B = text_input_ids.shape[0]

@@ -74,6 +74,15 @@ class DecodeStream:
             self.state = torch.empty(n, device=dac.device, dtype=torch.uint8)
             L.check(lib.echo_ae_decode_stream_init(C.byref(desc), self.state.data_ptr(), n, L.stream()))
 
+    def reset(self) -> None:
+        """Start a new utterance on this stream object (state zeroed, position 0).  A serving loop keeps its streams --
+        and the step graphs captured for them -- across requests (``DAC.stream_pool``)."""
+        self.pos = 0
+        self.carry.rows.clear()
+        if self.state is not None:
+            L.check(L.load().echo_ae_decode_stream_init(C.byref(self.dac.native_desc()), self.state.data_ptr(),
+                                                        self.state.numel(), L.stream()))
+
     # -- post_module: 8 causal window-128 layers with a key/value cache ---------------------------------------------
     def _transformer(self, x: torch.Tensor, T: int) -> torch.Tensor:
         dac, cfg, dev = self.dac, self.dac.cfg, self.dac.device
@@ -217,9 +226,37 @@ class DecodeStream:
             raise ValueError("a DecodeStream carries the state of one utterance: open one stream per batch row")
         dev = self.dac.device
         w, mean = self.dac.pca_operands(pca_components, pca_mean)
-        x = torch.empty((T, w.shape[0]), device=dev, dtype=F32)
-        ops.sgemm(z.to(dev, F32).contiguous().view(T, lat), w, addend=mean, out=x, out_scale=1.0 / latent_scale)
-        return self._run(x, T)
+
+        def launch(zin: torch.Tensor) -> torch.Tensor:
+            x = torch.empty((T, w.shape[0]), device=dev, dtype=F32)
+            ops.sgemm(zin.view(T, lat), w, addend=mean, out=x, out_scale=1.0 / latent_scale)
+            return self._run(x, T)
+
+        zin = z.to(dev, F32).contiguous()
+        from .sampler import _use_graphs
+        if self.state is None or not _use_graphs():
+            return launch(zin)
+        # CUDA graph per (frames, stream position): a step is ~230 launches of a few microseconds each (launch-bound when
+        # issued one by one).  The first step at a key runs plainly (it also sizes the cached scratch), the second is
+        # captured, later ones replay; the carried state lives in this stream's one state buffer, so replays continue it.
+        graphs = self.__dict__.setdefault("_step_graphs", {})
+        key = (T, self.pos, float(latent_scale), w.data_ptr())
+        ent = graphs.setdefault(key, dict(calls=0, graph=None))
+        ent["calls"] += 1
+        if ent["calls"] == 1:
+            return launch(zin)
+        if ent["graph"] is None:
+            ent["z"] = zin.clone()
+            pos0 = self.pos
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                ent["wav"] = launch(ent["z"])
+            self.pos = pos0                    # the capture advanced the position without running anything
+            ent["graph"] = g
+        ent["z"].copy_(zin)
+        ent["graph"].replay()
+        self.pos += T
+        return ent["wav"].clone()
 
 
 class PrefixKVStream:

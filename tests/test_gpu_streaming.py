@@ -343,3 +343,47 @@ def test_config5_full_size_properties():
     print(f"config 5 full size: incremental vs recomputed prefix rel-L2 {e_prefix:.3e}; streamed vs one-shot audio {e_audio:.3e}")
     assert e_prefix < 2e-2          # two bf16 realisations of the same prefix keys, through 3 x 40 sampling steps
     assert e_audio < 1e-2           # stream == one-shot decode up to tile-order rounding (5.7e-3 measured on random latents)
+
+
+def test_blockwise_and_stream_graph_replay_equal_eager(monkeypatch):
+    """Serving path of configs[4]: per-block CUDA graphs (block 0 = conditioning + steps, block i = prefix-KV append + steps)
+    and per-block decode-stream step graphs.  Same seed: first request (plain launches), second (capture + replay) and third
+    (replay) give bit-identical latents and audio, equal to a run with graphs switched off."""
+    from echo_tts_b200.inference import load_model_from_state_dict, load_fish_ae_from_state_dict, PCAState
+    from echo_tts_b200.inference_blockwise import stream_blockwise_audio, sample_blockwise_euler_cfg_independent_guidances as sample
+    cfg, acfg = S.ECHO_TINY, S.AE_TINY
+    model = load_model_from_state_dict(S.synth_state_dict(S.dit_schema(cfg)), cfg=cfg)
+    ae = load_fish_ae_from_state_dict(S.synth_ae_state_dict(acfg), cfg=acfg)
+    comp, mean, scale = S.synth_pca(latent_dim=acfg.latent_dim)
+    pca = PCAState(comp.cuda(), mean.cuda(), scale)
+    g = torch.Generator().manual_seed(4)
+    ids = torch.randint(1, 255, (2, 24), generator=g, dtype=torch.int32).cuda()
+    tmask = torch.ones(2, 24, dtype=torch.bool).cuda(); tmask[1, 15:] = False
+    spk = torch.randn(2, 16, 80, generator=g).cuda()
+    smask = torch.ones(2, 16, dtype=torch.bool).cuda()
+    kw = dict(num_steps=4, cfg_scale_text=3.0, cfg_scale_speaker=5.0, cfg_min_t=0.5, cfg_max_t=1.0, truncation_factor=0.9,
+              rescale_k=None, rescale_sigma=None, speaker_kv_scale=1.5, speaker_kv_max_layers=1, speaker_kv_min_t=0.6)
+    blocks = [8, 12, 8]
+
+    def request(seed):
+        lat = sample(model, spk, smask, ids, tmask, seed, blocks, **kw)
+        chunks = [(w.clone(), a, b) for w, a, b in stream_blockwise_audio(model, ae, pca, spk, smask, ids, tmask, seed, blocks, **kw)]
+        return lat, torch.cat([c[0] for c in chunks], -1), [(a, b) for _, a, b in chunks]
+
+    monkeypatch.setenv("ECHO_CUDA_GRAPH", "0")
+    ref_lat, ref_wav, ref_spans = request(11)
+    other_lat, _, _ = request(12)
+    monkeypatch.setenv("ECHO_CUDA_GRAPH", "1")
+    runs = [request(11) for _ in range(3)]                       # plain launches, capture + replay, replay
+    assert ref_spans == [(0, 8), (8, 20), (20, 28)] and ref_wav.shape == (2, 1, 28 * acfg.hop)
+    for lat, wav, spans in runs:
+        assert spans == ref_spans
+        assert torch.equal(lat, ref_lat) and torch.equal(wav, ref_wav)
+    lat12, _, _ = request(12)                                    # another seed through the captured graphs
+    assert torch.equal(lat12, other_lat) and not torch.equal(lat12, ref_lat)
+    # other guidance scales through the SAME graphs (device-side guidance vector)
+    monkeypatch.setenv("ECHO_CUDA_GRAPH", "0")
+    want = sample(model, spk, smask, ids, tmask, 11, blocks, **dict(kw, cfg_scale_text=1.0, cfg_scale_speaker=2.0))
+    monkeypatch.setenv("ECHO_CUDA_GRAPH", "1")
+    got = sample(model, spk, smask, ids, tmask, 11, blocks, **dict(kw, cfg_scale_text=1.0, cfg_scale_speaker=2.0))
+    assert torch.equal(got, want)
