@@ -35,7 +35,7 @@ class GemmDesc(C.Structure):
         ("snake_alpha", c_p),
         ("n_sections", i32), ("section_width", i32), ("head_dim", i32), ("rope_heads", i32),
         ("pos_offset", i32), ("pos_stride", i32), ("rows_per_seq", i32), ("a_ctx", i32),
-        ("eps", f32), ("_pad2", f32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
+        ("eps", f32), ("b_static", i32), ("rope_cos", c_p), ("rope_sin", c_p), ("ld_sec_out", i64),
         ("sections", GemmSection * 4), ("split_stride", i64),
         ("workspace", c_p), ("workspace_bytes", i64),
     ]

@@ -31,6 +31,7 @@ void gemm_init(const echo_encode_kv_desc* D, echo_gemm_desc* g, const void* a, i
   g->epilogue = epilogue;
   g->impl = D->gemm_impl;
   g->rows_per_gate = 1;
+  g->b_static = 1;             // w is a load-time tensor of the descriptor (weights)
   if (D->gemm_impl == 2) { g->workspace = D->gemm_workspace; g->workspace_bytes = D->gemm_workspace_bytes; }
 }
 

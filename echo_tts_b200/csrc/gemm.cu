@@ -66,6 +66,7 @@ static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   for (int i = 0; i < 8; ++i) G.tap_shift[i] = d->tap_shift[i];
   G.rows = d->rows; G.n = d->n; G.lda = d->lda; G.a_batch_stride = d->a_batch_stride; G.ldb = d->ldb;
   G.a = (const bf16*)d->a; G.b = (const bf16*)d->b;
+  G.b_static = d->b_static == 1;
   ECHO_CHECK_ARG(d->a_ctx >= 0 && d->a_ctx < (1 << 20), "gemm: bad a_ctx");
   if (d->a_ctx > 0) {   // left context: the operand view starts a_ctx rows earlier, every tap moves with it
     G.a_ctx = d->a_ctx;

@@ -76,15 +76,28 @@ constexpr long long SK_SLOT_FLOATS = 2LL * BM * ACC_COLS;      // one pair's par
 
 // One work unit: k-blocks [kb0, kb1) of `tile`.  All three warp roles walk the same sequence.
 // sub: -1 = full-width tile, 0 / 1 = left / right half-width tile of `tile`
-struct Unit { int tile, split, kb0, kb1, sub; };
+// mt / nt / batch: the tile's coordinates, decoded here so that the divisions of a CTA's FIRST unit run during set-up
+// (every role fetches it before the grid-dependency wait) instead of between the wait and the first operand request --
+// one thread takes ~150 clocks per 32-bit and ~700 per 64-bit division, which used to put ~2.8 k clocks there.
+struct Unit { int tile, split, kb0, kb1, sub, mt, nt, batch; };
 struct Sched {
-  int sk, total_kb, splits, unit, step, end, tail;
+  int sk, total_kb, splits, unit, step, end, tail, tiles_m, tiles_n;
   long long u, e;
   __device__ Sched(const Tiling& T, int pair, int npairs, int total_kb_) {
     sk = T.stream_k; total_kb = total_kb_; splits = T.splits; tail = T.tail_start;
+    tiles_m = T.tiles_m; tiles_n = T.tiles_n;
     unit = pair; step = npairs; end = T.num_tiles;
-    const long long U = (long long)T.num_tiles * total_kb;
-    u = U * pair / npairs; e = U * (pair + 1) / npairs;
+    u = e = 0;
+    if (sk) {
+      const long long U = (long long)T.num_tiles * total_kb;
+      u = U * pair / npairs; e = U * (pair + 1) / npairs;
+    }
+  }
+  __device__ __forceinline__ void decode(Unit& w) const {
+    w.mt = w.tile % tiles_m;
+    const int rest = w.tile / tiles_m;
+    w.batch = rest / tiles_n;
+    w.nt = rest - w.batch * tiles_n;
   }
   __device__ bool next(Unit& w) {
     if (sk) {
@@ -94,17 +107,21 @@ struct Sched {
       const long long rem = e - u;
       w.kb1 = rem < (long long)(total_kb - w.kb0) ? w.kb0 + (int)rem : total_kb;
       u += w.kb1 - w.kb0;
+      decode(w);
       return true;
     }
     if (unit >= end) return false;
     if (tail >= 0 && unit >= tail) {       // narrow tail (splits == 1): two half-width units per remaining wide tile
       const int j = unit - tail;
       w.tile = tail + (j >> 1); w.sub = j & 1; w.split = 0; w.kb0 = 0; w.kb1 = total_kb;
+    } else if (splits == 1) {
+      w.tile = unit; w.split = 0; w.sub = -1; w.kb0 = 0; w.kb1 = total_kb;
     } else {
       w.tile = unit / splits; w.split = unit - w.tile * splits; w.sub = -1;
       w.kb0 = total_kb * w.split / splits; w.kb1 = total_kb * (w.split + 1) / splits;    // 32-bit: k-blocks x splits is tiny
     }
     unit += step;
+    decode(w);
     return true;
   }
 };
@@ -239,6 +256,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   constexpr long long* trace = nullptr;
 #endif
   if (trace && threadIdx.x == 0) trace[0] = clock64();
+  // every role walks the same unit sequence; the first unit (and its divisions) is ready before the dependency wait
+  Sched sch(T, pair, npairs, total_kb);
+  Unit w;
+  bool have = sch.next(w);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tmap_a);
@@ -265,39 +286,47 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
   if (trace && threadIdx.x == 0) trace[1] = clock64();
   pdl_launch_dependents();    // the next kernel may begin its own setup
-  pdl_wait();                 // everything below reads / writes memory the previous kernel may still be producing
+  // The grid dependency is waited for PER ROLE, as late as each role allows: the A producer immediately in front of its
+  // first load (scheduling arithmetic, barrier bookkeeping and the instruction fetches of the loop head are done by then:
+  // they used to cost ~1.2 k clocks between the wait and the first request), the B producer never when B is a load-time
+  // tensor (its first tiles stream from HBM while the previous launch drains), the MMA thread never (no global access),
+  // the epilogue warps before their first global access.
 
   // TMA producer loop.  do_a / do_b: which operand this thread loads; the leader CTA's A producer also posts the
   // transaction count of the whole stage (both CTAs, both operands) on the leader's full barrier.
   auto produce = [&](const bool do_a, const bool do_b) {
     int s = 0;
     uint32_t ph = 0;
-    Sched sch(T, pair, npairs, total_kb);
-    Unit w;
     bool first_unit = true;
-    while (sch.next(w)) {
-      const int tile = w.tile;
-      const int mt = tile % T.tiles_m;
-      const int rest = tile / T.tiles_m;
-      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
-      const int m0 = mt * (2 * BM) + (int)rank * BM;
+    bool must_wait = do_a || !G.b_static;
+    for (; have; have = sch.next(w)) {
+      const int batch = w.batch;
+      const int m0 = w.mt * (2 * BM) + (int)rank * BM;
       const int half_u = w.sub < 0 ? half_n : half_n >> 1;            // rows of B this CTA stages for the unit
-      const int n0 = nt * T.bn + (w.sub > 0 ? half_n : 0) + (int)rank * half_u;
+      const int n0 = w.nt * T.bn + (w.sub > 0 ? half_n : 0) + (int)rank * half_u;
       const uint32_t stage_tx = 2u * (uint32_t)(A_BYTES + half_u * BK * 2);
       const int kb0 = w.kb0, kb1 = w.kb1;
       const bool first_u = first_unit;
       first_unit = false;
-      for (int kb = kb0; kb < kb1; ++kb) {
+      int tap = 0, kk = kb0;                                          // k-block kb = (tap, kk), tracked without dividing
+      if (G.taps > 1) { tap = kb0 / G.k_blocks_per_tap; kk = kb0 - tap * G.k_blocks_per_tap; }
+      for (int kb = kb0; kb < kb1; ++kb, ++kk) {
         if (T.noload && (kb - kb0 >= STAGES || !first_u)) break;
+        if (kk == G.k_blocks_per_tap) { kk = 0; ++tap; }
         ptx::mbar_wait(&empty_bar[s], ph ^ 1);
-        const int tap = kb / G.k_blocks_per_tap, kk = kb - tap * G.k_blocks_per_tap;
         uint8_t* sa = smem + s * STAGE_SZ;
         uint8_t* sb = sa + A_BYTES;
         const uint32_t tx = T.skip == 1 ? 2u * (uint32_t)(half_u * BK * 2) : T.skip == 2 ? 2u * (uint32_t)A_BYTES : stage_tx;
         if (do_a && rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[s], tx);
         const uint32_t lbar = ptx::peer0_addr(&full_bar[s]);
+        if (must_wait) {
+          must_wait = false;
+          pdl_wait();
+          if (trace && do_a && !T.stream_k) trace[3] = clock64();    // grid dependency resolved (A producer's view)
+        }
         if (do_a && T.skip != 1) ptx::tma_load_3d_cg2(sa, &tmap_a, lbar, kk * BK, m0 + G.tap_shift[tap], batch);
         if (do_b && T.skip != 2) ptx::tma_load_2d_cg2(sb, w.sub < 0 ? &tmap_b : &tmap_bn, lbar, tap * G.k_tap + kk * BK, n0);
+        if (trace && do_a && first_u && kb == kb0 && !T.stream_k) trace[4] = clock64();   // first stage requested
         if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
@@ -316,9 +345,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       uint32_t tc = 0, ph = 0;
       int s = 0;
       bool first = true, first_unit = true;
-      Sched sch(T, pair, npairs, total_kb);
-      Unit w;
-      for (; sch.next(w); ++tc) {
+      for (; have; have = sch.next(w), ++tc) {
         const int kb0 = w.kb0, kb1 = w.kb1;
         const uint32_t idesc = w.sub < 0 ? idesc_wide : idesc_narrow;
         const bool first_u = first_unit;
@@ -353,13 +380,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     __syncwarp();
   } else {
+    pdl_wait();                              // bias / gate / residual reads and every store below
     const int q = warp & 3;                  // TMEM lane quarter this warp may read
     const int ew = warp - 2, half = ew >> 2;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     uint32_t tc = 0;
-    Sched sch(T, pair, npairs, total_kb);
-    Unit w;
-    bool have = sch.next(w);
     auto release_acc = [&](uint32_t as) {
       ptx::tc_fence_before();
       __syncwarp();
@@ -380,11 +405,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       have = sch.next(w);
     }
     for (; have && !(T.stream_k && w.kb1 < total_kb); have = sch.next(w), ++tc) {
-      const int tile = w.tile, split = w.split;
-      const int mt = tile % T.tiles_m;
-      const int rest = tile / T.tiles_m;
-      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
-      const int m0 = mt * (2 * BM) + (int)rank * BM;
+      const int split = w.split;
+      const int nt = w.nt, batch = w.batch;
+      const int m0 = w.mt * (2 * BM) + (int)rank * BM;
       const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
       const int bn_u = w.sub < 0 ? T.bn : T.bn >> 1;
       const int nc0 = nt * T.bn + (w.sub > 0 ? (T.bn >> 1) : 0);
@@ -415,11 +438,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       // stream-K head: k-blocks [0, kb1) of a tile that later pairs continue (always this pair's last unit).  The other
       // accumulator stage is idle from here on: fill it with their partial sum while our MMAs still run, merge, then
       // run the fused epilogue on the complete accumulator.
-      const int tile = w.tile;
-      const int mt = tile % T.tiles_m;
-      const int rest = tile / T.tiles_m;
-      const int nt = rest % T.tiles_n, batch = rest / T.tiles_n;
-      const int m0 = mt * (2 * BM) + (int)rank * BM;
+      const int nt = w.nt, batch = w.batch;
+      const int m0 = w.mt * (2 * BM) + (int)rank * BM;
       const uint32_t as = tc & 1, aph = (tc >> 1) & 1;
       const uint32_t tacc = tmem_base + as * ACC_COLS + lane_base, tside = tmem_base + (as ^ 1u) * ACC_COLS + lane_base;
       if (trace && warp == 2 && lane == 0) trace[3] = clock64();
@@ -585,6 +605,13 @@ extern "C" int echo_debug_gemm_trace(long long* device_buf) {
   g_debug_noload = (device_buf && e && e[0] == '1') ? 1 : 0;
   const char* k = getenv("ECHO_GEMM_SKIP");      // "A" / "B": leave that operand's loads out (timing experiments only)
   g_debug_skip = (device_buf && k) ? (k[0] == 'A' ? 1 : k[0] == 'B' ? 2 : 0) : 0;
+  // lean-epilogue experiments (bitmask, see gemm_epilogue_t.cuh) and its per-chunk stamps: the buffer's second half
+  // ([grid .. 2 grid) x 32 slots) when ECHO_GEMM_EPITRACE=<grid> is set
+  const int dbg = device_buf ? getenv_int("ECHO_GEMM_EPIDBG", 0) : 0;
+  const int egrid = device_buf ? getenv_int("ECHO_GEMM_EPITRACE", 0) : 0;
+  long long* etr = egrid > 0 ? device_buf + (long long)egrid * 32 : nullptr;
+  ECHO_CUDA(cudaMemcpyToSymbol(g_epi_dbg, &dbg, sizeof(int)));
+  ECHO_CUDA(cudaMemcpyToSymbol(g_epi_trace, &etr, sizeof(etr)));
   return ECHO_OK;
 #else
   if (!device_buf) return ECHO_OK;

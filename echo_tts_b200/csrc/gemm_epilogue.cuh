@@ -8,6 +8,7 @@ struct GemmShape {
   int tap_shift[8];
   int rows, n;
   int a_ctx;                 // rows of left context in memory before row 0 (already folded into a and tap_shift)
+  int b_static;              // echo_gemm_desc.b_static: B may be requested before the grid dependency resolves
   long long lda, a_batch_stride, ldb;
   const bf16* a;
   const bf16* b;

@@ -17,7 +17,16 @@
 constexpr int EPI_SC_FLOATS = 32 * 32;
 // Kernel-internal epilogue id: GENERIC without activation / bf16 / Snake outputs and with the residual either absent or
 // updated in place (the DiT's two residual projections and their split-K form): leaves through TMA (epi_t_lean_tma).
-constexpr int EPI_GENERIC_LEAN = 3;               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
+constexpr int EPI_GENERIC_LEAN = 3;
+#ifdef ECHO_DEBUG
+// timing experiments of the debug library only (RESULTS ARE GARBAGE when g_epi_dbg != 0): bit 0 = no bulk store issued,
+// bit 1 = no gate / bias shuffles, bit 2 = no staging stores; g_epi_trace: [cta][32] clock stamps of epilogue warp 0
+__device__ int g_epi_dbg = 0;
+__device__ long long* g_epi_trace = nullptr;
+#define EPI_STAMP(k) do { if (etr && (k) < 32) etr[(k)] = clock64(); } while (0)
+#else
+#define EPI_STAMP(k) do { } while (0)
+#endif               // per-warp scratch: 32 rows x 32 fp32, 16-byte chunks swizzled
 
 // The scratch is addressed in the shared state space explicitly: through a generic pointer the compiler emits
 // generic LD/ST (address translation, long-scoreboard latency) instead of LDS/STS.
@@ -423,19 +432,30 @@ __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P,
   uint32_t row_addr = smem_u32(sc) + (uint32_t)lane * 128u;
   bool pending = false;
   int i = 0;
+#ifdef ECHO_DEBUG
+  const int dbg = g_epi_dbg;
+  long long* const etr = (g_epi_trace && (threadIdx.x >> 5) == 2 && lane == 0) ? g_epi_trace + (long long)blockIdx.x * 32 : nullptr;
+#else
+  constexpr int dbg = 0;
+#endif
+  EPI_STAMP(0);
 #pragma unroll 1
   for (int c = R.half * 32; c < cend; c += 64, ++i) {
     const int n = R.n0 + c;
     float v[32];
     L.load32(c, v);
+    EPI_STAMP(1 + 4 * i);
     const float ga = i == 0 ? A.ga[0] : (i == 1 ? A.ga[1] : (i == 2 ? A.ga[2] : A.ga[3]));
     const float gb = i == 0 ? A.gb[0] : (i == 1 ? A.gb[1] : (i == 2 ? A.gb[2] : A.gb[3]));
     const float bs = i == 0 ? A.bs[0] : (i == 1 ? A.bs[1] : (i == 2 ? A.bs[2] : A.bs[3]));
-    if (has_bias) {
+    if (has_bias && !(dbg & 2)) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, bs, j);
     }
-    if (P.gate && !slow_gate) {
+    if (dbg & 2) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = v[j] * ga + bs;
+    } else if (P.gate && !slow_gate) {
       if (two) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -455,18 +475,28 @@ __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P,
         }
       }
     }
+    EPI_STAMP(2 + 4 * i);
     if (pending && sc_stride == 0) {                       // the previous chunk's bulk operation has read the scratch
       if (lane == 0) tma_out_wait_read();
       __syncwarp();
     }
+    if (!(dbg & 4)) {
 #pragma unroll
     for (int k = 0; k < 8; ++k)
       asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_addr + (uint32_t)((k ^ (lane & 7)) << 4)),
                    "f"(v[4 * k]), "f"(v[4 * k + 1]), "f"(v[4 * k + 2]), "f"(v[4 * k + 3])
                    : "memory");
+    } else {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) acc += v[k];
+      if (acc == 12345.678f) asm volatile("st.shared.f32 [%0], %1;" ::"r"(row_addr), "f"(acc) : "memory");
+    }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the bulk copy
     __syncwarp();
-    if (lane == 0) tma_out_4d(tmap_out, sc, P.red_resid != 0, n, R.mb0, R.batch_idx, R.split);
+    EPI_STAMP(3 + 4 * i);
+    if (lane == 0 && !(dbg & 1)) tma_out_4d(tmap_out, sc, P.red_resid != 0, n, R.mb0, R.batch_idx, R.split);
+    EPI_STAMP(4 + 4 * i);
     pending = true;
     sc += sc_stride;
     row_addr += (uint32_t)sc_stride * 4u;
@@ -475,6 +505,7 @@ __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P,
     if (lane == 0) tma_out_wait_read();
     __syncwarp();
   }
+  EPI_STAMP(17);
 }
 
 // What an epilogue can fetch before its accumulator exists (kept in registers across the wait for the MMAs).

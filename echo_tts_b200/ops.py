@@ -58,6 +58,7 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
     assert a_ctx == 0 or batch == 1
     d.a_ctx = a_ctx
     d.rows_per_gate = 1
+    d.b_static = 1          # every caller in this package passes load-time weights as `w` (include/echo_b200.h: b_static)
     if d.impl == 2 and STREAM_K:
         ws = gemm_workspace(a.device)
         d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()

@@ -80,7 +80,10 @@ typedef struct echo_gemm_desc {
                              * batch entry of `a`; rows -a_ctx..-1 are read instead of zero-filled (the causal padding of
                              * the first call is an all-zero context).  a_batch_stride must span them.  0 = none. */
   float eps;
-  float _pad2;
+  int32_t b_static;         /* 1 = `b` is a load-time tensor (weights): nothing launched on `stream` since the last
+                             * synchronisation or non-library launch writes it.  The kernel then requests its first B
+                             * tiles while the previous launch is still draining (programmatic dependent launch) instead of
+                             * after it; results are identical.  0 = no such promise (always safe). */
   const float* rope_cos;    /* fp32 [max_pos][head_dim/2] */
   const float* rope_sin;
   int64_t ld_sec_out;

@@ -53,17 +53,34 @@ def main():
             fn()
         torch.cuda.synchronize()
         buf.zero_()
+        os.environ["ECHO_GEMM_EPITRACE"] = "256"             # lean-epilogue chunk stamps in rows [256, 512)
         L.check(lib.echo_debug_gemm_trace(buf.data_ptr()))   # needs the debug build: make -C echo_tts_b200/csrc DEBUG=1
         fn()
         torch.cuda.synchronize()
         lib.echo_debug_gemm_trace(None)
         t = buf.cpu()
-        t = t[t[:, 0] != 0]
+        et, t = t[256:], t[:256]
+        nz = t[:, 0] != 0
+        et = et[nz][0::2]
+        t = t[nz]
         ld, fo = t[0::2], t[1::2]          # leader / follower CTA of each pair
         med = lambda v: float(v.float().median())
         print(f"== {name} M={M}: {t.shape[0]} CTAs; SM clocks, median over pairs")
         print(f"   setup {med(ld[:, 1] - ld[:, 0]):8.0f}   first operands after setup {med(ld[:, 2] - ld[:, 1]):8.0f}   "
               f"whole CTA {med(ld[:, 6] - ld[:, 0]):8.0f}   teardown {med(ld[:, 7] - ld[:, 6]):8.0f}")
+        if bool((ld[:, 3] != 0).all()) and bool((ld[:, 4] != 0).all()) and os.environ.get("ECHO_STREAM_K", "0") != "1":
+            print(f"   after setup: dependency resolved +{med(ld[:, 3] - ld[:, 1]):6.0f}  first stage requested +{med(ld[:, 4] - ld[:, 3]):6.0f}  "
+                  f"landed (MMA thread's view) +{med(ld[:, 2] - ld[:, 4]):6.0f}")
+        if bool((et[:, 0] != 0).any()):
+            e = et[et[:, 0] != 0]
+            d = lambda a, b: med(e[:, a] - e[:, b])
+            row = "   lean epilogue, leader warp 2, per chunk (tmem ld | math | staged+fenced | bulk issued): "
+            for i in range(4):
+                if bool((e[:, 4 + 4 * i] != 0).all()):
+                    prev = 0 if i == 0 else 4 * i
+                    row += f"[{d(1 + 4 * i, prev):5.0f} {d(2 + 4 * i, 1 + 4 * i):5.0f} {d(3 + 4 * i, 2 + 4 * i):5.0f} {d(4 + 4 * i, 3 + 4 * i):5.0f}] "
+            last = max(i for i in range(4) if bool((e[:, 4 + 4 * i] != 0).all()))
+            print(row + f" drain {d(17, 4 + 4 * last):5.0f}  total {d(17, 0):6.0f}")
         mx = lambda v: float(v.float().max())
         sk = ld[ld[:, 3] != 0]
         if sk.shape[0]:
