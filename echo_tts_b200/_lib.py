@@ -66,8 +66,9 @@ class AttnDesc(C.Structure):
     _fields_ = [
         ("q", c_p), ("q_row_stride", i64), ("q_batch_stride", i64), ("gate", c_p), ("out", c_p),
         ("rows", i32), ("seq", i32), ("heads", i32), ("head_dim", i32),
-        ("n_seg", i32), ("impl", i32), ("softmax_scale", f32), ("_pad1", f32),
+        ("n_seg", i32), ("impl", i32), ("softmax_scale", f32), ("kv_splits", i32),
         ("seg", AttnSegment * 4),
+        ("workspace", c_p), ("workspace_bytes", i64),
     ]
 
 
@@ -151,6 +152,7 @@ class DitStepDesc(C.Structure):
         ("x", c_p), ("xn", c_p), ("qkvg", c_p), ("ao", c_p), ("hmid", c_p), ("delta", c_p),
         ("gemm_workspace", c_p), ("gemm_workspace_bytes", i64), ("gemm_impl", i32), ("attn_impl", i32),
         ("tail", C.POINTER(TailDesc)), ("pending_out", C.POINTER(i32)),
+        ("attn_workspace", c_p), ("attn_workspace_bytes", i64),
     ]
 
 
@@ -175,6 +177,7 @@ EXPORTS = {
     "echo_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, c_p, i64, C.c_int, c_p, i64, c_p, i64, c_p]),
     "echo_add_rmsnorm_mod": (C.c_int, [c_p, i64, C.c_int, C.c_int, f32, c_p, C.c_int, i64, c_p, c_p, i64, C.c_int, c_p, i64, c_p]),
     "echo_attention": (C.c_int, [C.POINTER(AttnDesc), c_p]),
+    "echo_attention_workspace_bytes": (C.c_longlong, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "echo_mask_extent": (C.c_int, [c_p, C.c_int, C.c_int, i64, c_p, c_p]),
     "echo_cfg_euler_tail": (C.c_int, [C.POINTER(TailDesc), c_p]),
     "echo_cfg_combine_euler": (C.c_int, [C.POINTER(TailDesc), c_p]),

@@ -27,6 +27,11 @@ constexpr int MAX_TILES = 128;                // <= 8192 keys in total
 constexpr int SMEM_ATTN = Q_BYTES + 4 * KV_BYTES + 1024 /*align*/ + 256 /*barriers*/ + MAX_TILES * 16;
 constexpr int TM_S0 = 0, TM_S1 = 64, TM_O = 128, TM_COLS = 256;
 constexpr float RESCALE_TAU = 8.f;            // lazy-rescale threshold (log2 domain): P <= 2^8
+// split-KV exchange: one part = un-normalised O [32 float4 column groups][128 rows] (a warp reads / writes 512
+// contiguous bytes per instruction) + m[128] + l[128]
+constexpr int PART_FLOATS = QT * HD + 2 * QT;
+constexpr int WS_COUNTERS = 16384;            // ints at the head of the workspace
+constexpr int MAX_SPLITS = 4;
 
 struct AttnSeg {
   int len, kv_batch_mod;
@@ -41,6 +46,10 @@ struct AttnParams {
   static constexpr long long* trace = nullptr;
 #endif
   int rows, seq, heads, n_seg;
+  int splits;            // > 1: split-KV -- `splits` CTAs per (row, head, query tile), each a contiguous share of the key
+                         // tiles; partial (O, m, l) through `ws_parts`, merged in a fixed order by the last CTA to arrive
+  float* ws_parts;       // [group][split][PART_FLOATS]
+  int* ws_count;         // [group] arrival counters, zero between launches (the merging CTA resets its own)
   int static_first;      // segment 0 has no mask / extent and len > 0: tile 0 is known before the tile list is built
   float softmax_scale;
   const bf16* gate;
@@ -143,7 +152,9 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   TileInfo* tiles = reinterpret_cast<TileInfo*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int q0 = blockIdx.x * QT, head = blockIdx.y, row = blockIdx.z;
+  const int nsplit = A.splits > 1 ? A.splits : 1;
+  const int qt = (int)blockIdx.x / nsplit, part = (int)blockIdx.x - qt * nsplit;
+  const int q0 = qt * QT, head = blockIdx.y, row = blockIdx.z;
 #ifdef ECHO_DEBUG
   long long* const trace = A.trace ? A.trace + ((long long)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 64 : nullptr;
 #else
@@ -221,7 +232,7 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&p_full[i], 128); ptx::mbar_init(&pv_done[i], 1);
     }
     ptx::fence_barrier_init();
-    if (A.static_first) {
+    if (A.static_first && part == 0) {
       // Q and the first K / V tile do not depend on the tile list: put them in flight under the rest of the set-up.
       pdl_wait();
       const int kvrow = A.seg[0].kv_batch_mod > 0 ? row % A.seg[0].kv_batch_mod : row;
@@ -244,14 +255,20 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int ntiles = *s_ntiles;
+  // split-KV: this CTA's contiguous share of the tile list (every part builds the same list)
+  const int ntiles_all = *s_ntiles;
+  const int nparts = ntiles_all < nsplit ? (ntiles_all > 0 ? ntiles_all : 1) : nsplit;     // parts that have tiles
+  const int j_first = part < nparts ? (int)((long long)ntiles_all * part / nparts) : 0;
+  const int ntiles = part < nparts ? (int)((long long)ntiles_all * (part + 1) / nparts) - j_first : 0;
+  tiles += j_first;
+  const bool idle_part = part >= nparts;      // more parts than tiles: nothing to do, nothing to publish
   pdl_wait();
   if (trace && tid == 0) trace[1] = clock64();
 
   if (warp == 4) {
     // ===== TMA producer =====
     if (lane == 0 && ntiles > 0) {
-      const bool early = A.static_first != 0;     // Q, K(0), V(0) already in flight
+      const bool early = A.static_first != 0 && part == 0;     // Q, K(0), V(0) already in flight
       if (!early) {
         ptx::mbar_arrive_expect_tx(q_full, Q_BYTES);
         tma_load_4d(sQ, &M.q, q_full, 0, head, q0, row);
@@ -452,12 +469,70 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       if (A.gate) ptx::mbar_wait(g_full, 0);
     }
     if (trace && tid == 0) trace[60] = clock64();
+    // ---- split-KV: publish this part's (O, m, l); the LAST part of the group to arrive sums all of them in part order
+    //      (so the result does not depend on who that is) and runs the epilogue; the others are done ----
+    const bool merging = nparts > 1;
+    bool do_out = !idle_part;
+    float wp[MAX_SPLITS] = {1.f, 0.f, 0.f, 0.f};
+    const float* parts = nullptr;
+    if (merging && !idle_part) {
+      const int group = ((int)row * A.heads + head) * ((int)gridDim.x / nsplit) + qt;
+      parts = A.ws_parts + (long long)group * nsplit * PART_FLOATS;
+      float* mine = A.ws_parts + ((long long)group * nsplit + part) * PART_FLOATS;
+#pragma unroll 1
+      for (int c = 0; c < HD; c += 32) {
+        float o[32];
+        ptx::tmem_ld32(tmem_base + TM_O + lane_off + c, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          __stcg(reinterpret_cast<float4*>(mine) + ((c >> 2) + k) * QT + tid,
+                 make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]));
+      }
+      __stcg(mine + QT * HD + tid, m);
+      __stcg(mine + QT * HD + QT + tid, l);
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (tid == 0) s_ntiles[1] = atomicAdd(A.ws_count + group, 1);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      do_out = s_ntiles[1] == nparts - 1;
+      if (do_out) {
+        __threadfence();
+        float mp[MAX_SPLITS], mx = -INFINITY;
+#pragma unroll
+        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
+          mp[p2] = p2 < nparts ? __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + tid) : -INFINITY;
+          mx = fmaxf(mx, mp[p2]);
+        }
+        l = 0.f;
+#pragma unroll
+        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
+          wp[p2] = (p2 < nparts && mp[p2] != -INFINITY) ? exp2f(mp[p2] - mx) : 0.f;
+          if (p2 < nparts) l = fmaf(wp[p2], __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + QT + tid), l);
+        }
+        if (tid == 0) A.ws_count[group] = 0;               // ready for the next launch
+      }
+    }
     const float inv = l > 0.f ? 1.f / l : 0.f;
     uint8_t* const stage_row = sK + tid * 128;
 #pragma unroll 1
-    for (int c = 0; c < HD; c += 32) {
+    for (int c = 0; c < HD && do_out; c += 32) {
       float o[32];
-      if (ntiles > 0) {
+      if (merging) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = 0.f;
+#pragma unroll
+        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
+          if (p2 < nparts) {
+            const float4* src = reinterpret_cast<const float4*>(parts + (long long)p2 * PART_FLOATS) + (c >> 2) * QT + tid;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float4 v = __ldcg(src + k * QT);
+              o[4 * k] = fmaf(wp[p2], v.x, o[4 * k]); o[4 * k + 1] = fmaf(wp[p2], v.y, o[4 * k + 1]);
+              o[4 * k + 2] = fmaf(wp[p2], v.z, o[4 * k + 2]); o[4 * k + 3] = fmaf(wp[p2], v.w, o[4 * k + 3]);
+            }
+          }
+        }
+      } else if (ntiles > 0) {
         ptx::tmem_ld32(tmem_base + TM_O + lane_off + c, o);
       } else {
 #pragma unroll
@@ -483,7 +558,7 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
     }
     ptx::fence_proxy_async();                              // generic-proxy writes -> visible to the TMA store
     asm volatile("bar.sync 1, 128;" ::: "memory");         // the four softmax warps only
-    if (tid == 0) {
+    if (tid == 0 && do_out) {
       tma_store_4d(&M.out, sK, 0, head, q0, row);
       tma_store_4d(&M.out, sK + Q_BYTES / 2, 64, head, q0, row);
       tma_store_commit_wait();
@@ -496,6 +571,15 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   if (trace && tid == 0) { trace[62] = clock64(); trace[63] = ntiles; }
 }
 }  // namespace
+
+// Bytes of the split-KV exchange buffer (echo_attn_desc.workspace) that lets a call with this many (row, head, query
+// tile) groups use up to `kv_splits` parts: counters + one partial (O, m, l) per part.  Zeroed once by the caller.
+extern "C" long long echo_attention_workspace_bytes(int rows, int seq, int heads, int kv_splits) {
+  if (kv_splits < 1) kv_splits = MAX_SPLITS;
+  if (kv_splits > MAX_SPLITS) kv_splits = MAX_SPLITS;
+  const long long groups = (long long)ceil_div(seq, QT) * heads * rows;
+  return (long long)WS_COUNTERS * 4 + groups * kv_splits * (long long)PART_FLOATS * 4;
+}
 
 // Debug aid: >= 64 int64 per CTA; [0] start, [1] setup done, per tile j < 12: [4+4j] S(j) ready, [5+4j] PV(j-1) done,
 // [6+4j] P(j) published, [7+4j] PV(j) issued (MMA lane); [2] warp 0 past the PDL wait, [3] tile list built,
@@ -577,7 +661,27 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
     ECHO_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ATTN));
     attr_set = true;
   }
-  dim3 grid(ceil_div(d->seq, QT), d->heads, d->rows);
+  // split-KV when the (row, head, query tile) groups alone leave SMs idle (two CTAs fit one SM): the un-guided 640-token
+  // step has 80 groups, a 160-latent streaming block 32.  The caller lends the exchange buffer.
+  const int qtiles = ceil_div(d->seq, QT);
+  const long long groups = (long long)qtiles * d->heads * d->rows;
+  int splits = 1;
+  if (d->kv_splits != 1 && d->workspace && groups > 0 && groups <= WS_COUNTERS) {
+    static const int forced = [] { const char* e = getenv("ECHO_ATTN_SPLITS"); return e && e[0] ? atoi(e) : 0; }();
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int slots = 2 * sms;
+    int want = d->kv_splits > 1 ? d->kv_splits : (forced > 0 ? forced : (int)(slots / groups));
+    if (want > MAX_SPLITS) want = MAX_SPLITS;
+    if (want > total_tiles / 2) want = (int)(total_tiles / 2);          // at least two key tiles per part
+    const long long room = (d->workspace_bytes - (long long)WS_COUNTERS * 4) / ((long long)PART_FLOATS * 4);
+    if (want > 1 && room >= groups * want) splits = want;
+  }
+  A.splits = splits;
+  A.ws_count = reinterpret_cast<int*>(d->workspace);
+  A.ws_parts = d->workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(d->workspace) + (long long)WS_COUNTERS * 4) : nullptr;
+  dim3 grid(qtiles * splits, d->heads, d->rows);
   ECHO_CUDA(echo_launch(attention_tc_kernel, grid, dim3(192), SMEM_ATTN, st, M, A));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();

@@ -48,6 +48,21 @@ static int g_debug_skip = 0;     // 1 = never load A, 2 = never load B
 constexpr int g_debug_noload = 0;
 #endif
 
+// n / d for 0 <= n < 2^31 with a host-made multiplier: 3 instructions instead of the ~40 of a 32-bit division (every
+// thread decodes its CTA's units)
+struct FastDiv {
+  uint32_t mul, shift;
+  __device__ __forceinline__ int div(int n) const { return (int)((__umulhi((uint32_t)n, mul) + (uint32_t)n) >> shift); }
+};
+static FastDiv make_fastdiv(int d) {
+  FastDiv f;
+  uint32_t sh = 0;
+  while ((1u << sh) < (uint32_t)d) ++sh;
+  f.shift = sh;
+  f.mul = (uint32_t)((((uint64_t)1 << 32) * (((uint64_t)1 << sh) - (uint64_t)d)) / (uint64_t)d + 1);
+  return f;
+}
+
 struct Tiling {
 #ifdef ECHO_DEBUG
   long long* trace;       // nullptr unless tracing: [cta][32] SM-clock stamps
@@ -60,6 +75,7 @@ struct Tiling {
   int stages, stage_bytes; // operand ring: stage = A (16 KB) + this CTA's half of B (bn/2 rows x 128 B)
   int bn;                 // tile width (multiple of 32, <= 256); each CTA stages bn/2 rows of B
   int tiles_m, tiles_n;   // pair tiles per batch entry
+  FastDiv fd_m, fd_n, fd_s;   // divisions by tiles_m / tiles_n / splits
   int num_tiles;          // work units: tiles_m * tiles_n * batch * splits
   int splits;             // split-K: units per tile (unit index = tile * splits + split)
   long long split_stride; // elements between the partial outputs
@@ -82,10 +98,12 @@ constexpr long long SK_SLOT_FLOATS = 2LL * BM * ACC_COLS;      // one pair's par
 struct Unit { int tile, split, kb0, kb1, sub, mt, nt, batch; };
 struct Sched {
   int sk, total_kb, splits, unit, step, end, tail, tiles_m, tiles_n;
+  FastDiv fd_m, fd_n, fd_s;
   long long u, e;
   __device__ Sched(const Tiling& T, int pair, int npairs, int total_kb_) {
     sk = T.stream_k; total_kb = total_kb_; splits = T.splits; tail = T.tail_start;
     tiles_m = T.tiles_m; tiles_n = T.tiles_n;
+    fd_m = T.fd_m; fd_n = T.fd_n; fd_s = T.fd_s;
     unit = pair; step = npairs; end = T.num_tiles;
     u = e = 0;
     if (sk) {
@@ -94,9 +112,9 @@ struct Sched {
     }
   }
   __device__ __forceinline__ void decode(Unit& w) const {
-    w.mt = w.tile % tiles_m;
-    const int rest = w.tile / tiles_m;
-    w.batch = rest / tiles_n;
+    const int rest = fd_m.div(w.tile);
+    w.mt = w.tile - rest * tiles_m;
+    w.batch = fd_n.div(rest);
     w.nt = rest - w.batch * tiles_n;
   }
   __device__ bool next(Unit& w) {
@@ -117,8 +135,8 @@ struct Sched {
     } else if (splits == 1) {
       w.tile = unit; w.split = 0; w.sub = -1; w.kb0 = 0; w.kb1 = total_kb;
     } else {
-      w.tile = unit / splits; w.split = unit - w.tile * splits; w.sub = -1;
-      w.kb0 = total_kb * w.split / splits; w.kb1 = total_kb * (w.split + 1) / splits;    // 32-bit: k-blocks x splits is tiny
+      w.tile = fd_s.div(unit); w.split = unit - w.tile * splits; w.sub = -1;
+      w.kb0 = fd_s.div(total_kb * w.split); w.kb1 = fd_s.div(total_kb * (w.split + 1));   // 32-bit: k-blocks x splits is tiny
     }
     unit += step;
     decode(w);
@@ -568,6 +586,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   if (T.stages > max_stages()) T.stages = max_stages();
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
+  T.fd_m = make_fastdiv(T.tiles_m); T.fd_n = make_fastdiv(T.tiles_n); T.fd_s = make_fastdiv(splits);
   T.splits = splits;
   T.split_stride = split_stride;
   T.num_tiles = T.tiles_m * T.tiles_n * batch * splits;

@@ -33,7 +33,7 @@ extern "C" void echo_reset_launch_count(void) { g_echo_launches = 0; }
 // Four warps per row, two rows per CTA: every load a row needs (x, up to four split-K partials, scale, shift) is in
 // flight before the first use -- one memory round trip per row, and 4x the CTAs of a warp-per-row layout when only
 // a few hundred rows exist (the single-branch Euler steps).
-constexpr int NORM_MAX_DELTA = 4;
+constexpr int NORM_MAX_DELTA = 4;    // partials in flight at a time (registers); up to 16 are summed
 template <int VEC>
 __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restrict__ x, long long ldx, int m, int d,
                                                           float eps, const float* __restrict__ delta, int n_delta,
@@ -109,6 +109,28 @@ __global__ void __launch_bounds__(256) rmsnorm_mod_kernel(const float* __restric
           }
         }
       }
+      for (int s0 = NORM_MAX_DELTA; s0 < n_delta; s0 += NORM_MAX_DELTA) {   // more partials: four at a time, same order
+#pragma unroll
+        for (int s = 0; s < NORM_MAX_DELTA; ++s) {
+          if (s0 + s < n_delta) {
+            const float4* dr = reinterpret_cast<const float4*>(delta + (s0 + s) * delta_stride + (long long)row * ldx);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+              const int c = t + i * 128;
+              if (c < nvec) dl[s][i] = dr[c];
+            }
+          }
+        }
+#pragma unroll
+        for (int s = 0; s < NORM_MAX_DELTA; ++s) {
+          if (s0 + s < n_delta) {
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+              if (t + i * 128 < nvec) { v[i].x += dl[s][i].x; v[i].y += dl[s][i].y; v[i].z += dl[s][i].z; v[i].w += dl[s][i].w; }
+            }
+          }
+        }
+      }
       float4* xo = reinterpret_cast<float4*>(x_out + (long long)row * ldx);
 #pragma unroll
       for (int i = 0; i < VEC; ++i) {
@@ -144,8 +166,8 @@ static int launch_rmsnorm(const float* x, int64_t ldx, int m, int d, float eps, 
                           int rows_per_mod, const int32_t* step, int64_t mod_step_stride, void* y, int64_t ldy,
                           echo_stream_t stream) {
   ECHO_CHECK_ARG(x && scale1 && y && m > 0, "rmsnorm: null argument");
-  ECHO_CHECK_ARG(n_delta >= 0 && n_delta <= NORM_MAX_DELTA && (n_delta == 0 || (delta && x_out && delta_stride % 4 == 0)),
-                 "rmsnorm: bad delta arguments (at most %d partials)", NORM_MAX_DELTA);
+  ECHO_CHECK_ARG(n_delta >= 0 && n_delta <= 16 && (n_delta == 0 || (delta && x_out && delta_stride % 4 == 0)),
+                 "rmsnorm: bad delta arguments (at most 16 partials)");
   ECHO_CHECK_ARG(d % 4 == 0 && d <= 4096 && ldx % 4 == 0 && ldy % 4 == 0 && mod_ld % 4 == 0, "rmsnorm: d must be <=4096, %%4");
   if (rows_per_mod <= 0) rows_per_mod = 1 << 30;
   dim3 grid(ceil_div(m, 2));

@@ -156,6 +156,7 @@ extern "C" int echo_dit_step(const echo_dit_step_desc* D, echo_stream_t stream) 
       a.rows = D->rows; a.seq = D->seq; a.heads = D->heads; a.head_dim = D->head_dim;
       a.softmax_scale = (float)pow((double)D->head_dim, -0.5);
       a.impl = D->attn_impl;
+      a.workspace = D->attn_workspace; a.workspace_bytes = D->attn_workspace_bytes;
       int ns = 0;
       echo_attn_segment* s = &a.seg[ns++];
       s->k = qkvg + Md; s->v = qkvg + 2 * Md;

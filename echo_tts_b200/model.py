@@ -363,7 +363,8 @@ class EchoDiT:
         (one un-guided row of 640) a 256 x 256 tiling leaves most of the 74 CTA pairs idle, so the K loop is split
         over enough work units to fill them; the partial products are summed by the next norm kernel."""
         tiles = -(-M // 256) * -(-self.cfg.model_size // 256)
-        return max(1, min(4, 74 // tiles, self.cfg.model_size // 64))
+        cap = 8 if M <= 256 else 4        # one row tile (a 160-latent streaming block): w2's 92 k-blocks over 8 units
+        return max(1, min(cap, 74 // tiles, self.cfg.model_size // 64))
 
     def _layer_array(self):
         """HOST array of per-layer weight pointers for echo_dit_step (built once; the tensors live in self.layers)."""
@@ -448,6 +449,8 @@ class EchoDiT:
         d.delta = L.ptr(ws["delta"])
         gws = ops.gemm_workspace(self._device)
         d.gemm_workspace, d.gemm_workspace_bytes = gws.data_ptr(), gws.numel()
+        aws = ops.attn_workspace(self._device)
+        d.attn_workspace, d.attn_workspace_bytes = aws.data_ptr(), aws.numel()
         d.gemm_impl, d.attn_impl = ops.GEMM_IMPL, ops.ATTN_IMPL
         if tail is not None:
             d.tail = C.pointer(tail)

@@ -36,6 +36,21 @@ def gemm_workspace(device: torch.device) -> torch.Tensor:
     return ws
 
 
+_ATTN_WS = {}
+
+
+def attn_workspace(device: torch.device) -> torch.Tensor:
+    """Split-KV exchange buffer lent to every tcgen05 attention launch on ``device`` (echo_attn_desc.workspace: arrival
+    counters + 296 partial (O, m, l) = two CTAs per SM, zeroed once).  One buffer per device: attention launches of this
+    package run on one stream at a time per device."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _ATTN_WS.get(key)
+    if ws is None:
+        ws = torch.zeros(int(L.load().echo_attention_workspace_bytes(1, 128 * 74, 1, 4)), device=device, dtype=torch.uint8)
+        _ATTN_WS[key] = ws
+    return ws
+
+
 def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), batch: int = 1,
                impl: Optional[int] = None, block_n: int = 0, a_ctx: int = 0) -> L.GemmDesc:
     """a: bf16 [batch*rows, k_tap] (row-major, contiguous rows); w: bf16 [n, taps*k_tap].  ``a_ctx``: rows of left
@@ -230,8 +245,9 @@ ATTN_IMPL = 0     # echo_attn_desc.impl: 0 = tcgen05 kernel where eligible (head
 
 
 def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate: Optional[torch.Tensor] = None,
-              softmax_scale: Optional[float] = None, impl: Optional[int] = None) -> None:
-    """q bf16 [R, S, H, Dh] (last two dims contiguous); out bf16 [R*S, H*Dh]."""
+              softmax_scale: Optional[float] = None, impl: Optional[int] = None, kv_splits: int = 0) -> None:
+    """q bf16 [R, S, H, Dh] (last two dims contiguous); out bf16 [R*S, H*Dh].  ``kv_splits``: 0 = automatic split-KV
+    (few query tiles: several CTAs share one tile's keys), 1 = off, 2..4 = forced."""
     _need(q, BF16, "q"); _need(out, BF16, "out")
     R, S, H, Dh = q.shape
     assert q.stride(3) == 1 and q.stride(2) == Dh and out.shape == (R * S, H * Dh) and out.is_contiguous()
@@ -245,6 +261,10 @@ def attention(q: torch.Tensor, segs: Sequence[Segment], out: torch.Tensor, gate:
     d.softmax_scale = softmax_scale if softmax_scale is not None else Dh ** -0.5
     d.n_seg = len(segs)
     d.impl = ATTN_IMPL if impl is None else impl
+    d.kv_splits = kv_splits
+    if kv_splits != 1 and Dh == 128:
+        ws = attn_workspace(q.device)
+        d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
     for i, s in enumerate(segs):
         sg = d.seg[i]
         sg.len = s.length

@@ -197,10 +197,19 @@ typedef struct echo_attn_desc {
   int32_t rows, seq, heads, head_dim;
   int32_t n_seg;
   int32_t impl;             /* 0 = tcgen05 kernel when eligible (head_dim 128, non-causal), else mma.sync kernel; 1 = force mma.sync */
-  float softmax_scale, _pad1;
+  float softmax_scale;
+  int32_t kv_splits;        /* tcgen05 kernel: 0 = automatic, 1 = never, 2..4 = that many CTAs per (row, head, query tile),
+                             * each a contiguous share of the key tiles (split-KV; needs `workspace`) */
   echo_attn_segment seg[4];
+  void* workspace;          /* optional split-KV exchange buffer of >= echo_attention_workspace_bytes(...), zeroed ONCE by
+                             * the caller, not shared between streams that run attention concurrently.  With few
+                             * (row, head, query tile) groups -- the un-guided 640-token step has 80 for 148 SMs, a
+                             * 160-latent streaming block 32 -- the parts' un-normalised (O, m, l) go through it and the
+                             * last part to arrive merges them in part order: deterministic. NULL = never split. */
+  int64_t workspace_bytes;
 } echo_attn_desc;
 int echo_attention(const echo_attn_desc* d, echo_stream_t stream);
+long long echo_attention_workspace_bytes(int rows, int seq, int heads, int kv_splits);
 /* Debug aid (no reference counterpart; debug builds only, as echo_debug_gemm_trace): while non-NULL, every tcgen05
  * attention launch records 64 clock64() stamps per CTA (layout documented at the definition in csrc/attention2.cu). */
 int echo_debug_attn_trace(long long* device_buf);
@@ -309,6 +318,7 @@ typedef struct echo_dit_step_desc {
   int32_t gemm_impl, attn_impl; /* echo_gemm_desc.impl / echo_attn_desc.impl for every launch (2 / 0 = product path) */
   const echo_tail_desc* tail;   /* nullable; h, ldh, delta, n_delta, delta_stride are filled in by the library */
   int32_t* pending_out;     /* HOST, nullable: set to 1 when tail == NULL and `delta` still has to be added to x */
+  void* attn_workspace; int64_t attn_workspace_bytes; /* as echo_attn_desc.workspace (split-KV); NULL = never split */
 } echo_dit_step_desc;
 int echo_dit_step(const echo_dit_step_desc* d, echo_stream_t stream);
 

@@ -96,6 +96,47 @@ def test_joint_attention_dit_shapes(ops, impl, R, S, Lt, valid_t, Ls):
     assert rel_l2(out.float(), ref) < 6e-3
 
 
+@pytest.mark.parametrize("splits", [0, 2, 3, 4])
+@pytest.mark.parametrize("R,S,Lt,valid_t,Ls,Lp", [(1, 640, 768, 256, 53, 0),      # un-guided 640-token step: 80 groups
+                                                   (3, 160, 768, 256, 53, 480),    # guided 160-latent block behind 480
+                                                   (1, 160, 768, 0, 0, 0),         # self keys only: 3 tiles, 4 parts asked
+                                                   (1, 100, 64, 1, 5, 0)])         # two tiles in all
+def test_split_kv_attention(ops, splits, R, S, Lt, valid_t, Ls, Lp):
+    """Split-KV (several CTAs share one query tile's keys, partial (O, m, l) merged in part order by the last to arrive):
+    equal to the dense fp32 reference at the tolerance of the unsplit kernel, close to the unsplit kernel, bit-identical
+    from run to run (the merge order is fixed), counters self-resetting (three launches in a row)."""
+    H, Dh = 16, 128
+    qkv = _rand((3, R, S, H, Dh), 41, dtype=BF16)
+    kt, vt = _rand((1, Lt, H, Dh), 42, dtype=BF16), _rand((1, Lt, H, Dh), 43, dtype=BF16)
+    ksp, vsp = _rand((1, max(Ls, 1), H, Dh), 44, dtype=BF16), _rand((1, max(Ls, 1), H, Dh), 45, dtype=BF16)
+    kp, vp = _rand((1, max(Lp, 1), H, Dh), 46, dtype=BF16), _rand((1, max(Lp, 1), H, Dh), 47, dtype=BF16)
+    gate = torch.sigmoid(_rand((R * S, H * Dh), 48)).to(BF16)
+    tm = torch.zeros(R, Lt, dtype=torch.uint8, device="cuda"); tm[:, :valid_t] = 1
+    sm = torch.ones(R, max(Ls, 1), dtype=torch.uint8, device="cuda")
+    if Ls == 0:
+        sm[:] = 0
+    if R == 3:
+        tm[1] = 0; sm[2] = 0
+    segs = [ops.Segment(qkv[1], qkv[2])]
+    refs = [dict(k=qkv[1], v=qkv[2])]
+    if Lp:
+        segs.append(ops.Segment(kp, vp, kv_batch_mod=1, length=Lp)); refs.append(dict(k=kp, v=vp))
+    segs += [ops.Segment(kt, vt, kv_batch_mod=1, mask=tm, extent=ops.mask_extent(tm)),
+             ops.Segment(ksp, vsp, kv_batch_mod=1, mask=sm, extent=ops.mask_extent(sm))]
+    refs += [dict(k=kt, v=vt, mask=tm), dict(k=ksp, v=vsp, mask=sm)]
+    outs = []
+    for _ in range(3):
+        out = torch.full((R * S, H * Dh), float("nan"), device="cuda", dtype=BF16)
+        ops.attention(qkv[0], segs, out, gate=gate, kv_splits=splits)
+        outs.append(out)
+    base = torch.empty_like(outs[0])
+    ops.attention(qkv[0], segs, base, gate=gate, kv_splits=1)
+    ref = _ref_attention(qkv[0], refs, gate)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+    assert rel_l2(outs[0].float(), ref) < 6e-3 and rel_l2(base.float(), ref) < 6e-3
+    assert rel_l2(outs[0].float(), base.float()) < 4e-3
+
+
 @pytest.mark.parametrize("Dh,window", [(128, 0), (64, 16), (64, 128)])
 def test_causal_window_attention(ops, Dh, window):
     B, S, H = 2, 333, 4
