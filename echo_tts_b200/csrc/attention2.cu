@@ -160,7 +160,12 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
 #else
   constexpr long long* trace = nullptr;
 #endif
-  if (trace && tid == 0) trace[0] = clock64();
+  if (trace && tid == 0) {
+    trace[0] = clock64();
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    trace[57] = (long long)gt;                       // ns, comparable across SMs
+  }
   pdl_launch_dependents();
 
   // ---- tile list: every 64-key tile any query of this row can see, with its key-valid bits.  Two memory round
@@ -568,7 +573,12 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 5) ptx::tmem_dealloc(tmem_base, TM_COLS);
-  if (trace && tid == 0) { trace[62] = clock64(); trace[63] = ntiles; }
+  if (trace && tid == 0) {
+    trace[62] = clock64(); trace[63] = ntiles;
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    trace[58] = (long long)gt;
+  }
 }
 }  // namespace
 

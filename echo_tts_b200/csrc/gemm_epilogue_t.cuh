@@ -245,28 +245,39 @@ struct SecAux {
 };
 
 // norm weight + RoPE rows of one 32-column chunk (columns h0 + c .. of the tile) for this lane's 4 columns x 8 rows
-__device__ __forceinline__ void sec_load_aux(const EpiParams& P, const EpiRows& R, int lane, int h0, int c, SecAux& A) {
+// Per-tile invariants of the sections epilogue (one division / modulo each per tile instead of per chunk: the address
+// arithmetic of sec_load_aux used to take ~1.3 k clocks per head).
+struct SecTile {
+  int sec_idx, sec_col0;       // section of the tile and the tile's first column inside it
+  int seq0;                    // sequence index of the warp's local row 0
+};
+__device__ __forceinline__ SecTile sec_tile(const EpiParams& P, const EpiRows& R) {
+  SecTile t;
+  t.sec_idx = R.n0 / P.section_width;
+  t.sec_col0 = R.n0 - t.sec_idx * P.section_width;
+  t.seq0 = R.mb0 % P.rows_per_seq;
+  return t;
+}
+__device__ __forceinline__ void sec_load_aux(const EpiParams& P, const EpiRows& R, const SecTile& T, int lane, int h0, int c,
+                                             bool do_rope, SecAux& A) {
   const int cg = lane & 7, rsub = lane >> 3;
-  const int sec_idx = R.n0 / P.section_width;
-  const EpiSection& S = P.sec[sec_idx];
-  const int sec_col0 = R.n0 - sec_idx * P.section_width;
-  const int hd = P.head_dim;
-  const bool norm = S.type == ECHO_SEC_NORM_ROPE;
-  const bool do_rope = (norm || S.type == ECHO_SEC_ROPE) && (sec_col0 + h0) / hd < P.rope_heads;
-  const int col = sec_col0 + h0 + c + 4 * cg;               // first of this lane's 4 columns inside the section
-  A.w = norm ? __ldg(reinterpret_cast<const float4*>(S.norm_w + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
+  const EpiSection& S = P.sec[T.sec_idx];
+  const int col = T.sec_col0 + h0 + c + 4 * cg;             // first of this lane's 4 columns inside the section
+  A.w = S.type == ECHO_SEC_NORM_ROPE ? __ldg(reinterpret_cast<const float4*>(S.norm_w + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
   if (do_rope) {                                            // lane's columns = rotary pairs p0, p0 + 1 of the head
-    const int seq0 = R.mb0 % P.rows_per_seq;                // sequence index of local row 0
-    const int p0 = (c + 4 * cg) >> 1;
+    const int p0 = (c + 4 * cg) >> 1, hp = P.head_dim >> 1;
+    int sq = T.seq0 + rsub;                                 // sequence index of row r = 4 i + rsub, wrapped by subtraction
+    while (sq >= P.rows_per_seq) sq -= P.rows_per_seq;
+    const int step = 4 % P.rows_per_seq;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = 4 * i + rsub;
-      int sq = seq0 + r;
-      if (sq >= P.rows_per_seq) sq %= P.rows_per_seq;
-      const long long off = (long long)(P.pos_offset + sq * P.pos_stride) * (hd / 2) + p0;
+      const int off = (P.pos_offset + sq * P.pos_stride) * hp + p0;     // < 2^31: rotary tables are a few MB
       const bool ok = r < R.nrows;
       A.co[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_cos + off)) : make_float2(1.f, 1.f);
       A.si[i] = ok ? __ldg(reinterpret_cast<const float2*>(P.rope_sin + off)) : make_float2(0.f, 0.f);
+      sq += step;
+      if (sq >= P.rows_per_seq) sq -= P.rows_per_seq;
     }
   }
 }
@@ -275,12 +286,23 @@ __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P,
                                                const EpiRows& R) {
   if (R.nrows <= 0) return;
   const int cg = lane & 7, rsub = lane >> 3;
-  const int sec_idx = R.n0 / P.section_width;
-  const EpiSection S = P.sec[sec_idx];
-  const int sec_col0 = R.n0 - sec_idx * P.section_width;   // column of the tile inside its section
+  const SecTile ST = sec_tile(P, R);
+  const EpiSection S = P.sec[ST.sec_idx];
+  const int sec_col0 = ST.sec_col0;                        // column of the tile inside its section
   const int hd = P.head_dim;
   const long long ld = P.ld_sec_out;
   const bool norm = S.type == ECHO_SEC_NORM_ROPE;
+  int head = sec_col0 / hd;                                // head of the tile's first column; + 1 per iteration below
+#ifdef ECHO_DEBUG
+  // stamps of the CTA's first two tiles (slots 0..14 and 16..30; slot 31 counts the calls), epilogue warp 0 only
+  long long* etr = (g_epi_trace && (threadIdx.x >> 5) == 2 && lane == 0) ? g_epi_trace + (long long)blockIdx.x * 32 : nullptr;
+  if (etr) { const long long n = etr[31]++; etr = n < 2 ? etr + 16 * n : nullptr; }
+  int stamp = 0;
+#define SEC_STAMP() do { if (etr && stamp < 15) etr[stamp++] = clock64(); } while (0)
+#else
+#define SEC_STAMP() do { } while (0)
+#endif
+  SEC_STAMP();
 
   auto process = [&](int h0, int c, bool do_rope, float rstd, const SecAux& A) {
     float v[32];
@@ -313,31 +335,42 @@ __device__ __forceinline__ void epi_t_sections(const int BN, const EpiParams& P,
   };
 
 #pragma unroll 1
-  for (int h0 = 0; h0 < BN; h0 += hd) {                    // one head at a time; both warps of the quarter visit it
+  for (int h0 = 0; h0 < BN; h0 += hd, ++head) {            // one head at a time; both warps of the quarter visit it
     if (R.n0 + h0 >= P.n) break;
-    const int head = (sec_col0 + h0) / hd;
     const bool do_rope = (norm || S.type == ECHO_SEC_ROPE) && head < P.rope_heads;
     // this warp's chunks of the head: c = half*32 (+64 when the head is 128 wide); their aux loads go out first
     const int c0 = R.half * 32, c1 = c0 + 64;
     SecAux A0, A1;
-    sec_load_aux(P, R, lane, h0, c0, A0);
-    if (c1 < hd) sec_load_aux(P, R, lane, h0, c1, A1);
+    sec_load_aux(P, R, ST, lane, h0, c0, do_rope, A0);
+    if (c1 < hd) sec_load_aux(P, R, ST, lane, h0, c1, do_rope, A1);
+    SEC_STAMP();
     float rstd = 1.f;
-    if (norm) {                                            // row-per-thread: sum of squares over the whole head
+    if (norm) {
+      // row-per-thread sum of squares over the whole head: each of the quarter's two warps sums the columns it will
+      // process (half the TMEM reads of a full pass per warp) and the two exchange their partial sums through
+      // the first 128 bytes of their scratch (idle between chunks), fenced by a 64-thread named barrier on each side
       float ssq = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < hd; c += 32) {
-        float v[32];
-        L.load32(h0 + c, v);
+      for (int c = c0; c < hd; c += 64) {                  // (keeping a chunk in registers for process() spills)
+        float t[32];
+        L.load32(h0 + c, t);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) ssq = fmaf(v[j], v[j], ssq);
+        for (int j = 0; j < 32; ++j) ssq = fmaf(t[j], t[j], ssq);
       }
+      const int bar_id = 4 + (int)((threadIdx.x >> 5) & 3);
+      const float* other = R.half ? sc - 4 * EPI_SC_FLOATS : sc + 4 * EPI_SC_FLOATS;
+      sc[lane] = ssq;
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+      ssq += other[lane];
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
       rstd = rsqrtf(ssq / (float)hd + P.eps);
     }
+    SEC_STAMP();
 #pragma unroll 1
     for (int c = c0; c < hd; c += 64) {                   // one rolled call site (instruction-cache footprint)
       process(h0, c, do_rope, rstd, A0);
       A0 = A1;
+      SEC_STAMP();
     }
   }
 }

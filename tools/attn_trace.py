@@ -38,14 +38,23 @@ def main():
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
-    n = 5 * H * R
+    n = 5 * H * R * 4
     buf = torch.zeros((n, 64), device="cuda", dtype=torch.int64)
     L.check(lib.echo_debug_attn_trace(buf.data_ptr()))   # needs the debug build: make -C echo_tts_b200/csrc DEBUG=1
     torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
     fn()
+    e1.record()
     torch.cuda.synchronize()
     lib.echo_debug_attn_trace(None)
     t = buf.cpu()
+    t = t[t[:, 0] != 0]
+    n = t.shape[0]
+    gs, ge = t[:, 57], t[:, 58]
+    print(f"globaltimer: first CTA start -> last CTA exit {int(ge.max() - gs.min())} ns; CTA starts spread over "
+          f"{int(gs.max() - gs.min())} ns; median CTA lifetime {int((ge - gs).median())} ns; events around the launch "
+          f"{e0.elapsed_time(e1) * 1e3:.1f} us")
     med = lambda v: float(v.float().median())
     t0 = t[:, 0]
     print(f"rows={R}: {n} CTAs, tiles/CTA median {med(t[:, 63]):.0f}; span first start -> last exit "

@@ -71,7 +71,16 @@ def main():
         if bool((ld[:, 3] != 0).all()) and bool((ld[:, 4] != 0).all()) and os.environ.get("ECHO_STREAM_K", "0") != "1":
             print(f"   after setup: dependency resolved +{med(ld[:, 3] - ld[:, 1]):6.0f}  first stage requested +{med(ld[:, 4] - ld[:, 3]):6.0f}  "
                   f"landed (MMA thread's view) +{med(ld[:, 2] - ld[:, 4]):6.0f}")
-        if bool((et[:, 0] != 0).any()):
+        if name.startswith("qkvg") and bool((et[:, 0] != 0).any()):
+            e = et[et[:, 0] != 0]
+            for k, lab in ((0, "first tile"), (16, "second tile")):
+                if bool((e[:, k + 8] != 0).all()):
+                    d = lambda a, b: med(e[:, k + a] - e[:, k + b])
+                    print(f"   sections epilogue, leader warp 2, {lab}: " + "  ".join(
+                        f"head {h}: aux issued {d(1 + 4 * h, 4 * h):5.0f} ssq {d(2 + 4 * h, 1 + 4 * h):5.0f} "
+                        f"chunk {d(3 + 4 * h, 2 + 4 * h):5.0f} chunk {d(4 + 4 * h, 3 + 4 * h):5.0f}" for h in (0, 1))
+                        + f"  total {d(8, 0):6.0f}")
+        elif bool((et[:, 0] != 0).any()):
             e = et[et[:, 0] != 0]
             d = lambda a, b: med(e[:, a] - e[:, b])
             row = "   lean epilogue, leader warp 2, per chunk (tmem ld | math | staged+fenced | bulk issued): "
@@ -83,7 +92,7 @@ def main():
             print(row + f" drain {d(17, 4 + 4 * last):5.0f}  total {d(17, 0):6.0f}")
         mx = lambda v: float(v.float().max())
         sk = ld[ld[:, 3] != 0]
-        if sk.shape[0]:
+        if sk.shape[0] and os.environ.get("ECHO_STREAM_K", "0") == "1":
             last = torch.stack([sk[i, 8 + 4 * tc + 2: 8 + 4 * tc + 4] for i in range(sk.shape[0])
                                 for tc in [max(k for k in range(6) if sk[i, 9 + 4 * k] != 0)]])
             print(f"   stream-K head units ({sk.shape[0]} pairs): sideload start @{med(sk[:, 3] - sk[:, 0]):8.0f}  took "
