@@ -35,7 +35,8 @@ constexpr int EPI_WARPS = 8;       // two per TMEM lane quarter
 constexpr int B_PRODUCER_WARP = 2 + EPI_WARPS;   // optional second TMA producer (the B operand), Tiling::split_b
 constexpr int NTHREADS = 64 + 32 * EPI_WARPS + 32;   // 352: register allocation rounds the CTA to 384 threads either way
 constexpr int SCRATCH_BYTES = EPI_WARPS * EPI_SC_FLOATS * 4;   // per-epilogue-warp 32x32 fp32 transpose scratch
-constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES;
+constexpr int GATE_BYTES = ACC_COLS * 4;                       // LEAN epilogue: the tile's gate row, one float per column
+constexpr int SMEM2 = RING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + SCRATCH_BYTES + GATE_BYTES;
 
 // Debug builds only (make DEBUG=1 -> -DECHO_DEBUG): an in-kernel timeline (32 clock64 slots per CTA, enabled with
 // echo_debug_gemm_trace(ptr)) and two timing experiments whose RESULTS ARE GARBAGE (operand loads left out).  None of it
@@ -81,6 +82,7 @@ struct Tiling {
   long long split_stride; // elements between the partial outputs
   int tail_start;         // >= 0: units from this index on are HALF-width tiles, two per wide tile (the ragged last round
                           // of a launch runs as one round of narrow tiles: shorter main loop and exposed epilogue); -1 off
+  int gate_sm;            // 1: LEAN epilogue reads the gate row from shared memory (0: shuffles; A/B switch ECHO_GEMM_GATESM)
   int split_b;            // 1: warp B_PRODUCER_WARP issues the B-operand loads, warp 0 the A-operand loads (two issue streams)
   int stream_k;           // 1: contiguous k-block ranges per pair (num_tiles = plain tile count, splits = 1)
   int* sk_flags;          // [pairs][2 CTAs][EPI_WARPS] 0/1, self-resetting
@@ -261,6 +263,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full_bar = empty_bar + MAX_STAGES;
   uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+  float* gate_sm = reinterpret_cast<float*>(smem + RING_BYTES + SCRATCH_BYTES + 256);
   const int STAGES = T.stages, STAGE_SZ = T.stage_bytes;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -431,6 +434,23 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const int nc0 = nt * T.bn + (w.sub > 0 ? (T.bn >> 1) : 0);
       EpiPre<EPI> pre;
       epilogue_prefetch_t<EPI>(bn_u, P, lane, half, batch, m0 + q * 32, nc0, pre);
+      // LEAN: when the CTA's 128 rows share ONE gate row (CTA-uniform test), the eight warps stage that row's bn_u values
+      // in shared memory -- a broadcast LDS.128 per four columns replaces 32 shuffles per chunk in the exposed epilogue.
+      // Barrier in front: the previous tile's readers are done; barrier behind: the row is complete.
+      const float* gsm = nullptr;
+      if (EPI == EPI_GENERIC_LEAN && T.gate_sm && P.gate && m0 < P.rows) {
+        const unsigned rpg = (unsigned)P.rows_per_gate;
+        const unsigned mg_first = (unsigned)batch * (unsigned)P.rows + (unsigned)m0;
+        const unsigned mg_last = mg_first + (unsigned)(min(BM, P.rows - m0) - 1);
+        const unsigned g_first = mg_first / rpg;
+        if (g_first == mg_last / rpg) {
+          asm volatile("bar.sync 3, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+          const int col = ew * 32 + lane;
+          if (col < bn_u) gate_sm[col] = nc0 + col < P.n ? __ldg(P.gate + (long long)g_first * P.gate_ld + nc0 + col) : 0.f;
+          asm volatile("bar.sync 3, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+          gsm = gate_sm;
+        }
+      }
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
@@ -448,7 +468,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
       run_epilogue_t<EPI>(bn_u, P, L, stage, lane, half, batch, m0 + q * 32, nc0, pre, &tmap_out, split,
-                          split * T.split_stride, stage_stride);
+                          split * T.split_stride, stage_stride, gsm);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
@@ -494,6 +514,7 @@ int getenv_int(const char* name, int dflt) {
 // scheduler switches (A/B measurements), read ONCE per process -- not per launch
 int use_narrow_tail() { static const int v = getenv_int("ECHO_GEMM_TAIL", 1); return v; }
 int use_stream_k() { static const int v = getenv_int("ECHO_STREAM_K", 0); return v; }
+int use_gate_sm() { static const int v = getenv_int("ECHO_GEMM_GATESM", 1); return v; }
 int use_split_b() { static const int v = getenv_int("ECHO_GEMM_SPLITB", 1); return v; }
 int max_stages() { static const int v = getenv_int("ECHO_GEMM_STAGES", MAX_STAGES); return v < 2 ? 2 : v; }
 int num_sms() {
@@ -575,6 +596,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   }
   Tiling T;
   T.split_b = use_split_b();
+  T.gate_sm = use_gate_sm();
 #ifdef ECHO_DEBUG
   T.trace = g_trace_ptr;
   T.noload = g_debug_noload;

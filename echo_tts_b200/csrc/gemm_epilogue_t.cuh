@@ -450,8 +450,11 @@ __device__ __forceinline__ void epi_t_lean_prefetch(const int BN, const EpiParam
 // before chunk i + 1 is written); > 0 = chunk i is staged at sc + i * sc_stride (the CTA's LAST tile: the operand ring is
 // idle by then and serves as staging, so no chunk waits for the one before -- this is the exposed epilogue of a launch).
 template <class Loader>
+// gsm (nullable): the tile's gate row in shared memory, one float per tile column (gemm2.cu stages it when all of the
+// CTA's 128 rows share one gate row -- always, in the DiT): broadcast LDS.128 instead of 32 shuffles per chunk.
 __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P, Loader& L, float* sc, int lane,
-                                               const EpiRows& R, const void* tmap_out, const LeanPre& A, int sc_stride = 0) {
+                                               const EpiRows& R, const void* tmap_out, const LeanPre& A, int sc_stride = 0,
+                                               const float* gsm = nullptr) {
   if (R.nrows <= 0) return;                                // warp-uniform
   const int cend = min(BN, P.n - R.n0);                    // columns of this tile that exist (multiple of 8)
   const unsigned rpg = (unsigned)P.rows_per_gate;
@@ -488,6 +491,14 @@ __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P,
     if (dbg & 2) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = v[j] * ga + bs;
+    } else if (gsm) {
+      const uint32_t ga_addr = smem_u32(gsm + c);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float4 g;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(ga_addr + 16u * k));
+        v[4 * k] *= g.x; v[4 * k + 1] *= g.y; v[4 * k + 2] *= g.z; v[4 * k + 3] *= g.w;
+      }
     } else if (P.gate && !slow_gate) {
       if (two) {
 #pragma unroll
@@ -565,10 +576,11 @@ __device__ __forceinline__ void epilogue_prefetch_t(const int BN, const EpiParam
 template <int EPI, class Loader>
 __device__ __forceinline__ void run_epilogue_t(const int BN, const EpiParams& P, Loader& L, float* sc, int lane, int half,
                                                int batch_idx, int mb0, int n0, EpiPre<EPI>& pre, const void* tmap_out,
-                                               int split = 0, long long out_off = 0, int sc_stride = 0) {
+                                               int split = 0, long long out_off = 0, int sc_stride = 0,
+                                               const float* gsm = nullptr) {
   const EpiRows R = epi_rows(P, half, batch_idx, mb0, n0, split, out_off);
   if constexpr (EPI == ECHO_EPI_GENERIC) epi_t_generic<false>(BN, P, L, sc, lane, R, pre.a);
-  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_lean_tma(BN, P, L, sc, lane, R, tmap_out, pre.a, sc_stride);
+  else if constexpr (EPI == EPI_GENERIC_LEAN) epi_t_lean_tma(BN, P, L, sc, lane, R, tmap_out, pre.a, sc_stride, gsm);
   else if constexpr (EPI == ECHO_EPI_SECTIONS) epi_t_sections(BN, P, L, sc, lane, R);
   else epi_t_swiglu(BN, P, L, sc, lane, R);
 }
