@@ -13,8 +13,8 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libecho_b200.so")
-if os.environ.get("ECHO_B200_LIB") == "debug":      # profiling tools only: the -DECHO_DEBUG build (in-kernel timelines)
-    LIB_PATH = os.path.join(_HERE, "libecho_b200_debug.so")
+if os.environ.get("ECHO_B200_LIB"):                 # profiling tools only: "debug" = the -DECHO_DEBUG build (in-kernel
+    LIB_PATH = os.path.join(_HERE, "libecho_b200_%s.so" % os.environ["ECHO_B200_LIB"])   # timelines); other names = A/B builds
 
 c_p = C.c_void_p
 i32, i64, f32 = C.c_int32, C.c_int64, C.c_float

@@ -47,9 +47,9 @@ struct AttnParams {
 #endif
   int rows, seq, heads, n_seg;
   int splits;            // > 1: split-KV -- `splits` CTAs per (row, head, query tile), each a contiguous share of the key
-                         // tiles; partial (O, m, l) through `ws_parts`, merged in a fixed order by the last CTA to arrive
+                         // tiles; partial (O, m, l) through `ws_parts`, every part merges its share of the columns
   float* ws_parts;       // [group][split][PART_FLOATS]
-  int* ws_count;         // [group] arrival counters, zero between launches (the merging CTA resets its own)
+  int* ws_count;         // [group][2]: parts arrived / parts done merging; zero between launches (the last part resets)
   int static_first;      // segment 0 has no mask / extent and len > 0: tile 0 is known before the tile list is built
   float softmax_scale;
   const bf16* gate;
@@ -267,6 +267,7 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
   const int ntiles = part < nparts ? (int)((long long)ntiles_all * (part + 1) / nparts) - j_first : 0;
   tiles += j_first;
   const bool idle_part = part >= nparts;      // more parts than tiles: nothing to do, nothing to publish
+  const bool merging = nparts > 1;            // split-KV: output written by the parts' merge, not by the TMA epilogue
   pdl_wait();
   if (trace && tid == 0) trace[1] = clock64();
 
@@ -304,7 +305,7 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
         if (j + 1 < ntiles) load_k(j + 1);
         if (j > 0 || !early) load_v(j);
       }
-      if (A.gate) {
+      if (A.gate && !merging) {
         // every QK^T has been issued: once the last one per stage retires, the K ring (32 KB) is free to take this
         // CTA's [128 x 128] gate tile, which then doubles as the staging buffer of the output TMA store
         const int jl = ntiles - 1;
@@ -471,19 +472,20 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
     if (ntiles > 0) {
       ptx::mbar_wait(&pv_done[(ntiles - 1) & 1], ((ntiles - 1) >> 1) & 1);
       ptx::tc_fence_after();
-      if (A.gate) ptx::mbar_wait(g_full, 0);
+      if (A.gate && !merging) ptx::mbar_wait(g_full, 0);
     }
     if (trace && tid == 0) trace[60] = clock64();
-    // ---- split-KV: publish this part's (O, m, l); the LAST part of the group to arrive sums all of them in part order
-    //      (so the result does not depend on who that is) and runs the epilogue; the others are done ----
-    const bool merging = nparts > 1;
+    // ---- split-KV: every part publishes its un-normalised (O, m, l), waits until all parts of the group have (they are
+    //      co-resident: the host splits only when groups x parts fit the SMs' CTA slots), then merges ITS share of the
+    //      128 output columns (32-column chunks dealt round-robin) over all parts in part order and writes it: the merge
+    //      traffic is spread over the group's SMs instead of 64 KB x parts into one, and the result does not depend on
+    //      arrival order.  The last part through resets the group's two counters for the next launch. ----
     bool do_out = !idle_part;
-    float wp[MAX_SPLITS] = {1.f, 0.f, 0.f, 0.f};
-    const float* parts = nullptr;
     if (merging && !idle_part) {
       const int group = ((int)row * A.heads + head) * ((int)gridDim.x / nsplit) + qt;
-      parts = A.ws_parts + (long long)group * nsplit * PART_FLOATS;
+      const float* parts = A.ws_parts + (long long)group * nsplit * PART_FLOATS;
       float* mine = A.ws_parts + ((long long)group * nsplit + part) * PART_FLOATS;
+      int* cnt = A.ws_count + 2 * group;
 #pragma unroll 1
       for (int c = 0; c < HD; c += 32) {
         float o[32];
@@ -495,49 +497,112 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       }
       __stcg(mine + QT * HD + tid, m);
       __stcg(mine + QT * HD + QT + tid, l);
+      if (trace && tid == 0) trace[48] = clock64();
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (tid == 0) s_ntiles[1] = atomicAdd(A.ws_count + group, 1);
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      do_out = s_ntiles[1] == nparts - 1;
-      if (do_out) {
-        __threadfence();
-        float mp[MAX_SPLITS], mx = -INFINITY;
-#pragma unroll
-        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
-          mp[p2] = p2 < nparts ? __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + tid) : -INFINITY;
-          mx = fmaxf(mx, mp[p2]);
+      if (trace && tid == 0) trace[49] = clock64();
+      if (tid == 0) {
+        atomicAdd(cnt, 1);
+        int v = 0;
+        const long long t0 = clock64();
+        for (;;) {
+          asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+          if (v >= nparts) break;
+          if (clock64() - t0 > 4000000000LL) { printf("echo attention: split-KV part never arrived\n"); __trap(); }
+          __nanosleep(32);
         }
-        l = 0.f;
-#pragma unroll
-        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
-          wp[p2] = (p2 < nparts && mp[p2] != -INFINITY) ? exp2f(mp[p2] - mx) : 0.f;
-          if (p2 < nparts) l = fmaf(wp[p2], __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + QT + tid), l);
-        }
-        if (tid == 0) A.ws_count[group] = 0;               // ready for the next launch
       }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (trace && tid == 0) trace[50] = clock64();
+      // (the partials were released at gpu scope before each part's count; they are read from the L2 below: no L1 copy
+      // can be stale and no second fence is needed)
+      // Everything the merge needs is requested before anything is used: the parts' (m, l), the gate values and the
+      // first two parts' columns share ONE memory round trip; later parts follow two at a time.
+      float mp[MAX_SPLITS], lp[MAX_SPLITS];
+#pragma unroll
+      for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
+        mp[p2] = p2 < nparts ? __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + tid) : -INFINITY;
+        lp[p2] = p2 < nparts ? __ldcg(parts + (long long)p2 * PART_FLOATS + QT * HD + QT + tid) : 0.f;
+      }
+      const bool row_ok = q0 + tid < A.seq;
+      const long long oidx = ((long long)row * A.seq + q0 + tid) * ((long long)A.heads * HD) + (long long)head * HD;
+      float wp[MAX_SPLITS], invm = 0.f;
+#pragma unroll 1
+      for (int c = 32 * part; c < HD; c += 32 * nparts) {
+        uint4 gv[4];
+        if (A.gate && row_ok) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) gv[g] = __ldg(reinterpret_cast<const uint4*>(A.gate + oidx + c + 8 * g));
+        }
+        float4 t0[8], t1[8];
+        const float4* src = reinterpret_cast<const float4*>(parts) + (c >> 2) * QT + tid;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          t0[k] = __ldcg(src + k * QT);
+          t1[k] = __ldcg(src + (PART_FLOATS >> 2) + k * QT);                  // nparts >= 2 here
+        }
+        if (c == 32 * part) {                                                // weights of the parts, once
+          float mx = -INFINITY;
+#pragma unroll
+          for (int p2 = 0; p2 < MAX_SPLITS; ++p2) mx = fmaxf(mx, mp[p2]);
+          float lm = 0.f;
+#pragma unroll
+          for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
+            wp[p2] = (p2 < nparts && mp[p2] != -INFINITY) ? exp2f(mp[p2] - mx) : 0.f;
+            lm = fmaf(wp[p2], lp[p2], lm);
+          }
+          invm = lm > 0.f ? 1.f / lm : 0.f;
+        }
+        float o[32];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          o[4 * k] = fmaf(wp[1], t1[k].x, wp[0] * t0[k].x); o[4 * k + 1] = fmaf(wp[1], t1[k].y, wp[0] * t0[k].y);
+          o[4 * k + 2] = fmaf(wp[1], t1[k].z, wp[0] * t0[k].z); o[4 * k + 3] = fmaf(wp[1], t1[k].w, wp[0] * t0[k].w);
+        }
+        if (nparts > 2) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            t0[k] = __ldcg(src + 2 * (PART_FLOATS >> 2) + k * QT);
+            t1[k] = nparts > 3 ? __ldcg(src + 3 * (PART_FLOATS >> 2) + k * QT) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            o[4 * k] = fmaf(wp[3], t1[k].x, fmaf(wp[2], t0[k].x, o[4 * k]));
+            o[4 * k + 1] = fmaf(wp[3], t1[k].y, fmaf(wp[2], t0[k].y, o[4 * k + 1]));
+            o[4 * k + 2] = fmaf(wp[3], t1[k].z, fmaf(wp[2], t0[k].z, o[4 * k + 2]));
+            o[4 * k + 3] = fmaf(wp[3], t1[k].w, fmaf(wp[2], t0[k].w, o[4 * k + 3]));
+          }
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int g = 0; g < 32; g += 8) {
+            float w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[i] = o[g + i] * invm;
+            if (A.gate) {
+              const uint4 gvv = gv[g >> 3];
+              const uint4 gv = gvv;
+              const float2 g0 = unpack_bf16x2(gv.x), g1 = unpack_bf16x2(gv.y), g2 = unpack_bf16x2(gv.z), g3 = unpack_bf16x2(gv.w);
+              w[0] *= g0.x; w[1] *= g0.y; w[2] *= g1.x; w[3] *= g1.y; w[4] *= g2.x; w[5] *= g2.y; w[6] *= g3.x; w[7] *= g3.y;
+            }
+            uint4 u;
+            u.x = pack_bf16x2(w[0], w[1]); u.y = pack_bf16x2(w[2], w[3]);
+            u.z = pack_bf16x2(w[4], w[5]); u.w = pack_bf16x2(w[6], w[7]);
+            *reinterpret_cast<uint4*>(A.out + oidx + c + g) = u;
+          }
+        }
+      }
+      if (trace && tid == 0) trace[51] = clock64();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (tid == 0 && atomicAdd(cnt + 1, 1) == nparts - 1) { cnt[0] = 0; cnt[1] = 0; }
+      do_out = false;
     }
     const float inv = l > 0.f ? 1.f / l : 0.f;
     uint8_t* const stage_row = sK + tid * 128;
 #pragma unroll 1
     for (int c = 0; c < HD && do_out; c += 32) {
       float o[32];
-      if (merging) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = 0.f;
-#pragma unroll
-        for (int p2 = 0; p2 < MAX_SPLITS; ++p2) {
-          if (p2 < nparts) {
-            const float4* src = reinterpret_cast<const float4*>(parts + (long long)p2 * PART_FLOATS) + (c >> 2) * QT + tid;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const float4 v = __ldcg(src + k * QT);
-              o[4 * k] = fmaf(wp[p2], v.x, o[4 * k]); o[4 * k + 1] = fmaf(wp[p2], v.y, o[4 * k + 1]);
-              o[4 * k + 2] = fmaf(wp[p2], v.z, o[4 * k + 2]); o[4 * k + 3] = fmaf(wp[p2], v.w, o[4 * k + 3]);
-            }
-          }
-        }
-      } else if (ntiles > 0) {
+      if (ntiles > 0) {
         ptx::tmem_ld32(tmem_base + TM_O + lane_off + c, o);
       } else {
 #pragma unroll
@@ -676,13 +741,15 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
   const int qtiles = ceil_div(d->seq, QT);
   const long long groups = (long long)qtiles * d->heads * d->rows;
   int splits = 1;
-  if (d->kv_splits != 1 && d->workspace && groups > 0 && groups <= WS_COUNTERS) {
+  if (d->kv_splits != 1 && d->workspace && groups > 0 && 2 * groups <= WS_COUNTERS) {
     static const int forced = [] { const char* e = getenv("ECHO_ATTN_SPLITS"); return e && e[0] ? atoi(e) : 0; }();
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int slots = 2 * sms;
     int want = d->kv_splits > 1 ? d->kv_splits : (forced > 0 ? forced : (int)(slots / groups));
+    if (d->kv_splits <= 1 && forced <= 0 && want < MAX_SPLITS) want = 1;   // measured: fewer than four parts do not pay
+                                                                            // for the exchange (the 640-token step: 80 groups)
     if (want > MAX_SPLITS) want = MAX_SPLITS;
     if (want > total_tiles / 2) want = (int)(total_tiles / 2);          // at least two key tiles per part
     const long long room = (d->workspace_bytes - (long long)WS_COUNTERS * 4) / ((long long)PART_FLOATS * 4);

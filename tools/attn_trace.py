@@ -14,11 +14,13 @@ BF16 = torch.bfloat16
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=1)
+    ap.add_argument("--seq", type=int, default=640, help="queries per row (160 = a streaming block)")
+    ap.add_argument("--prefix", type=int, default=0, help="keys of a latent prefix segment (480 behind three blocks)")
     ap.add_argument("--nomask", action="store_true", help="no masks / extents: the tile list needs no global loads")
     args = ap.parse_args()
     from echo_tts_b200 import ops, _lib as L
     lib = L.load()
-    R, S, H = args.rows, 640, 16
+    R, S, H = args.rows, args.seq, 16
     g = torch.Generator(device="cuda").manual_seed(0)
     rnd = lambda *s: torch.randn(s, device="cuda", generator=g).to(BF16)
     qkvg = rnd(4, R, S, H, 128)
@@ -31,6 +33,9 @@ def main():
     te, se = ops.mask_extent(tm), ops.mask_extent(sm)
     segs = [ops.Segment(qkvg[1], qkvg[2]), ops.Segment(kt, vt, kv_batch_mod=1, mask=tm, extent=te),
             ops.Segment(ks, vs, kv_batch_mod=1, mask=sm, extent=se)]
+    if args.prefix:
+        kp, vp = rnd(1, args.prefix, H, 128), rnd(1, args.prefix, H, 128)
+        segs.insert(1, ops.Segment(kp, vp, kv_batch_mod=1))
     if args.nomask:
         segs = [ops.Segment(qkvg[1], qkvg[2]), ops.Segment(kt[:, :256], vt[:, :256], kv_batch_mod=1),
                 ops.Segment(ks, vs, kv_batch_mod=1)]
@@ -38,7 +43,7 @@ def main():
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
-    n = 5 * H * R * 4
+    n = ((S + 127) // 128) * H * R * 4
     buf = torch.zeros((n, 64), device="cuda", dtype=torch.int64)
     L.check(lib.echo_debug_attn_trace(buf.data_ptr()))   # needs the debug build: make -C echo_tts_b200/csrc DEBUG=1
     torch.cuda.synchronize()
@@ -53,7 +58,8 @@ def main():
     n = t.shape[0]
     gs, ge = t[:, 57], t[:, 58]
     print(f"globaltimer: first CTA start -> last CTA exit {int(ge.max() - gs.min())} ns; CTA starts spread over "
-          f"{int(gs.max() - gs.min())} ns; median CTA lifetime {int((ge - gs).median())} ns; events around the launch "
+          f"{int(gs.max() - gs.min())} ns; CTA lifetime median {int((ge - gs).median())} / p90 "
+          f"{int((ge - gs).float().quantile(0.9))} / max {int((ge - gs).max())} ns; events around the launch "
           f"{e0.elapsed_time(e1) * 1e3:.1f} us")
     med = lambda v: float(v.float().median())
     t0 = t[:, 0]
@@ -64,6 +70,11 @@ def main():
           f"K(0) landed @{med(t[:, 54] - t0):7.0f}  S(0) issued @{med(t[:, 55] - t0):7.0f}")
     print(f"  relative to CTA start, median over CTAs: setup done @{med(t[:, 1] - t0):7.0f}   last PV done "
           f"@{med(t[:, 60] - t0):7.0f}   epilogue done @{med(t[:, 61] - t0):7.0f}   exit @{med(t[:, 62] - t0):7.0f}")
+    if bool((t[:, 48] != 0).any()) and med(t[:, 63]) < 11:
+        e = t[t[:, 48] != 0]
+        print(f"  split-KV (stamps in tile 11's slots), relative to last PV done: partial stored @{med(e[:, 48] - e[:, 60]):7.0f}  "
+              f"fenced + CTA barrier @{med(e[:, 49] - e[:, 60]):7.0f}  all parts arrived @{med(e[:, 50] - e[:, 60]):7.0f}  "
+              f"own columns merged + stored @{med(e[:, 51] - e[:, 60]):7.0f}")
     for j in range(12):
         b = 4 + 4 * j
         print(f"  tile {j:2d}: S ready @{med(t[:, b] - t0):7.0f}  PV(j-1) done @{med(t[:, b + 1] - t0):7.0f}  "
