@@ -240,7 +240,7 @@ extern "C" int echo_attention(const echo_attn_desc* d, echo_stream_t stream) {
     ECHO_CHECK_ARG(d->seg[i].row_stride % 8 == 0 && d->seg[i].batch_stride % 8 == 0, "attention: segment strides %%8");
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (d->impl == 0) {   // tcgen05 kernel when the shape is in its domain (head_dim 128, no causal/window segment)
+  if (d->impl == 0) {   // tcgen05 kernel when the shape is in its domain (head_dim 128, no sliding window)
     const int rc = echo_attention_tc(d, st);
     if (rc != ECHO_ERR_UNSUPPORTED) return rc;
   }

@@ -1,5 +1,5 @@
-// Joint attention for the DiT decoder on tcgen05 (head_dim 128, non-causal, up to four KV segments walked in
-// place: self | latent prefix | text | speaker).  Replaces torch.cat + F.scaled_dot_product_attention + the sigmoid
+// Joint attention for the DiT decoder and the causal speaker / latent-prefix encoders on tcgen05 (head_dim 128, up to four
+// KV segments walked in place: self | latent prefix | text | speaker; a segment may be causal with a query offset).  Replaces torch.cat + F.scaled_dot_product_attention + the sigmoid
 // gating of model.py:246-264 and the cache replication / scaling helpers of inference.py:409-428.
 //
 // One CTA = 128 queries of one (row, head).  Per 64-key tile:
@@ -35,6 +35,8 @@ constexpr int MAX_SPLITS = 4;
 
 struct AttnSeg {
   int len, kv_batch_mod;
+  int causal, q_offset;  // causal: key j visible to query i iff j <= i + q_offset (tiles past the diagonal are never
+                         // listed; tiles ON it carry a flag and are masked per row)
   const uint8_t* mask; long long mask_stride;
   const int* extent;
   const float* kv_scale;
@@ -56,7 +58,7 @@ struct AttnParams {
   bf16* out;
   AttnSeg seg[4];
 };
-struct TileInfo { int seg, key0; unsigned long long valid; };   // 16 bytes
+struct TileInfo { int seg, key0; unsigned long long valid; };   // 16 bytes; seg bit 8: diagonal tile of a causal segment
 
 __device__ __forceinline__ void tma_load_4d(void* dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
   asm volatile(
@@ -212,13 +214,18 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
         mbits = ((unsigned long long)bits[1] << 32) | bits[0];
         if (nvalid < 64) mbits &= (1ull << nvalid) - 1ull;
       }
-      const int e = min(__shfl_sync(0xffffffffu, ext_l, sgi), sg.len);
+      int e = min(__shfl_sync(0xffffffffu, ext_l, sgi), sg.len);
+      int diag = 0;
+      if (in && sg.causal) {                               // keys past the last query's horizon are never visited
+        e = min(e, q0 + QT + sg.q_offset);                 // key j <= (q0 + QT - 1) + q_offset
+        diag = key0 + KT - 1 > q0 + sg.q_offset;           // the tile's last key is hidden from the tile's first query
+      }
       const unsigned long long valid =
           (!in || e <= key0) ? 0ull : (mbits & ((e - key0 >= 64) ? ~0ull : ((1ull << (e - key0)) - 1ull)));
       const unsigned keep = __ballot_sync(0xffffffffu, valid != 0ull);
       if (valid != 0ull) {
         const int pos = nkept + __popc(keep & ((1u << lane) - 1u));
-        tiles[pos].seg = sgi; tiles[pos].key0 = key0; tiles[pos].valid = valid;
+        tiles[pos].seg = sgi | (diag << 8); tiles[pos].key0 = key0; tiles[pos].valid = valid;
       }
       nkept += __popc(keep);
     }
@@ -283,7 +290,8 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       auto load_k = [&](int j) {
         const int s = j & 1;
         const uint32_t ph = (j >> 1) & 1;
-        const TileInfo t = tiles[j];
+        TileInfo t = tiles[j];
+        t.seg &= 0xff;
         const int kvrow = A.seg[t.seg].kv_batch_mod > 0 ? row % A.seg[t.seg].kv_batch_mod : row;
         ptx::mbar_wait(&k_empty[s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&k_full[s], KV_BYTES);
@@ -293,7 +301,8 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       auto load_v = [&](int j) {
         const int s = j & 1;
         const uint32_t ph = (j >> 1) & 1;
-        const TileInfo t = tiles[j];
+        TileInfo t = tiles[j];
+        t.seg &= 0xff;
         const int kvrow = A.seg[t.seg].kv_batch_mod > 0 ? row % A.seg[t.seg].kv_batch_mod : row;
         ptx::mbar_wait(&v_empty[s], ph ^ 1);
         ptx::mbar_arrive_expect_tx(&v_full[s], KV_BYTES);
@@ -386,7 +395,9 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
     for (int j = 0; j < ntiles; ++j) {
       const int b = j & 1;
       const uint32_t ph = (j >> 1) & 1;
-      const TileInfo t = tiles[j];
+      TileInfo t = tiles[j];
+      const bool diag = (t.seg >> 8) != 0;
+      t.seg &= 0xff;
       const float f = t.seg == 0 ? fseg[0] : (t.seg == 1 ? fseg[1] : (t.seg == 2 ? fseg[2] : fseg[3]));
       const float sc = sl2 * f;
       ptx::mbar_wait(&s_full[b], ph);
@@ -397,8 +408,13 @@ __global__ void __launch_bounds__(192, 2) attention_tc_kernel(const __grid_const
       tmem_ld32_nowait(s_addr, s);
       tmem_ld32_nowait(s_addr + 32, s + 32);
       tmem_ld_wait();
-      if (t.valid != ~0ull) {                              // partial tile (warp-uniform; most tiles are full)
-        const unsigned lo = (unsigned)t.valid, hi = (unsigned)(t.valid >> 32);
+      if (t.valid != ~0ull || diag) {                      // partial tile (warp-uniform test; most tiles are full)
+        unsigned long long vm = t.valid;
+        if (diag) {                                        // causal diagonal: this row sees keys <= q0 + tid + q_offset
+          const int nvis = q0 + tid + A.seg[t.seg].q_offset - t.key0 + 1;
+          vm &= nvis >= 64 ? ~0ull : (nvis <= 0 ? 0ull : ((1ull << nvis) - 1ull));
+        }
+        const unsigned lo = (unsigned)vm, hi = (unsigned)(vm >> 32);
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
           if (!((lo >> c) & 1u)) s[c] = -INFINITY;
@@ -676,7 +692,8 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
   if (d->head_dim != HD) return ECHO_ERR_UNSUPPORTED;
   long long total_tiles = 0;
   for (int i = 0; i < d->n_seg; ++i) {
-    if (d->seg[i].causal || d->seg[i].window > 0) return ECHO_ERR_UNSUPPORTED;
+    if (d->seg[i].window > 0) return ECHO_ERR_UNSUPPORTED;
+    if (d->seg[i].causal && d->seg[i].q_offset < 0) return ECHO_ERR_UNSUPPORTED;
     total_tiles += ceil_div(d->seg[i].len, KT);
   }
   if (total_tiles > MAX_TILES) return ECHO_ERR_UNSUPPORTED;
@@ -717,6 +734,7 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
   for (int i = 0; i < d->n_seg; ++i) {
     const echo_attn_segment& s = d->seg[i];
     A.seg[i].len = s.len; A.seg[i].kv_batch_mod = s.kv_batch_mod;
+    A.seg[i].causal = s.causal ? 1 : 0; A.seg[i].q_offset = s.causal ? s.q_offset : 0;
     A.seg[i].mask = s.mask; A.seg[i].mask_stride = s.mask_stride;
     A.seg[i].extent = s.extent; A.seg[i].kv_scale = s.kv_scale;
     if (s.len <= 0) { M.k[i] = M.q; M.v[i] = M.q; continue; }

@@ -196,7 +196,8 @@ typedef struct echo_attn_desc {
   void* out;                /* bf16 [rows*seq, heads*head_dim] */
   int32_t rows, seq, heads, head_dim;
   int32_t n_seg;
-  int32_t impl;             /* 0 = tcgen05 kernel when eligible (head_dim 128, non-causal), else mma.sync kernel; 1 = force mma.sync */
+  int32_t impl;             /* 0 = tcgen05 kernel when eligible (head_dim 128, no sliding window; causal segments with
+                             * q_offset >= 0 included), else the mma.sync kernel; 1 = force mma.sync */
   float softmax_scale;
   int32_t kv_splits;        /* tcgen05 kernel: 0 = automatic, 1 = never, 2..4 = that many CTAs per (row, head, query tile),
                              * each a contiguous share of the key tiles (split-KV; needs `workspace`) */

@@ -147,6 +147,25 @@ def test_causal_window_attention(ops, Dh, window):
     assert rel_l2(out.float(), ref) < 6e-3
 
 
+@pytest.mark.parametrize("S,off", [(333, 0), (128, 0), (1600, 0), (100, 480), (64, 1), (200, 63)])
+@pytest.mark.parametrize("impl", [0, 1])
+def test_causal_encoder_attention_with_query_offset(ops, impl, S, off):
+    """The causal speaker / latent-prefix encoders' attention (head_dim 128; 1600 patches = a 6400-latent reference; queries
+    that are the LAST S positions of off + S keys = the incremental prefix encoder): tcgen05 kernel (impl 0: tiles past the
+    diagonal skipped, tiles on it masked per row) and mma.sync kernel (impl 1) against the dense fp32 reference, gated."""
+    B, H, Dh = 2, 4, 128
+    q = _rand((B, S, H, Dh), 61, dtype=BF16)
+    k, v = _rand((B, off + S, H, Dh), 62, dtype=BF16), _rand((B, off + S, H, Dh), 63, dtype=BF16)
+    gate = torch.sigmoid(_rand((B * S, H * Dh), 64)).to(BF16)
+    out = torch.full((B * S, H * Dh), float("nan"), device="cuda", dtype=BF16)
+    ops.attention(q, [ops.Segment(k, v, causal=True, q_offset=off)], out, gate=gate, impl=impl)
+    sc = torch.einsum("rshd,rlhd->rhsl", q.float(), k.float()) / math.sqrt(Dh)
+    i, j = torch.arange(S, device="cuda")[:, None], torch.arange(off + S, device="cuda")[None, :]
+    sc = sc.masked_fill(~(j <= i + off)[None, None], float("-inf"))
+    ref = torch.einsum("rhsl,rlhd->rshd", torch.softmax(sc, -1), v.float()).reshape(B * S, H * Dh) * gate.float()
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
 def test_key_padding_attention_strided_views(ops):
     """encoder-style: q/k/v are slices of one fused buffer; key padding mask with extent."""
     B, S, H, Dh = 3, 90, 2, 128
