@@ -219,50 +219,14 @@ extern "C" int echo_rmsnorm_f32(const float* x, int64_t ldx, int m, int d, float
 }
 
 // ---------------------------------------------------------------------------------------------
-// fp32 CUDA-core GEMM: 64x64 tile, 16x16 threads, 4x4 micro-tile, K step 16.  Small/accuracy-critical.
+// fp32 CUDA-core GEMM: 64x64 tile, 16x16 threads, 4x4 micro-tile.  Small / accuracy-critical products; the big ones
+// are weight streams with a handful of rows (the AdaLN modulation table: 40 timesteps x 600 MB of fp32 weights per
+// generation), so the loop is built for memory-level parallelism: K step 32, 16-byte loads, the next tile requested into
+// registers before the current one is multiplied (VEC; K, the leading dimensions and the bases must be multiples of 4
+// floats -- otherwise the scalar K-step-16 form).  Measured on the table's down-projection (40 x 12288 x 2048): 400 -> see
+// DESIGN.md.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo_sgemm_desc D) {
-  __shared__ float sA[16][64 + 4];
-  __shared__ float sW[16][64 + 4];
-  const int z = blockIdx.z;
-  // NO early trigger here (the implicit one at grid exit applies): this kernel writes the AdaLN modulation table, which
-  // rmsnorm_mod_kernel requests BEFORE its own griddepcontrol.wait.  With an early trigger, a kernel two launches behind
-  // (table sgemm -> in_proj sgemm -> norm, the model.__call__ path) could be resident while the table is still being
-  // written; without it every kernel launched after an sgemm starts only once that sgemm has completed.
-  pdl_wait();
-  const float* A = D.a + z * D.a_zstride;
-  const float* W = D.w + z * D.w_zstride;
-  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  float acc[4][4] = {};
-  for (int k0 = 0; k0 < D.k; k0 += 16) {
-    for (int i = threadIdx.x; i < 64 * 16; i += 256) {
-      const int r = i >> 4, kk = i & 15;
-      const int k = k0 + kk;
-      float a = 0.f, w = 0.f;
-      if (k < D.k) {
-        if (m0 + r < D.m) {
-          a = A[(long long)(m0 + r) * D.lda + k];
-          if (D.pre_silu) a = a / (1.f + expf(-a));
-        }
-        if (n0 + r < D.n) w = W[(long long)(n0 + r) * D.ldw + k];
-      }
-      sA[kk][r] = a;
-      sW[kk][r] = w;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int kk = 0; kk < 16; ++kk) {
-      float a[4], w[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) { a[i] = sA[kk][ty * 4 + i]; w[i] = sW[kk][tx * 4 + i]; }
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
-    }
-    __syncthreads();
-  }
+__device__ __forceinline__ void sgemm_store(const echo_sgemm_desc& D, int z, int m0, int n0, int tx, int ty, float (&acc)[4][4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int m = m0 + ty * 4 + i;
@@ -284,11 +248,104 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo
   }
 }
 
+template <bool VEC>
+__global__ void __launch_bounds__(256) sgemm_kernel(const __grid_constant__ echo_sgemm_desc D) {
+  constexpr int KS = VEC ? 32 : 16;
+  __shared__ float sA[KS][64 + 4];
+  __shared__ float sW[KS][64 + 4];
+  const int z = blockIdx.z;
+  // NO early trigger here (the implicit one at grid exit applies): this kernel writes the AdaLN modulation table, which
+  // rmsnorm_mod_kernel requests BEFORE its own griddepcontrol.wait.  With an early trigger, a kernel two launches behind
+  // (table sgemm -> in_proj sgemm -> norm, the model.__call__ path) could be resident while the table is still being
+  // written; without it every kernel launched after an sgemm starts only once that sgemm has completed.
+  pdl_wait();
+  const float* A = D.a + z * D.a_zstride;
+  const float* W = D.w + z * D.w_zstride;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4] = {};
+  if constexpr (VEC) {
+    // thread -> two (row, 4-float k group) cells of each operand tile: rows r0 and r0 + 32, k group kq
+    const int r0 = threadIdx.x >> 3, kq = (threadIdx.x & 7) * 4;
+    float4 ra[2], rw[2];
+    auto fetch = [&](int k0) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = r0 + 32 * h, k = k0 + kq;
+        ra[h] = (k < D.k && m0 + r < D.m) ? __ldg(reinterpret_cast<const float4*>(A + (long long)(m0 + r) * D.lda + k))
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+        rw[h] = (k < D.k && n0 + r < D.n) ? __ldg(reinterpret_cast<const float4*>(W + (long long)(n0 + r) * D.ldw + k))
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    };
+    fetch(0);
+    for (int k0 = 0; k0 < D.k; k0 += KS) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = r0 + 32 * h;
+        float4 a = ra[h];
+        if (D.pre_silu) {
+          a.x = a.x / (1.f + expf(-a.x)); a.y = a.y / (1.f + expf(-a.y));
+          a.z = a.z / (1.f + expf(-a.z)); a.w = a.w / (1.f + expf(-a.w));
+        }
+        sA[kq][r] = a.x; sA[kq + 1][r] = a.y; sA[kq + 2][r] = a.z; sA[kq + 3][r] = a.w;
+        sW[kq][r] = rw[h].x; sW[kq + 1][r] = rw[h].y; sW[kq + 2][r] = rw[h].z; sW[kq + 3][r] = rw[h].w;
+      }
+      __syncthreads();
+      if (k0 + KS < D.k) fetch(k0 + KS);          // in flight under the multiplies below
+#pragma unroll
+      for (int kk = 0; kk < KS; ++kk) {
+        float a[4], w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { a[i] = sA[kk][ty * 4 + i]; w[i] = sW[kk][tx * 4 + i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  } else {
+    for (int k0 = 0; k0 < D.k; k0 += KS) {
+      for (int i = threadIdx.x; i < 64 * KS; i += 256) {
+        const int r = i / KS, kk = i % KS;
+        const int k = k0 + kk;
+        float a = 0.f, w = 0.f;
+        if (k < D.k) {
+          if (m0 + r < D.m) {
+            a = A[(long long)(m0 + r) * D.lda + k];
+            if (D.pre_silu) a = a / (1.f + expf(-a));
+          }
+          if (n0 + r < D.n) w = W[(long long)(n0 + r) * D.ldw + k];
+        }
+        sA[kk][r] = a;
+        sW[kk][r] = w;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < KS; ++kk) {
+        float a[4], w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { a[i] = sA[kk][ty * 4 + i]; w[i] = sW[kk][tx * 4 + i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+  sgemm_store(D, z, m0, n0, tx, ty, acc);
+}
+
 extern "C" int echo_sgemm_f32(const echo_sgemm_desc* d, echo_stream_t stream) {
   ECHO_CHECK_ARG(d && d->a && d->w && (d->out || d->out_bf16), "sgemm: null argument");
   ECHO_CHECK_ARG(d->m > 0 && d->n > 0 && d->k > 0 && d->nz > 0, "sgemm: bad shape");
   dim3 grid(ceil_div(d->n, 64), ceil_div(d->m, 64), d->nz);
-  ECHO_CUDA(echo_launch(sgemm_kernel, grid, dim3(256), 0, (cudaStream_t)stream, *d));
+  const bool vec = d->k % 4 == 0 && d->lda % 4 == 0 && d->ldw % 4 == 0 && d->a_zstride % 4 == 0 && d->w_zstride % 4 == 0 &&
+                   ((uintptr_t)d->a % 16) == 0 && ((uintptr_t)d->w % 16) == 0;
+  if (vec) ECHO_CUDA(echo_launch(sgemm_kernel<true>, grid, dim3(256), 0, (cudaStream_t)stream, *d));
+  else ECHO_CUDA(echo_launch(sgemm_kernel<false>, grid, dim3(256), 0, (cudaStream_t)stream, *d));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
