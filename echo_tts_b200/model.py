@@ -297,6 +297,26 @@ class EchoDiT:
         return self._project_kv(x, norm_w, key, B, Ls, rope_patch=rope_patch)
 
     @torch.inference_mode()
+    def kv_caches_text_speaker(self, text_input_ids, text_mask, speaker_latent) -> Tuple[KVCache, KVCache]:
+        """``get_kv_cache_text`` and ``get_kv_cache_speaker`` (inference.py:482-483) side by side: the two encoders are
+        independent stacks of small launches (14 layers at 768 tokens / a few dozen patches), so the speaker encoder runs on
+        a second stream forked from and joined back into the current one (inside a CUDA-graph capture this becomes two
+        parallel branches of the graph).  The side stream always waits for the current stream first, so buffers the caching
+        allocator hands back to it are never reused under work the current stream still has in flight."""
+        if os.environ.get("ECHO_STREAM_K") == "1" or os.environ.get("ECHO_ENCODER_STREAMS") == "0":
+            # (the stream-K schedule exchanges partial tiles through ONE workspace per device: no concurrent GEMM streams)
+            return self.get_kv_cache_text(text_input_ids, text_mask), self.get_kv_cache_speaker(speaker_latent)
+        cur = torch.cuda.current_stream(self._device)
+        side = self.__dict__.get("_side_stream")
+        if side is None:
+            side = self._side_stream = torch.cuda.Stream(device=self._device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            kv_spk = self.get_kv_cache_speaker(speaker_latent)
+        kv_text = self.get_kv_cache_text(text_input_ids, text_mask)
+        cur.wait_stream(side)
+        return kv_text, kv_spk
+
     def get_kv_cache_text(self, text_input_ids: torch.Tensor, text_mask: Optional[torch.Tensor]) -> KVCache:
         """model.py:606-613."""
         B, Lt = text_input_ids.shape

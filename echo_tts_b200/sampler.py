@@ -191,8 +191,7 @@ def sample_euler_cfg_independent_guidances(
 
     def conditioning(ids, tmask, spk, smask):
         torch.cuda.nvtx.range_push("echo.conditioning")
-        kv_t = model.get_kv_cache_text(ids, tmask)                                         # inference.py:482
-        kv_s = model.get_kv_cache_speaker(spk)                                             # inference.py:483
+        kv_t, kv_s = model.kv_caches_text_speaker(ids, tmask, spk)                         # inference.py:482-483
         out = kv_t, kv_s, _prep_masks(model, tmask, smask)
         torch.cuda.nvtx.range_pop()
         return out
@@ -288,7 +287,7 @@ def _blockwise_graphed(model: EchoDiT, ent: "_GraphEntry", speaker_latent, speak
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 if bi == 0:
-                    st["cond"] = (model.get_kv_cache_text(st["ids"], st["tmask"]), model.get_kv_cache_speaker(st["spk"]),
+                    st["cond"] = (*model.kv_caches_text_speaker(st["ids"], st["tmask"], st["spk"]),
                                   _prep_masks(model, st["tmask"], st["smask"]))
                 else:
                     pstream.append(st["blocks"][bi - 1]["x_t"])
@@ -357,8 +356,7 @@ def blockwise_blocks(
                                           num_steps, cfg_min_t, cfg_max_t, truncation_factor, speaker_kv_scale,
                                           speaker_kv_max_layers, speaker_kv_min_t, p)
             return
-    kv_text = model.get_kv_cache_text(text_input_ids, text_mask)
-    kv_spk = model.get_kv_cache_speaker(speaker_latent)
+    kv_text, kv_spk = model.kv_caches_text_speaker(text_input_ids, text_mask, speaker_latent)
     masks = _prep_masks(model, text_mask, speaker_mask)
     pstream = None
     if incremental_prefix and aligned and model.has_blockwise and prefix.shape[1] >= ps:
