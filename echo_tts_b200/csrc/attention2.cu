@@ -749,10 +749,14 @@ int echo_attention_tc(const echo_attn_desc* d, cudaStream_t st) {
     rc = echo_make_tmap_bf16(&M.v[i], s.v, 4, dims, str, box);
     if (rc) return rc;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    ECHO_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ATTN));
-    attr_set = true;
+  {   // the attribute is per device: a process that drives several GPUs sets it once on each
+    static bool attr_set[64] = {};
+    int dev = 0;
+    ECHO_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+      ECHO_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_ATTN));
+      if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
   }
   // split-KV when the (row, head, query tile) groups alone leave SMs idle (two CTAs fit one SM): the un-guided 640-token
   // step has 80 groups, a 160-latent streaming block 32.  The caller lends the exchange buffer.

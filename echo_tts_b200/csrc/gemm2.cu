@@ -589,10 +589,14 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     int rc = echo_make_tmap_f32(&tout, P.out_f32, 4, dims, str, box);
     if (rc) return rc;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    ECHO_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
-    attr_set = true;
+  {   // the attribute is per device: a process that drives several GPUs sets it once on each
+    static bool attr_set[64] = {};
+    int dev = 0;
+    ECHO_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+      ECHO_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
+      if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
   }
   Tiling T;
   T.split_b = use_split_b();
