@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--seq", type=int, default=640, help="latents per row (160 = a streaming block)")
     ap.add_argument("--bn", type=int, default=0, help="force block_n of the four projections (0 = library's choice)")
     ap.add_argument("--quick", action="store_true", help="1 rep, 1 weight set (for ncu)")
+    ap.add_argument("--splits-wo", type=int, default=0, help="split-K units per tile of wo (0 = the model's choice)")
+    ap.add_argument("--splits-w2", type=int, default=0, help="split-K units per tile of w2 (0 = the model's choice)")
     args = ap.parse_args()
     from echo_tts_b200 import ops, _lib as L
     D, F_, H = 2048, 5888, 16
@@ -65,17 +67,23 @@ def main():
         def f_wo(i):
             ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x, block_n=args.bn)
 
-        ns = max(1, min(4, 74 // (-(-M // 256) * 8)))
-        parts = torch.empty((ns, M, D), device="cuda")
+        ns = max(1, min(8 if M <= 256 else 4, 74 // (-(-M // 256) * 8)))       # model.EchoDiT.k_splits
+        ns_wo, ns_w2 = args.splits_wo or ns, args.splits_w2 or ns
+        if max(ns_wo, ns_w2) > 1:
+            ns = max(ns, 2)
+        parts = torch.empty((max(ns_wo, ns_w2, ns), M, D), device="cuda")
 
         def f_wo_split(i):
-            ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, split_out=parts)
+            ops.gemm_generic(ao, W["wo"][i % nw], gate=gate, rows_per_gate=S, split_out=parts[:ns_wo])
 
         def f_w2_split(i):
-            ops.gemm_generic(hm, W["w2"][i % nw], gate=gate, rows_per_gate=S, split_out=parts)
+            ops.gemm_generic(hm, W["w2"][i % nw], gate=gate, rows_per_gate=S, split_out=parts[:ns_w2])
 
         def f_addnorm(i):
-            ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0), delta=parts)
+            ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0), delta=parts[:ns_wo])
+
+        def f_addnorm2(i):
+            ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0), delta=parts[:ns_w2])
 
         def f_w13(i):
             ops.gemm_swiglu(xn, W["w13"][i % nw], hmid, block_n=args.bn)
@@ -93,7 +101,11 @@ def main():
             ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0))
 
         def f_seq(i):      # one decoder layer in launch order: cross-kernel effects (instruction cache, L2 state, PDL hand-offs)
-            f_norm(i); f_qkvg(i); f_attn(i)
+            if ns > 1:
+                f_addnorm2(i)
+            else:
+                f_norm(i)
+            f_qkvg(i); f_attn(i)
             if ns > 1:
                 f_wo_split(i); f_addnorm(i)
             else:
@@ -116,7 +128,7 @@ def main():
                  ("norm", f_norm, 0.0)]
         cases += [("seq", f_seq, 0.0), ("seq2", f_seq2, 0.0)]
         if ns > 1:
-            cases += [(f"wo/s{ns}", f_wo_split, 2.0 * M * D * D), (f"w2/s{ns}", f_w2_split, 2.0 * M * D * F_),
+            cases += [(f"wo/s{ns_wo}", f_wo_split, 2.0 * M * D * D), (f"w2/s{ns_w2}", f_w2_split, 2.0 * M * D * F_),
                       ("addnorm", f_addnorm, 0.0)]
         tot_us, tot_fl = 0.0, 0.0
         for name, fn, fl in cases:
