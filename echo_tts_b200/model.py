@@ -312,7 +312,11 @@ class EchoDiT:
             side = self._side_stream = torch.cuda.Stream(device=self._device)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
-            kv_spk = self.get_kv_cache_speaker(speaker_latent)
+            ops.ATTN_WS_SLOT = 1                 # its attention launches may overlap the text encoder's: own exchange buffer
+            try:
+                kv_spk = self.get_kv_cache_speaker(speaker_latent)
+            finally:
+                ops.ATTN_WS_SLOT = 0
         kv_text = self.get_kv_cache_text(text_input_ids, text_mask)
         cur.wait_stream(side)
         return kv_text, kv_spk

@@ -37,13 +37,16 @@ def gemm_workspace(device: torch.device) -> torch.Tensor:
 
 
 _ATTN_WS = {}
+ATTN_WS_SLOT = 0     # which of the per-device exchange buffers attention launches use: work that runs on a second stream
+                     # next to the main one (the speaker encoder, model.kv_caches_text_speaker) switches to slot 1
 
 
 def attn_workspace(device: torch.device) -> torch.Tensor:
     """Split-KV exchange buffer lent to every tcgen05 attention launch on ``device`` (echo_attn_desc.workspace: arrival
-    counters + 296 partial (O, m, l) = two CTAs per SM, zeroed once).  One buffer per device: attention launches of this
-    package run on one stream at a time per device."""
-    key = device.index if device.index is not None else torch.cuda.current_device()
+    counters + 296 partial (O, m, l) = two CTAs per SM, zeroed once).  One buffer per (device, slot): launches that may
+    overlap on two streams must not share one (``ATTN_WS_SLOT``).  Created at the first -- eager -- request of a shape,
+    i.e. before any CUDA-graph capture needs it."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), ATTN_WS_SLOT)
     ws = _ATTN_WS.get(key)
     if ws is None:
         ws = torch.zeros(int(L.load().echo_attention_workspace_bytes(1, 128 * 74, 1, 4)), device=device, dtype=torch.uint8)

@@ -210,6 +210,27 @@ def test_sgemm_and_batched(ops, L):
     assert rel_l2(outz, torch.einsum("zmk,znk->zmn", az, wz) + bz[:, None] + 1) < 1e-5
 
 
+def test_sgemm_scalar_and_vector_paths_and_b_static_flag(ops, L):
+    """fp32 sgemm: K not a multiple of 4 / misaligned rows take the scalar K-step-16 form, everything else the 16-byte
+    prefetching form -- same results; echo_gemm_desc.b_static only moves WHEN the first weight tiles are requested."""
+    import ctypes as C
+    for (m, n, k) in ((40, 200, 81), (40, 200, 84), (3, 64, 2048), (130, 70, 36)):
+        a, w = _rand((m, k), 70), _rand((n, k), 71, k ** -0.5)
+        out = torch.empty((m, n), device="cuda")
+        ops.sgemm(a, w, out=out, pre_silu=True)
+        assert rel_l2(out, torch.nn.functional.silu(a) @ w.t()) < 1e-5, (m, n, k)
+    a, w = _rand((300, 512), 72, dtype=BF16), _rand((384, 512), 73, 512 ** -0.5, BF16)
+    outs = []
+    for flag in (1, 0):
+        d = ops._base_gemm(a, w)
+        d.epilogue, d.b_static = L.EPI_GENERIC, flag
+        o = torch.empty((300, 384), device="cuda", dtype=F32)
+        d.out_f32, d.ld_out_f32 = o.data_ptr(), o.stride(0)
+        L.check(L.load().echo_gemm_bf16(C.byref(d), L.stream()))
+        outs.append(o)
+    assert torch.equal(outs[0], outs[1]) and rel_l2(outs[0], a.float() @ w.float().t()) < 2e-5
+
+
 def test_rmsnorm_mod(ops):
     M, D, S = 96, 2048, 32
     x = _rand((M, D), 28, 3.0)

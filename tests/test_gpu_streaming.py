@@ -305,6 +305,25 @@ def test_native_encoders_equal_python_launch_sequence(tiny_model, monkeypatch):
         assert a.shape == b.shape and torch.equal(a, b)
 
 
+@pytest.mark.parametrize("native", ["1", "0"])
+def test_text_and_speaker_encoders_side_by_side_equal_one_after_the_other(tiny_model, monkeypatch, native):
+    """model.kv_caches_text_speaker runs the speaker encoder on a forked stream next to the text encoder (two branches of
+    the sampler's graph): same caches, bit for bit, as the two calls in sequence -- with the native encoder entry point and
+    with the per-kernel Python path, whose attention launches are long enough here to use split-KV (each stream its own
+    exchange buffer)."""
+    monkeypatch.setenv("ECHO_ENC_NATIVE", native)
+    B = 2
+    ids = torch.randint(1, 200, (B, 300), dtype=torch.int32, device="cuda")
+    mask = torch.ones(B, 300, dtype=torch.bool, device="cuda")
+    mask[1, 170:] = False
+    spk = _rand((B, 600, 80), 61)
+    stack = lambda c: torch.stack([torch.stack([k, v]) for k, v in c])
+    ref_t, ref_s = stack(tiny_model.get_kv_cache_text(ids, mask)), stack(tiny_model.get_kv_cache_speaker(spk))
+    for _ in range(3):
+        kt, ks = tiny_model.kv_caches_text_speaker(ids, mask, spk)
+        assert torch.equal(stack(kt), ref_t) and torch.equal(stack(ks), ref_s)
+
+
 @pytest.mark.slow
 def test_config5_full_size_properties():
     """BASELINE configs[4] at its full size (echo-tts-base architecture, 4 blocks of 160 latents, 40 steps, cfg 3.0 / 5.0,
