@@ -61,43 +61,62 @@ __global__ void dwconv_ln_kernel(const float* __restrict__ x, int t_len, int c_l
 }
 
 // Last stage (autoencoder.py:994): causal conv k=7, C -> 1, + tanh on Snake'd bf16 input.  HBM-bound (C*2 bytes in, 4 out
-// per sample).  One warp per run of 32*RUNS outputs, channels across lanes (lane l owns channels l, l+32, ...): every
-// input row is read ONCE from global (64-byte warp loads, no shared memory) and scattered into the <= 7 outputs it feeds;
-// 32 per-lane partial outputs live in registers and one 31-shuffle transpose-reduction per 32 outputs leaves output
-// t0 + l in lane l for a coalesced store.  left_ctx as in dwconv_ln_kernel.
-template <int NC>
+// per sample).  One warp per run of 32*RUNS outputs, channel PAIRS across lanes (lane l owns pairs l, l+32, ...: 4-byte
+// loads, a warp load covers 128 contiguous bytes of a row): every input row is read ONCE from global (no shared memory)
+// and scattered into the <= 7 outputs it feeds; the 38 rows of a run are requested in batches of 10 (19) that are each
+// wholly in flight before the first use (1.9 KB per warp: the kernel is a pure stream, and bytes in flight are what it
+// needs); 32 per-lane partial outputs live in registers and one 31-shuffle transpose-reduction per 32 outputs leaves
+// output t0 + l in lane l for a coalesced store.  left_ctx as in dwconv_ln_kernel.  c_len must be even.
+template <int NP>
 __global__ void __launch_bounds__(256, 2) conv_out_tanh_kernel(const bf16* __restrict__ x, int t_len, int c_len,
                                                             const float* __restrict__ w, float bias,
                                                             float* __restrict__ wav, int left_ctx, int runs) {
   const int lane = threadIdx.x & 31, bt = blockIdx.y;
   const long long warp_id = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const bf16* xb = x + (long long)bt * t_len * c_len;
-  float wk[7][NC];
+  const int npairs = c_len >> 1;
+  float wk[7][NP][2];
 #pragma unroll
   for (int k = 0; k < 7; ++k)
 #pragma unroll
-    for (int j = 0; j < NC; ++j) wk[k][j] = (lane + 32 * j < c_len) ? __ldg(w + k * c_len + lane + 32 * j) : 0.f;
+    for (int j = 0; j < NP; ++j) {
+      const int pr = lane + 32 * j;
+      wk[k][j][0] = pr < npairs ? __ldg(w + k * c_len + 2 * pr) : 0.f;
+      wk[k][j][1] = pr < npairs ? __ldg(w + k * c_len + 2 * pr + 1) : 0.f;
+    }
   for (int run = 0; run < runs; ++run) {
     const long long t0 = (warp_id * runs + run) * 32;
     if (t0 >= t_len) return;
     float acc[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+    constexpr int BR = NP >= 2 ? 10 : 19;      // rows per batch (registers): 4 or 2 batches cover the run's 38 rows
 #pragma unroll
-    for (int rl = 0; rl < 38; ++rl) {
-      const long long r = t0 - 6 + rl;
-      float xv[NC];
+    for (int r0 = 0; r0 < 38; r0 += BR) {
+      uint32_t xr[BR][NP];
 #pragma unroll
-      for (int j = 0; j < NC; ++j) {
-        const int c = lane + 32 * j;
-        xv[j] = (r >= -left_ctx && r < t_len && c < c_len) ? bf2f(xb[r * c_len + c]) : 0.f;
+      for (int i = 0; i < BR; ++i) {
+        const long long r = t0 - 6 + r0 + i;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          const int pr = lane + 32 * j;
+          xr[i][j] = (r0 + i < 38 && r >= -left_ctx && r < t_len && pr < npairs)
+                         ? __ldg(reinterpret_cast<const uint32_t*>(xb + r * c_len) + pr) : 0u;
+        }
       }
 #pragma unroll
-      for (int k = 0; k < 7; ++k) {
-        const int tl = rl - k;                 // row r = t - 6 + k of output t = t0 + tl
-        if (tl >= 0 && tl < 32) {
+      for (int i = 0; i < BR; ++i) {
+        const int rl = r0 + i;
 #pragma unroll
-          for (int j = 0; j < NC; ++j) acc[tl] = fmaf(wk[k][j], xv[j], acc[tl]);
+        for (int k = 0; k < 7; ++k) {
+          const int tl = rl - k;               // row r = t - 6 + k of output t = t0 + tl
+          if (tl >= 0 && tl < 32) {
+#pragma unroll
+            for (int j = 0; j < NP; ++j) {
+              const float2 v = unpack_bf16x2(xr[i][j]);
+              acc[tl] = fmaf(wk[k][j][1], v.y, fmaf(wk[k][j][0], v.x, acc[tl]));
+            }
+          }
         }
       }
     }
@@ -329,12 +348,9 @@ extern "C" int echo_conv_out_tanh_ctx(const void* x, int batch, int t, int c, in
   const dim3 grid(ceil_div(t, per_cta), batch);
   cudaStream_t st = (cudaStream_t)stream;
   const bf16* xp = (const bf16*)x;
-  switch ((c + 31) / 32) {
-    case 1: conv_out_tanh_kernel<1><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
-    case 2: conv_out_tanh_kernel<2><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
-    case 3: conv_out_tanh_kernel<3><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
-    default: conv_out_tanh_kernel<4><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs); break;
-  }
+  ECHO_CHECK_ARG(c % 2 == 0 && ((uintptr_t)x % 4) == 0, "conv_out: channel count must be even, input 4-byte aligned");
+  if (c <= 64) conv_out_tanh_kernel<1><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs);   // pairs across lanes
+  else conv_out_tanh_kernel<2><<<grid, 256, 0, st>>>(xp, t, c, w, bias, wav, left_ctx, runs);
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;

@@ -86,7 +86,7 @@ void gemm_init(const Ctx& c, echo_gemm_desc* g, const void* a, int64_t lda, int 
   g->impl = c.D->gemm_impl;
   g->rows_per_gate = 1;
   g->b_static = 1;             // w is a load-time tensor of the descriptor (weights)
-  if (c.D->gemm_impl == 2) { g->workspace = c.D->gemm_workspace; g->workspace_bytes = c.D->gemm_workspace_bytes; }
+  if (c.D->gemm_impl >= 2) { g->workspace = c.D->gemm_workspace; g->workspace_bytes = c.D->gemm_workspace_bytes; }
 }
 
 // x += gamma * (a w^T)   (LayerScale residual, autoencoder.py:718-723)

@@ -32,7 +32,7 @@ void gemm_init(const echo_encode_kv_desc* D, echo_gemm_desc* g, const void* a, i
   g->impl = D->gemm_impl;
   g->rows_per_gate = 1;
   g->b_static = 1;             // w is a load-time tensor of the descriptor (weights)
-  if (D->gemm_impl == 2) { g->workspace = D->gemm_workspace; g->workspace_bytes = D->gemm_workspace_bytes; }
+  if (D->gemm_impl >= 2) { g->workspace = D->gemm_workspace; g->workspace_bytes = D->gemm_workspace_bytes; }
 }
 
 int check(const echo_encode_kv_desc* D) {

@@ -49,7 +49,7 @@ static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, i
 }
 
 int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
-                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st);  // gemm2.cu
+                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st, int sched_flags);  // gemm2.cu; bit 0 stream-K allowed, bit 1 no narrow last round
 
 static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
@@ -164,7 +164,8 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
   int rc = fill_params(d, G, P);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  ECHO_CHECK_ARG(d->impl == 0 || d->impl == 2, "gemm: impl %d: only the CTA-pair tcgen05 kernel (0 / 2) exists", d->impl);
+  ECHO_CHECK_ARG(d->impl == 0 || (d->impl >= 2 && d->impl <= 4),
+                 "gemm: impl %d: only the CTA-pair tcgen05 kernel exists (0 / 2; 3 = stream-K schedule allowed; 4 = plain schedule without the narrow last round)", d->impl);
   const int bn = pick_block_n_pair(d);
   ECHO_CHECK_ARG(bn > 0, "pair gemm: no tile width fits epilogue %d (n=%d)", d->epilogue, d->n);
   if (d->epilogue == ECHO_EPI_SECTIONS)
@@ -174,5 +175,5 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
     ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
                    !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
   return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
-                               d->batch, st);
+                               d->batch, st, (d->impl == 3 ? 1 : 0) | (d->impl == 4 ? 2 : 0));
 }

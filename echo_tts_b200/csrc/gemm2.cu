@@ -513,7 +513,6 @@ int getenv_int(const char* name, int dflt) {
 }
 // scheduler switches (A/B measurements), read ONCE per process -- not per launch
 int use_narrow_tail() { static const int v = getenv_int("ECHO_GEMM_TAIL", 1); return v; }
-int use_stream_k() { static const int v = getenv_int("ECHO_STREAM_K", 0); return v; }
 int use_gate_sm() { static const int v = getenv_int("ECHO_GEMM_GATESM", 1); return v; }
 int use_split_b() { static const int v = getenv_int("ECHO_GEMM_SPLITB", 1); return v; }
 int max_stages() { static const int v = getenv_int("ECHO_GEMM_STAGES", MAX_STAGES); return v < 2 ? 2 : v; }
@@ -542,7 +541,7 @@ extern "C" long long echo_gemm_workspace_bytes(void) {
 
 template <int EPI>
 static int launch_pair_t(int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
-                         const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+                         const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st, int sched_flags) {
   CUtensorMap ta, tb, tbn;
   // Narrow tail: when the last round of whole-tile scheduling is ragged and its tiles, cut in two along N, still fit ONE
   // round, those tiles run half-width -- a shorter main loop and half the exposed epilogue at the end of the launch
@@ -552,7 +551,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     const int P2 = num_sms() / 2;
     const int wide = ceil_div(G.rows, 2 * BM) * ceil_div(G.n, bn) * batch;
     const int rem = wide % P2;
-    if (splits == 1 && bn == 256 && G.n % 256 == 0 && !g_debug_noload && use_narrow_tail()) {
+    if (splits == 1 && bn == 256 && G.n % 256 == 0 && !g_debug_noload && use_narrow_tail() && !(sched_flags & 2)) {
       if (wide > P2 && rem > 0 && 2 * rem <= P2) tail_start = wide - rem;
       else if (2 * wide <= P2) tail_start = 0;      // a single sparse round: every tile half-width, twice the pairs busy
     }
@@ -626,7 +625,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     const int P2 = num_sms() / 2, total_kb = G.k_blocks_per_tap * G.taps;
     const long long tiles = T.num_tiles, rounds = (tiles + P2 - 1) / P2;
     const bool ragged = tiles * 100 < rounds * P2 * 92;
-    if (ragged && total_kb >= 8 && tiles * total_kb >= 4LL * P2 && use_stream_k()) {
+    if (ragged && total_kb >= 8 && tiles * total_kb >= 4LL * P2 && (sched_flags & 1)) {
       T.stream_k = 1;
       T.sk_flags = reinterpret_cast<int*>(workspace);
       T.sk_partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + SK_FLAG_BYTES);
@@ -667,7 +666,7 @@ extern "C" int echo_debug_gemm_trace(long long* device_buf) {
 
 // bn: multiple of 32 in [64, 256] (so that each CTA's half is a legal UMMA_N/2 and a whole number of 16-column groups)
 int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
-                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st) {
+                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st, int sched_flags) {
   if (splits < 1) splits = 1;
   if (splits > 1 && (epi != ECHO_EPI_GENERIC || splits > G.k_blocks_per_tap * G.taps)) {
     echo_set_error("pair gemm: k_splits %d needs the GENERIC epilogue and at least one k-block per split", splits);
@@ -681,9 +680,9 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, v
     case ECHO_EPI_GENERIC:
       // LEAN (TMA epilogue): fp32 output only, residual absent or updated in place
       if (P.act == ECHO_ACT_NONE && !P.out_bf16 && !P.out2_bf16 && P.out_f32 && (P.red_resid || !P.resid))
-        return launch_pair_t<EPI_GENERIC_LEAN>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
-      return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st);
-    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);
-    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st);
+        return launch_pair_t<EPI_GENERIC_LEAN>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st, sched_flags);
+      return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st, sched_flags);
+    case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);
+    default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);
   }
 }

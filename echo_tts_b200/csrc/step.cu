@@ -29,7 +29,7 @@ void gemm_base(const echo_dit_step_desc* D, echo_gemm_desc* g, const void* a, in
   g->impl = D->gemm_impl;
   g->rows_per_gate = 1;
   g->b_static = 1;             // w is a load-time tensor of the descriptor (weights)
-  if (D->gemm_impl == 2) { g->workspace = D->gemm_workspace; g->workspace_bytes = D->gemm_workspace_bytes; }
+  if (D->gemm_impl >= 2) { g->workspace = D->gemm_workspace; g->workspace_bytes = D->gemm_workspace_bytes; }
 }
 
 // gated residual projection (model.py:385, 388): x += gate * (a w^T), or its split-K form into `delta`

@@ -303,7 +303,7 @@ class EchoDiT:
         a second stream forked from and joined back into the current one (inside a CUDA-graph capture this becomes two
         parallel branches of the graph).  The side stream always waits for the current stream first, so buffers the caching
         allocator hands back to it are never reused under work the current stream still has in flight."""
-        if os.environ.get("ECHO_STREAM_K") == "1" or os.environ.get("ECHO_ENCODER_STREAMS") == "0":
+        if ops.GEMM_IMPL == 3 or os.environ.get("ECHO_ENCODER_STREAMS") == "0":
             # (the stream-K schedule exchanges partial tiles through ONE workspace per device: no concurrent GEMM streams)
             return self.get_kv_cache_text(text_input_ids, text_mask), self.get_kv_cache_speaker(speaker_latent)
         cur = torch.cuda.current_stream(self._device)

@@ -4,6 +4,7 @@ CUDA stream.  Nothing here computes on the CPU."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -11,8 +12,9 @@ import torch
 from . import _lib as L
 
 BF16, F32 = torch.bfloat16, torch.float32
-STREAM_K = True   # lend the stream-K workspace; the library decides (ECHO_STREAM_K=1 enables it, default off)
-GEMM_IMPL = 2     # echo_gemm_desc.impl: the CTA-pair persistent tcgen05 kernel -- the only GEMM kernel of the library
+STREAM_K = os.environ.get("ECHO_STREAM_K") == "1"   # read once at import: allow the stream-K schedule (off by default)
+GEMM_IMPL = 3 if STREAM_K else 2   # echo_gemm_desc.impl: the CTA-pair persistent tcgen05 kernel (the only GEMM kernel of
+                                   # the library); 3 = the same with stream-K scheduling of ragged launches allowed
 
 
 def _need(t: torch.Tensor, dtype, name: str):
@@ -77,7 +79,7 @@ def _base_gemm(a: torch.Tensor, w: torch.Tensor, taps: Sequence[int] = (0,), bat
     d.a_ctx = a_ctx
     d.rows_per_gate = 1
     d.b_static = 1          # every caller in this package passes load-time weights as `w` (include/echo_b200.h: b_static)
-    if d.impl == 2 and STREAM_K:
+    if d.impl == 3:
         ws = gemm_workspace(a.device)
         d.workspace, d.workspace_bytes = ws.data_ptr(), ws.numel()
     return d

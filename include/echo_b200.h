@@ -49,7 +49,10 @@ typedef struct echo_gemm_desc {
   int32_t rows, batch, n, k_tap, taps;
   int32_t tap_shift[8];
   int32_t epilogue;         /* ECHO_EPI_* */
-  int32_t impl;             /* 0 or 2: the CTA-pair tcgen05 kernel (the only GEMM kernel); anything else is refused */
+  int32_t impl;             /* 0 or 2: the CTA-pair tcgen05 kernel (the only GEMM kernel); 3: the same, and the library may
+                             * schedule ragged launches stream-K through `workspace`; 4: the same with the plain tile
+                             * schedule (no half-width last round; results are bit-identical to 2, kept for A/B and
+                             * the tests); anything else is refused */
   int32_t block_n;          /* 0 = auto; 64 / 128 / 256 */
   int32_t act;              /* GENERIC: activation applied after bias */
   /* GENERIC: v = act(acc + bias[n]) * gate[(m / rows_per_gate) * gate_ld + n] + resid[m, n]
@@ -90,8 +93,8 @@ typedef struct echo_gemm_desc {
   echo_gemm_section sections[4];
   int64_t split_stride;     /* elements between the k_splits partial outputs */
   /* SWIGLU: B rows interleaved in groups of 64 (w1 | w3); out_bf16[m, j] = silu(a)*b (model.py:308) */
-  void* workspace;          /* optional, impl 2: device scratch of >= echo_gemm_workspace_bytes(), zeroed once by the
-                             * caller, not shared between concurrently running streams.  When present the library may
+  void* workspace;          /* optional: device scratch of >= echo_gemm_workspace_bytes(), zeroed once by the
+                             * caller, not shared between concurrently running streams.  With impl 3 the library may
                              * schedule the launch stream-K (equal k-block ranges per CTA pair, partial accumulators
                              * exchanged through this buffer in a fixed order: deterministic, same epilogues). */
   int64_t workspace_bytes;

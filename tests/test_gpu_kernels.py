@@ -128,7 +128,7 @@ def test_gemm_sections_norm_rope(ops, L, impl, hd, H, rope_heads):
 
 
 @pytest.mark.parametrize("M,N,K", [(1920, 2048, 2048), (1920, 2048, 5888), (640, 2048, 2048), (640, 8192, 2048), (2304, 768, 1024)])
-def test_gemm_stream_k_generic(ops, M, N, K, monkeypatch):
+def test_gemm_stream_k_generic(ops, M, N, K):
     """Ragged tile counts are scheduled stream-K (partial accumulators exchanged through the lent workspace): same
     result as whole-tile scheduling up to fp32 summation order, identical from run to run (self-resetting flags)."""
     a, w = _rand((M, K), 41, dtype=BF16), _rand((N, K), 42, K ** -0.5, BF16)
@@ -136,17 +136,16 @@ def test_gemm_stream_k_generic(ops, M, N, K, monkeypatch):
     rpg = (M + 2) // 3
     ref = (a.float() @ w.float().t() + bias) * gate[torch.arange(M, device="cuda") // rpg] + resid
     outs = []
-    for sk in ("1", "1", "0"):
-        monkeypatch.setenv("ECHO_STREAM_K", sk)
+    for impl in (3, 3, 2):                                   # impl 3: the stream-K schedule is allowed
         x = resid.clone()
-        ops.gemm_generic(a, w, bias=bias, gate=gate, rows_per_gate=rpg, resid=x, out_f32=x, impl=2)
+        ops.gemm_generic(a, w, bias=bias, gate=gate, rows_per_gate=rpg, resid=x, out_f32=x, impl=impl)
         outs.append(x)
     assert torch.equal(outs[0], outs[1])
     assert rel_l2(outs[0], ref) < 2e-5 and rel_l2(outs[2], ref) < 2e-5
     assert rel_l2(outs[0], outs[2]) < 5e-6
 
 
-def test_gemm_stream_k_fused_epilogues(ops, L, monkeypatch):
+def test_gemm_stream_k_fused_epilogues(ops, L):
     """SECTIONS (per-head norm needs the whole fixed-up accumulator row) and SWIGLU epilogues on stream-K tiles."""
     from oracle import echo_oracle as O
     R, S, K, H, hd = 1, 640, 2048, 16, 128
@@ -157,12 +156,11 @@ def test_gemm_stream_k_fused_epilogues(ops, L, monkeypatch):
     cos, sin = O.rope_table(hd, 4096)
     rope = (cos.cuda().contiguous(), sin.cuda().contiguous())
     res = {}
-    for sk in ("1", "0"):
-        monkeypatch.setenv("ECHO_STREAM_K", sk)
+    for sk, impl in (("1", 3), ("0", 2)):
         outs = torch.empty((4, M, D), device="cuda", dtype=BF16)
         ops.gemm_sections(a, w, [(L.SEC_NORM_ROPE, outs[0], qn), (L.SEC_NORM_ROPE, outs[1], kn), (L.SEC_PLAIN, outs[2], None),
                                  (L.SEC_SIGMOID, outs[3], None)], head_dim=hd, rope_heads=8, rope=rope, pos_offset=0,
-                          rows_per_seq=S, eps=1e-5, impl=2)
+                          rows_per_seq=S, eps=1e-5, impl=impl)
         res[sk] = outs.float()
     assert rel_l2(res["1"], res["0"]) < 2e-3          # bf16 outputs: an fp32 reordering flips a few roundings
     acc = (a.float() @ w.float().t())
@@ -172,11 +170,10 @@ def test_gemm_stream_k_fused_epilogues(ops, L, monkeypatch):
     w13 = ops.pack_w13(w1, w3)
     a2 = _rand((896, K), 52, dtype=BF16)               # 4 x 46 = 184 tiles on 74 pairs: ragged
     ref = torch.nn.functional.silu(a2.float() @ w1.float().t()) * (a2.float() @ w3.float().t())
-    for sk in ("1", "0"):
-        monkeypatch.setenv("ECHO_STREAM_K", sk)
+    for impl in (3, 2):
         out = torch.empty((896, F_), device="cuda", dtype=BF16)
-        ops.gemm_swiglu(a2, w13, out, impl=2)
-        assert rel_l2(out.float(), ref) < 4e-3, sk
+        ops.gemm_swiglu(a2, w13, out, impl=impl)
+        assert rel_l2(out.float(), ref) < 4e-3, impl
 
 
 @pytest.mark.parametrize("M,N,K,S", [(640, 2048, 5888, 3), (640, 2048, 2048, 3), (100, 256, 256, 4), (300, 512, 1024, 2)])
@@ -244,7 +241,7 @@ def test_rmsnorm_mod(ops):
 
 # ---- narrow tail: the ragged last round of a launch runs as half-width tiles (gemm2.cu launch_pair_t) ------------------
 @pytest.mark.parametrize("M,N,K", [(1920, 8192, 320), (640, 8192, 256), (2000, 5120, 192), (700, 8192, 64)])
-def test_gemm_narrow_tail_matches_plain_schedule(ops, M, N, K, monkeypatch):
+def test_gemm_narrow_tail_matches_plain_schedule(ops, M, N, K):
     """Shapes whose 256-wide tiles leave a ragged last round that fits one round of 128-wide tiles (e.g. 8 x 32 = 256
     tiles on 74 CTA pairs: 3 rounds + 34).  Same per-element sums as the plain schedule -> bit-identical results, for
     the generic, sections (per-head RMSNorm + RoPE + sigmoid) and SwiGLU epilogues; and both match the fp32 reference."""
@@ -258,23 +255,22 @@ def test_gemm_narrow_tail_matches_plain_schedule(ops, M, N, K, monkeypatch):
     cos, sin = O.rope_table(128, 4096)
     rope = (cos.cuda().contiguous(), sin.cuda().contiguous())
     res = {}
-    for tail in ("1", "0"):
-        monkeypatch.setenv("ECHO_GEMM_TAIL", tail)
+    for tail, impl in (("1", 2), ("0", 4)):   # impl 4 = the plain schedule, no half-width last round
         out = torch.full((M, N), float("nan"), device="cuda", dtype=F32)
-        ops.gemm_generic(a, w, bias=bias, out_f32=out, impl=2)
+        ops.gemm_generic(a, w, bias=bias, out_f32=out, impl=impl)
         sec = torch.full((4, M, D), float("nan"), device="cuda", dtype=BF16)
         ops.gemm_sections(a, w, [(L.SEC_NORM_ROPE, sec[0], qn), (L.SEC_NORM_ROPE, sec[1], kn), (L.SEC_PLAIN, sec[2], None),
                                  (L.SEC_SIGMOID, sec[3], None)], head_dim=128, rope_heads=D // 256, rope=rope,
-                          rows_per_seq=M, eps=1e-5, impl=2)
+                          rows_per_seq=M, eps=1e-5, impl=impl)
         sw = torch.full((M, N // 2), float("nan"), device="cuda", dtype=BF16)
-        ops.gemm_swiglu(a, w, sw, impl=2)
+        ops.gemm_swiglu(a, w, sw, impl=impl)
         res[tail] = (out, sec, sw)
     for x, y in zip(res["1"], res["0"]):
         assert torch.equal(x, y)
     assert rel_l2(res["1"][0], a.float() @ w.float().t() + bias) < 2e-5
 
 
-def test_gemm_narrow_tail_with_batches_and_taps(ops, monkeypatch):
+def test_gemm_narrow_tail_with_batches_and_taps(ops):
     """Narrow tail on a batched implicit-GEMM conv (6 row tiles x 4 column tiles x 4 batch entries = 96 tiles -> 74 + 22
     -> 44 half-width tiles): tile -> (row tile, column tile, batch) decoding of the half tiles, bit-identical to the plain
     schedule and equal to the fp32 conv."""
@@ -283,10 +279,9 @@ def test_gemm_narrow_tail_with_batches_and_taps(ops, monkeypatch):
     w = _rand((N, C, 7), 72, (C * 7) ** -0.5, BF16)
     wp = w.permute(0, 2, 1).reshape(N, 7 * C).contiguous()
     outs = {}
-    for tail in ("1", "0"):
-        monkeypatch.setenv("ECHO_GEMM_TAIL", tail)
+    for tail, impl in (("1", 2), ("0", 4)):   # impl 4 = the plain schedule, no half-width last round
         out = torch.full((B * T, N), float("nan"), device="cuda", dtype=F32)
-        ops.gemm_generic(x.view(B * T, C), wp, taps=tuple(-(6 - k) * dil for k in range(7)), batch=B, out_f32=out, impl=2)
+        ops.gemm_generic(x.view(B * T, C), wp, taps=tuple(-(6 - k) * dil for k in range(7)), batch=B, out_f32=out, impl=impl)
         outs[tail] = out
     assert torch.equal(outs["1"], outs["0"])
     xin = torch.nn.functional.pad(x.float().transpose(1, 2), (6 * dil, 0))
