@@ -153,7 +153,6 @@ class DitStepDesc(C.Structure):
         ("gemm_workspace", c_p), ("gemm_workspace_bytes", i64), ("gemm_impl", i32), ("attn_impl", i32),
         ("tail", C.POINTER(TailDesc)), ("pending_out", C.POINTER(i32)),
         ("attn_workspace", c_p), ("attn_workspace_bytes", i64),
-        ("chain_sync", c_p), ("chain_sync_bytes", i64),
     ]
 
 
@@ -169,8 +168,6 @@ EXPORTS = {
     "echo_reset_launch_count": (None, []),
     "echo_gemm_bf16": (C.c_int, [C.POINTER(GemmDesc), c_p]),
     "echo_gemm_workspace_bytes": (C.c_longlong, []),
-    "echo_gemm_chain_bf16": (C.c_int, [C.POINTER(GemmDesc), C.POINTER(GemmDesc), c_p, i64, c_p]),
-    "echo_gemm_chain_sync_bytes": (C.c_longlong, []),
     "echo_gemm_bf16_splitk_noalloc": (C.c_int, [C.POINTER(GemmDesc), c_p]),
     "echo_noalloc_scratch_bytes": (C.c_longlong, []),
     "echo_debug_gemm_trace": (C.c_int, [c_p]),

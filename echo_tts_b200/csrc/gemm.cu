@@ -177,20 +177,3 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
   return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
                                d->batch, st, (d->impl == 3 ? 1 : 0) | (d->impl == 4 ? 2 : 0));
 }
-
-int echo_launch_gemm_chain(const GemmShape& G0, const EpiParams& P0, const GemmShape& G1, const EpiParams& P1, int splits1,
-                           long long split_stride1, void* sync, long long sync_bytes, cudaStream_t st);   // gemm2.cu
-
-// `up` (SWIGLU) and `down` (GENERIC in its lean form, optionally k_splits > 1) as ONE persistent launch: down->a must be
-// up->out_bf16.  ECHO_ERR_UNSUPPORTED when the pair of shapes does not fit (the caller then launches the two GEMMs).
-extern "C" int echo_gemm_chain_bf16(const echo_gemm_desc* up, const echo_gemm_desc* down, void* sync, int64_t sync_bytes,
-                                    echo_stream_t stream) {
-  GemmShape G0, G1;
-  EpiParams P0, P1;
-  if (int rc = fill_params(up, G0, P0)) return rc;
-  if (int rc = fill_params(down, G1, P1)) return rc;
-  ECHO_CHECK_ARG(up->batch == 1 && down->batch == 1, "gemm chain: batch must be 1");
-  if (down->k_splits > 1)
-    ECHO_CHECK_ARG(!down->resid && down->out_f32 && down->split_stride % 4 == 0, "gemm chain: k_splits needs a plain fp32 output");
-  return echo_launch_gemm_chain(G0, P0, G1, P1, down->k_splits, down->split_stride, sync, sync_bytes, (cudaStream_t)stream);
-}

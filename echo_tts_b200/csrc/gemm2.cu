@@ -528,8 +528,6 @@ int num_sms() {
 }
 }  // namespace
 
-#include "gemm_chain.cuh"
-
 int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                         const cuuint32_t* box);   // gemm.cu
 int echo_make_tmap_f32(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
@@ -687,94 +685,4 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, v
     case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);
     default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);
   }
-}
-
-// ---- MLP chain: SwiGLU up-projection and gated-residual down-projection in one persistent launch (gemm_chain.cuh) -------
-extern "C" long long echo_gemm_chain_sync_bytes(void) { return CHAIN_SYNC_BYTES; }
-
-// Shapes the chain kernel takes: one tap, 256-wide tiles in both phases, the down-projection reading exactly what the
-// up-projection writes.  Returns ECHO_ERR_UNSUPPORTED (with a message) otherwise; callers test with echo_gemm_chain_ok().
-static const char* chain_reject(const GemmShape& G0, const EpiParams& P0, const GemmShape& G1, const EpiParams& P1, int splits1) {
-  if (G0.taps != 1 || G1.taps != 1 || G0.a_ctx || G1.a_ctx) return "taps / context rows";
-  if (G0.rows != G1.rows || G0.rows <= 0) return "row counts differ";
-  if (ceil_div(G0.rows, 2 * BM) > CHAIN_MAX_ROW_BLOCKS) return "too many rows";
-  if (G0.n % 256 != 0 || G1.n % 256 != 0) return "n must be a multiple of 256 in both phases";
-  if (G0.k_tap % BK != 0 || G1.k_tap % BK != 0) return "k must be a multiple of 64 in both phases";
-  if (!G0.b_static || !G1.b_static) return "both weight operands must be b_static";
-  if (P0.kind != ECHO_EPI_SWIGLU || !P0.out_bf16) return "phase 0 must be SWIGLU";
-  if (reinterpret_cast<const bf16*>(P0.out_bf16) != G1.a || P0.ld_out_bf16 != G1.lda || G1.k_tap != G0.n / 2)
-    return "phase 1 must read phase 0's output";
-  if (P1.kind != ECHO_EPI_GENERIC || P1.act != ECHO_ACT_NONE || P1.out_bf16 || P1.out2_bf16 || !P1.out_f32 ||
-      (P1.resid && !P1.red_resid))
-    return "phase 1 must be the lean form (fp32 output, residual absent or in place)";
-  if (splits1 < 1 || splits1 > G1.k_blocks_per_tap) return "bad k_splits";
-  return nullptr;
-}
-
-int echo_launch_gemm_chain(const GemmShape& G0, const EpiParams& P0, const GemmShape& G1, const EpiParams& P1, int splits1,
-                           long long split_stride1, void* sync, long long sync_bytes, cudaStream_t st) {
-  if (splits1 < 1) splits1 = 1;
-  if (const char* why = chain_reject(G0, P0, G1, P1, splits1)) {
-    echo_set_error("gemm chain: unsupported pair of descriptors (%s)", why);
-    return ECHO_ERR_UNSUPPORTED;
-  }
-  if (!sync || sync_bytes < CHAIN_SYNC_BYTES || ((uintptr_t)sync % 4) != 0) {
-    echo_set_error("gemm chain: sync needs echo_gemm_chain_sync_bytes() zeroed bytes");
-    return ECHO_ERR_INVALID;
-  }
-  CUtensorMap ta[2], tb[2], tout;
-  const GemmShape* Gs[2] = {&G0, &G1};
-  for (int i = 0; i < 2; ++i) {
-    const GemmShape& G = *Gs[i];
-    cuuint64_t adims[3] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.rows, 1};
-    cuuint64_t astr[2] = {(cuuint64_t)G.lda * 2, (cuuint64_t)((long long)G.rows * G.lda) * 2};
-    cuuint32_t abox[3] = {BK, BM, 1};
-    if (int rc = echo_make_tmap_bf16(&ta[i], G.a, 3, adims, astr, abox)) return rc;
-    cuuint64_t bdims[2] = {(cuuint64_t)G.k_tap, (cuuint64_t)G.n};
-    cuuint64_t bstr[1] = {(cuuint64_t)G.ldb * 2};
-    cuuint32_t bbox[2] = {BK, (cuuint32_t)(ACC_COLS / 2)};
-    if (int rc = echo_make_tmap_bf16(&tb[i], G.b, 2, bdims, bstr, bbox)) return rc;
-  }
-  {
-    const long long ld = P1.ld_out_f32, bstride = (long long)G1.rows * ld;
-    const long long sstride = splits1 > 1 ? split_stride1 : bstride;
-    cuuint64_t dims[4] = {(cuuint64_t)G1.n, (cuuint64_t)G1.rows, 1, (cuuint64_t)splits1};
-    cuuint64_t str[3] = {(cuuint64_t)ld * 4, (cuuint64_t)bstride * 4, (cuuint64_t)sstride * 4};
-    cuuint32_t box[4] = {32, 32, 1, 1};
-    if (int rc = echo_make_tmap_f32(&tout, P1.out_f32, 4, dims, str, box)) return rc;
-  }
-  {
-    static bool attr_set[64] = {};
-    int dev = 0;
-    ECHO_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-      ECHO_CUDA(cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
-      if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-  }
-  ChainTiling T;
-#ifdef ECHO_DEBUG
-  T.trace = g_trace_ptr;
-#endif
-  T.stage_bytes = STAGE_BYTES;
-  T.stages = RING_BYTES / STAGE_BYTES;
-  if (T.stages > max_stages()) T.stages = max_stages();
-  T.tiles_m = ceil_div(G0.rows, 2 * BM);
-  T.tiles_n0 = G0.n / ACC_COLS; T.units0 = T.tiles_m * T.tiles_n0; T.kb_total0 = G0.k_blocks_per_tap;
-  T.tiles_n1 = G1.n / ACC_COLS; T.splits1 = splits1; T.units_mt1 = T.tiles_n1 * splits1;
-  T.units1 = T.tiles_m * T.units_mt1; T.kb_total1 = G1.k_blocks_per_tap;
-  T.fd_m = make_fastdiv(T.tiles_m); T.m_fastest = getenv_int("ECHO_CHAIN_ORDER", 0);
-  T.fd_n0 = make_fastdiv(T.tiles_n0); T.fd_u1 = make_fastdiv(T.units_mt1); T.fd_s1 = make_fastdiv(splits1);
-  T.split_stride1 = split_stride1;
-  T.gate_sm = use_gate_sm();
-  T.ready_expect = 2 * EPI_WARPS * T.tiles_n0;
-  T.drain_expect = 2 * T.units_mt1;
-  T.ready = reinterpret_cast<int*>(sync);
-  T.drained = T.ready + CHAIN_MAX_ROW_BLOCKS;
-  const int units = T.units0 + T.units1;
-  const int pairs = units < num_sms() / 2 ? units : num_sms() / 2;
-  ECHO_CUDA(echo_launch(gemm_chain_kernel, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta[0], tb[0], ta[1], tb[1], tout, P0, P1, T));
-  ECHO_COUNT_LAUNCH();
-  ECHO_LAUNCH_CHECK();
-  return ECHO_OK;
 }

@@ -33,25 +33,21 @@ void gemm_base(const echo_dit_step_desc* D, echo_gemm_desc* g, const void* a, in
 }
 
 // gated residual projection (model.py:385, 388): x += gate * (a w^T), or its split-K form into `delta`
-void residual_projection_desc(const echo_dit_step_desc* D, const StepShape& sh, echo_gemm_desc* g, const void* a, int k,
-                              const void* w, int l, int j) {
-  gemm_base(D, g, a, k, sh.M, k, w, sh.d, ECHO_EPI_GENERIC);
-  g->gate = mod_vec(D, l, j, 2);
-  g->gate_ld = sh.mod_ld;
-  g->rows_per_gate = sh.rows_per_mod > 0 ? sh.rows_per_mod : (1 << 30);
-  if (D->k_splits > 1) {
-    g->k_splits = D->k_splits;
-    g->split_stride = (int64_t)sh.M * sh.d;
-    g->out_f32 = D->delta; g->ld_out_f32 = sh.d;
-  } else {
-    g->resid = D->x; g->ld_resid = sh.d;
-    g->out_f32 = D->x; g->ld_out_f32 = sh.d;
-  }
-}
 int residual_projection(const echo_dit_step_desc* D, const StepShape& sh, const void* a, int k, const void* w, int l,
                         int j, cudaStream_t st) {
   echo_gemm_desc g;
-  residual_projection_desc(D, sh, &g, a, k, w, l, j);
+  gemm_base(D, &g, a, k, sh.M, k, w, sh.d, ECHO_EPI_GENERIC);
+  g.gate = mod_vec(D, l, j, 2);
+  g.gate_ld = sh.mod_ld;
+  g.rows_per_gate = sh.rows_per_mod > 0 ? sh.rows_per_mod : (1 << 30);
+  if (D->k_splits > 1) {
+    g.k_splits = D->k_splits;
+    g.split_stride = (int64_t)sh.M * sh.d;
+    g.out_f32 = D->delta; g.ld_out_f32 = sh.d;
+  } else {
+    g.resid = D->x; g.ld_resid = sh.d;
+    g.out_f32 = D->x; g.ld_out_f32 = sh.d;
+  }
   return echo_gemm_bf16(&g, st);
 }
 
@@ -130,9 +126,6 @@ extern "C" int echo_dit_step(const echo_dit_step_desc* D, echo_stream_t stream) 
     if (int rc = echo_sgemm_f32(&g, st)) return rc;
   }
 
-  // The MLP as one chained launch (gemm_chain.cuh): the product kernel only, shapes that tile by 256 / 64
-  const bool chain = D->chain_sync && (D->gemm_impl == 0 || D->gemm_impl == 2) && d % 256 == 0 && (2 * D->ffn) % 256 == 0 &&
-                     M <= 64 * 256 && (D->k_splits <= 1 || D->k_splits <= D->ffn / 64);
   bool pending = false;   // split-K partial products of the last w2 not yet added to x
   for (int l = 0; l < D->n_layers; ++l) {
     const echo_dit_layer& W = D->layers[l];
@@ -176,18 +169,13 @@ extern "C" int echo_dit_step(const echo_dit_step_desc* D, echo_stream_t stream) 
     }
     if (int rc = residual_projection(D, sh, D->ao, d, W.w_o, l, 0, st)) return rc;
     if (int rc = adaln_norm(D, sh, l, 1, D->k_splits > 1, st)) return rc;
-    {  // SwiGLU up-projection (model.py:308) and gated down-projection (model.py:388): one chained launch when they fit
-      echo_gemm_desc g, g2;
+    {  // SwiGLU up-projection (model.py:308)
+      echo_gemm_desc g;
       gemm_base(D, &g, D->xn, d, M, d, W.w13, 2 * D->ffn, ECHO_EPI_SWIGLU);
       g.out_bf16 = D->hmid; g.ld_out_bf16 = D->ffn;
-      if (chain) {
-        residual_projection_desc(D, sh, &g2, D->hmid, D->ffn, W.w2, l, 1);
-        if (int rc = echo_gemm_chain_bf16(&g, &g2, D->chain_sync, D->chain_sync_bytes, st)) return rc;
-      } else {
-        if (int rc = echo_gemm_bf16(&g, st)) return rc;
-        if (int rc = residual_projection(D, sh, D->hmid, D->ffn, W.w2, l, 1, st)) return rc;
-      }
+      if (int rc = echo_gemm_bf16(&g, st)) return rc;
     }
+    if (int rc = residual_projection(D, sh, D->hmid, D->ffn, W.w2, l, 1, st)) return rc;
     pending = D->k_splits > 1;
   }
   if (D->pending_out) *D->pending_out = pending ? 1 : 0;

@@ -475,9 +475,6 @@ class EchoDiT:
         d.gemm_workspace, d.gemm_workspace_bytes = gws.data_ptr(), gws.numel()
         aws = ops.attn_workspace(self._device)
         d.attn_workspace, d.attn_workspace_bytes = aws.data_ptr(), aws.numel()
-        if ops.MLP_CHAIN:
-            cs = ops.chain_sync(self._device)
-            d.chain_sync, d.chain_sync_bytes = cs.data_ptr(), cs.numel()
         d.gemm_impl, d.attn_impl = ops.GEMM_IMPL, ops.ATTN_IMPL
         if tail is not None:
             d.tail = C.pointer(tail)

@@ -165,50 +165,6 @@ def gemm_swiglu(a, w13, out_bf16, *, impl=None, block_n=0) -> None:
     L.check(L.load().echo_gemm_bf16(C.byref(d), L.stream()))
 
 
-_CHAIN_SYNC = {}
-MLP_CHAIN = os.environ.get("ECHO_MLP_CHAIN", "0") == "1"   # the DiT step runs each layer's MLP as one chained launch
-
-
-def chain_sync(device: torch.device) -> torch.Tensor:
-    """Row-block counters of the chained MLP launch (echo_gemm_chain_bf16 ``sync``): zeroed once, left zero by every
-    launch.  One buffer per device: chained launches of this package run on one stream at a time per device."""
-    key = device.index if device.index is not None else torch.cuda.current_device()
-    ws = _CHAIN_SYNC.get(key)
-    if ws is None:
-        ws = torch.zeros(int(L.load().echo_gemm_chain_sync_bytes()), device=device, dtype=torch.uint8)
-        _CHAIN_SYNC[key] = ws
-    return ws
-
-
-def gemm_mlp_chain(a, w13, hmid, w2, *, gate=None, rows_per_gate=0, x=None, split_out=None) -> None:
-    """hmid = silu(a w1^T) * (a w3^T); then x += gate * (hmid w2^T) in place, or its split-K partial products into
-    ``split_out`` [S, M, N] -- ONE persistent launch (echo_gemm_chain_bf16), bit-identical to gemm_swiglu followed by
-    gemm_generic.  Raises when the shapes do not fit the chained kernel."""
-    up = _base_gemm(a, w13, (0,), 1, 2, 0)
-    up.epilogue = L.EPI_SWIGLU
-    _need(hmid, BF16, "hmid"); assert hmid.shape == (a.shape[0], w13.shape[0] // 2) and hmid.stride(1) == 1
-    up.out_bf16, up.ld_out_bf16 = hmid.data_ptr(), hmid.stride(0)
-    down = _base_gemm(hmid, w2, (0,), 1, 2, 0)
-    down.epilogue, down.act = L.EPI_GENERIC, L.ACT_NONE
-    M, N = a.shape[0], w2.shape[0]
-    if gate is not None:
-        _need(gate, F32, "gate"); assert gate.shape[-1] == N and gate.stride(-1) == 1
-        down.gate = gate.data_ptr()
-        down.gate_ld = gate.stride(0) if gate.dim() == 2 else 0
-        down.rows_per_gate = rows_per_gate if rows_per_gate > 0 else (1 << 30)
-    if split_out is not None:
-        _need(split_out, F32, "split_out")
-        assert x is None and split_out.dim() == 3 and split_out.shape[1:] == (M, N) and split_out.is_contiguous()
-        down.k_splits, down.split_stride = split_out.shape[0], split_out.stride(0)
-        down.out_f32, down.ld_out_f32 = split_out.data_ptr(), split_out.stride(1)
-    else:
-        _need(x, F32, "x"); assert x.shape == (M, N) and x.stride(1) == 1
-        down.resid, down.ld_resid = x.data_ptr(), x.stride(0)
-        down.out_f32, down.ld_out_f32 = x.data_ptr(), x.stride(0)
-    ws = chain_sync(a.device)
-    L.check(L.load().echo_gemm_chain_bf16(C.byref(up), C.byref(down), ws.data_ptr(), ws.numel(), L.stream()))
-
-
 def pack_w13(w1: torch.Tensor, w3: torch.Tensor) -> torch.Tensor:
     """[F, K] x2 -> [2F, K] with 64-row groups alternating w1, w3 (F % 64 == 0)."""
     F_, K = w1.shape

@@ -103,21 +103,6 @@ typedef struct echo_gemm_desc {
 int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream);
 long long echo_gemm_workspace_bytes(void);
 
-/* The MLP of a transformer block (reference MLP.forward model.py:296-308 followed by the gated residual add of
- * TransformerBlock.forward model.py:388) as ONE persistent launch of the CTA-pair kernel (csrc/gemm_chain.cuh):
- * `up` is the ECHO_EPI_SWIGLU GEMM, `down` an ECHO_EPI_GENERIC GEMM in its lean form (fp32 output; residual absent or
- * updated in place; k_splits allowed) whose A operand is up->out_bf16.  The down-projection of a 256-row block starts as
- * soon as that block of the intermediate is complete, so the pipeline of the kernel never drains between the two GEMMs.
- * Results are bit-identical to echo_gemm_bf16(up) followed by echo_gemm_bf16(down).
- * Requirements: batch 1, one tap, n a multiple of 256 and k a multiple of 64 in both, b_static weights, rows <= 16384.
- * `sync`: echo_gemm_chain_sync_bytes() bytes of device memory, zeroed once by the caller; the kernel leaves them zero.
- * Launches that share `sync` must be stream-ordered, and the kernel assumes its (at most one per SM) CTAs become
- * resident without waiting for another chain launch -- do not run two of them concurrently on one device.
- * Returns ECHO_ERR_UNSUPPORTED (nothing launched) when the descriptors do not fit. */
-int echo_gemm_chain_bf16(const echo_gemm_desc* up, const echo_gemm_desc* down, void* sync, int64_t sync_bytes,
-                         echo_stream_t stream);
-long long echo_gemm_chain_sync_bytes(void);
-
 /* NO COUNTERPART IN THE REFERENCE.  Allocation-free split-K GEMM for
  * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it):
  * echo_gemm_bf16 in its split-K form (d->k_splits >= 2, GENERIC epilogue, no activation, fp32 output) with the partial
@@ -338,8 +323,6 @@ typedef struct echo_dit_step_desc {
   const echo_tail_desc* tail;   /* nullable; h, ldh, delta, n_delta, delta_stride are filled in by the library */
   int32_t* pending_out;     /* HOST, nullable: set to 1 when tail == NULL and `delta` still has to be added to x */
   void* attn_workspace; int64_t attn_workspace_bytes; /* as echo_attn_desc.workspace (split-KV); NULL = never split */
-  void* chain_sync; int64_t chain_sync_bytes; /* as echo_gemm_chain_bf16's sync: non-NULL lets every layer's MLP run as one
-                                               * chained launch when its shapes fit (gemm_impl 0 / 2); NULL = two launches */
 } echo_dit_step_desc;
 int echo_dit_step(const echo_dit_step_desc* d, echo_stream_t stream);
 

@@ -287,53 +287,3 @@ def test_gemm_narrow_tail_with_batches_and_taps(ops):
     xin = torch.nn.functional.pad(x.float().transpose(1, 2), (6 * dil, 0))
     ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil).transpose(1, 2).reshape(B * T, N)
     assert rel_l2(outs["1"], ref) < 2e-5
-
-
-# ---- chained MLP: SwiGLU up-projection + gated down-projection as one persistent launch (gemm_chain.cuh) ---------------
-@pytest.mark.parametrize("M,D,F_,S,splits", [(1920, 2048, 5888, 640, 1), (640, 2048, 5888, 640, 3), (160, 2048, 5888, 160, 8),
-                                             (480, 2048, 5888, 160, 4), (300, 256, 384, 100, 1), (300, 256, 384, 100, 2),
-                                             (2000, 512, 1024, 500, 1)])
-def test_gemm_mlp_chain_bit_identical_to_two_launches(ops, M, D, F_, S, splits):
-    """One launch walks all SwiGLU tiles and then all down-projection units; a down-projection unit starts when its
-    256-row block of the intermediate is complete (per-row-block counters, self-resetting).  Same tiles, k order and
-    split boundaries as the two-launch form -> identical bits, for the in-place gated residual and for split-K
-    partials, on repeated launches (counters back at zero), and equal to the fp32 reference."""
-    a = _rand((M, D), 81, dtype=BF16)
-    w1, w3 = _rand((F_, D), 82, D ** -0.5, BF16), _rand((F_, D), 83, D ** -0.5, BF16)
-    w13 = ops.pack_w13(w1, w3)
-    w2 = _rand((D, F_), 84, F_ ** -0.5, BF16)
-    gate = _rand((-(-M // S), D), 85)
-    x0 = _rand((M, D), 86)
-    h_ref = torch.empty((M, F_), device="cuda", dtype=BF16)
-    ops.gemm_swiglu(a, w13, h_ref, impl=2)
-    if splits > 1:
-        ref = torch.empty((splits, M, D), device="cuda")
-        ops.gemm_generic(h_ref, w2, gate=gate, rows_per_gate=S, split_out=ref, impl=2)
-    else:
-        ref = x0.clone()
-        ops.gemm_generic(h_ref, w2, gate=gate, rows_per_gate=S, resid=ref, out_f32=ref, impl=2)
-    for rep in range(3):
-        h = torch.full((M, F_), float("nan"), device="cuda", dtype=BF16)
-        if splits > 1:
-            out = torch.full((splits, M, D), float("nan"), device="cuda")
-            ops.gemm_mlp_chain(a, w13, h, w2, gate=gate, rows_per_gate=S, split_out=out)
-        else:
-            out = x0.clone()
-            ops.gemm_mlp_chain(a, w13, h, w2, gate=gate, rows_per_gate=S, x=out)
-        assert torch.equal(h, h_ref), rep
-        assert torch.equal(out, ref), rep
-    assert int(ops.chain_sync(a.device).view(torch.int32).abs().sum()) == 0          # counters reset themselves
-    hf = torch.nn.functional.silu(a.float() @ w1.float().t()) * (a.float() @ w3.float().t())
-    y = (hf.to(BF16).float() @ w2.float().t()) * gate[torch.arange(M, device="cuda") // S]
-    got = out.sum(0) if splits > 1 else out - x0
-    assert rel_l2(got, y) < 5e-3
-
-
-def test_gemm_mlp_chain_rejects_shapes_it_cannot_tile(ops):
-    a = _rand((128, 192), 87, dtype=BF16)
-    w13 = _rand((384, 192), 88, dtype=BF16)          # n = 384 is not a multiple of 256
-    h = torch.empty((128, 192), device="cuda", dtype=BF16)
-    w2 = _rand((256, 192), 89, dtype=BF16)
-    x = torch.zeros((128, 256), device="cuda")
-    with pytest.raises(RuntimeError, match="gemm chain"):
-        ops.gemm_mlp_chain(a, w13, h, w2, x=x)

@@ -116,37 +116,6 @@ def main():
             else:
                 f_w2(i)
 
-        def f_mlp2(i):     # the MLP as two launches
-            f_w13(i)
-            if ns > 1:
-                f_w2_split_h(i)
-            else:
-                f_w2_h(i)
-
-        def f_w2_h(i):
-            ops.gemm_generic(hmid, W["w2"][i % nw], gate=gate, rows_per_gate=S, resid=x, out_f32=x)
-
-        def f_w2_split_h(i):
-            ops.gemm_generic(hmid, W["w2"][i % nw], gate=gate, rows_per_gate=S, split_out=parts[:ns_w2])
-
-        def f_chain(i):    # the MLP as one chained launch (csrc/gemm_chain.cuh)
-            if ns > 1:
-                ops.gemm_mlp_chain(xn, W["w13"][i % nw], hmid, W["w2"][i % nw], gate=gate, rows_per_gate=S, split_out=parts[:ns_w2])
-            else:
-                ops.gemm_mlp_chain(xn, W["w13"][i % nw], hmid, W["w2"][i % nw], gate=gate, rows_per_gate=S, x=x)
-
-        def f_seqc(i):     # f_seq with the chained MLP
-            if ns > 1:
-                f_addnorm2(i)
-            else:
-                f_norm(i)
-            f_qkvg(i); f_attn(i)
-            if ns > 1:
-                f_wo_split(i); f_addnorm(i)
-            else:
-                f_wo(i); f_norm(i)
-            f_chain(i)
-
         def f_seq2(i):     # the same launches, each kernel twice in a row (2 layers' worth): isolates per-kernel cold-start cost
             for f in ([f_norm, f_qkvg, f_attn] + ([f_wo_split, f_addnorm] if ns > 1 else [f_wo, f_norm]) + [f_w13] +
                       ([f_w2_split] if ns > 1 else [f_w2])):
@@ -158,7 +127,6 @@ def main():
                  ("w2", f_w2, 2.0 * M * D * F_), ("attn", f_attn, sum(4.0 * S * lv * D for lv in valid)),
                  ("norm", f_norm, 0.0)]
         cases += [("seq", f_seq, 0.0), ("seq2", f_seq2, 0.0)]
-        cases += [("mlp2", f_mlp2, 2.0 * M * 3 * F_ * D), ("chain", f_chain, 2.0 * M * 3 * F_ * D), ("seqc", f_seqc, 0.0)]
         if ns > 1:
             cases += [(f"wo/s{ns_wo}", f_wo_split, 2.0 * M * D * D), (f"w2/s{ns_w2}", f_w2_split, 2.0 * M * D * F_),
                       ("addnorm", f_addnorm, 0.0)]
@@ -189,7 +157,7 @@ def main():
                 e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / n
-            if name not in ("seq", "seq2", "mlp2", "chain", "seqc"):
+            if name not in ("seq", "seq2"):
                 tot_us += us; tot_fl += fl
             extra = f"{fl / us / 1e6:8.1f} TFLOP/s" if fl else f"{M * D * 6 / us / 1e3:8.1f} GB/s"
             print(f"M={M:5d} {name:5s} {us:8.2f} us  {extra}", flush=True)
