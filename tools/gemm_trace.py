@@ -45,6 +45,18 @@ def main():
         w2=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, resid=x, out_f32=x),
         wo_split=lambda: ops.gemm_generic(xn, W["wo"], gate=gate, rows_per_gate=S, split_out=parts),
         w2_split=lambda: ops.gemm_generic(hm, W["w2"], gate=gate, rows_per_gate=S, split_out=parts))
+    # S1-DAC ResidualUnit launches at the decoder's C = 192 stage (6 tiles per CTA pair): --case ae_k7,ae_k1,ae_k1_bf16
+    Ta, Ca = 74 * 6 * 256, 192
+    if "ae_" in args.case:
+        s1a = rnd(Ta, Ca).to(BF16)
+        w7a, w1a = rnd(Ca, 7 * Ca, sc=(7 * Ca) ** -0.5).to(BF16), rnd(Ca, Ca, sc=Ca ** -0.5).to(BF16)
+        ba, ala, xa = rnd(Ca), rnd(Ca).abs() + 0.5, rnd(Ta, Ca)
+        s2a, s3a = torch.empty((Ta, Ca), device="cuda", dtype=BF16), torch.empty((Ta, Ca), device="cuda", dtype=BF16)
+        xoa = torch.empty((Ta, Ca), device="cuda")
+        fns.update(
+            ae_k7=lambda: ops.gemm_generic(s1a, w7a, taps=tuple(-(6 - k) * 9 for k in range(7)), bias=ba, out2_bf16=s2a, snake_alpha=ala),
+            ae_k1=lambda: ops.gemm_generic(s2a, w1a, bias=ba, resid=xa, out_f32=xoa, out2_bf16=s3a, snake_alpha=ala),
+            ae_k1_bf16=lambda: ops.gemm_generic(s2a, w1a, bias=ba, out_bf16=s3a))
     parts = torch.empty((3, M, D), device="cuda")
     buf = torch.zeros((512, 32), device="cuda", dtype=torch.int64)
     for name in args.case.split(","):
