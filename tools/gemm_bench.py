@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--quick", action="store_true", help="1 rep, 1 weight set (for ncu)")
     ap.add_argument("--splits-wo", type=int, default=0, help="split-K units per tile of wo (0 = the model's choice)")
     ap.add_argument("--splits-w2", type=int, default=0, help="split-K units per tile of w2 (0 = the model's choice)")
+    ap.add_argument("--drop", default="", help="comma list of launches left out of `seq` (norm1,qkvg,attn,wo,norm2,w13,w2): the "
+                    "marginal cost of a kernel inside the layer sequence")
     args = ap.parse_args()
     from echo_tts_b200 import ops, _lib as L
     D, F_, H = 2048, 5888, 16
@@ -100,21 +102,23 @@ def main():
         def f_norm(i):
             ops.rmsnorm_mod(x, gate[0], gate[0], xn, 1e-5, S, gate.stride(0))
 
+        drop = set(args.drop.split(",")) if args.drop else set()
+
         def f_seq(i):      # one decoder layer in launch order: cross-kernel effects (instruction cache, L2 state, PDL hand-offs)
-            if ns > 1:
-                f_addnorm2(i)
-            else:
-                f_norm(i)
-            f_qkvg(i); f_attn(i)
-            if ns > 1:
-                f_wo_split(i); f_addnorm(i)
-            else:
-                f_wo(i); f_norm(i)
-            f_w13(i)
-            if ns > 1:
-                f_w2_split(i)
-            else:
-                f_w2(i)
+            if "norm1" not in drop:
+                f_addnorm2(i) if ns > 1 else f_norm(i)
+            if "qkvg" not in drop:
+                f_qkvg(i)
+            if "attn" not in drop:
+                f_attn(i)
+            if "wo" not in drop:
+                f_wo_split(i) if ns > 1 else f_wo(i)
+            if "norm2" not in drop:
+                f_addnorm(i) if ns > 1 else f_norm(i)
+            if "w13" not in drop:
+                f_w13(i)
+            if "w2" not in drop:
+                f_w2_split(i) if ns > 1 else f_w2(i)
 
         def f_seq2(i):     # the same launches, each kernel twice in a row (2 layers' worth): isolates per-kernel cold-start cost
             for f in ([f_norm, f_qkvg, f_attn] + ([f_wo_split, f_addnorm] if ns > 1 else [f_wo, f_norm]) + [f_w13] +
