@@ -26,7 +26,12 @@ static PFN_encodeTiled get_encode() {
 }
 
 static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
-                     const cuuint64_t* strides_b, const cuuint32_t* box);
+                     const cuuint64_t* strides_b, const cuuint32_t* box, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B);
+// bf16 output tiles of the row epilogue (box rows of 32 elements = 64 B, staged unswizzled)
+int echo_make_tmap_bf16_linear(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                               const cuuint32_t* box) {
+  return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, dims, strides_b, box, CU_TENSOR_MAP_SWIZZLE_NONE);
+}
 int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                         const cuuint32_t* box) {
   return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, dims, strides_b, box);
@@ -37,19 +42,19 @@ int echo_make_tmap_f32(CUtensorMap* m, const void* base, int rank, const cuuint6
   return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_b, box);
 }
 static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
-                     const cuuint64_t* strides_b, const cuuint32_t* box) {
+                     const cuuint64_t* strides_b, const cuuint32_t* box, CUtensorMapSwizzle swz) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { echo_set_error("cuTensorMapEncodeTiled entry point unavailable"); return ECHO_ERR_CUDA; }
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(m, dt, rank, const_cast<void*>(base), dims, strides_b, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { echo_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return ECHO_ERR_CUDA; }
   return ECHO_OK;
 }
 
 int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, void* workspace, long long workspace_bytes,
-                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st, int sched_flags);  // gemm2.cu; bit 0 stream-K allowed, bit 1 no narrow last round
+                          const GemmShape& G, const EpiParams& P, int batch, cudaStream_t st, int sched_flags);  // gemm2.cu; bit 0 stream-K allowed, bit 1 no narrow last round, bit 2 no row epilogue
 
 static int fill_params(const echo_gemm_desc* d, GemmShape& G, EpiParams& P) {
   ECHO_CHECK_ARG(d && d->a && d->b, "gemm: null operand");
@@ -164,8 +169,8 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
   int rc = fill_params(d, G, P);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  ECHO_CHECK_ARG(d->impl == 0 || (d->impl >= 2 && d->impl <= 4),
-                 "gemm: impl %d: only the CTA-pair tcgen05 kernel exists (0 / 2; 3 = stream-K schedule allowed; 4 = plain schedule without the narrow last round)", d->impl);
+  ECHO_CHECK_ARG(d->impl == 0 || (d->impl >= 2 && d->impl <= 5),
+                 "gemm: impl %d: only the CTA-pair tcgen05 kernel exists (0 / 2; 3 = stream-K schedule allowed; 4 = plain schedule without the narrow last round; 5 = transposing GENERIC epilogue instead of the row / TMA one)", d->impl);
   const int bn = pick_block_n_pair(d);
   ECHO_CHECK_ARG(bn > 0, "pair gemm: no tile width fits epilogue %d (n=%d)", d->epilogue, d->n);
   if (d->epilogue == ECHO_EPI_SECTIONS)
@@ -175,5 +180,5 @@ extern "C" int echo_gemm_bf16(const echo_gemm_desc* d, echo_stream_t stream) {
     ECHO_CHECK_ARG(d->epilogue == ECHO_EPI_GENERIC && d->act == ECHO_ACT_NONE && !d->resid && d->out_f32 && !d->out_bf16 &&
                    !d->out2_bf16 && d->split_stride % 4 == 0, "gemm: k_splits needs GENERIC, no act/resid, fp32 output only");
   return echo_launch_gemm_pair(d->epilogue, bn, d->k_splits, d->split_stride, d->workspace, d->workspace_bytes, G, P,
-                               d->batch, st, (d->impl == 3 ? 1 : 0) | (d->impl == 4 ? 2 : 0));
+                               d->batch, st, (d->impl == 3 ? 1 : 0) | (d->impl == 4 ? 2 : 0) | (d->impl == 5 ? 4 : 0));
 }

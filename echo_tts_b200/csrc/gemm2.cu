@@ -83,6 +83,9 @@ struct Tiling {
   int tail_start;         // >= 0: units from this index on are HALF-width tiles, two per wide tile (the ragged last round
                           // of a launch runs as one round of narrow tiles: shorter main loop and exposed epilogue); -1 off
   int gate_sm;            // 1: LEAN epilogue reads the gate row from shared memory (0: shuffles; A/B switch ECHO_GEMM_GATESM)
+  int row_off;            // EPI_GENERIC_ROW: byte offset (from the aligned shared-memory base, inside the ring area behind the
+                          // stages in use) of its staging: [residual ping-pong 8 x 2 x 4 KB when a residual is read] |
+                          // bf16 chunks 8 x 2 KB | bias / alpha / 1/alpha rows 3 x 1 KB | 16 mbarriers
   int split_b;            // 1: warp B_PRODUCER_WARP issues the B-operand loads, warp 0 the A-operand loads (two issue streams)
   int stream_k;           // 1: contiguous k-block ranges per pair (num_tiles = plain tile count, splits = 1)
   int* sk_flags;          // [pairs][2 CTAs][EPI_WARPS] 0/1, self-resetting
@@ -253,6 +256,7 @@ template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_bn, const __grid_constant__ CUtensorMap tmap_out,
+                 const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_ob,
                  const __grid_constant__ GemmShape G, const __grid_constant__ EpiParams P, const __grid_constant__ Tiling T) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -286,7 +290,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     ptx::prefetch_tensormap(&tmap_a);
     ptx::prefetch_tensormap(&tmap_b);
     if (T.tail_start >= 0) ptx::prefetch_tensormap(&tmap_bn);
-    if (EPI == EPI_GENERIC_LEAN) ptx::prefetch_tensormap(&tmap_out);
+    if (EPI == EPI_GENERIC_LEAN || EPI == EPI_GENERIC_ROW) ptx::prefetch_tensormap(&tmap_out);
+    if (EPI == EPI_GENERIC_ROW) { ptx::prefetch_tensormap(&tmap_res); ptx::prefetch_tensormap(&tmap_ob); }
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full_bar[s], 1);        // leader's producer: arrive.expect_tx (both CTAs' bytes)
       ptx::mbar_init(&empty_bar[s], 1);       // tcgen05.commit multicast to both CTAs
@@ -411,6 +416,26 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::peer0_addr(&tmem_empty_bar[as]));
     };
+    RowStage RS;
+    if constexpr (EPI == EPI_GENERIC_ROW) {
+      uint8_t* base = smem + T.row_off;
+      const bool has_res = P.resid != nullptr;
+      uint8_t* after_res = base + (has_res ? EPI_WARPS * 2 * 4096 : 0);
+      RS.out = scratch + ew * EPI_SC_FLOATS;
+      RS.res[0] = reinterpret_cast<float*>(base + ew * 8192);
+      RS.res[1] = RS.res[0] + 1024;
+      RS.outb = reinterpret_cast<uint32_t*>(after_res + ew * 2048);
+      RS.rows = reinterpret_cast<const float*>(after_res + EPI_WARPS * 2048);
+      RS.res_bar = reinterpret_cast<uint64_t*>(after_res + EPI_WARPS * 2048 + 3 * ACC_COLS * 4) + 2 * ew;
+      RS.res_phase = 0;
+      RS.ld_rows = ACC_COLS;
+      if (lane == 0) {
+        ptx::mbar_init(&RS.res_bar[0], 1);
+        ptx::mbar_init(&RS.res_bar[1], 1);
+        ptx::fence_barrier_init();
+      }
+      __syncwarp();
+    }
     // The stream-K special cases are peeled off the steady-state loop (first unit = dump, last unit = head) so that
     // their register needs do not lengthen live ranges inside it.
     if (have && T.stream_k && w.kb0 > 0) {
@@ -451,6 +476,21 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           gsm = gate_sm;
         }
       }
+      if constexpr (EPI == EPI_GENERIC_ROW) {
+        // the tile's bias / Snake vectors as shared-memory rows (broadcast reads in the row-per-thread layout).  Barrier in
+        // front: the previous tile's readers are done; barrier behind: the rows are complete.
+        float* rows = const_cast<float*>(RS.rows);
+        asm volatile("bar.sync 3, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+        const int col = ew * 32 + lane, n = nc0 + col;
+        const bool ok = col < bn_u && n < P.n;
+        rows[col] = (ok && P.bias) ? __ldg(P.bias + n) : 0.f;
+        if (P.out2_bf16) {
+          const float al = ok ? __ldg(P.snake_alpha + n) : 1.f;
+          rows[ACC_COLS + col] = al;
+          rows[2 * ACC_COLS + col] = __fdividef(1.f, al + 1e-9f);
+        }
+        asm volatile("bar.sync 3, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+      }
       ptx::mbar_wait(&tmem_full_bar[as], aph);
       ptx::tc_fence_after();
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 2] = clock64();
@@ -467,8 +507,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           stage_stride = EPI_SC_FLOATS;
         }
       }
-      run_epilogue_t<EPI>(bn_u, P, L, stage, lane, half, batch, m0 + q * 32, nc0, pre, &tmap_out, split,
-                          split * T.split_stride, stage_stride, gsm);
+      if constexpr (EPI == EPI_GENERIC_ROW) {
+        const EpiRows R = epi_rows(P, half, batch, m0 + q * 32, nc0, 0, 0);
+        epi_t_row(bn_u, P, L, lane, R, RS, &tmap_out, &tmap_res, &tmap_ob);
+      } else {
+        run_epilogue_t<EPI>(bn_u, P, L, stage, lane, half, batch, m0 + q * 32, nc0, pre, &tmap_out, split,
+                            split * T.split_stride, stage_stride, gsm);
+      }
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
@@ -494,8 +539,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       TmemLoader2 L{tacc};
       EpiPre<EPI> pre;
       epilogue_prefetch_t<EPI>(T.bn, P, lane, half, batch, m0 + q * 32, nt * T.bn, pre);
-      run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre,
-                          &tmap_out, 0, 0);
+      if constexpr (EPI != EPI_GENERIC_ROW)     // (the row epilogue is never scheduled stream-K)
+        run_epilogue_t<EPI>(T.bn, P, L, scratch + ew * EPI_SC_FLOATS, lane, half, batch, m0 + q * 32, nt * T.bn, pre,
+                            &tmap_out, 0, 0);
       release_acc(as);
       if (trace && tc < 6 && warp == 2 && lane == 0) trace[8 + tc * 4 + 3] = clock64();
     }
@@ -514,6 +560,12 @@ int getenv_int(const char* name, int dflt) {
 // scheduler switches (A/B measurements), read ONCE per process -- not per launch
 int use_narrow_tail() { static const int v = getenv_int("ECHO_GEMM_TAIL", 1); return v; }
 int use_gate_sm() { static const int v = getenv_int("ECHO_GEMM_GATESM", 1); return v; }
+int use_row_epilogue() { static const int v = getenv_int("ECHO_GEMM_ROWEPI", 1); return v; }
+bool row_epilogue_aligned(const EpiParams& P) {
+  auto al16 = [](const void* p) { return ((uintptr_t)p % 16) == 0; };
+  return al16(P.out_f32) && al16(P.resid) && al16(P.out_bf16) && al16(P.out2_bf16) && P.ld_out_f32 % 4 == 0 &&
+         P.ld_resid % 4 == 0 && P.ld_out_bf16 % 8 == 0 && P.ld_out2_bf16 % 8 == 0;
+}
 int use_split_b() { static const int v = getenv_int("ECHO_GEMM_SPLITB", 1); return v; }
 int max_stages() { static const int v = getenv_int("ECHO_GEMM_STAGES", MAX_STAGES); return v < 2 ? 2 : v; }
 int num_sms() {
@@ -532,6 +584,8 @@ int echo_make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint
                         const cuuint32_t* box);   // gemm.cu
 int echo_make_tmap_f32(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
                        const cuuint32_t* box);    // gemm.cu
+int echo_make_tmap_bf16_linear(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                               const cuuint32_t* box);   // gemm.cu
 
 // Bytes of the optional stream-K workspace (echo_gemm_desc.workspace): flags + one partial accumulator per CTA pair.
 // The caller zeroes it once after allocation and must not share it between streams that run GEMMs concurrently.
@@ -588,6 +642,29 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
     int rc = echo_make_tmap_f32(&tout, P.out_f32, 4, dims, str, box);
     if (rc) return rc;
   }
+  CUtensorMap tres = ta, tob = ta;              // row epilogue: residual (fp32, loaded) and bf16 output (stored) tiles
+  if (EPI == EPI_GENERIC_ROW) {
+    cuuint32_t box[4] = {32, 32, 1, 1};
+    if (P.out_f32) {
+      const long long ld = P.ld_out_f32;
+      cuuint64_t dims[4] = {(cuuint64_t)G.n, (cuuint64_t)G.rows, (cuuint64_t)batch, 1};
+      cuuint64_t str[3] = {(cuuint64_t)ld * 4, (cuuint64_t)G.rows * ld * 4, (cuuint64_t)G.rows * ld * batch * 4};
+      if (int rc = echo_make_tmap_f32(&tout, P.out_f32, 4, dims, str, box)) return rc;
+    }
+    if (P.resid) {
+      const long long ld = P.ld_resid;
+      cuuint64_t dims[4] = {(cuuint64_t)G.n, (cuuint64_t)G.rows, (cuuint64_t)batch, 1};
+      cuuint64_t str[3] = {(cuuint64_t)ld * 4, (cuuint64_t)G.rows * ld * 4, (cuuint64_t)G.rows * ld * batch * 4};
+      if (int rc = echo_make_tmap_f32(&tres, P.resid, 4, dims, str, box)) return rc;
+    }
+    if (P.out2_bf16 || P.out_bf16) {
+      const bf16* ob = P.out2_bf16 ? P.out2_bf16 : P.out_bf16;
+      const long long ld = P.out2_bf16 ? P.ld_out2_bf16 : P.ld_out_bf16;
+      cuuint64_t dims[4] = {(cuuint64_t)G.n, (cuuint64_t)G.rows, (cuuint64_t)batch, 1};
+      cuuint64_t str[3] = {(cuuint64_t)ld * 2, (cuuint64_t)G.rows * ld * 2, (cuuint64_t)G.rows * ld * batch * 2};
+      if (int rc = echo_make_tmap_bf16_linear(&tob, ob, 4, dims, str, box)) return rc;
+    }
+  }
   {   // the attribute is per device: a process that drives several GPUs sets it once on each
     static bool attr_set[64] = {};
     int dev = 0;
@@ -609,6 +686,17 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
   T.stage_bytes = A_BYTES + (bn / 2) * BK * 2;
   T.stages = RING_BYTES / T.stage_bytes < MAX_STAGES ? RING_BYTES / T.stage_bytes : MAX_STAGES;
   if (T.stages > max_stages()) T.stages = max_stages();
+  T.row_off = 0;
+  if (EPI == EPI_GENERIC_ROW) {                 // its staging lives in the ring area, behind the stages in use
+    const int extra = (P.resid ? EPI_WARPS * 2 * 4096 : 0) + EPI_WARPS * 2048 + 3 * ACC_COLS * 4 + 2 * EPI_WARPS * 8;
+    const int fit = (RING_BYTES - extra) / T.stage_bytes;
+    if (T.stages > fit) T.stages = fit;
+    T.row_off = (T.stages * T.stage_bytes + 1023) & ~1023;
+    if (T.stages < 2 || T.row_off + extra > RING_BYTES) {
+      echo_set_error("pair gemm: row epilogue staging does not fit (block_n %d)", bn);
+      return ECHO_ERR_UNSUPPORTED;
+    }
+  }
   T.tiles_m = ceil_div(G.rows, 2 * BM);
   T.tiles_n = ceil_div(G.n, bn);
   T.fd_m = make_fastdiv(T.tiles_m); T.fd_n = make_fastdiv(T.tiles_n); T.fd_s = make_fastdiv(splits);
@@ -632,7 +720,7 @@ static int launch_pair_t(int bn, int splits, long long split_stride, void* works
       pairs = P2;
     }
   }
-  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, tbn, tout, G, P, T));
+  ECHO_CUDA(echo_launch(gemm_pair_kernel<EPI>, dim3(2 * pairs), dim3(NTHREADS), SMEM2, st, ta, tb, tbn, tout, tres, tob, G, P, T));
   ECHO_COUNT_LAUNCH();
   ECHO_LAUNCH_CHECK();
   return ECHO_OK;
@@ -681,6 +769,12 @@ int echo_launch_gemm_pair(int epi, int bn, int splits, long long split_stride, v
       // LEAN (TMA epilogue): fp32 output only, residual absent or updated in place
       if (P.act == ECHO_ACT_NONE && !P.out_bf16 && !P.out2_bf16 && P.out_f32 && (P.red_resid || !P.resid))
         return launch_pair_t<EPI_GENERIC_LEAN>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st, sched_flags);
+      // ROW (TMA in and out, row per thread): bias [+ residual that is read] -> fp32 and / or one bf16 output (plain or
+      // Snake) -- the S1-DAC convolutions; needs TMA-legal bases and pitches
+      if (use_row_epilogue() && splits == 1 && P.act == ECHO_ACT_NONE && !P.gate && !P.red_resid &&
+          !(P.out_bf16 && P.out2_bf16) && (P.out_f32 || P.out_bf16 || P.out2_bf16) && !(sched_flags & 5) &&
+          row_epilogue_aligned(P))
+        return launch_pair_t<EPI_GENERIC_ROW>(bn, 1, 0, nullptr, 0, G, P, batch, st, sched_flags);
       return launch_pair_t<ECHO_EPI_GENERIC>(bn, splits, split_stride, workspace, workspace_bytes, G, P, batch, st, sched_flags);
     case ECHO_EPI_SECTIONS: return launch_pair_t<ECHO_EPI_SECTIONS>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);
     default: return launch_pair_t<ECHO_EPI_SWIGLU>(bn, 1, 0, workspace, workspace_bytes, G, P, batch, st, sched_flags);

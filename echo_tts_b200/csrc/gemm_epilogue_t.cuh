@@ -552,6 +552,135 @@ __device__ __forceinline__ void epi_t_lean_tma(const int BN, const EpiParams& P,
   EPI_STAMP(17);
 }
 
+// ---- GENERIC, row per thread, all traffic through TMA (the S1-DAC convolutions) ----------------------------------------
+// v = acc + bias [+ resid];  out_f32 <- v;  bf16 out <- snake(v) (out2_bf16) or v (out_bf16).  The transposing GENERIC
+// epilogue above spends ~5 k clocks per 32-column chunk on the k = 1 residual-unit convolutions (per-lane address
+// arithmetic with spilled bases, two shared-memory passes, 24 predicated global accesses per lane), which makes those
+// launches epilogue-bound at 60 % of the HBM rate.  Here the chunk stays in the TMEM layout (lane = row): the residual
+// block arrives as a TMA load into a ping-pong buffer two chunks ahead, bias / Snake vectors are broadcast reads of a
+// per-tile shared-memory row, and both outputs leave as bulk tensor stores (clipped by the tensor maps at the ends).
+constexpr int EPI_GENERIC_ROW = 4;
+struct RowStage {
+  float* out;            // 4 KB  fp32 chunk, SWIZZLE_128B rows (this warp's slot of the transpose scratch)
+  float* res[2];         // 2 x 4 KB residual chunks (TMA destinations)
+  uint64_t* res_bar;     // [2]
+  uint32_t* outb;        // 2 KB  bf16 chunk, linear 64-byte rows
+  const float* rows;     // [3][ACC_COLS]: bias | alpha | 1 / (alpha + 1e-9) of the tile's columns
+  uint32_t res_phase;    // bit b: parity res_bar[b] completes next
+  int ld_rows;           // floats between the three rows
+};
+__device__ __forceinline__ void tma_load_res_4d(void* dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(0)
+      : "memory");
+}
+__device__ __forceinline__ void tma_wait_read_1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+template <class Loader>
+__device__ __forceinline__ void epi_t_row(const int BN, const EpiParams& P, Loader& L, int lane, const EpiRows& R, RowStage& S,
+                                          const void* tmap_out, const void* tmap_res, const void* tmap_ob) {
+  if (R.nrows <= 0) return;                                // warp-uniform
+  const int cend = min(BN, P.n - R.n0);
+  const bool has_res = P.resid != nullptr, has_f32 = P.out_f32 != nullptr, snake = P.out2_bf16 != nullptr;
+  const bool has_b = snake || P.out_bf16 != nullptr;
+  const bool both = has_f32 && has_b;
+  const int c_first = R.half * 32;
+  if (has_res && lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int cc = c_first + 64 * k;
+      if (cc < cend) {
+        ptx::mbar_arrive_expect_tx(&S.res_bar[k], 32 * 32 * 4);
+        tma_load_res_4d(S.res[k], tmap_res, &S.res_bar[k], R.n0 + cc, R.mb0, R.batch_idx);
+      }
+    }
+  }
+  const uint32_t out_row = smem_u32(S.out) + (uint32_t)lane * 128u;
+  const uint32_t outb_row = smem_u32(S.outb) + (uint32_t)lane * 64u;
+  bool pend_f = false, pend_b = false;
+  int i = 0;
+#pragma unroll 1
+  for (int c = c_first; c < cend; c += 64, ++i) {
+    const int b = i & 1;
+    float v[32];
+    L.load32(c, v);
+    const uint32_t rows_addr = smem_u32(S.rows + c);
+    // v = acc + (bias + resid): the association of the transposing epilogue, so both forms give the same bits
+    if (has_res) {
+      ptx::mbar_wait(&S.res_bar[b], (S.res_phase >> b) & 1u);
+      S.res_phase ^= 1u << b;
+      const uint32_t ra = smem_u32(S.res[b]) + (uint32_t)lane * 128u;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float4 g, bs = make_float4(0.f, 0.f, 0.f, 0.f);
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w)
+                     : "r"(ra + (uint32_t)((k ^ (lane & 7)) << 4)) : "memory");
+        if (P.bias)
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(bs.x), "=f"(bs.y), "=f"(bs.z), "=f"(bs.w) : "r"(rows_addr + 16u * k));
+        v[4 * k] += bs.x + g.x; v[4 * k + 1] += bs.y + g.y; v[4 * k + 2] += bs.z + g.z; v[4 * k + 3] += bs.w + g.w;
+      }
+      __syncwarp();                                        // every lane has read the buffer: refill it two chunks ahead
+      if (lane == 0 && c + 128 < cend) {
+        ptx::mbar_arrive_expect_tx(&S.res_bar[b], 32 * 32 * 4);
+        tma_load_res_4d(S.res[b], tmap_res, &S.res_bar[b], R.n0 + c + 128, R.mb0, R.batch_idx);
+      }
+    }
+    else if (P.bias) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float4 g;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(rows_addr + 16u * k));
+        v[4 * k] += g.x; v[4 * k + 1] += g.y; v[4 * k + 2] += g.z; v[4 * k + 3] += g.w;
+      }
+    }
+    if (has_f32) {
+      if (pend_f) {                                        // the previous fp32 chunk has left the staging slot
+        if (lane == 0) { if (both) tma_wait_read_1(); else tma_out_wait_read(); }
+        __syncwarp();
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(out_row + (uint32_t)((k ^ (lane & 7)) << 4)),
+                     "f"(v[4 * k]), "f"(v[4 * k + 1]), "f"(v[4 * k + 2]), "f"(v[4 * k + 3]) : "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) tma_out_4d(tmap_out, S.out, false, R.n0 + c, R.mb0, R.batch_idx, 0);
+      pend_f = true;
+    }
+    if (has_b) {
+      if (snake) {                                         // x + sin^2(alpha x) / alpha (autoencoder.py:31-41)
+        const uint32_t al = rows_addr + (uint32_t)S.ld_rows * 4u, ia = rows_addr + (uint32_t)S.ld_rows * 8u;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float4 a, r;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(al + 16u * k));
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(ia + 16u * k));
+          float s0 = __sinf(a.x * v[4 * k]), s1 = __sinf(a.y * v[4 * k + 1]), s2 = __sinf(a.z * v[4 * k + 2]), s3 = __sinf(a.w * v[4 * k + 3]);
+          v[4 * k] = fmaf(s0 * s0, r.x, v[4 * k]); v[4 * k + 1] = fmaf(s1 * s1, r.y, v[4 * k + 1]);
+          v[4 * k + 2] = fmaf(s2 * s2, r.z, v[4 * k + 2]); v[4 * k + 3] = fmaf(s3 * s3, r.w, v[4 * k + 3]);
+        }
+      }
+      if (pend_b) {
+        if (lane == 0) { if (both) tma_wait_read_1(); else tma_out_wait_read(); }
+        __syncwarp();
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(outb_row + 16u * k),
+                     "r"(pack_bf16x2(v[8 * k], v[8 * k + 1])), "r"(pack_bf16x2(v[8 * k + 2], v[8 * k + 3])),
+                     "r"(pack_bf16x2(v[8 * k + 4], v[8 * k + 5])), "r"(pack_bf16x2(v[8 * k + 6], v[8 * k + 7])) : "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) tma_out_4d(tmap_ob, S.outb, false, R.n0 + c, R.mb0, R.batch_idx, 0);
+      pend_b = true;
+    }
+  }
+  if (pend_f || pend_b) {
+    if (lane == 0) tma_out_wait_read();
+    __syncwarp();
+  }
+}
+
 // What an epilogue can fetch before its accumulator exists (kept in registers across the wait for the MMAs).
 template <int EPI> struct EpiPre {};
 template <> struct EpiPre<ECHO_EPI_GENERIC> { GenAux a; };

@@ -52,7 +52,9 @@ typedef struct echo_gemm_desc {
   int32_t impl;             /* 0 or 2: the CTA-pair tcgen05 kernel (the only GEMM kernel); 3: the same, and the library may
                              * schedule ragged launches stream-K through `workspace`; 4: the same with the plain tile
                              * schedule (no half-width last round; results are bit-identical to 2, kept for A/B and
-                             * the tests); anything else is refused */
+                             * the tests); 5: the same with the transposing GENERIC epilogue where 2 would take the row-per-thread
+                             * TMA epilogue (bias [+ residual] -> fp32 / one bf16 output: bit-identical, for A/B and the
+                             * tests); anything else is refused */
   int32_t block_n;          /* 0 = auto; 64 / 128 / 256 */
   int32_t act;              /* GENERIC: activation applied after bias */
   /* GENERIC: v = act(acc + bias[n]) * gate[(m / rows_per_gate) * gate_ld + n] + resid[m, n]

@@ -287,3 +287,55 @@ def test_gemm_narrow_tail_with_batches_and_taps(ops):
     xin = torch.nn.functional.pad(x.float().transpose(1, 2), (6 * dil, 0))
     ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil).transpose(1, 2).reshape(B * T, N)
     assert rel_l2(outs["1"], ref) < 2e-5
+
+
+# ---- row-per-thread TMA epilogue of the GENERIC GEMM (gemm_epilogue_t.cuh epi_t_row; the S1-DAC convolutions) ----------
+@pytest.mark.parametrize("T,C,N,taps,batch", [(5000, 192, 192, 1, 1), (3001, 96, 96, 7, 1), (700, 384, 384, 1, 3),
+                                             (1500, 128, 1024, 7, 2), (257, 64, 40, 1, 1), (33, 256, 256, 1, 1)])
+@pytest.mark.parametrize("mode", ["resid_f32_snake", "inplace_snake", "snake_only", "f32_only", "bf16_only", "f32_bf16"])
+def test_gemm_row_epilogue_bit_identical_to_transposing_epilogue(ops, T, C, N, taps, batch, mode):
+    """impl 2 takes the row / TMA epilogue for bias [+ residual] -> fp32 and / or one bf16 output, impl 5 the transposing
+    one: same per-element arithmetic -> identical bits, for ragged row / column ends (TMA clipping), batches, taps,
+    narrow tiles, the in-place residual and every output combination; and both match the fp32 reference."""
+    dil = 3
+    x = _rand((batch, T, C), 91, dtype=BF16)
+    w = _rand((N, C, taps), 92, (C * taps) ** -0.5, BF16)
+    wp = w.permute(0, 2, 1).reshape(N, taps * C).contiguous()
+    tp = tuple(-(taps - 1 - k) * dil for k in range(taps))
+    bias, alpha = _rand((N,), 93), _rand((N,), 94).abs() + 0.5
+    r0 = _rand((batch * T, N), 95)
+    outs = {}
+    for impl in (2, 5):
+        kw = dict(taps=tp, batch=batch, bias=bias, impl=impl)
+        res = r0.clone()
+        f32 = torch.full((batch * T, N), float("nan"), device="cuda")
+        b16 = torch.full((batch * T, N), float("nan"), device="cuda", dtype=BF16)
+        a = x.view(batch * T, C)
+        if mode == "resid_f32_snake":
+            ops.gemm_generic(a, wp, resid=res, out_f32=f32, out2_bf16=b16, snake_alpha=alpha, **kw)
+        elif mode == "inplace_snake":
+            ops.gemm_generic(a, wp, resid=res, out_f32=res, out2_bf16=b16, snake_alpha=alpha, **kw); f32 = res
+        elif mode == "snake_only":
+            ops.gemm_generic(a, wp, out2_bf16=b16, snake_alpha=alpha, **kw)
+        elif mode == "f32_only":
+            ops.gemm_generic(a, wp, resid=res, out_f32=f32, **kw)
+        elif mode == "bf16_only":
+            ops.gemm_generic(a, wp, out_bf16=b16, **kw)
+        else:
+            ops.gemm_generic(a, wp, out_f32=f32, out_bf16=b16, **kw)
+        outs[impl] = (f32, b16)
+    has_f32 = mode not in ("snake_only", "bf16_only")
+    has_b16 = mode != "f32_only"
+    if has_f32:
+        assert torch.equal(outs[2][0], outs[5][0])
+    if has_b16:
+        assert torch.equal(outs[2][1].view(torch.int16), outs[5][1].view(torch.int16))
+    xin = torch.nn.functional.pad(x.float().transpose(1, 2), ((taps - 1) * dil, 0))
+    ref = torch.nn.functional.conv1d(xin, w.float(), dilation=dil).transpose(1, 2).reshape(batch * T, N) + bias
+    if mode in ("resid_f32_snake", "inplace_snake", "f32_only"):
+        ref = ref + r0
+    if has_f32:
+        assert rel_l2(outs[2][0], ref) < 3e-5
+    if has_b16:
+        want = ref + torch.sin(alpha * ref) ** 2 / (alpha + 1e-9) if "snake" in mode else ref
+        assert rel_l2(outs[2][1].float(), want) < 5e-3
